@@ -1,0 +1,38 @@
+// Library-wide runtime support: launch accounting and error reporting.
+#include <atomic>
+#include <stdarg.h>
+#include <stdio.h>
+
+#include "common.cuh"
+
+static std::atomic<long long> g_launches{0};
+static thread_local char g_err[512] = "";
+
+void dph_count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+namespace dph {
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+}  // namespace dph
+
+int dph_check_last(const char* what) {
+  // cudaPeekAtLastError does not synchronise; it only reports launch-configuration errors.
+  cudaError_t e = cudaPeekAtLastError();
+  if (e != cudaSuccess) {
+    dph::set_error("%s: %s", what, cudaGetErrorString(e));
+    cudaGetLastError();
+    return DPH_ERR_CUDA;
+  }
+  return DPH_OK;
+}
+
+extern "C" {
+long long dph_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+void dph_launch_count_reset(void) { g_launches.store(0, std::memory_order_relaxed); }
+int dph_abi_version(void) { return 1; }
+const char* dph_last_error(void) { return g_err; }
+}

@@ -1,0 +1,137 @@
+"""Python-side descriptors for the C-ABI GEMMs (`dph_gemm_bf16`, `dph_gemm_f32`).
+
+An operand is a strided *view* described by plain integers; strided convolutions, grouped convolutions and
+per-head attention batches are all expressed as views of the activation buffers, never as copies.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import GemmDesc, GemmF32Desc, Operand, OperandF32
+
+BF16 = 0
+F32 = 1
+
+
+def dtype_code(t):
+    if t.dtype == torch.bfloat16:
+        return BF16
+    if t.dtype == torch.float32:
+        return F32
+    raise _lib.DphError("unsupported dtype %s" % t.dtype)
+
+
+class View:
+    """Dtype-agnostic operand view.  element(row, k, b0, b1) =
+    base[offset + b0*sb0 + b1*sb1 + row*rs + (k // kin)*kxs + (k % kin)*cs].
+    For the bf16 tensor-core path either cs == 1 (K-major) or rs == 1 (MN-major, kin == K) must hold."""
+
+    __slots__ = ("t", "offset", "rows", "K", "rs", "cs", "kin", "kxs", "sb0", "sb1")
+
+    def __init__(self, t, rows, K, rs, cs=1, kin=None, kxs=0, sb0=0, sb1=0, offset=0):
+        self.t, self.rows, self.K, self.rs, self.cs = t, rows, K, rs, cs
+        self.kin = K if kin is None else kin
+        self.kxs, self.sb0, self.sb1, self.offset = kxs, sb0, sb1, offset
+
+
+def mat(t):
+    """2-D row-major tensor (rows, K) as a K-major view."""
+    assert t.dim() == 2 and t.stride(1) == 1
+    return View(t, t.shape[0], t.shape[1], t.stride(0))
+
+
+def mat_t(t):
+    """2-D row-major tensor (K, rows) used transposed: MN-major view (reduction index is the slow dim)."""
+    assert t.dim() == 2 and t.stride(1) == 1
+    return View(t, t.shape[1], t.shape[0], 1, cs=t.stride(0))
+
+
+def _operand_bf16(v, nb0, nb1):
+    o = Operand()
+    esz = v.t.element_size()
+    o.ptr = v.t.data_ptr() + v.offset * esz
+    d3 = nb0 if v.sb0 != 0 else 1
+    d4 = nb1 if v.sb1 != 0 else 1
+    if v.cs == 1:
+        o.major_mn = 0
+        kx = (v.K + v.kin - 1) // v.kin
+        dims = (v.kin, v.rows, kx, d3, d4)
+        strides = (v.rs, v.kxs if kx > 1 else 8, v.sb0 if d3 > 1 else 8, v.sb1 if d4 > 1 else 8)
+        o.b0_mul = 1 if d3 > 1 else 0
+        o.b1_mul = 1 if d4 > 1 else 0
+    elif v.rs == 1 and v.kin == v.K:
+        o.major_mn = 1
+        dims = (v.rows, v.K, d3, d4, 1)
+        strides = (v.cs, v.sb0 if d3 > 1 else 8, v.sb1 if d4 > 1 else 8, 8)
+        o.b0_mul = 1 if d3 > 1 else 0
+        o.b1_mul = 1 if d4 > 1 else 0
+    else:
+        raise _lib.DphError("bf16 GEMM operand must be K-major (cs==1) or MN-major (rs==1)")
+    for i in range(5):
+        o.dims[i] = int(dims[i])
+    for i in range(4):
+        o.strides[i] = int(strides[i])
+    return o
+
+
+def _operand_f32(v):
+    o = OperandF32()
+    o.ptr = v.t.data_ptr() + v.offset * 4
+    o.rs, o.cs, o.kxs, o.kin, o.bs0, o.bs1 = v.rs, v.cs, v.kxs, v.kin, v.sb0, v.sb1
+    return o
+
+
+def gemm(a, b, c, M, N, K, *, ldc=None, nb0=1, nb1=1, c_sb0=0, c_sb1=0, c_offset=0, alpha=1.0, bias=None, act=0,
+         colmask=None, scalar_mask=None, residual=None, ldr=None, r_sb0=0, r_sb1=0, r_offset=0, c2=None,
+         accumulate=False, atomic=False, ksplit=1, drop_p=0.0, seed=0, block_n=0):
+    """C[b][m, n] = epilogue(alpha * sum_k a(m,k) b(n,k)).  `a`, `b` are `View`s; dtype of `a.t` selects the path:
+    bf16 -> tcgen05 tensor-core kernel, fp32 -> CUDA-core kernel."""
+    L = _lib.lib()
+    if ldc is None:
+        ldc = N
+    if ldr is None:
+        ldr = ldc
+    if a.t.dtype == torch.bfloat16:
+        assert b.t.dtype == torch.bfloat16
+        d = GemmDesc()
+        d.a = _operand_bf16(a, nb0, nb1)
+        d.b = _operand_bf16(b, nb0, nb1)
+        d.M, d.N, d.K, d.nb0, d.nb1 = M, N, K, nb0, nb1
+        d.block_n, d.ksplit = block_n, ksplit
+        d.c = c.data_ptr() + c_offset * c.element_size()
+        d.c2 = None if c2 is None else c2.data_ptr() + c_offset * c2.element_size()
+        d.ldc, d.c_sb0, d.c_sb1 = ldc, c_sb0, c_sb1
+        d.c_dtype = dtype_code(c)
+        d.c_mode = 1 if atomic else (2 if accumulate else 0)
+        d.alpha = alpha
+        d.bias = None if bias is None else bias.data_ptr()
+        d.act = act
+        d.colmask = None if colmask is None else colmask.data_ptr()
+        d.scalar_mask = None if scalar_mask is None else scalar_mask.data_ptr()
+        if residual is not None:
+            d.residual = residual.data_ptr() + r_offset * residual.element_size()
+            d.r_dtype = dtype_code(residual)
+        d.ldr, d.r_sb0, d.r_sb1 = ldr, r_sb0, r_sb1
+        d.drop_p, d.seed = drop_p, seed
+        _lib.check(L.dph_gemm_bf16(ctypes.byref(d), _lib.stream_ptr()), "dph_gemm_bf16")
+    else:
+        assert a.t.dtype == torch.float32 and b.t.dtype == torch.float32 and c.dtype == torch.float32
+        d = GemmF32Desc()
+        d.a = _operand_f32(a)
+        d.b = _operand_f32(b)
+        d.M, d.N, d.K, d.nb0, d.nb1 = M, N, K, nb0, nb1
+        d.c = c.data_ptr() + c_offset * 4
+        d.c2 = None if c2 is None else c2.data_ptr() + c_offset * 4
+        d.ldc, d.c_sb0, d.c_sb1 = ldc, c_sb0, c_sb1
+        d.accumulate = 1 if (accumulate or atomic) else 0
+        d.alpha = alpha
+        d.bias = None if bias is None else bias.data_ptr()
+        d.act = act
+        d.colmask = None if colmask is None else colmask.data_ptr()
+        d.scalar_mask = None if scalar_mask is None else scalar_mask.data_ptr()
+        d.residual = None if residual is None else residual.data_ptr() + r_offset * 4
+        d.ldr, d.r_sb0, d.r_sb1 = ldr, r_sb0, r_sb1
+        d.drop_p, d.seed = drop_p, seed
+        _lib.check(L.dph_gemm_f32(ctypes.byref(d), _lib.stream_ptr()), "dph_gemm_f32")
+    return c
