@@ -1,0 +1,449 @@
+// Layer 0 of the waveform feature extractor: Conv1d(1 -> C, k, stride, bias?) -> GroupNorm(C groups) -> GELU -> mask,
+// fused into one pass that reads the waveform once and writes the (B, T1, C) channels-last activation exactly once.
+//
+// Replaces wav2vec2/components.py:107-114 for conv_layers[0] (k=10, s=5, C=512) and its autograd backward.
+//
+// GroupNorm statistics are obtained WITHOUT touching the big activation: z[t,c] = sum_k w[c,k] x[s t + k], hence
+//   sum_t z      = w[c,:] . S          S[k]    = sum_t x[s t + k]
+//   sum_t z^2    = w[c,:] R w[c,:]^T   R[k,k'] = sum_t x[s t + k] x[s t + k']
+// i.e. a k + k(k+1)/2 element autocorrelation of the waveform per utterance (accumulated in fp64) gives the exact
+// per-(utterance, channel) mean / variance.  The backward recomputes z from the waveform instead of saving it.
+#include "common.cuh"
+#include "vec.cuh"
+#include "../../include/dphubert_b200.h"
+
+namespace dph {
+void set_error(const char* fmt, ...);
+
+constexpr int C0_MAXK = 10;
+constexpr int C0_TT = 128;       // output frames per CTA
+constexpr int C0_THREADS = 256;  // 64 channel groups (8 channels each) x 4 frame lanes
+constexpr int C0_NR = C0_MAXK + C0_MAXK * (C0_MAXK + 1) / 2;  // 65 moments
+
+// ------------------------------------------------------------------------------------------------------------
+// waveform moments  (B, 65) fp64
+// ------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+    conv0_moments_kernel(const float* __restrict__ wave, long long wave_bs, int T1, int k, int stride,
+                         double* __restrict__ R) {
+  const int b = blockIdx.y;
+  const float* x = wave + (long long)b * wave_bs;
+  double acc[C0_NR];
+#pragma unroll
+  for (int i = 0; i < C0_NR; ++i) acc[i] = 0.0;
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < T1; t += gridDim.x * blockDim.x) {
+    float xs[C0_MAXK];
+#pragma unroll
+    for (int j = 0; j < C0_MAXK; ++j) xs[j] = (j < k) ? x[(long long)t * stride + j] : 0.f;
+    int idx = C0_MAXK;
+#pragma unroll
+    for (int j = 0; j < C0_MAXK; ++j) {
+      acc[j] += (double)xs[j];
+#pragma unroll
+      for (int l = j; l < C0_MAXK; ++l) acc[idx++] += (double)xs[j] * (double)xs[l];
+    }
+  }
+  __shared__ double sh[8];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int i = 0; i < C0_NR; ++i) {
+    double v = acc[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) sh[w] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double tot = 0.0;
+      for (int q = 0; q < (int)(blockDim.x >> 5); ++q) tot += sh[q];
+      atomicAdd(R + (long long)b * C0_NR + i, tot);
+    }
+    __syncthreads();
+  }
+}
+
+// mean / rstd per (b, c) from the moments
+__global__ void conv0_stats_kernel(const double* __restrict__ R, const float* __restrict__ w,
+                                   const float* __restrict__ bias, float* __restrict__ mean, float* __restrict__ rstd,
+                                   int B, int C, int k, int T1, float eps) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * C) return;
+  const int b = i / C, c = i - b * C;
+  const double* r = R + (long long)b * C0_NR;
+  double wk[C0_MAXK];
+  for (int j = 0; j < C0_MAXK; ++j) wk[j] = j < k ? (double)w[c * k + j] : 0.0;
+  double s = 0.0, q = 0.0;
+  int idx = C0_MAXK;
+  for (int j = 0; j < C0_MAXK; ++j) {
+    s += wk[j] * r[j];
+    for (int l = j; l < C0_MAXK; ++l) {
+      double term = wk[j] * wk[l] * r[idx++];
+      q += (l == j) ? term : 2.0 * term;
+    }
+  }
+  const double m0 = s / T1;  // mean without bias
+  double var = q / T1 - m0 * m0;
+  if (var < 0.0) var = 0.0;
+  mean[i] = (float)(m0 + (bias ? (double)bias[c] : 0.0));
+  rstd[i] = (float)(1.0 / sqrt(var + (double)eps));
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// forward apply
+// ------------------------------------------------------------------------------------------------------------
+template <typename T, bool FAST_GELU>
+DPH_DEVICE float gelu_sel(float x) {
+  return gelu_erf(x);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(C0_THREADS)
+    conv0_apply_kernel(const float* __restrict__ wave, long long wave_bs, const float* __restrict__ w,
+                       const float* __restrict__ bias, const float* __restrict__ gamma, const float* __restrict__ beta,
+                       const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ mask,
+                       T* __restrict__ y, int C, int k, int stride, int T1, int norm, int act, int vec_ok) {
+  __shared__ float sx[C0_TT * 8 + C0_MAXK + 8];
+  const int b = blockIdx.y;
+  const int t0 = blockIdx.x * C0_TT;
+  const int nt = min(C0_TT, T1 - t0);
+  const float* x = wave + (long long)b * wave_bs + (long long)t0 * stride;
+  const int nsamp = (nt - 1) * stride + k;
+  for (int i = threadIdx.x; i < nsamp; i += blockDim.x) sx[i] = x[i];
+  __syncthreads();
+  const int cg = threadIdx.x & 63, fl = threadIdx.x >> 6;
+  for (int cbase = 0; cbase < C; cbase += 512) {
+    const int c0 = cbase + cg * 8;
+    if (c0 >= C) continue;
+    float wr[8][C0_MAXK], scale[8], shift[8], mk[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = c0 + j;
+      const bool ok = c < C;
+#pragma unroll
+      for (int q = 0; q < C0_MAXK; ++q) wr[j][q] = (ok && q < k) ? __ldg(w + c * k + q) : 0.f;
+      float bb = (ok && bias) ? __ldg(bias + c) : 0.f;
+      if (norm && ok) {
+        const float rs = rstd[b * C + c], mu = mean[b * C + c], g = __ldg(gamma + c);
+        scale[j] = rs * g;
+        shift[j] = __ldg(beta + c) + (bb - mu) * rs * g;
+      } else {
+        scale[j] = 1.f;
+        shift[j] = bb;
+      }
+      mk[j] = (ok && mask) ? __ldg(mask + c) : 1.f;
+    }
+    for (int tt = fl; tt < nt; tt += 4) {
+      float xs[C0_MAXK];
+#pragma unroll
+      for (int q = 0; q < C0_MAXK; ++q) xs[q] = (q < k) ? sx[tt * stride + q] : 0.f;
+      float o[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float z = 0.f;
+#pragma unroll
+        for (int q = 0; q < C0_MAXK; ++q) z = fmaf(wr[j][q], xs[q], z);
+        float u = fmaf(z, scale[j], shift[j]);
+        if (act) u = gelu_erf(u);
+        o[j] = u * mk[j];
+      }
+      T* dst = y + ((long long)b * T1 + t0 + tt) * C + c0;
+      if (vec_ok) {
+        if constexpr (sizeof(T) == 2) {
+          store_vec(reinterpret_cast<bf16*>(dst), o);
+        } else {
+          float lo[4] = {o[0], o[1], o[2], o[3]}, hi[4] = {o[4], o[5], o[6], o[7]};
+          store_vec(reinterpret_cast<float*>(dst), lo);
+          store_vec(reinterpret_cast<float*>(dst) + 4, hi);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (c0 + j < C) dst[j] = from_f<T>(o[j]);
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// backward pass 1: per (b, c) sums  A = sum_t du,  Bq = sum_t du * yn,  and dmask partial  sum dy * act(u)
+//   u = yn * gamma + beta,  du = dy * mask * act'(u)
+// ------------------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(C0_THREADS)
+    conv0_bwd_reduce_kernel(const float* __restrict__ wave, long long wave_bs, const float* __restrict__ w,
+                            const float* __restrict__ bias, const float* __restrict__ gamma,
+                            const float* __restrict__ beta, const float* __restrict__ mean,
+                            const float* __restrict__ rstd, const float* __restrict__ mask, const T* __restrict__ dy,
+                            float* __restrict__ sumA, float* __restrict__ sumB, float* __restrict__ dmask, int C, int k,
+                            int stride, int T1, int norm, int act, int vec_ok) {
+  __shared__ float sx[C0_TT * 8 + C0_MAXK + 8];
+  const int b = blockIdx.y;
+  const int t0 = blockIdx.x * C0_TT;
+  const int nt = min(C0_TT, T1 - t0);
+  const float* x = wave + (long long)b * wave_bs + (long long)t0 * stride;
+  const int nsamp = (nt - 1) * stride + k;
+  for (int i = threadIdx.x; i < nsamp; i += blockDim.x) sx[i] = x[i];
+  __syncthreads();
+  const int cg = threadIdx.x & 63, fl = threadIdx.x >> 6;
+  for (int cbase = 0; cbase < C; cbase += 512) {
+    const int c0 = cbase + cg * 8;
+    if (c0 >= C) continue;
+    float wr[8][C0_MAXK], nsc[8], nsh[8], gm[8], bt[8], mk[8];
+    float aA[8], aB[8], aM[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = c0 + j;
+      const bool ok = c < C;
+#pragma unroll
+      for (int q = 0; q < C0_MAXK; ++q) wr[j][q] = (ok && q < k) ? __ldg(w + c * k + q) : 0.f;
+      float bb = (ok && bias) ? __ldg(bias + c) : 0.f;
+      if (norm && ok) {
+        const float rs = rstd[b * C + c], mu = mean[b * C + c];
+        nsc[j] = rs;
+        nsh[j] = (bb - mu) * rs;
+        gm[j] = __ldg(gamma + c);
+        bt[j] = __ldg(beta + c);
+      } else {
+        nsc[j] = 1.f;
+        nsh[j] = bb;
+        gm[j] = 1.f;
+        bt[j] = 0.f;
+      }
+      mk[j] = (ok && mask) ? __ldg(mask + c) : 1.f;
+      aA[j] = aB[j] = aM[j] = 0.f;
+    }
+    for (int tt = fl; tt < nt; tt += 4) {
+      float xs[C0_MAXK];
+#pragma unroll
+      for (int q = 0; q < C0_MAXK; ++q) xs[q] = (q < k) ? sx[tt * stride + q] : 0.f;
+      float d[8];
+      const T* src = dy + ((long long)b * T1 + t0 + tt) * C + c0;
+      if (vec_ok) {
+        if constexpr (sizeof(T) == 2) {
+          load_vec(reinterpret_cast<const bf16*>(src), d);
+        } else {
+          load_vec_f32(reinterpret_cast<const float*>(src), d);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) d[j] = (c0 + j < C) ? to_f(src[j]) : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float z = 0.f;
+#pragma unroll
+        for (int q = 0; q < C0_MAXK; ++q) z = fmaf(wr[j][q], xs[q], z);
+        const float yn = fmaf(z, nsc[j], nsh[j]);
+        const float u = fmaf(yn, gm[j], bt[j]);
+        const float au = act ? gelu_erf(u) : u;
+        aM[j] += d[j] * au;
+        const float du = d[j] * mk[j] * (act ? gelu_erf_grad(u) : 1.f);
+        aA[j] += du;
+        aB[j] += du * yn;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = c0 + j;
+      if (c < C) {
+        atomicAdd(sumA + b * C + c, aA[j]);
+        atomicAdd(sumB + b * C + c, aB[j]);
+        if (dmask) atomicAdd(dmask + c, aM[j]);
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// backward pass 2: dz = rstd * gamma * (du - A/T1 - yn * Bq/T1);  dW[c,q] += sum_t dz * x[s t + q];  dbias += sum dz
+// ------------------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(C0_THREADS)
+    conv0_bwd_wgrad_kernel(const float* __restrict__ wave, long long wave_bs, const float* __restrict__ w,
+                           const float* __restrict__ bias, const float* __restrict__ gamma,
+                           const float* __restrict__ beta, const float* __restrict__ mean,
+                           const float* __restrict__ rstd, const float* __restrict__ mask, const T* __restrict__ dy,
+                           const float* __restrict__ sumA, const float* __restrict__ sumB, float* __restrict__ dW,
+                           float* __restrict__ dbias, int C, int k, int stride, int T1, int norm, int act, int vec_ok) {
+  __shared__ float sx[C0_TT * 8 + C0_MAXK + 8];
+  const int b = blockIdx.y;
+  const int t0 = blockIdx.x * C0_TT;
+  const int nt = min(C0_TT, T1 - t0);
+  const float* x = wave + (long long)b * wave_bs + (long long)t0 * stride;
+  const int nsamp = (nt - 1) * stride + k;
+  for (int i = threadIdx.x; i < nsamp; i += blockDim.x) sx[i] = x[i];
+  __syncthreads();
+  const float invT = 1.f / (float)T1;
+  // 2 adjacent channels per thread: a warp reads 64 consecutive channels (128 B of bf16) per frame, and the
+  // 2 x k weight-gradient accumulators stay in registers across all frames of the tile.
+  for (int cbase = 0; cbase < C; cbase += 2 * C0_THREADS) {
+    const int c0 = cbase + 2 * threadIdx.x;
+    if (c0 >= C) continue;
+    float wr[2][C0_MAXK], acc[2][C0_MAXK], nsc[2], nsh[2], gm[2], bt[2], mA[2], mB[2], rs[2], mk[2], accb[2];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int c = c0 + j;
+      const bool ok = c < C;
+#pragma unroll
+      for (int q = 0; q < C0_MAXK; ++q) {
+        wr[j][q] = (ok && q < k) ? __ldg(w + c * k + q) : 0.f;
+        acc[j][q] = 0.f;
+      }
+      const float bb = (ok && bias) ? __ldg(bias + c) : 0.f;
+      nsc[j] = 1.f; nsh[j] = bb; gm[j] = 1.f; bt[j] = 0.f; mA[j] = 0.f; mB[j] = 0.f; rs[j] = 1.f;
+      if (norm && ok) {
+        rs[j] = rstd[b * C + c];
+        const float mu = mean[b * C + c];
+        nsc[j] = rs[j];
+        nsh[j] = (bb - mu) * rs[j];
+        gm[j] = __ldg(gamma + c);
+        bt[j] = __ldg(beta + c);
+        mA[j] = sumA[b * C + c] * invT;
+        mB[j] = sumB[b * C + c] * invT;
+      }
+      mk[j] = (ok && mask) ? __ldg(mask + c) : 1.f;
+      accb[j] = 0.f;
+    }
+    const bool pair_ok = vec_ok && (c0 + 1 < C);
+    for (int tt = 0; tt < nt; ++tt) {
+      float xs[C0_MAXK];
+#pragma unroll
+      for (int q = 0; q < C0_MAXK; ++q) xs[q] = (q < k) ? sx[tt * stride + q] : 0.f;
+      const T* src = dy + ((long long)b * T1 + t0 + tt) * C + c0;
+      float d[2];
+      if constexpr (sizeof(T) == 2) {
+        if (pair_ok) {
+          float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(src));
+          d[0] = f.x;
+          d[1] = f.y;
+        } else {
+          d[0] = to_f(src[0]);
+          d[1] = (c0 + 1 < C) ? to_f(src[1]) : 0.f;
+        }
+      } else {
+        d[0] = to_f(src[0]);
+        d[1] = (c0 + 1 < C) ? to_f(src[1]) : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        float z = 0.f;
+#pragma unroll
+        for (int q = 0; q < C0_MAXK; ++q) z = fmaf(wr[j][q], xs[q], z);
+        const float yn = fmaf(z, nsc[j], nsh[j]);
+        const float u = fmaf(yn, gm[j], bt[j]);
+        const float du = d[j] * mk[j] * (act ? gelu_erf_grad(u) : 1.f);
+        const float dz = norm ? rs[j] * gm[j] * (du - mA[j] - yn * mB[j]) : du;
+        accb[j] += dz;
+#pragma unroll
+        for (int q = 0; q < C0_MAXK; ++q) acc[j][q] = fmaf(dz, xs[q], acc[j][q]);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int c = c0 + j;
+      if (c < C) {
+        for (int q = 0; q < k; ++q) atomicAdd(dW + c * k + q, acc[j][q]);
+        if (dbias) atomicAdd(dbias + c, accb[j]);
+      }
+    }
+  }
+}
+
+// dgamma[c] += sum_b Bq[b,c];  dbeta[c] += sum_b A[b,c]
+__global__ void conv0_bwd_affine_kernel(const float* __restrict__ sumA, const float* __restrict__ sumB,
+                                        float* __restrict__ dgamma, float* __restrict__ dbeta, int B, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float a = 0.f, q = 0.f;
+  for (int b = 0; b < B; ++b) {
+    a += sumA[b * C + c];
+    q += sumB[b * C + c];
+  }
+  if (dgamma) atomicAdd(dgamma + c, q);
+  if (dbeta) atomicAdd(dbeta + c, a);
+}
+
+}  // namespace dph
+
+using namespace dph;
+
+static int conv0_check(int C, int k, int stride, int T1) {
+  if (C <= 0 || k <= 0 || k > C0_MAXK || stride <= 0 || stride > 8 || T1 <= 0) {
+    set_error("conv0: unsupported shape C=%d k=%d stride=%d T1=%d (k <= 10, stride <= 8)", C, k, stride, T1);
+    return DPH_ERR_UNSUPPORTED;
+  }
+  return DPH_OK;
+}
+
+extern "C" int dph_conv0_stats(const float* wave, int64_t wave_bs, const float* w, const float* bias, double* moments,
+                               float* mean, float* rstd, int B, int C, int k, int stride, int T1, float eps,
+                               void* stream) {
+  int rc = conv0_check(C, k, stride, T1);
+  if (rc) return rc;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  cudaMemsetAsync(moments, 0, sizeof(double) * B * C0_NR, s);
+  int gx = (T1 + 256 * 4 - 1) / (256 * 4);
+  if (gx > 64) gx = 64;
+  conv0_moments_kernel<<<dim3(gx, B), 256, 0, s>>>(wave, wave_bs, T1, k, stride, moments);
+  conv0_stats_kernel<<<(B * C + 127) / 128, 128, 0, s>>>(moments, w, bias, mean, rstd, B, C, k, T1, eps);
+  dph_count_launch(2);
+  return dph_check_last("conv0_stats");
+}
+
+extern "C" int dph_conv0_fwd(const float* wave, int64_t wave_bs, const float* w, const float* bias, const float* gamma,
+                             const float* beta, const float* mean, const float* rstd, const float* mask, void* y, int B,
+                             int C, int k, int stride, int T1, int norm, int act, int dtype, void* stream) {
+  int rc = conv0_check(C, k, stride, T1);
+  if (rc) return rc;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  dim3 grid((T1 + C0_TT - 1) / C0_TT, B);
+  const int vec_ok = (C % 8 == 0) && ((reinterpret_cast<uintptr_t>(y) & 15) == 0);
+  if (dtype == DPH_DTYPE_BF16)
+    conv0_apply_kernel<bf16><<<grid, C0_THREADS, 0, s>>>(wave, wave_bs, w, bias, gamma, beta, mean, rstd, mask,
+                                                         (bf16*)y, C, k, stride, T1, norm, act, vec_ok);
+  else
+    conv0_apply_kernel<float><<<grid, C0_THREADS, 0, s>>>(wave, wave_bs, w, bias, gamma, beta, mean, rstd, mask,
+                                                          (float*)y, C, k, stride, T1, norm, act, vec_ok);
+  dph_count_launch();
+  return dph_check_last("conv0_fwd");
+}
+
+// scratch: 2 * B * C floats (sumA, sumB), zeroed here.
+extern "C" int dph_conv0_bwd(const float* wave, int64_t wave_bs, const float* w, const float* bias, const float* gamma,
+                             const float* beta, const float* mean, const float* rstd, const float* mask, const void* dy,
+                             float* scratch, float* dW, float* dbias, float* dgamma, float* dbeta, float* dmask, int B,
+                             int C, int k, int stride, int T1, int norm, int act, int dtype, void* stream) {
+  int rc = conv0_check(C, k, stride, T1);
+  if (rc) return rc;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  dim3 grid((T1 + C0_TT - 1) / C0_TT, B);
+  const int vec_ok = (C % 8 == 0) && ((reinterpret_cast<uintptr_t>(dy) & 15) == 0);
+  float* sumA = scratch;
+  float* sumB = scratch + (size_t)B * C;
+  int launches = 0;
+  if (norm || dmask) {
+    cudaMemsetAsync(scratch, 0, sizeof(float) * 2 * B * C, s);
+    if (dtype == DPH_DTYPE_BF16)
+      conv0_bwd_reduce_kernel<bf16><<<grid, C0_THREADS, 0, s>>>(wave, wave_bs, w, bias, gamma, beta, mean, rstd, mask,
+                                                                (const bf16*)dy, sumA, sumB, dmask, C, k, stride, T1,
+                                                                norm, act, vec_ok);
+    else
+      conv0_bwd_reduce_kernel<float><<<grid, C0_THREADS, 0, s>>>(wave, wave_bs, w, bias, gamma, beta, mean, rstd, mask,
+                                                                 (const float*)dy, sumA, sumB, dmask, C, k, stride, T1,
+                                                                 norm, act, vec_ok);
+    ++launches;
+  }
+  if (dtype == DPH_DTYPE_BF16)
+    conv0_bwd_wgrad_kernel<bf16><<<grid, C0_THREADS, 0, s>>>(wave, wave_bs, w, bias, gamma, beta, mean, rstd, mask,
+                                                             (const bf16*)dy, sumA, sumB, dW, dbias, C, k, stride, T1,
+                                                             norm, act, vec_ok);
+  else
+    conv0_bwd_wgrad_kernel<float><<<grid, C0_THREADS, 0, s>>>(wave, wave_bs, w, bias, gamma, beta, mean, rstd, mask,
+                                                              (const float*)dy, sumA, sumB, dW, dbias, C, k, stride, T1,
+                                                              norm, act, vec_ok);
+  ++launches;
+  if (norm && (dgamma || dbeta)) {
+    conv0_bwd_affine_kernel<<<(C + 127) / 128, 128, 0, s>>>(sumA, sumB, dgamma, dbeta, B, C);
+    ++launches;
+  }
+  dph_count_launch(launches);
+  return dph_check_last("conv0_bwd");
+}

@@ -1,0 +1,329 @@
+// Memory-bound elementwise / column-reduction kernels around the GEMMs (all 128-bit vectorised when aligned).
+//
+//  * dph_epilogue_bwd : backward of the fused GEMM epilogue  o = dropout(scalar * colmask * act(z))  -> dz plus the
+//    column reductions the reference gets from autograd: bias grad, HardConcrete column-mask grad, layer-gate grad
+//    (components.py:110-114 conv blocks, :424-434 attention, :733-746 FFN).
+//  * dph_pad_rows_zero: `x[mask] = 0` for padded frames (components.py:979-980).
+//  * dph_posconv_pad  : scatter (B,T,D) into the zero-padded, group-padded staging buffer of the positional conv.
+//  * casts / small vector ops used by the weight cache and the mask plumbing.
+#include "common.cuh"
+#include "vec.cuh"
+#include "../../include/dphubert_b200.h"
+
+namespace dph {
+void set_error(const char* fmt, ...);
+
+template <typename T, int VEC>
+__global__ void __launch_bounds__(128)
+    epilogue_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ z, const float* __restrict__ colmask,
+                        const float* __restrict__ scalar, T* __restrict__ dout, float* __restrict__ dmask,
+                        float* __restrict__ dbias, float* __restrict__ dscalar, int rows, int C, int rows_per_blk,
+                        int act, float drop_p, unsigned long long seed, int rows_per_batch, long long out_bs,
+                        int out_row_off, long long in_ld, long long z_ld) {
+  __shared__ float red[32];
+  const int c0 = (blockIdx.x * blockDim.x + threadIdx.x) * VEC;
+  const int r0 = blockIdx.y * rows_per_blk;
+  const int r1 = min(rows, r0 + rows_per_blk);
+  const bool active = c0 < C;
+  float cm[VEC], a_mask[VEC], a_bias[VEC];
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) {
+    cm[j] = (active && colmask && c0 + j < C) ? __ldg(colmask + c0 + j) : 1.f;
+    a_mask[j] = 0.f;
+    a_bias[j] = 0.f;
+  }
+  const float sc = scalar ? __ldg(scalar) : 1.f;
+  float a_scalar = 0.f;
+  const uint32_t thresh = (uint32_t)(drop_p * 4294967296.0);
+  const float inv_keep = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+  const bool need_z = (z != nullptr);
+  if (active) {
+    for (int r = r0; r < r1; ++r) {
+      float d[VEC], zz[VEC];
+      const long long ioff = (long long)r * in_ld + c0;
+      if constexpr (VEC > 1) {
+        load_vec(dy + ioff, d);
+        if (need_z) load_vec(z + (long long)r * z_ld + c0, zz);
+      } else {
+        d[0] = to_f(dy[ioff]);
+        if (need_z) zz[0] = to_f(z[(long long)r * z_ld + c0]);
+      }
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) {
+        float ds = d[j];
+        if (drop_p > 0.f) ds *= dropout_scale(seed, (unsigned long long)r * C + c0 + j, thresh, inv_keep);
+        float az = need_z ? (act == 1 ? gelu_erf(zz[j]) : zz[j]) : 0.f;
+        a_scalar += ds * az * cm[j];
+        float dm = ds * sc;
+        a_mask[j] += dm * az;
+        float dv = dm * cm[j];
+        if (act == 1) dv *= gelu_erf_grad(zz[j]);
+        a_bias[j] += dv;
+        d[j] = dv;
+      }
+      if (dout) {
+        const int b = r / rows_per_batch, t = r - b * rows_per_batch;
+        const long long ooff = (long long)b * out_bs + (long long)(t + out_row_off) * C + c0;
+        if constexpr (VEC > 1) {
+          store_vec(dout + ooff, d);
+        } else {
+          dout[ooff] = from_f<T>(d[0]);
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+      if (c0 + j < C) {
+        if (dmask) atomicAdd(dmask + c0 + j, a_mask[j]);
+        if (dbias) atomicAdd(dbias + c0 + j, a_bias[j]);
+      }
+    }
+  }
+  if (dscalar) {
+    float tot = block_sum(a_scalar, red);
+    if (threadIdx.x == 0) atomicAdd(dscalar, tot);
+  }
+}
+
+template <typename T>
+__global__ void pad_rows_zero_kernel(T* __restrict__ x, const long long* __restrict__ lengths, int B, int Tn, int D) {
+  // one block per (b, t) candidate row in the padded region; grid = B * Tn blocks is wasteful, so walk rows per block
+  const int b = blockIdx.y;
+  long long len = lengths[b];
+  if (len < 0) len = 0;
+  for (int t = (int)len + blockIdx.x; t < Tn; t += gridDim.x) {
+    T* row = x + ((long long)b * Tn + t) * D;
+    for (int i = threadIdx.x; i < D; i += blockDim.x) row[i] = from_f<T>(0.f);
+  }
+}
+
+// (B, T, G*Cg) -> staging buffer rows [front + b*(T+pad) + t], each row G * Cgp wide (channels of a group padded
+// with zeros from Cg to Cgp). Pad rows / pad channels are NOT written here (the buffer is zeroed once at allocation).
+template <typename T>
+__global__ void posconv_pad_kernel(const T* __restrict__ x, T* __restrict__ xp, int B, int Tn, int G, int Cg, int Cgp,
+                                   int front, int pad) {
+  const long long total = (long long)B * Tn * G * Cgp;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    int c = (int)(i % Cgp);
+    long long r = i / Cgp;
+    int g = (int)(r % G);
+    r /= G;
+    int t = (int)(r % Tn);
+    int b = (int)(r / Tn);
+    T v = from_f<T>(0.f);
+    if (c < Cg) v = x[((long long)b * Tn + t) * (G * Cg) + g * Cg + c];
+    xp[((long long)front + (long long)b * (Tn + pad) + t) * (G * Cgp) + g * Cgp + c] = v;
+  }
+}
+
+// inverse gather: staging rows -> dense (B,T,G*Cg), optionally accumulating into the destination
+template <typename T>
+__global__ void posconv_unpad_kernel(const T* __restrict__ xp, T* __restrict__ x, int B, int Tn, int G, int Cg, int Cgp,
+                                     int front, int pad, int accumulate) {
+  const long long total = (long long)B * Tn * G * Cg;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    int c = (int)(i % Cg);
+    long long r = i / Cg;
+    int g = (int)(r % G);
+    r /= G;
+    int t = (int)(r % Tn);
+    int b = (int)(r / Tn);
+    float v = to_f(xp[((long long)front + (long long)b * (Tn + pad) + t) * (G * Cgp) + g * Cgp + c]);
+    if (accumulate) v += to_f(x[i]);
+    x[i] = from_f<T>(v);
+  }
+}
+
+template <typename TI, typename TO>
+__global__ void cast_kernel(const TI* __restrict__ in, TO* __restrict__ out, long long n) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    out[i] = from_f<TO>(to_f(in[i]));
+}
+
+// out[i] = a[i] * (b ? b[i] : 1) * alpha + (beta ? beta * out[i] : 0)     (fp32 vectors: masks, gates)
+__global__ void vec_mul_kernel(const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ out,
+                               float alpha, float beta, int n) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    float v = a[i] * (b ? b[i] : 1.f) * alpha;
+    if (beta != 0.f) v += beta * out[i];
+    out[i] = v;
+  }
+}
+
+// (B, C, T) <-> (B, T, C) tile transpose (API-compat path of ConvLayerBlock.forward, not on the hot path)
+template <typename TI, typename TO>
+__global__ void transpose_kernel(const TI* __restrict__ in, TO* __restrict__ out, int R, int Ccols) {
+  // in: (B, R, Ccols) -> out: (B, Ccols, R)
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z;
+  const TI* ib = in + (long long)b * R * Ccols;
+  TO* ob = out + (long long)b * R * Ccols;
+  int c = blockIdx.x * 32 + threadIdx.x;
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    int r = blockIdx.y * 32 + j;
+    tile[j][threadIdx.x] = (r < R && c < Ccols) ? to_f(ib[(long long)r * Ccols + c]) : 0.f;
+  }
+  __syncthreads();
+  int r = blockIdx.y * 32 + threadIdx.x;
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    int cc = blockIdx.x * 32 + j;
+    if (r < R && cc < Ccols) ob[(long long)cc * R + r] = from_f<TO>(tile[threadIdx.x][j]);
+  }
+}
+
+}  // namespace dph
+
+using namespace dph;
+
+extern "C" int dph_epilogue_bwd(const void* dy, const void* z, const float* colmask, const float* scalar, void* dout,
+                                float* dmask, float* dbias, float* dscalar, int rows, int C, int act, float drop_p,
+                                uint64_t seed, int rows_per_batch, int64_t out_bs, int out_row_off, int64_t in_ld,
+                                int64_t z_ld, int dtype, void* stream) {
+  if (!dy || rows <= 0 || C <= 0) {
+    set_error("epilogue_bwd: bad arguments");
+    return DPH_ERR_ARG;
+  }
+  if ((act == 1 || dmask || dscalar) && !z) {
+    set_error("epilogue_bwd: z required for act / dmask / dscalar");
+    return DPH_ERR_ARG;
+  }
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (rows_per_batch <= 0) {
+    rows_per_batch = rows;
+    out_bs = 0;
+  }
+  if (in_ld <= 0) in_ld = C;
+  if (z_ld <= 0) z_ld = C;
+  const int vecw = dtype == DPH_DTYPE_BF16 ? 8 : 4;
+  auto al = [&](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  const bool vec_ok = (C % vecw == 0) && (in_ld % vecw == 0) && (z_ld % vecw == 0) && al(dy) && al(z) && al(dout) &&
+                      (out_bs % vecw == 0);
+  const int VECW = vec_ok ? vecw : 1;
+  const int cols_per_blk = 128 * VECW;
+  const int gx = (C + cols_per_blk - 1) / cols_per_blk;
+  int target_y = (148 * 8 + gx - 1) / gx;
+  int rows_per_blk = (rows + target_y - 1) / target_y;
+  if (rows_per_blk < 8) rows_per_blk = 8;
+  const int gy = (rows + rows_per_blk - 1) / rows_per_blk;
+  dim3 grid(gx, gy);
+#define EB_LAUNCH(T, V)                                                                                             \
+  epilogue_bwd_kernel<T, V><<<grid, 128, 0, s>>>((const T*)dy, (const T*)z, colmask, scalar, (T*)dout, dmask, dbias, \
+                                                 dscalar, rows, C, rows_per_blk, act, drop_p, seed, rows_per_batch,  \
+                                                 out_bs, out_row_off, in_ld, z_ld)
+  if (dtype == DPH_DTYPE_BF16) {
+    if (vec_ok) EB_LAUNCH(bf16, 8);
+    else EB_LAUNCH(bf16, 1);
+  } else {
+    if (vec_ok) EB_LAUNCH(float, 4);
+    else EB_LAUNCH(float, 1);
+  }
+#undef EB_LAUNCH
+  dph_count_launch();
+  return dph_check_last("epilogue_bwd");
+}
+
+extern "C" int dph_pad_rows_zero(void* x, const int64_t* lengths, int B, int T, int D, int dtype, void* stream) {
+  if (!x || !lengths || B <= 0 || T <= 0 || D <= 0) {
+    set_error("pad_rows_zero: bad arguments");
+    return DPH_ERR_ARG;
+  }
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  dim3 grid(8, B);
+  if (dtype == DPH_DTYPE_BF16)
+    pad_rows_zero_kernel<bf16><<<grid, 128, 0, s>>>((bf16*)x, (const long long*)lengths, B, T, D);
+  else
+    pad_rows_zero_kernel<float><<<grid, 128, 0, s>>>((float*)x, (const long long*)lengths, B, T, D);
+  dph_count_launch();
+  return dph_check_last("pad_rows_zero");
+}
+
+extern "C" int dph_posconv_pad(const void* x, void* xp, int B, int T, int G, int Cg, int Cgp, int front, int pad,
+                               int dtype, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  long long total = (long long)B * T * G * Cgp;
+  int grid = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+  if (dtype == DPH_DTYPE_BF16)
+    posconv_pad_kernel<bf16><<<grid, 256, 0, s>>>((const bf16*)x, (bf16*)xp, B, T, G, Cg, Cgp, front, pad);
+  else
+    posconv_pad_kernel<float><<<grid, 256, 0, s>>>((const float*)x, (float*)xp, B, T, G, Cg, Cgp, front, pad);
+  dph_count_launch();
+  return dph_check_last("posconv_pad");
+}
+
+extern "C" int dph_posconv_unpad(const void* xp, void* x, int B, int T, int G, int Cg, int Cgp, int front, int pad,
+                                 int accumulate, int dtype, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  long long total = (long long)B * T * G * Cg;
+  int grid = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+  if (dtype == DPH_DTYPE_BF16)
+    posconv_unpad_kernel<bf16><<<grid, 256, 0, s>>>((const bf16*)xp, (bf16*)x, B, T, G, Cg, Cgp, front, pad, accumulate);
+  else
+    posconv_unpad_kernel<float><<<grid, 256, 0, s>>>((const float*)xp, (float*)x, B, T, G, Cg, Cgp, front, pad,
+                                                     accumulate);
+  dph_count_launch();
+  return dph_check_last("posconv_unpad");
+}
+
+extern "C" int dph_cast(const void* in, int in_dtype, void* out, int out_dtype, int64_t n, void* stream) {
+  if (!in || !out || n <= 0) {
+    set_error("cast: bad arguments");
+    return DPH_ERR_ARG;
+  }
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  int grid = (int)((n + 255) / 256 < 148 * 16 ? (n + 255) / 256 : 148 * 16);
+  if (in_dtype == DPH_DTYPE_F32 && out_dtype == DPH_DTYPE_BF16)
+    cast_kernel<float, bf16><<<grid, 256, 0, s>>>((const float*)in, (bf16*)out, n);
+  else if (in_dtype == DPH_DTYPE_BF16 && out_dtype == DPH_DTYPE_F32)
+    cast_kernel<bf16, float><<<grid, 256, 0, s>>>((const bf16*)in, (float*)out, n);
+  else if (in_dtype == DPH_DTYPE_F32)
+    cast_kernel<float, float><<<grid, 256, 0, s>>>((const float*)in, (float*)out, n);
+  else
+    cast_kernel<bf16, bf16><<<grid, 256, 0, s>>>((const bf16*)in, (bf16*)out, n);
+  dph_count_launch();
+  return dph_check_last("cast");
+}
+
+extern "C" int dph_vec_mul(const float* a, const float* b, float* out, float alpha, float beta, int n, void* stream) {
+  if (!a || !out || n <= 0) {
+    set_error("vec_mul: bad arguments");
+    return DPH_ERR_ARG;
+  }
+  vec_mul_kernel<<<(n + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a, b, out, alpha, beta, n);
+  dph_count_launch();
+  return dph_check_last("vec_mul");
+}
+
+extern "C" int dph_transpose(const void* in, int in_dtype, void* out, int out_dtype, int B, int R, int C, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  dim3 grid((C + 31) / 32, (R + 31) / 32, B), blk(32, 8);
+  if (in_dtype == DPH_DTYPE_F32 && out_dtype == DPH_DTYPE_F32)
+    transpose_kernel<float, float><<<grid, blk, 0, s>>>((const float*)in, (float*)out, R, C);
+  else if (in_dtype == DPH_DTYPE_F32)
+    transpose_kernel<float, bf16><<<grid, blk, 0, s>>>((const float*)in, (bf16*)out, R, C);
+  else if (out_dtype == DPH_DTYPE_F32)
+    transpose_kernel<bf16, float><<<grid, blk, 0, s>>>((const bf16*)in, (float*)out, R, C);
+  else
+    transpose_kernel<bf16, bf16><<<grid, blk, 0, s>>>((const bf16*)in, (bf16*)out, R, C);
+  dph_count_launch();
+  return dph_check_last("transpose");
+}
+
+extern "C" int dph_memset(void* p, int value, int64_t bytes, void* stream) {
+  cudaError_t e = cudaMemsetAsync(p, value, (size_t)bytes, reinterpret_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) {
+    set_error("memset: %s", cudaGetErrorString(e));
+    return DPH_ERR_CUDA;
+  }
+  return DPH_OK;
+}
+
+extern "C" int dph_memset2d(void* p, int64_t pitch, int value, int64_t width, int64_t height, void* stream) {
+  cudaError_t e = cudaMemset2DAsync(p, (size_t)pitch, value, (size_t)width, (size_t)height,
+                                    reinterpret_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) {
+    set_error("memset2d: %s", cudaGetErrorString(e));
+    return DPH_ERR_CUDA;
+  }
+  return DPH_OK;
+}

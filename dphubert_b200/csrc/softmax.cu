@@ -1,0 +1,322 @@
+// Attention-probability kernels: masked / biased softmax forward and backward, WavLM gated relative position bias.
+//
+// Replaces wav2vec2/components.py:411-420 (scores += mask; -rowmax; softmax; dropout) and, for WavLM,
+// :629-647 (bucketed relative-position embedding x per-(batch, head, query) GRU gate added to the scores) plus
+// their autograd backward.  The additive padding mask (components.py:979-983) is rebuilt from `lengths` on the fly:
+// no (B,1,T,T) tensor and no (B*H,T,T) bias tensor is ever materialised.
+//
+// One warp owns one score row (T <= 1024 keys, i.e. ~20 s of audio; the reference caps utterances at 15.6 s).
+#include "common.cuh"
+#include "../../include/dphubert_b200.h"
+
+namespace dph {
+void set_error(const char* fmt, ...);
+
+constexpr int SM_NPL = 32;  // keys per lane -> T <= 1024
+
+struct WavlmBias {
+  const int* rel_table;   // (2T-1) bucket index of (j - i) + T - 1, built on the host exactly like the reference
+  const float* emb;       // (num_buckets, Htot)
+  const float* gate;      // (B, Htot, T) or null (ungated)
+  const int* head_index;  // (H) remaining head -> index in [0, Htot)
+  int Htot;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+    softmax_fwd_kernel(const float* __restrict__ S, long long lds, T* __restrict__ P, T* __restrict__ Pd, long long ldp,
+                       const long long* __restrict__ lengths, int B, int H, int Tn, float drop_p,
+                       unsigned long long seed, WavlmBias wb) {
+  const long long row = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  const long long nrows = (long long)B * H * Tn;
+  if (row >= nrows) return;
+  const int i = (int)(row % Tn);
+  const int bh = (int)(row / Tn);
+  const int h = bh % H, b = bh / H;
+  const float* s = S + row * lds;
+  const int len = lengths ? (int)lengths[b] : Tn;
+  float gate = 1.f;
+  int htot = h;
+  if (wb.emb) {
+    htot = wb.head_index ? wb.head_index[h] : h;
+    if (wb.gate) gate = wb.gate[((long long)b * wb.Htot + htot) * Tn + i];
+  }
+  float v[SM_NPL];
+  float mx = -INFINITY;
+#pragma unroll
+  for (int k = 0; k < SM_NPL; ++k) {
+    const int j = lane + 32 * k;
+    float x = -INFINITY;
+    if (j < Tn) {
+      x = s[j];
+      if (wb.emb) x += gate * __ldg(wb.emb + (long long)wb.rel_table[j - i + Tn - 1] * wb.Htot + htot);
+      if (j >= len) x += -10000.0f;
+    }
+    v[k] = x;
+    mx = fmaxf(mx, x);
+  }
+  mx = warp_max(mx);
+  float sum = 0.f;
+#pragma unroll
+  for (int k = 0; k < SM_NPL; ++k) {
+    const int j = lane + 32 * k;
+    float e = (j < Tn) ? expf(v[k] - mx) : 0.f;
+    v[k] = e;
+    sum += e;
+  }
+  sum = warp_sum(sum);
+  const float inv = 1.f / sum;
+  const uint32_t thresh = (uint32_t)(drop_p * 4294967296.0);
+  const float inv_keep = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+#pragma unroll
+  for (int k = 0; k < SM_NPL; ++k) {
+    const int j = lane + 32 * k;
+    if (j < Tn) {
+      const float p = v[k] * inv;
+      P[row * ldp + j] = from_f<T>(p);
+      if (Pd) Pd[row * ldp + j] = from_f<T>(p * dropout_scale(seed, (unsigned long long)row * Tn + j, thresh, inv_keep));
+    } else if (j < ldp) {
+      // keep the row padding (ldp >= Tn, multiple of 8) finite and zero: it is read as K-tail by the P*V GEMM
+      P[row * ldp + j] = from_f<T>(0.f);
+      if (Pd) Pd[row * ldp + j] = from_f<T>(0.f);
+    }
+  }
+}
+
+// dS = P * (dP - sum_j dP_j P_j), dP = dPd * dropout mask.  Optionally accumulates the WavLM bias gradients.
+template <typename T>
+__global__ void __launch_bounds__(256)
+    softmax_bwd_kernel(const T* __restrict__ P, const float* __restrict__ dPd, long long lds, T* __restrict__ dS,
+                       long long ldp, int B, int H, int Tn, float drop_p, unsigned long long seed, WavlmBias wb,
+                       float* __restrict__ dgate, float* __restrict__ demb, int num_buckets, int rows_per_blk) {
+  extern __shared__ float s_emb[];  // [num_buckets] when demb != null
+  const int warps = blockDim.x >> 5, w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // a block walks rows_per_blk consecutive rows; rows_per_blk divides T so that a block never crosses (b, h)
+  const long long row0 = (long long)blockIdx.x * rows_per_blk;
+  const long long nrows = (long long)B * H * Tn;
+  if (demb) {
+    for (int q = threadIdx.x; q < num_buckets; q += blockDim.x) s_emb[q] = 0.f;
+    __syncthreads();
+  }
+  const uint32_t thresh = (uint32_t)(drop_p * 4294967296.0);
+  const float inv_keep = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+  int htot_blk = 0;
+  for (int rr = w; rr < rows_per_blk; rr += warps) {
+    const long long row = row0 + rr;
+    if (row >= nrows) break;
+    const int i = (int)(row % Tn);
+    const int bh = (int)(row / Tn);
+    const int h = bh % H, b = bh / H;
+    float p[SM_NPL], d[SM_NPL];
+    float dot = 0.f;
+#pragma unroll
+    for (int k = 0; k < SM_NPL; ++k) {
+      const int j = lane + 32 * k;
+      p[k] = 0.f;
+      d[k] = 0.f;
+      if (j < Tn) {
+        p[k] = to_f(P[row * ldp + j]);
+        float g = dPd[row * lds + j];
+        if (drop_p > 0.f) g *= dropout_scale(seed, (unsigned long long)row * Tn + j, thresh, inv_keep);
+        d[k] = g;
+        dot += g * p[k];
+      }
+    }
+    dot = warp_sum(dot);
+    float gate = 1.f, dg = 0.f;
+    int htot = h;
+    if (wb.emb) {
+      htot = wb.head_index ? wb.head_index[h] : h;
+      htot_blk = htot;
+      if (wb.gate) gate = wb.gate[((long long)b * wb.Htot + htot) * Tn + i];
+    }
+#pragma unroll
+    for (int k = 0; k < SM_NPL; ++k) {
+      const int j = lane + 32 * k;
+      if (j < Tn) {
+        const float ds = p[k] * (d[k] - dot);
+        dS[row * ldp + j] = from_f<T>(ds);
+        if (wb.emb) {
+          const int bucket = wb.rel_table[j - i + Tn - 1];
+          if (dgate) dg += ds * __ldg(wb.emb + (long long)bucket * wb.Htot + htot);
+          if (demb) atomicAdd(&s_emb[bucket], ds * gate);
+        }
+      } else if (j < ldp) {
+        dS[row * ldp + j] = from_f<T>(0.f);
+      }
+    }
+    if (dgate) {
+      dg = warp_sum(dg);
+      if (lane == 0) dgate[((long long)b * wb.Htot + htot) * Tn + i] = dg;
+    }
+  }
+  if (demb) {
+    __syncthreads();
+    // all rows of this block share (b, h): flush the per-block histogram
+    const int bh = (int)(row0 / Tn);
+    const int h = bh % H;
+    const int htot = wb.head_index ? wb.head_index[h] : h;
+    (void)htot_blk;
+    for (int q = threadIdx.x; q < num_buckets; q += blockDim.x) {
+      const float val = s_emb[q];
+      if (val != 0.f) atomicAdd(demb + (long long)q * wb.Htot + htot, val);
+    }
+  }
+}
+
+// WavLM gate (components.py:636-644):  g8 = Linear(64->8)(x[b,t,h,:]);  ga = sigmoid(sum g8[0:4]); gb = sigmoid(sum g8[4:8])
+//   gate = ga * (gb * const[h] - 1) + 2.   x is the layer input viewed as (B, T, Htot, head_dim).
+template <typename T>
+__global__ void wavlm_gate_fwd_kernel(const T* __restrict__ x, const float* __restrict__ Wg, const float* __restrict__ bg,
+                                      const float* __restrict__ cst, float* __restrict__ gate, float* __restrict__ ga_out,
+                                      float* __restrict__ gb_out, int B, int Tn, int Htot, int Dh) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // over (b, t, h)
+  const long long total = (long long)B * Tn * Htot;
+  if (idx >= total) return;
+  const int h = (int)(idx % Htot);
+  const long long bt = idx / Htot;
+  const int t = (int)(bt % Tn), b = (int)(bt / Tn);
+  const T* xv = x + bt * ((long long)Htot * Dh) + (long long)h * Dh;
+  float acc[8];
+#pragma unroll
+  for (int o = 0; o < 8; ++o) acc[o] = bg[o];
+  for (int d = 0; d < Dh; ++d) {
+    const float xd = to_f(xv[d]);
+#pragma unroll
+    for (int o = 0; o < 8; ++o) acc[o] = fmaf(xd, __ldg(Wg + o * Dh + d), acc[o]);
+  }
+  const float ga = sigmoidf_(acc[0] + acc[1] + acc[2] + acc[3]);
+  const float gb = sigmoidf_(acc[4] + acc[5] + acc[6] + acc[7]);
+  const long long o = ((long long)b * Htot + h) * Tn + t;
+  gate[o] = ga * (gb * cst[h] - 1.f) + 2.f;
+  if (ga_out) ga_out[o] = ga;
+  if (gb_out) gb_out[o] = gb;
+}
+
+// backward of the gate: accumulates dWg (8,Dh), dbg (8), dconst (Htot) and ADDS the input gradient into dx.
+template <typename T>
+__global__ void __launch_bounds__(256)
+    wavlm_gate_bwd_kernel(const T* __restrict__ x, const float* __restrict__ Wg, const float* __restrict__ cst,
+                          const float* __restrict__ ga_in, const float* __restrict__ gb_in,
+                          const float* __restrict__ dgate, T* __restrict__ dx, float* __restrict__ dWg,
+                          float* __restrict__ dbg, float* __restrict__ dcst, int B, int Tn, int Htot, int Dh) {
+  extern __shared__ float sh[];  // [8*Dh + 8 + Htot]
+  float* s_dW = sh;
+  float* s_db = sh + 8 * Dh;
+  float* s_dc = s_db + 8;
+  for (int q = threadIdx.x; q < 8 * Dh + 8 + Htot; q += blockDim.x) sh[q] = 0.f;
+  __syncthreads();
+  const long long total = (long long)B * Tn * Htot;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int h = (int)(idx % Htot);
+    const long long bt = idx / Htot;
+    const int t = (int)(bt % Tn), b = (int)(bt / Tn);
+    const long long o = ((long long)b * Htot + h) * Tn + t;
+    const float dg = dgate[o], ga = ga_in[o], gb = gb_in[o], c = cst[h];
+    // gate = ga * (gb * c - 1) + 2
+    const float dga = dg * (gb * c - 1.f), dgb = dg * ga * c;
+    atomicAdd(&s_dc[h], dg * ga * gb);
+    const float dpa = dga * ga * (1.f - ga), dpb = dgb * gb * (1.f - gb);  // wrt the pre-sigmoid sums
+    const long long xo = bt * ((long long)Htot * Dh) + (long long)h * Dh;
+#pragma unroll
+    for (int o8 = 0; o8 < 8; ++o8) atomicAdd(&s_db[o8], o8 < 4 ? dpa : dpb);
+    for (int d = 0; d < Dh; ++d) {
+      const float xd = to_f(x[xo + d]);
+      float gx = 0.f;
+#pragma unroll
+      for (int o8 = 0; o8 < 8; ++o8) {
+        const float dp = o8 < 4 ? dpa : dpb;
+        atomicAdd(&s_dW[o8 * Dh + d], dp * xd);
+        gx = fmaf(dp, __ldg(Wg + o8 * Dh + d), gx);
+      }
+      if (dx) dx[xo + d] = from_f<T>(to_f(dx[xo + d]) + gx);
+    }
+  }
+  __syncthreads();
+  for (int q = threadIdx.x; q < 8 * Dh; q += blockDim.x) atomicAdd(dWg + q, s_dW[q]);
+  for (int q = threadIdx.x; q < 8; q += blockDim.x) atomicAdd(dbg + q, s_db[q]);
+  for (int q = threadIdx.x; q < Htot; q += blockDim.x) atomicAdd(dcst + q, s_dc[q]);
+}
+
+}  // namespace dph
+
+using namespace dph;
+
+extern "C" int dph_softmax_fwd(const float* S, int64_t lds, void* P, void* Pd, int64_t ldp, const int64_t* lengths, int B,
+                               int H, int T, float drop_p, uint64_t seed, const int* rel_table, const float* emb,
+                               const float* gate, const int* head_index, int Htot, int dtype, void* stream) {
+  if (!S || !P || B <= 0 || H <= 0 || T <= 0 || T > 32 * SM_NPL || ldp < T || lds < T) {
+    set_error("softmax_fwd: bad arguments (T=%d, max %d)", T, 32 * SM_NPL);
+    return DPH_ERR_ARG;
+  }
+  WavlmBias wb{rel_table, emb, gate, head_index, Htot};
+  const long long nrows = (long long)B * H * T;
+  const int grid = (int)((nrows + 7) / 8);
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (dtype == DPH_DTYPE_BF16)
+    softmax_fwd_kernel<bf16><<<grid, 256, 0, s>>>(S, lds, (bf16*)P, (bf16*)Pd, ldp, (const long long*)lengths, B, H, T,
+                                                  drop_p, seed, wb);
+  else
+    softmax_fwd_kernel<float><<<grid, 256, 0, s>>>(S, lds, (float*)P, (float*)Pd, ldp, (const long long*)lengths, B, H,
+                                                   T, drop_p, seed, wb);
+  dph_count_launch();
+  return dph_check_last("softmax_fwd");
+}
+
+extern "C" int dph_softmax_bwd(const void* P, const float* dPd, int64_t lds, void* dS, int64_t ldp, int B, int H, int T,
+                               float drop_p, uint64_t seed, const int* rel_table, const float* emb, const float* gate,
+                               const int* head_index, int Htot, float* dgate, float* demb, int num_buckets, int dtype,
+                               void* stream) {
+  if (!P || !dPd || !dS || B <= 0 || H <= 0 || T <= 0 || T > 32 * SM_NPL) {
+    set_error("softmax_bwd: bad arguments");
+    return DPH_ERR_ARG;
+  }
+  WavlmBias wb{rel_table, emb, gate, head_index, Htot};
+  // rows per block: largest divisor of T that is <= 64 (so a block stays within one (b, h))
+  int rpb = 1;
+  for (int d = 1; d <= 64; ++d)
+    if (T % d == 0) rpb = d;
+  const long long nrows = (long long)B * H * T;
+  const int grid = (int)(nrows / rpb);
+  const size_t smem = demb ? sizeof(float) * num_buckets : 0;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (dtype == DPH_DTYPE_BF16)
+    softmax_bwd_kernel<bf16><<<grid, 256, smem, s>>>((const bf16*)P, dPd, lds, (bf16*)dS, ldp, B, H, T, drop_p, seed, wb,
+                                                     dgate, demb, num_buckets, rpb);
+  else
+    softmax_bwd_kernel<float><<<grid, 256, smem, s>>>((const float*)P, dPd, lds, (float*)dS, ldp, B, H, T, drop_p, seed,
+                                                      wb, dgate, demb, num_buckets, rpb);
+  dph_count_launch();
+  return dph_check_last("softmax_bwd");
+}
+
+extern "C" int dph_wavlm_gate_fwd(const void* x, const float* Wg, const float* bg, const float* cst, float* gate,
+                                  float* ga, float* gb, int B, int T, int Htot, int Dh, int dtype, void* stream) {
+  const long long total = (long long)B * T * Htot;
+  const int grid = (int)((total + 127) / 128);
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (dtype == DPH_DTYPE_BF16)
+    wavlm_gate_fwd_kernel<bf16><<<grid, 128, 0, s>>>((const bf16*)x, Wg, bg, cst, gate, ga, gb, B, T, Htot, Dh);
+  else
+    wavlm_gate_fwd_kernel<float><<<grid, 128, 0, s>>>((const float*)x, Wg, bg, cst, gate, ga, gb, B, T, Htot, Dh);
+  dph_count_launch();
+  return dph_check_last("wavlm_gate_fwd");
+}
+
+extern "C" int dph_wavlm_gate_bwd(const void* x, const float* Wg, const float* cst, const float* ga, const float* gb,
+                                  const float* dgate, void* dx, float* dWg, float* dbg, float* dcst, int B, int T,
+                                  int Htot, int Dh, int dtype, void* stream) {
+  const size_t smem = sizeof(float) * (8 * Dh + 8 + Htot);
+  const int grid = 148;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (dtype == DPH_DTYPE_BF16)
+    wavlm_gate_bwd_kernel<bf16><<<grid, 256, smem, s>>>((const bf16*)x, Wg, cst, ga, gb, dgate, (bf16*)dx, dWg, dbg, dcst,
+                                                        B, T, Htot, Dh);
+  else
+    wavlm_gate_bwd_kernel<float><<<grid, 256, smem, s>>>((const float*)x, Wg, cst, ga, gb, dgate, (float*)dx, dWg, dbg,
+                                                         dcst, B, T, Htot, Dh);
+  dph_count_launch();
+  return dph_check_last("wavlm_gate_bwd");
+}
