@@ -59,6 +59,8 @@ class GemmDesc(ctypes.Structure):
         ("r_dtype", ctypes.c_int),
         ("drop_p", ctypes.c_float),
         ("seed", ctypes.c_uint64),
+        ("vec_sb0", ctypes.c_int64),
+        ("scalar_sb0", ctypes.c_int64),
     ]
 
 
@@ -100,6 +102,8 @@ class GemmF32Desc(ctypes.Structure):
         ("r_sb1", ctypes.c_int64),
         ("drop_p", ctypes.c_float),
         ("seed", ctypes.c_uint64),
+        ("vec_sb0", ctypes.c_int64),
+        ("scalar_sb0", ctypes.c_int64),
     ]
 
 

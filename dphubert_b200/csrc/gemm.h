@@ -31,6 +31,7 @@ struct GemmParams {
   int r_dtype;
   float drop_p;
   unsigned long long seed;
+  long long vec_sb0, scalar_sb0;
 };
 
 int gemm_bf16_launch(const dph_gemm_desc_t* d, cudaStream_t stream);

@@ -25,6 +25,7 @@ struct SimtParams {
   long long ldr, r_sb0, r_sb1;
   float drop_p;
   unsigned long long seed;
+  long long vec_sb0, scalar_sb0;
 };
 
 DPH_DEVICE long long opnd_off(const dph_operand_f32_t& o, int row, int k) {
@@ -90,7 +91,7 @@ __global__ void __launch_bounds__(256) gemm_f32_kernel(const SimtParams p) {
     __syncthreads();
   }
 
-  const float smask = p.scalar_mask ? __ldg(p.scalar_mask) : 1.0f;
+  const float smask = p.scalar_mask ? __ldg(p.scalar_mask + b0 * p.scalar_sb0) : 1.0f;
   const uint32_t thresh = (uint32_t)(p.drop_p * 4294967296.0);
   const float inv_keep = p.drop_p > 0.0f ? 1.0f / (1.0f - p.drop_p) : 1.0f;
 #pragma unroll
@@ -102,11 +103,11 @@ __global__ void __launch_bounds__(256) gemm_f32_kernel(const SimtParams p) {
       int n = n0 + tx * 4 + j;
       if (n >= p.N) continue;
       float v = acc[i][j] * p.alpha;
-      if (p.bias) v += __ldg(p.bias + n);
+      if (p.bias) v += __ldg(p.bias + b0 * p.vec_sb0 + n);
       long long coff = (long long)b0 * p.c_sb0 + (long long)b1 * p.c_sb1 + (long long)m * p.ldc + n;
       if (p.C2) p.C2[coff] = v;
       if (p.act == 1) v = gelu_erf(v);
-      if (p.colmask) v *= __ldg(p.colmask + n);
+      if (p.colmask) v *= __ldg(p.colmask + b0 * p.vec_sb0 + n);
       v *= smask;
       if (p.drop_p > 0.0f) {
         unsigned long long idx =
@@ -115,8 +116,12 @@ __global__ void __launch_bounds__(256) gemm_f32_kernel(const SimtParams p) {
       }
       if (p.residual)
         v += p.residual[(long long)b0 * p.r_sb0 + (long long)b1 * p.r_sb1 + (long long)m * p.ldr + n];
-      if (p.accumulate) v += p.C[coff];
-      p.C[coff] = v;
+      if (p.accumulate == 2) {
+        atomicAdd(&p.C[coff], v);
+      } else {
+        if (p.accumulate) v += p.C[coff];
+        p.C[coff] = v;
+      }
     }
   }
 }
@@ -156,6 +161,8 @@ extern "C" int dph_gemm_f32(const dph_gemm_f32_desc_t* d, void* stream) {
   p.r_sb1 = d->r_sb1;
   p.drop_p = d->drop_p;
   p.seed = d->seed;
+  p.vec_sb0 = d->vec_sb0;
+  p.scalar_sb0 = d->scalar_sb0;
   long long nz = (long long)d->nb0 * d->nb1;
   if (nz > 65535) {
     set_error("gemm_f32: too many batches");

@@ -63,7 +63,7 @@ DPH_DEVICE void epilogue_chunk(const GemmParams& p, const TileCoord& tc, int row
   if (p.bias != nullptr) {
 #pragma unroll
     for (int j = 0; j < 32; ++j)
-      if (j < nvalid) v[j] += __ldg(p.bias + col0 + j);
+      if (j < nvalid) v[j] += __ldg(p.bias + tc.b0 * p.vec_sb0 + col0 + j);
   }
   const bool full = (nvalid == 32) && p.vec_ok;
   if (p.C2 != nullptr) {
@@ -94,10 +94,10 @@ DPH_DEVICE void epilogue_chunk(const GemmParams& p, const TileCoord& tc, int row
   if (p.colmask != nullptr) {
 #pragma unroll
     for (int j = 0; j < 32; ++j)
-      if (j < nvalid) v[j] *= __ldg(p.colmask + col0 + j);
+      if (j < nvalid) v[j] *= __ldg(p.colmask + tc.b0 * p.vec_sb0 + col0 + j);
   }
   if (p.scalar_mask != nullptr) {
-    const float s = __ldg(p.scalar_mask);
+    const float s = __ldg(p.scalar_mask + tc.b0 * p.scalar_sb0);
 #pragma unroll
     for (int j = 0; j < 32; ++j) v[j] *= s;
   }
@@ -549,6 +549,8 @@ int gemm_bf16_launch(const dph_gemm_desc_t* d, cudaStream_t stream) {
   p.r_dtype = d->r_dtype;
   p.drop_p = d->drop_p;
   p.seed = d->seed;
+  p.vec_sb0 = d->vec_sb0;
+  p.scalar_sb0 = d->scalar_sb0;
   // vector access legality
   const int celt = d->c_dtype == 0 ? 8 : 4;
   bool vec = (d->ldc % celt == 0) && (d->c_sb0 % celt == 0) && (d->c_sb1 % celt == 0) &&

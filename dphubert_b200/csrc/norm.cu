@@ -72,7 +72,8 @@ __global__ void __launch_bounds__(256)
                          const float* __restrict__ w, const float* __restrict__ b, const float* __restrict__ mean_in,
                          const float* __restrict__ rstd_in, T* __restrict__ dx, float* __restrict__ dw,
                          float* __restrict__ db, const float* __restrict__ colmask, float* __restrict__ dmask, int rows,
-                         int D, int act, float drop_p, unsigned long long seed, int rows_per_warp) {
+                         int D, int act, float drop_p, unsigned long long seed, int rows_per_warp,
+                         int rows_per_batch, long long out_bs, int out_row_off) {
   extern __shared__ float sh[];  // [3][D] : dw, db, dmask partials
   float* s_dw = sh;
   float* s_db = sh + D;
@@ -126,10 +127,12 @@ __global__ void __launch_bounds__(256)
     }
     s1 = warp_sum(s1) / D;
     s2 = warp_sum(s2) / D;
+    const int ob = row / rows_per_batch;
+    const long long ooff = (long long)ob * out_bs + (long long)(row - ob * rows_per_batch + out_row_off) * D;
 #pragma unroll
     for (int k = 0; k < NPL; ++k) {
       const int i = lane + 32 * k;
-      if (i < D) dx[off + i] = from_f<T>(rstd * (g[k] - s1 - xh[k] * s2));
+      if (i < D) dx[ooff + i] = from_f<T>(rstd * (g[k] - s1 - xh[k] * s2));
     }
   }
 #pragma unroll
@@ -183,7 +186,13 @@ extern "C" int dph_layernorm_fwd(const void* x, const float* w, const float* b, 
 extern "C" int dph_layernorm_bwd(const void* dy, const void* dy2, const void* x, const float* w, const float* b,
                                  const float* mean, const float* rstd, void* dx, float* dw, float* db,
                                  const float* colmask, float* dmask, int rows, int D, int act, float drop_p,
-                                 uint64_t seed, int dtype, void* stream) {
+                                 uint64_t seed, int rows_per_batch, int64_t out_bs, int out_row_off, int dtype,
+                                 void* stream) {
+  if (rows_per_batch <= 0) {
+    rows_per_batch = rows;
+    out_bs = 0;
+    out_row_off = 0;
+  }
   if (!dy || !x || !w || !b || !mean || !rstd || !dx || rows <= 0 || D <= 0 || D > 32 * LN_MAX_PER_LANE) {
     set_error("layernorm_bwd: bad arguments (D=%d)", D);
     return DPH_ERR_ARG;
@@ -202,12 +211,14 @@ extern "C" int dph_layernorm_bwd(const void* dy, const void* dy2, const void* x,
     if (dtype == DPH_DTYPE_BF16)                                                                                 \
       layernorm_bwd_kernel<bf16, NPL><<<grid, 256, smem, s>>>((const bf16*)dy, (const bf16*)dy2, (const bf16*)x, \
                                                               w, b, mean, rstd, (bf16*)dx, dw, db, colmask,      \
-                                                              dmask, rows, D, act, drop_p, seed, rows_per_warp); \
+                                                              dmask, rows, D, act, drop_p, seed, rows_per_warp, \
+                                                              rows_per_batch, out_bs, out_row_off);              \
     else                                                                                                         \
       layernorm_bwd_kernel<float, NPL><<<grid, 256, smem, s>>>((const float*)dy, (const float*)dy2,              \
                                                                (const float*)x, w, b, mean, rstd, (float*)dx,    \
                                                                dw, db, colmask, dmask, rows, D, act, drop_p,     \
-                                                               seed, rows_per_warp);                             \
+                                                               seed, rows_per_warp, rows_per_batch, out_bs,      \
+                                                               out_row_off);                                     \
   } while (0)
   if (D <= 512) LN_BWD(16);
   else if (D <= 768) LN_BWD(24);

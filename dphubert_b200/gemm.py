@@ -84,7 +84,7 @@ def _operand_f32(v):
 
 def gemm(a, b, c, M, N, K, *, ldc=None, nb0=1, nb1=1, c_sb0=0, c_sb1=0, c_offset=0, alpha=1.0, bias=None, act=0,
          colmask=None, scalar_mask=None, residual=None, ldr=None, r_sb0=0, r_sb1=0, r_offset=0, c2=None,
-         accumulate=False, atomic=False, ksplit=1, drop_p=0.0, seed=0, block_n=0):
+         accumulate=False, atomic=False, ksplit=1, drop_p=0.0, seed=0, block_n=0, vec_sb0=0, scalar_sb0=0):
     """C[b][m, n] = epilogue(alpha * sum_k a(m,k) b(n,k)).  `a`, `b` are `View`s; dtype of `a.t` selects the path:
     bf16 -> tcgen05 tensor-core kernel, fp32 -> CUDA-core kernel."""
     L = _lib.lib()
@@ -114,6 +114,7 @@ def gemm(a, b, c, M, N, K, *, ldc=None, nb0=1, nb1=1, c_sb0=0, c_sb1=0, c_offset
             d.r_dtype = dtype_code(residual)
         d.ldr, d.r_sb0, d.r_sb1 = ldr, r_sb0, r_sb1
         d.drop_p, d.seed = drop_p, seed
+        d.vec_sb0, d.scalar_sb0 = vec_sb0, scalar_sb0
         _lib.check(L.dph_gemm_bf16(ctypes.byref(d), _lib.stream_ptr()), "dph_gemm_bf16")
     else:
         assert a.t.dtype == torch.float32 and b.t.dtype == torch.float32 and c.dtype == torch.float32
@@ -124,7 +125,7 @@ def gemm(a, b, c, M, N, K, *, ldc=None, nb0=1, nb1=1, c_sb0=0, c_sb1=0, c_offset
         d.c = c.data_ptr() + c_offset * 4
         d.c2 = None if c2 is None else c2.data_ptr() + c_offset * 4
         d.ldc, d.c_sb0, d.c_sb1 = ldc, c_sb0, c_sb1
-        d.accumulate = 1 if (accumulate or atomic) else 0
+        d.accumulate = 2 if atomic else (1 if accumulate else 0)
         d.alpha = alpha
         d.bias = None if bias is None else bias.data_ptr()
         d.act = act
@@ -133,5 +134,6 @@ def gemm(a, b, c, M, N, K, *, ldc=None, nb0=1, nb1=1, c_sb0=0, c_sb1=0, c_offset
         d.residual = None if residual is None else residual.data_ptr() + r_offset * 4
         d.ldr, d.r_sb0, d.r_sb1 = ldr, r_sb0, r_sb1
         d.drop_p, d.seed = drop_p, seed
+        d.vec_sb0, d.scalar_sb0 = vec_sb0, scalar_sb0
         _lib.check(L.dph_gemm_f32(ctypes.byref(d), _lib.stream_ptr()), "dph_gemm_f32")
     return c

@@ -76,6 +76,8 @@ typedef struct {
   int r_dtype;
   float drop_p;             /* 0 disables dropout */
   uint64_t seed;
+  int64_t vec_sb0;          /* element offset added to bias / colmask per batch index b0 (grouped conv, heads) */
+  int64_t scalar_sb0;       /* element offset added to scalar_mask per batch index b0 (per-head HardConcrete mask) */
 } dph_gemm_desc_t;
 
 int dph_gemm_bf16(const dph_gemm_desc_t* desc, void* stream);
@@ -97,7 +99,7 @@ typedef struct {
   float* c;
   float* c2;
   int64_t ldc, c_sb0, c_sb1;
-  int accumulate;     /* 1: C += result */
+  int accumulate;     /* 1: C += result; 2: atomicAdd (batches may alias the same C) */
   float alpha;
   const float* bias;
   int act;
@@ -107,6 +109,7 @@ typedef struct {
   int64_t ldr, r_sb0, r_sb1;
   float drop_p;
   uint64_t seed;
+  int64_t vec_sb0, scalar_sb0;
 } dph_gemm_f32_desc_t;
 
 int dph_gemm_f32(const dph_gemm_f32_desc_t* desc, void* stream);
