@@ -17,7 +17,7 @@ OBJ_DIR = os.path.join(ROOT, "build", "obj")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
-    "-O3", "-std=c++17", "-lineinfo",
+    "-O3", "-std=c++17", "-lineinfo", "-rdc=true",
     "-Xcompiler", "-fPIC",
     "--expt-relaxed-constexpr",
     "-I", os.path.join(ROOT, "include"),

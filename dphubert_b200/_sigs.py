@@ -13,6 +13,8 @@ SIGS = {
     "dph_launch_count_reset": [],
     "dph_abi_version": [],
     "dph_last_error": [],
+    "dph_rng_set": [u64, vp],
+    "dph_rng_advance": [vp],
     "dph_gemm_bf16": [vp, vp],
     "dph_gemm_f32": [vp, vp],
     # norm.cu
@@ -29,11 +31,14 @@ SIGS = {
     "dph_transpose": [vp, i32, vp, i32, i32, i32, i32, vp],
     "dph_memset": [vp, i32, i64, vp],
     "dph_memset2d": [vp, i64, i32, i64, i64, vp],
+    "dph_axpy": [vp, vp, i64, i32, vp],
+    "dph_group_mask_bwd": [vp, vp, vp, vp, vp, i32, i32, i32, i32, vp],
     # conv0.cu
     "dph_conv0_stats": [vp, i64, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f32, vp],
     "dph_conv0_fwd": [vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp],
     "dph_conv0_bwd": [vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32,
                       i32, i32, vp],
+    "dph_wave_norm": [vp, i64, vp, i64, vp, i32, i32, f32, vp],
     # softmax.cu
     "dph_softmax_fwd": [vp, i64, vp, vp, i64, vp, i32, i32, i32, f32, u64, vp, vp, vp, vp, i32, i32, vp],
     "dph_softmax_bwd": [vp, vp, i64, vp, i64, i32, i32, i32, f32, u64, vp, vp, vp, vp, i32, vp, vp, i32, i32, vp],

@@ -21,6 +21,8 @@ extern "C" long long dph_launch_count(void);
 void dph_count_launch(int n = 1);
 int dph_check_last(const char* what);
 
+extern __device__ unsigned long long dph_rng_epoch;
+
 namespace dph {
 
 constexpr int kNumSMsDefault = 148;
@@ -66,8 +68,10 @@ DPH_DEVICE float block_sum(float v, float* red) {
 
 // Counter-based RNG for dropout: one 32-bit hash per (seed, element index). Stateless so the
 // backward pass can regenerate the identical keep mask.
+// `dph_rng_epoch` lives in device memory and is advanced by a one-thread kernel (dph_rng_advance) once per
+// training step, so a step captured in a CUDA graph (kernel arguments frozen) still draws fresh masks every replay.
 DPH_DEVICE uint32_t hash_u32(uint64_t seed, uint64_t idx) {
-  uint64_t z = seed + idx * 0x9E3779B97F4A7C15ull + 0x632BE59BD9B4E019ull;
+  uint64_t z = seed + dph_rng_epoch * 0xD1B54A32D192ED03ull + idx * 0x9E3779B97F4A7C15ull + 0x632BE59BD9B4E019ull;
   z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
   z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
   z = z ^ (z >> 31);

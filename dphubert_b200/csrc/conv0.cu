@@ -361,6 +361,49 @@ __global__ void conv0_bwd_affine_kernel(const float* __restrict__ sumA, const fl
   if (dbeta) atomicAdd(dbeta + c, a);
 }
 
+
+// Per-utterance waveform normalisation (model.py:96-103: F.layer_norm over the valid samples, zero padding after).
+// One CTA per utterance: at most ~250 k samples, read three times from L2.
+__global__ void __launch_bounds__(1024)
+    wave_norm_kernel(const float* __restrict__ in, long long in_bs, float* __restrict__ out, long long out_bs,
+                     const long long* __restrict__ lengths, int T0, float eps) {
+  __shared__ double shd[32];
+  __shared__ double s_bcast;
+  const int b = blockIdx.x;
+  const float* x = in + (long long)b * in_bs;
+  float* y = out + (long long)b * out_bs;
+  long long len = lengths ? lengths[b] : T0;
+  if (len > T0) len = T0;
+  if (len < 0) len = 0;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  auto block_sum_d = [&](double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();
+    if (lane == 0) shd[w] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double t = 0.0;
+      for (int q = 0; q < (int)(blockDim.x >> 5); ++q) t += shd[q];
+      s_bcast = t;
+    }
+    __syncthreads();
+    return s_bcast;
+  };
+  double acc = 0.0;
+  for (long long i = threadIdx.x; i < len; i += blockDim.x) acc += (double)x[i];
+  const double mean = len > 0 ? block_sum_d(acc) / (double)len : 0.0;
+  acc = 0.0;
+  for (long long i = threadIdx.x; i < len; i += blockDim.x) {
+    const double d = (double)x[i] - mean;
+    acc += d * d;
+  }
+  const double var = len > 0 ? block_sum_d(acc) / (double)len : 0.0;
+  const float rstd = (float)(1.0 / sqrt(var + (double)eps));
+  const float mu = (float)mean;
+  for (long long i = threadIdx.x; i < T0; i += blockDim.x) y[i] = i < len ? (x[i] - mu) * rstd : 0.f;
+}
+
 }  // namespace dph
 
 using namespace dph;
@@ -446,4 +489,16 @@ extern "C" int dph_conv0_bwd(const float* wave, int64_t wave_bs, const float* w,
   }
   dph_count_launch(launches);
   return dph_check_last("conv0_bwd");
+}
+
+extern "C" int dph_wave_norm(const float* in, int64_t in_bs, float* out, int64_t out_bs, const int64_t* lengths, int B,
+                             int T0, float eps, void* stream) {
+  if (!in || !out || B <= 0 || T0 <= 0) {
+    set_error("wave_norm: bad arguments");
+    return DPH_ERR_ARG;
+  }
+  wave_norm_kernel<<<B, 1024, 0, reinterpret_cast<cudaStream_t>(stream)>>>(in, in_bs, out, out_bs,
+                                                                           (const long long*)lengths, T0, eps);
+  dph_count_launch();
+  return dph_check_last("wave_norm");
 }

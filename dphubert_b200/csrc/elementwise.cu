@@ -172,6 +172,55 @@ __global__ void transpose_kernel(const TI* __restrict__ in, TO* __restrict__ out
   }
 }
 
+
+// dst[i] += src[i]
+template <typename T, int VEC>
+__global__ void axpy_kernel(T* __restrict__ dst, const T* __restrict__ src, long long n) {
+  const long long nv = n / VEC;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += (long long)gridDim.x * blockDim.x) {
+    if constexpr (VEC == 1) {
+      dst[i] = from_f<T>(to_f(dst[i]) + to_f(src[i]));
+    } else {
+      float a[VEC], b[VEC];
+      load_vec(dst + i * VEC, a);
+      load_vec(src + i * VEC, b);
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) a[j] += b[j];
+      store_vec(dst + i * VEC, a);
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    for (long long i = nv * VEC; i < n; ++i) dst[i] = from_f<T>(to_f(dst[i]) + to_f(src[i]));
+}
+
+// Backward of a per-group column mask (attention-head HardConcrete mask, components.py:424-426):
+//   dout[r, c] = dy[r, c] * mask[c / group];   dmask[c / group] += sum_r dy[r, c] * z[r, c]
+template <typename T>
+__global__ void __launch_bounds__(128)
+    group_mask_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ z, const float* __restrict__ mask,
+                          T* __restrict__ dout, float* __restrict__ dmask, int rows, int C, int group, int rows_per_blk) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int r0 = blockIdx.y * rows_per_blk;
+  const int r1 = min(rows, r0 + rows_per_blk);
+  float acc = 0.f;
+  if (c < C) {
+    const float m = __ldg(mask + c / group);
+    for (int r = r0; r < r1; ++r) {
+      const long long o = (long long)r * C + c;
+      const float d = to_f(dy[o]);
+      acc += d * to_f(z[o]);
+      dout[o] = from_f<T>(d * m);
+    }
+  }
+  // threads of a warp cover 32 consecutive columns; when group is a multiple of 32 they share one gate
+  if (group % 32 == 0) {
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0 && c < C) atomicAdd(dmask + c / group, acc);
+  } else if (c < C) {
+    atomicAdd(dmask + c / group, acc);
+  }
+}
+
 }  // namespace dph
 
 using namespace dph;
@@ -326,4 +375,47 @@ extern "C" int dph_memset2d(void* p, int64_t pitch, int value, int64_t width, in
     return DPH_ERR_CUDA;
   }
   return DPH_OK;
+}
+
+extern "C" int dph_axpy(void* dst, const void* src, int64_t n, int dtype, void* stream) {
+  if (!dst || !src || n <= 0) {
+    set_error("axpy: bad arguments");
+    return DPH_ERR_ARG;
+  }
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const bool al = ((reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src)) & 15) == 0;
+  long long nv = n / (dtype == DPH_DTYPE_BF16 ? 8 : 4);
+  int grid = (int)((nv + 255) / 256 < 148 * 16 ? (nv + 255) / 256 : 148 * 16);
+  if (grid < 1) grid = 1;
+  if (dtype == DPH_DTYPE_BF16) {
+    if (al) axpy_kernel<bf16, 8><<<grid, 256, 0, s>>>((bf16*)dst, (const bf16*)src, n);
+    else axpy_kernel<bf16, 1><<<148 * 8, 256, 0, s>>>((bf16*)dst, (const bf16*)src, n);
+  } else {
+    if (al) axpy_kernel<float, 4><<<grid, 256, 0, s>>>((float*)dst, (const float*)src, n);
+    else axpy_kernel<float, 1><<<148 * 8, 256, 0, s>>>((float*)dst, (const float*)src, n);
+  }
+  dph_count_launch();
+  return dph_check_last("axpy");
+}
+
+extern "C" int dph_group_mask_bwd(const void* dy, const void* z, const float* mask, void* dout, float* dmask, int rows,
+                                  int C, int group, int dtype, void* stream) {
+  if (!dy || !z || !mask || !dout || !dmask || rows <= 0 || C <= 0 || group <= 0) {
+    set_error("group_mask_bwd: bad arguments");
+    return DPH_ERR_ARG;
+  }
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const int gx = (C + 127) / 128;
+  int target_y = (148 * 8 + gx - 1) / gx;
+  int rows_per_blk = (rows + target_y - 1) / target_y;
+  if (rows_per_blk < 4) rows_per_blk = 4;
+  dim3 grid(gx, (rows + rows_per_blk - 1) / rows_per_blk);
+  if (dtype == DPH_DTYPE_BF16)
+    group_mask_bwd_kernel<bf16><<<grid, 128, 0, s>>>((const bf16*)dy, (const bf16*)z, mask, (bf16*)dout, dmask, rows, C,
+                                                     group, rows_per_blk);
+  else
+    group_mask_bwd_kernel<float><<<grid, 128, 0, s>>>((const float*)dy, (const float*)z, mask, (float*)dout, dmask, rows,
+                                                      C, group, rows_per_blk);
+  dph_count_launch();
+  return dph_check_last("group_mask_bwd");
 }

@@ -5,6 +5,12 @@
 
 #include "common.cuh"
 
+__device__ unsigned long long dph_rng_epoch = 0;
+
+__global__ void rng_epoch_kernel(unsigned long long value, int advance) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) dph_rng_epoch = advance ? dph_rng_epoch + 1ull : value;
+}
+
 static std::atomic<long long> g_launches{0};
 static thread_local char g_err[512] = "";
 
@@ -31,6 +37,16 @@ int dph_check_last(const char* what) {
 }
 
 extern "C" {
+int dph_rng_set(unsigned long long value, void* stream) {
+  rng_epoch_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(value, 0);
+  dph_count_launch();
+  return dph_check_last("rng_set");
+}
+int dph_rng_advance(void* stream) {
+  rng_epoch_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(0ull, 1);
+  dph_count_launch();
+  return dph_check_last("rng_advance");
+}
 long long dph_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 void dph_launch_count_reset(void) { g_launches.store(0, std::memory_order_relaxed); }
 int dph_abi_version(void) { return 1; }

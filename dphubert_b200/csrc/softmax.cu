@@ -92,9 +92,10 @@ __global__ void __launch_bounds__(256)
                        float* __restrict__ dgate, float* __restrict__ demb, int num_buckets, int rows_per_blk) {
   extern __shared__ float s_emb[];  // [num_buckets] when demb != null
   const int warps = blockDim.x >> 5, w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // a block walks rows_per_blk consecutive rows; rows_per_blk divides T so that a block never crosses (b, h)
-  const long long row0 = (long long)blockIdx.x * rows_per_blk;
-  const long long nrows = (long long)B * H * Tn;
+  // grid.y = (b, h); grid.x walks the Tn query rows of that head in chunks of rows_per_blk
+  const int i0 = blockIdx.x * rows_per_blk;
+  const int nloc = min(rows_per_blk, Tn - i0);
+  const long long row0 = (long long)blockIdx.y * Tn + i0;
   if (demb) {
     for (int q = threadIdx.x; q < num_buckets; q += blockDim.x) s_emb[q] = 0.f;
     __syncthreads();
@@ -102,9 +103,8 @@ __global__ void __launch_bounds__(256)
   const uint32_t thresh = (uint32_t)(drop_p * 4294967296.0);
   const float inv_keep = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
   int htot_blk = 0;
-  for (int rr = w; rr < rows_per_blk; rr += warps) {
+  for (int rr = w; rr < nloc; rr += warps) {
     const long long row = row0 + rr;
-    if (row >= nrows) break;
     const int i = (int)(row % Tn);
     const int bh = (int)(row / Tn);
     const int h = bh % H, b = bh / H;
@@ -274,12 +274,9 @@ extern "C" int dph_softmax_bwd(const void* P, const float* dPd, int64_t lds, voi
     return DPH_ERR_ARG;
   }
   WavlmBias wb{rel_table, emb, gate, head_index, Htot};
-  // rows per block: largest divisor of T that is <= 64 (so a block stays within one (b, h))
-  int rpb = 1;
-  for (int d = 1; d <= 64; ++d)
-    if (T % d == 0) rpb = d;
-  const long long nrows = (long long)B * H * T;
-  const int grid = (int)(nrows / rpb);
+  // 32 query rows of one (b, h) per block (the bias-embedding histogram is flushed once per block)
+  const int rpb = 32;
+  const dim3 grid((T + rpb - 1) / rpb, B * H);
   const size_t smem = demb ? sizeof(float) * num_buckets : 0;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   if (dtype == DPH_DTYPE_BF16)

@@ -227,6 +227,32 @@ class Plan:
         o = self.offsets[id(p)]
         return self.lin16[o:o + p.numel()].view(p.shape)
 
+    def W(self, p, dtype):
+        """GEMM operand copy of a Linear weight in the compute dtype."""
+        return self.w16(p) if dtype == torch.bfloat16 else self.view(p)
+
+    def wcat(self, ps, dtype):
+        """Row-concatenation of consecutive Linear weights (same in_features) as one (sum out, in) matrix — valid
+        because the arena lays them out back to back (used for the fused K/V/Q projection)."""
+        o0 = self.offsets[id(ps[0])]
+        o = o0
+        for q in ps:
+            if self.offsets[id(q)] != o or q.numel() % ALIGN:
+                raise DphShapeError("parameters are not contiguous in the arena")
+            o += q.numel()
+        base = self.lin16 if dtype == torch.bfloat16 else self.arena
+        return base[o0:o].view(-1, ps[0].shape[1])
+
+    def vcat(self, ps):
+        """Concatenation of consecutive fp32 vectors (biases) in the arena."""
+        o0 = self.offsets[id(ps[0])]
+        o = o0
+        for q in ps:
+            if self.offsets[id(q)] != o or q.numel() % ALIGN:
+                raise DphShapeError("bias vectors are not contiguous in the arena")
+            o += q.numel()
+        return self.arena[o0:o]
+
 
 def _align_to(n, a):
     return (n + a - 1) // a * a
@@ -463,7 +489,7 @@ def _conv_weight_views(plan, blk, i, dtype):
     return fwd, phases
 
 
-def conv_stack_fwd(plan: Plan, wave, masks, save: bool):
+def conv_stack_fwd(plan: Plan, wave, masks, save: bool, A=None):
     """wave (B, T0) fp32 -> features (B, T, C) in the compute dtype. Returns (features, saved-state dict)."""
     model = plan.model
     fe = model.feature_extractor
@@ -471,6 +497,8 @@ def conv_stack_fwd(plan: Plan, wave, masks, save: bool):
     dev = plan.device
     B, T0 = wave.shape
     wave = wave.contiguous()
+    if A is None:
+        A = FreshAlloc(dev)
     if wave.dtype != torch.float32:
         raise _lib.DphError("waveforms must be float32")
     st = {"wave": wave, "layers": [], "B": B}
@@ -491,14 +519,14 @@ def conv_stack_fwd(plan: Plan, wave, masks, save: bool):
             if mask is None:
                 colmask = dummy
             else:
-                colmask = torch.empty_like(dummy)
+                colmask = A("conv_last_colmask", (dummy.numel(),), torch.float32)
                 ops.vec_mul(mask, dummy, colmask)
         ln = blk.layer_norm
         is_gn = isinstance(ln, torch.nn.GroupNorm)
         bias = plan.view(conv.bias) if conv.bias is not None else None
         rec = {"blk": blk, "i": i, "Tin": Tin, "Tout": Tout, "Cin": Cin, "Cout": Cout, "colmask": colmask,
                "has_mask": mask is not None, "x_in": x}
-        y = torch.empty(B, Tout, Cout, dtype=dt, device=dev)
+        y = A("conv%d_y" % i, (B, Tout, Cout), dt)
         if i == 0:
             if Cin != 1:
                 raise DphShapeError("first conv layer must have one input channel")
@@ -506,18 +534,18 @@ def conv_stack_fwd(plan: Plan, wave, masks, save: bool):
             if is_gn:
                 if ln.num_groups != Cout:
                     raise DphShapeError("GroupNorm must have one group per channel")
-                moments = torch.empty(B * 65, dtype=torch.float64, device=dev)
-                mean = torch.empty(B * Cout, dtype=torch.float32, device=dev)
-                rstd = torch.empty(B * Cout, dtype=torch.float32, device=dev)
+                moments = A("conv0_moments", (B * 65,), torch.float64)
+                mean = A("conv0_mean", (B * Cout,), torch.float32)
+                rstd = A("conv0_rstd", (B * Cout,), torch.float32)
                 ops.conv0_stats(wave, w, bias, moments, mean, rstd, B, Cout, k, s, Tout, ln.eps)
                 ops.conv0_fwd(wave, w, bias, plan.view(ln.weight), plan.view(ln.bias), mean, rstd, colmask, y, B, Cout,
                               k, s, Tout, 1, 1)
                 rec.update(mean=mean, rstd=rstd, mode="gn")
             elif ln is not None:
-                z = torch.empty(B, Tout, Cout, dtype=dt, device=dev)
+                z = A("conv%d_z" % i, (B, Tout, Cout), dt)
                 ops.conv0_fwd(wave, w, bias, None, None, None, None, None, z, B, Cout, k, s, Tout, 0, 0)
-                mean = torch.empty(B * Tout, dtype=torch.float32, device=dev)
-                rstd = torch.empty(B * Tout, dtype=torch.float32, device=dev)
+                mean = A("conv%d_mean" % i, (B * Tout,), torch.float32)
+                rstd = A("conv%d_rstd" % i, (B * Tout,), torch.float32)
                 ops.layernorm_fwd(z, plan.view(ln.weight), plan.view(ln.bias), y, B * Tout, Cout, ln.eps, mean, rstd,
                                   colmask=colmask, act=1)
                 rec.update(z=z, mean=mean, rstd=rstd, mode="ln")
@@ -528,17 +556,17 @@ def conv_stack_fwd(plan: Plan, wave, masks, save: bool):
             fwd_w, _ = _conv_weight_views(plan, blk, i, dt)
             a = View(x, Tout, k * Cin, s * Cin, sb0=Tin * Cin)
             if ln is None:
-                z = torch.empty(B, Tout, Cout, dtype=dt, device=dev) if save else None
+                z = A("conv%d_z" % i, (B, Tout, Cout), dt) if save else None
                 G.gemm(a, fwd_w, y, Tout, Cout, k * Cin, nb0=B, c_sb0=Tout * Cout, bias=bias, act=1, colmask=colmask,
                        c2=z)
                 rec.update(z=z, mode="none")
             else:
                 if is_gn:
                     raise DphShapeError("GroupNorm is only supported on the first conv layer (as in the reference)")
-                z = torch.empty(B, Tout, Cout, dtype=dt, device=dev)
+                z = A("conv%d_z" % i, (B, Tout, Cout), dt)
                 G.gemm(a, fwd_w, z, Tout, Cout, k * Cin, nb0=B, c_sb0=Tout * Cout, bias=bias)
-                mean = torch.empty(B * Tout, dtype=torch.float32, device=dev)
-                rstd = torch.empty(B * Tout, dtype=torch.float32, device=dev)
+                mean = A("conv%d_mean" % i, (B * Tout,), torch.float32)
+                rstd = A("conv%d_rstd" % i, (B * Tout,), torch.float32)
                 ops.layernorm_fwd(z, plan.view(ln.weight), plan.view(ln.bias), y, B * Tout, Cout, ln.eps, mean, rstd,
                                   colmask=colmask, act=1)
                 rec.update(z=z, mean=mean, rstd=rstd, mode="ln")
@@ -547,3 +575,799 @@ def conv_stack_fwd(plan: Plan, wave, masks, save: bool):
         x = y
         Tin, Cin = Tout, Cout
     return x, st
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# Buffer allocation: fresh tensors per call (autograd / module API) or a static, named workspace (training step:
+# addresses never change, so the whole step can be captured in a CUDA graph)
+# ----------------------------------------------------------------------------------------------------------------
+class FreshAlloc:
+    static = False
+
+    def __init__(self, device):
+        self.device = device
+
+    def __call__(self, name, shape, dtype, zero=False):
+        t = torch.empty(shape, dtype=dtype, device=self.device)
+        if zero:
+            ops.memset(t)
+        return t
+
+
+class StaticAlloc:
+    """`zero=True` buffers are cleared once, at creation: they are used for staging layouts whose padding is never
+    written afterwards."""
+    static = True
+
+    def __init__(self, device, prefix=""):
+        self.device = device
+        self.prefix = prefix
+        self.bufs = {}
+
+    def __call__(self, name, shape, dtype, zero=False):
+        key = (self.prefix + name, tuple(int(s) for s in shape), dtype)
+        t = self.bufs.get(key)
+        if t is None:
+            t = torch.empty(key[1], dtype=dtype, device=self.device)
+            if zero:
+                ops.memset(t)
+            self.bufs[key] = t
+        return t
+
+    def nbytes(self):
+        return sum(t.numel() * t.element_size() for t in self.bufs.values())
+
+
+def _p(module, train):
+    """dropout probability of an nn.Dropout in the current mode"""
+    return float(module.p) if train else 0.0
+
+
+def _seed(p):
+    return ops.next_seed() if p > 0.0 else 0
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# Convolutional feature extractor — backward
+# ----------------------------------------------------------------------------------------------------------------
+def conv_stack_bwd(plan: Plan, st, dfeat, dmasks, A):
+    """dfeat: gradient wrt the (B, T, C) extractor output. Accumulates parameter gradients into the gradient arena
+    and mask gradients into `dmasks` (flat, log_alpha layout)."""
+    model = plan.model
+    fe = model.feature_extractor
+    dt = model.compute_dtype
+    B = st["B"]
+    wave = st["wave"]
+    dy = dfeat
+    for rec in reversed(st["layers"]):
+        blk, i = rec["blk"], rec["i"]
+        conv = blk.conv
+        Cout, Cin, k, s = rec["Cout"], rec["Cin"], blk.kernel_size, blk.stride
+        Tin, Tout = rec["Tin"], rec["Tout"]
+        ln = blk.layer_norm
+        colmask = rec["colmask"]
+        dmask = None
+        if rec["has_mask"]:
+            o = plan.offsets[id(blk.hard_concrete.log_alpha)] - plan.la_off
+            dmask = dmasks[o:o + Cout]
+        # the last layer's colmask is mask * dummy_weight: d mask = d colmask * dummy
+        dm_tmp = None
+        if dmask is not None and i == len(fe.conv_layers) - 1:
+            dm_tmp = A("conv_dm_tmp", (Cout,), torch.float32)
+            ops.memset(dm_tmp)
+        dm_out = dm_tmp if dm_tmp is not None else dmask
+        gbias = plan.gview(conv.bias) if (conv.bias is not None and conv.bias.requires_grad) else None
+        bias = plan.view(conv.bias) if conv.bias is not None else None
+        wreq = conv.weight.requires_grad
+        if i == 0:
+            w = plan.view(conv.weight)
+            scratch = A("conv0_scratch", (2 * B * Cout,), torch.float32)
+            if rec["mode"] == "gn":
+                ops.conv0_bwd(wave, w, bias, plan.view(ln.weight), plan.view(ln.bias), rec["mean"], rec["rstd"], colmask,
+                              dy, scratch, plan.gview(conv.weight), gbias, plan.gview(ln.weight), plan.gview(ln.bias),
+                              dm_out, B, Cout, k, s, Tout, 1, 1)
+            elif rec["mode"] == "ln":
+                dz = A("conv0_dz", (B, Tout, Cout), dt)
+                ops.layernorm_bwd(dy, rec["z"], plan.view(ln.weight), plan.view(ln.bias), rec["mean"], rec["rstd"], dz,
+                                  plan.gview(ln.weight), plan.gview(ln.bias), B * Tout, Cout, colmask=colmask,
+                                  dmask=dm_out, act=1)
+                ops.conv0_bwd(wave, w, bias, None, None, None, None, None, dz, scratch, plan.gview(conv.weight), gbias,
+                              None, None, None, B, Cout, k, s, Tout, 0, 0)
+            else:
+                ops.conv0_bwd(wave, w, bias, None, None, None, None, colmask, dy, scratch, plan.gview(conv.weight),
+                              gbias, None, None, dm_out, B, Cout, k, s, Tout, 0, 1)
+        else:
+            # dz in a per-utterance zero-padded row layout so the dgrad GEMM can read rows t'-j out of range
+            Jmax = (k + s - 1) // s
+            padr = Jmax + 1
+            rows_pb = Tout + 2 * padr
+            dzp = A("conv%d_dzp" % i, (B, rows_pb, Cout), dt, zero=True)
+            if rec["mode"] == "ln":
+                ops.layernorm_bwd(dy, rec["z"], plan.view(ln.weight), plan.view(ln.bias), rec["mean"], rec["rstd"], dzp,
+                                  plan.gview(ln.weight), plan.gview(ln.bias), B * Tout, Cout, colmask=colmask,
+                                  dmask=dm_out, act=1, rows_per_batch=Tout, out_bs=rows_pb * Cout, out_row_off=padr)
+                if gbias is not None:
+                    # bias gradient = column sum of dz
+                    for b in range(B):
+                        ops.epilogue_bwd(dzp[b, padr:padr + Tout], Tout, Cout, dbias=gbias)
+            else:
+                ops.epilogue_bwd(dy, B * Tout, Cout, z=rec["z"], colmask=colmask, dout=dzp, dmask=dm_out, dbias=gbias,
+                                 act=1, rows_per_batch=Tout, out_bs=rows_pb * Cout, out_row_off=padr)
+            x_in = rec["x_in"]
+            # ---- weight gradient: dW[co][tap][ci] = sum_{b,t} dz[b,t,co] * x[b, s t + tap, ci]
+            if wreq:
+                wg = A("conv_wg_scratch", (Cout, k * Cin), torch.float32)
+                ops.memset(wg)
+                a = View(dzp, Cout, Tout, 1, cs=Cout, sb0=rows_pb * Cout, offset=padr * Cout)
+                bv = View(x_in, k * Cin, Tout, 1, cs=s * Cin, sb0=Tin * Cin)
+                G.gemm(a, bv, wg, Cout, k * Cin, Tout, nb0=B, c_sb0=0, atomic=True)
+                ops.conv_wgrad_unpermute(wg, plan.gview(conv.weight), Cout, Cin, k)
+            # ---- input gradient, one GEMM per output phase (u = s t' + phase)
+            _, phases = _conv_weight_views(plan, blk, i, dt)
+            dx = A("conv%d_dx" % i, (B, Tin, Cin), dt)
+            covered = set()
+            for ph, J, wv in phases:
+                rows = (Tin - ph + s - 1) // s
+                if rows <= 0:
+                    continue
+                a = View(dzp, rows, J * Cout, Cout, kin=Cout, kxs=Cout, sb0=rows_pb * Cout,
+                         offset=(padr - (J - 1)) * Cout)
+                G.gemm(a, wv, dx, rows, Cin, J * Cout, nb0=B, ldc=s * Cin, c_sb0=Tin * Cin, c_offset=ph * Cin)
+                covered.add(ph)
+            for ph in range(s):
+                if ph not in covered:  # stride > kernel: some input rows get no gradient
+                    rows = (Tin - ph + s - 1) // s
+                    for b in range(B):
+                        ops.memset2d(dx, (b * Tin + ph) * Cin, s * Cin, Cin, rows)
+            dy = dx
+        if dm_tmp is not None:
+            ops.vec_mul(dm_tmp, plan.view(fe.dummy_weight), dmask, 1.0, 1.0)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# Encoder forward (components.py:263-274, 319-333, 379-436, 604-659, 726-748, 814-857, 885-927, 968-1003)
+# ----------------------------------------------------------------------------------------------------------------
+def _a8(n):
+    return (n + 7) // 8 * 8
+
+
+def _mask_of(masks, hc):
+    return masks.get(id(hc)) if hc is not None else None
+
+
+def _rel_table(plan, att0, T):
+    """Bucket index of every relative offset j - i in [-(T-1), T-1] — the integer part of
+    WavLMSelfAttention.compute_bias / _relative_positions_bucket (components.py:546-600), built on the host."""
+    key = (T, att0.num_buckets, att0.max_distance)
+    tb = plan._rel_tables.get(key)
+    if tb is None:
+        rel = torch.arange(-(T - 1), T, dtype=torch.long)
+        nb = att0.num_buckets // 2
+        buckets = (rel > 0).to(torch.long) * nb
+        rp = rel.abs()
+        max_exact = nb // 2
+        is_small = rp < max_exact
+        large = max_exact + (torch.log(rp.float() / max_exact) / math.log(att0.max_distance / max_exact)
+                             * (nb - max_exact)).to(torch.long)
+        large = torch.min(large, torch.full_like(large, nb - 1))
+        buckets = buckets + torch.where(is_small, rp, large)
+        tb = buckets.to(torch.int32).to(plan.device)
+        plan._rel_tables[key] = tb
+    return tb
+
+
+def _head_index(plan, att):
+    key = ("hidx", id(att))
+    t = plan._rel_tables.get(key)
+    if t is None:
+        t = torch.tensor(list(att.remaining_heads), dtype=torch.int32).to(plan.device)
+        plan._rel_tables[key] = t
+    return t
+
+
+def _attention_fwd(plan, att, xin, resid, B, T, lengths, masks, A, tag, train, p_drop, wl):
+    """xin: attention input (M, D); resid: residual added after dropout. Returns (resid + dropout(attn)), record."""
+    dt = xin.dtype
+    D, H, Dh = att.embed_dim, att.num_heads, att.head_dim
+    inner = H * Dh
+    M = B * T
+    Tp = _a8(T)
+    rec = {"att": att, "xin": xin, "H": H}
+    Wkvq = plan.wcat([att.k_proj.weight, att.v_proj.weight, att.q_proj.weight], dt)
+    bkvq = plan.vcat([att.k_proj.bias, att.v_proj.bias, att.q_proj.bias])
+    qkv = A(tag + "qkv", (M, 3 * inner), dt)
+    G.gemm(G.mat(xin), G.mat(Wkvq), qkv, M, 3 * inner, D, bias=bkvq)
+    s_t, s_b = 3 * inner, T * 3 * inner
+    S = A("att_S", (B, H, T, Tp), torch.float32)
+    q = View(qkv, T, Dh, s_t, sb0=Dh, sb1=s_b, offset=2 * inner)
+    k = View(qkv, T, Dh, s_t, sb0=Dh, sb1=s_b, offset=0)
+    G.gemm(q, k, S, T, T, Dh, nb0=H, nb1=B, ldc=Tp, c_sb0=T * Tp, c_sb1=H * T * Tp, alpha=att.scaling)
+    wavlm = None
+    if wl is not None:
+        # gated relative position bias; the gate is a function of the attention input (components.py:636-644)
+        Htot = att.total_num_heads
+        gate = ga = gb = None
+        if att.gru_rel_pos:
+            gate = A(tag + "gate", (B, Htot, T), torch.float32)
+            ga = A(tag + "ga", (B, Htot, T), torch.float32)
+            gb = A(tag + "gb", (B, Htot, T), torch.float32)
+            ops.wavlm_gate_fwd(xin, plan.view(att.gru_rel_pos_linear.weight), plan.view(att.gru_rel_pos_linear.bias),
+                               plan.view(att.gru_rel_pos_const), gate, ga, gb, B, T, Htot, D // Htot)
+        wavlm = (wl["rel_table"], wl["emb"], gate, _head_index(plan, att), Htot)
+        rec.update(ga=ga, gb=gb, wavlm=wavlm)
+    p_att = _p(att.dropout, train)
+    seed_att = _seed(p_att)
+    P = A(tag + "P", (B, H, T, Tp), dt)
+    Pd = A(tag + "Pd", (B, H, T, Tp), dt) if p_att > 0 else None
+    ops.softmax_fwd(S, Tp, P, Pd, Tp, lengths, B, H, T, p_att, seed_att, wavlm)
+    hmask = _mask_of(masks, att.hard_concrete_for_heads)
+    lmask = _mask_of(masks, att.hard_concrete_for_layer)
+    ctx = A(tag + "ctx", (M, inner), dt)
+    ctx_un = A(tag + "ctx_un", (M, inner), dt) if hmask is not None else None
+    pv = View(Pd if Pd is not None else P, T, T, Tp, sb0=T * Tp, sb1=H * T * Tp)
+    v = View(qkv, Dh, T, 1, cs=s_t, sb0=Dh, sb1=s_b, offset=inner)
+    G.gemm(pv, v, ctx, T, Dh, T, nb0=H, nb1=B, ldc=inner, c_sb0=Dh, c_sb1=T * inner, scalar_mask=hmask,
+           scalar_sb0=1 if hmask is not None else 0, c2=ctx_un)
+    out = A(tag + "attn_out", (M, D), dt)
+    pre = A(tag + "attn_pre", (M, D), dt) if lmask is not None else None
+    seed_o = _seed(p_drop)
+    G.gemm(G.mat(ctx), G.mat(plan.W(att.out_proj.weight, dt)), out, M, D, inner, bias=plan.view(att.out_proj.bias),
+           scalar_mask=lmask, drop_p=p_drop, seed=seed_o, residual=resid, c2=pre)
+    rec.update(qkv=qkv, P=P, Pd=Pd, ctx=ctx, ctx_un=ctx_un, pre=pre, hmask=hmask, lmask=lmask, p_att=p_att,
+               seed_att=seed_att, p_drop=p_drop, seed_o=seed_o)
+    return out, rec
+
+
+def _ffn_fwd(plan, ff, xin, resid, M, masks, A, tag, train):
+    dt = xin.dtype
+    D = ff.intermediate_dense.in_features
+    F = ff.intermediate_dense.out_features
+    imask = _mask_of(masks, ff.hard_concrete_for_intermediate)
+    lmask = _mask_of(masks, ff.hard_concrete_for_layer)
+    p_i, p_o = _p(ff.intermediate_dropout, train), _p(ff.output_dropout, train)
+    seed_i, seed_o = _seed(p_i), _seed(p_o)
+    h = A(tag + "ff_h", (M, F), dt)
+    zpre = A(tag + "ff_z", (M, F), dt)
+    G.gemm(G.mat(xin), G.mat(plan.W(ff.intermediate_dense.weight, dt)), h, M, F, D,
+           bias=plan.view(ff.intermediate_dense.bias), act=1, colmask=imask, drop_p=p_i, seed=seed_i, c2=zpre)
+    out = A(tag + "ff_out", (M, D), dt)
+    pre = A(tag + "ff_pre", (M, D), dt) if lmask is not None else None
+    G.gemm(G.mat(h), G.mat(plan.W(ff.output_dense.weight, dt)), out, M, D, F, bias=plan.view(ff.output_dense.bias),
+           scalar_mask=lmask, drop_p=p_o, seed=seed_o, residual=resid, c2=pre)
+    rec = {"ff": ff, "xin": xin, "h": h, "zpre": zpre, "pre": pre, "imask": imask, "lmask": lmask, "p_i": p_i,
+           "seed_i": seed_i, "p_o": p_o, "seed_o": seed_o, "F": F}
+    return out, rec
+
+
+def _ln_fwd(plan, ln, x, rows, D, A, tag, drop_p=0.0):
+    y = A(tag + "y", (rows, D), x.dtype)
+    mean = A(tag + "mean", (rows,), torch.float32)
+    rstd = A(tag + "rstd", (rows,), torch.float32)
+    seed = _seed(drop_p)
+    ops.layernorm_fwd(x, plan.view(ln.weight), plan.view(ln.bias), y, rows, D, ln.eps, mean, rstd, drop_p=drop_p,
+                      seed=seed)
+    return y, {"ln": ln, "x": x, "mean": mean, "rstd": rstd, "drop_p": drop_p, "seed": seed}
+
+
+def _posconv_geometry(pc, dt):
+    conv = pc.conv
+    D = pc.embed_dim
+    K = pc.kernel_size
+    Gn = conv.groups
+    Cg = D // Gn
+    Cgp = _align_to(Cg, 64) if dt == torch.bfloat16 else Cg
+    return D, K, Gn, Cg, Cgp
+
+
+def _posconv_fwd(plan, pc, h0, B, T, A, tag):
+    """x + GELU(conv(x)) with the weight-normalised grouped conv as one batched implicit GEMM over a zero-padded,
+    group-padded staging copy of x (rows: front + b * (T + pad) + t)."""
+    dt = h0.dtype
+    D, K, Gn, Cg, Cgp = _posconv_geometry(pc, dt)
+    pad = K  # zero rows between utterances (>= K - 1 so windows never see a neighbour)
+    front = K // 2
+    rows = front + B * (T + pad) + K
+    Wd = Gn * Cgp
+    xp = A(tag + "pos_xp", (rows, Wd), dt, zero=True)
+    ops.posconv_pad(h0, xp, B, T, Gn, Cg, Cgp, front, pad)
+    _, wp, _, _ = plan.pos_w
+    zpc = A(tag + "pos_z", (B * T, D), dt)
+    xpre = A(tag + "pos_out", (B * T, D), dt)
+    # output frame t reads staging rows (front + b (T+pad) + t) - K/2 + tap
+    a = View(xp, T, K * Cgp, Wd, kin=Cgp, kxs=Wd, sb0=Cgp, sb1=(T + pad) * Wd, offset=(front - K // 2) * Wd)
+    bv = View(wp, Cg, K * Cgp, K * Cgp, kin=Cgp, kxs=Cgp, sb0=Cg * K * Cgp)
+    G.gemm(a, bv, xpre, T, Cg, K * Cgp, nb0=Gn, nb1=B, ldc=D, c_sb0=Cg, c_sb1=T * D, bias=plan.view(pc.conv.bias),
+           vec_sb0=Cg, act=1, residual=h0, ldr=D, r_sb0=Cg, r_sb1=T * D, c2=zpc)
+    return xpre, {"pc": pc, "xp": xp, "zpc": zpc, "front": front, "pad": pad, "rows": rows}
+
+
+def encoder_fwd(plan: Plan, feat, lengths, masks, A, train, num_layers=None, final_norm=False, layer_keep=None):
+    """feat (B, T, C) compute dtype -> list of hidden states [(B, T, D)] (index 0 = encoder input after padding
+    zeroing), plus the record needed by `encoder_bwd`."""
+    model = plan.model
+    enc = model.encoder
+    tr = enc.transformer
+    fp = enc.feature_projection
+    dt = feat.dtype
+    B, T, C = feat.shape
+    M = B * T
+    D = fp.projection.out_features
+    st = {"B": B, "T": T, "feat": feat, "lengths": lengths}
+    # ---- feature projection: LN -> Linear -> dropout, padded frames zeroed
+    xn, rec_ln = _ln_fwd(plan, fp.layer_norm, feat.view(M, C), M, C, A, "fp_ln_")
+    p_in = _p(fp.dropout, train)
+    seed_in = _seed(p_in)
+    h0 = A("h0", (M, D), dt)
+    G.gemm(G.mat(xn), G.mat(plan.W(fp.projection.weight, dt)), h0, M, D, C, bias=plan.view(fp.projection.bias),
+           drop_p=p_in, seed=seed_in)
+    if lengths is not None:
+        ops.pad_rows_zero(h0, lengths, B, T, D)
+    st["fp"] = {"ln": rec_ln, "xn": xn, "p_in": p_in, "seed_in": seed_in}
+    hiddens = [h0]
+    # ---- positional conv + (Base) LayerNorm + dropout
+    xpre, rec_pc = _posconv_fwd(plan, tr.pos_conv_embed, h0, B, T, A, "")
+    st["pc"] = rec_pc
+    p_tr = _p(tr.dropout, train)
+    if tr.layer_norm_first:
+        x, rec = _ln_fwd(plan, tr.layer_norm, xpre, M, D, A, "tr_ln_", drop_p=p_tr)
+        st["tr_ln"] = rec
+    elif p_tr > 0:
+        seed = _seed(p_tr)
+        x = A("tr_drop", (M, D), dt)
+        ops.epilogue_bwd(xpre, M, D, dout=x, drop_p=p_tr, seed=seed)  # plain dropout (no act / masks)
+        st["tr_drop"] = {"p": p_tr, "seed": seed}
+    else:
+        x = xpre
+    # ---- layers
+    wl = None
+    st["layers"] = []
+    for li, layer in enumerate(tr.layers):
+        if layer_keep is not None and not layer_keep[li]:
+            st["layers"].append(None)
+            continue
+        tag = "L%d_" % li
+        att, ff = layer.attention, layer.feed_forward
+        rec = {"layer": layer, "x_in": x}
+        p_drop = _p(layer.dropout, train)
+        if att is not None:
+            if getattr(att, "has_position_bias", False) and wl is None:
+                att0 = att if att.rel_attn_embed is not None else None
+                if att0 is None:
+                    raise DphShapeError("WavLM attention without a relative position embedding in the first layer")
+                wl = {"rel_table": _rel_table(plan, att0, T), "emb": plan.view(att0.rel_attn_embed.weight),
+                      "att0": att0}
+            wl_here = wl if getattr(att, "has_position_bias", False) else None
+            if layer.layer_norm_first:
+                xa, rec["ln1"] = _ln_fwd(plan, layer.layer_norm, x, M, D, A, tag + "ln1_")
+            else:
+                xa = x
+            x1, rec["att"] = _attention_fwd(plan, att, xa, x, B, T, lengths, masks, A, tag, train, p_drop, wl_here)
+        else:
+            x1 = x
+        if layer.layer_norm_first:
+            if ff is not None:
+                xf, rec["ln2"] = _ln_fwd(plan, layer.final_layer_norm, x1, M, D, A, tag + "ln2_")
+                x2, rec["ff"] = _ffn_fwd(plan, ff, xf, x1, M, masks, A, tag, train)
+            else:
+                x2 = x1
+        else:
+            xl, rec["ln1"] = _ln_fwd(plan, layer.layer_norm, x1, M, D, A, tag + "ln1_")
+            if ff is not None:
+                xs, rec["ff"] = _ffn_fwd(plan, ff, xl, xl, M, masks, A, tag, train)
+            else:
+                xs = xl
+            x2, rec["ln2"] = _ln_fwd(plan, layer.final_layer_norm, xs, M, D, A, tag + "ln2_")
+        st["layers"].append(rec)
+        x = x2
+        hiddens.append(x)
+        if num_layers is not None and len(hiddens) - 1 >= num_layers:
+            break
+    if final_norm and not tr.layer_norm_first:
+        x, st["final_ln"] = _ln_fwd(plan, tr.layer_norm, x, M, D, A, "final_ln_")
+        hiddens.append(x)
+    st["wl"] = wl
+    st["n_hidden"] = len(hiddens)
+    return [h.view(B, T, D) for h in hiddens], st
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# Encoder backward
+# ----------------------------------------------------------------------------------------------------------------
+def _ksplit(Mo, No, K):
+    """Split-K factor for weight-gradient GEMMs (small outputs, long reductions): aim for >= one wave of CTAs."""
+    tiles = ((Mo + 127) // 128) * ((No + 255) // 256)
+    ks = max(1, min(148 // max(tiles, 1), K // 512))
+    return ks
+
+
+def _wgrad(plan, dy2d, x2d, param, Mo, No, Krows):
+    """grad(param)[o, i] += sum_m dy[m, o] * x[m, i]   (fp32, atomically accumulated into the gradient arena)"""
+    if not param.requires_grad:
+        return
+    G.gemm(G.mat_t(dy2d), G.mat_t(x2d), plan.gview(param), Mo, No, Krows, atomic=True, ksplit=_ksplit(Mo, No, Krows))
+
+
+def _gslot(plan, dmasks, hc):
+    """slice of the flat mask-gradient buffer belonging to gate module `hc`"""
+    if hc is None:
+        return None
+    o = plan.offsets[id(hc.log_alpha)] - plan.la_off
+    return dmasks[o:o + hc.n_in]
+
+
+def _gb(plan, p):
+    return plan.gview(p) if (p is not None and p.requires_grad) else None
+
+
+def _ln_bwd(plan, rec, dy, dy2, A, tag):
+    ln = rec["ln"]
+    x = rec["x"]
+    rows, D = x.shape[0], x.shape[1]
+    dx = A(tag + "dx", (rows, D), x.dtype)
+    ops.layernorm_bwd(dy, x, plan.view(ln.weight), plan.view(ln.bias), rec["mean"], rec["rstd"], dx, _gb(plan, ln.weight),
+                      _gb(plan, ln.bias), rows, D, dy2=dy2, drop_p=rec["drop_p"], seed=rec["seed"])
+    return dx
+
+
+def _out_proj_bwd(plan, dout, pre, lmask, hc_layer, bias_p, p_drop, seed, dmasks, A, tag, M, D):
+    """Backward of  o = dropout(lmask * (lin + bias)) : returns d lin, accumulates d bias / d layer gate."""
+    if p_drop > 0 or lmask is not None:
+        g = A(tag + "g", (M, D), dout.dtype)
+        ops.epilogue_bwd(dout, M, D, z=pre, scalar=lmask, dout=g, dbias=_gb(plan, bias_p),
+                         dscalar=_gslot(plan, dmasks, hc_layer) if lmask is not None else None, drop_p=p_drop, seed=seed)
+        return g
+    if _gb(plan, bias_p) is not None:
+        ops.epilogue_bwd(dout, M, D, dbias=_gb(plan, bias_p))
+    return dout
+
+
+def _ffn_bwd(plan, rec, dout, dresid, dmasks, A, tag):
+    ff = rec["ff"]
+    dt = dout.dtype
+    M, D = dout.shape
+    F = rec["F"]
+    g = _out_proj_bwd(plan, dout, rec["pre"], rec["lmask"], ff.hard_concrete_for_layer, ff.output_dense.bias,
+                      rec["p_o"], rec["seed_o"], dmasks, A, tag + "ffo_", M, D)
+    dh = A(tag + "ff_dh", (M, F), dt)
+    G.gemm(G.mat(g), G.mat_t(plan.W(ff.output_dense.weight, dt)), dh, M, F, D)
+    _wgrad(plan, g, rec["h"], ff.output_dense.weight, D, F, M)
+    dz = A(tag + "ff_dz", (M, F), dt)
+    ops.epilogue_bwd(dh, M, F, z=rec["zpre"], colmask=rec["imask"], dout=dz,
+                     dmask=_gslot(plan, dmasks, ff.hard_concrete_for_intermediate) if rec["imask"] is not None else None,
+                     dbias=_gb(plan, ff.intermediate_dense.bias), act=1, drop_p=rec["p_i"], seed=rec["seed_i"])
+    dx = A(tag + "ff_dx", (M, D), dt)
+    G.gemm(G.mat(dz), G.mat_t(plan.W(ff.intermediate_dense.weight, dt)), dx, M, D, F, residual=dresid)
+    _wgrad(plan, dz, rec["xin"], ff.intermediate_dense.weight, F, D, M)
+    return dx
+
+
+def _attention_bwd(plan, rec, dout, dresid, B, T, dmasks, A, tag, wl):
+    att = rec["att"]
+    dt = dout.dtype
+    M, D = dout.shape
+    H, Dh = rec["H"], att.head_dim
+    inner = H * Dh
+    Tp = _a8(T)
+    s_t, s_b = 3 * inner, T * 3 * inner
+    g = _out_proj_bwd(plan, dout, rec["pre"], rec["lmask"], att.hard_concrete_for_layer, att.out_proj.bias,
+                      rec["p_drop"], rec["seed_o"], dmasks, A, tag + "ao_", M, D)
+    dctx = A(tag + "dctx", (M, inner), dt)
+    G.gemm(G.mat(g), G.mat_t(plan.W(att.out_proj.weight, dt)), dctx, M, inner, D)
+    _wgrad(plan, g, rec["ctx"], att.out_proj.weight, D, inner, M)
+    if rec["hmask"] is not None:
+        dctx2 = A(tag + "dctx2", (M, inner), dt)
+        ops.group_mask_bwd(dctx, rec["ctx_un"], rec["hmask"], dctx2, _gslot(plan, dmasks, att.hard_concrete_for_heads), M,
+                           inner, Dh)
+        dctx = dctx2
+    qkv = rec["qkv"]
+    P, Pd = rec["P"], rec["Pd"] if rec["Pd"] is not None else rec["P"]
+    # dPd = dctx V^T
+    dP = A("att_dP", (B, H, T, Tp), torch.float32)
+    a = View(dctx, T, Dh, inner, sb0=Dh, sb1=T * inner)
+    vk = View(qkv, T, Dh, s_t, sb0=Dh, sb1=s_b, offset=inner)
+    G.gemm(a, vk, dP, T, T, Dh, nb0=H, nb1=B, ldc=Tp, c_sb0=T * Tp, c_sb1=H * T * Tp)
+    dqkv = A(tag + "dqkv", (M, 3 * inner), dt)
+    # dV = Pd^T dctx
+    a = View(Pd, T, T, 1, cs=Tp, sb0=T * Tp, sb1=H * T * Tp)
+    bv = View(dctx, Dh, T, 1, cs=inner, sb0=Dh, sb1=T * inner)
+    G.gemm(a, bv, dqkv, T, Dh, T, nb0=H, nb1=B, ldc=s_t, c_sb0=Dh, c_sb1=s_b, c_offset=inner)
+    # dS = softmax'(P) . dropout'(dPd)  (+ WavLM bias gradients)
+    dS = A("att_dS", (B, H, T, Tp), dt)
+    wavlm = rec.get("wavlm")
+    dgate = None
+    demb = None
+    nbuckets = 0
+    if wavlm is not None:
+        att0 = wl["att0"]
+        nbuckets = att0.num_buckets
+        demb = _gb(plan, att0.rel_attn_embed.weight)
+        if wavlm[2] is not None:
+            dgate = A(tag + "dgate", (B, att.total_num_heads, T), torch.float32)
+            ops.memset(dgate)
+    ops.softmax_bwd(P, dP, Tp, dS, Tp, B, H, T, rec["p_att"], rec["seed_att"], wavlm, dgate, demb, nbuckets)
+    # dQ = scaling * dS K ; dK = scaling * dS^T Q
+    a = View(dS, T, T, Tp, sb0=T * Tp, sb1=H * T * Tp)
+    bv = View(qkv, Dh, T, 1, cs=s_t, sb0=Dh, sb1=s_b, offset=0)
+    G.gemm(a, bv, dqkv, T, Dh, T, nb0=H, nb1=B, ldc=s_t, c_sb0=Dh, c_sb1=s_b, c_offset=2 * inner, alpha=att.scaling)
+    a = View(dS, T, T, 1, cs=Tp, sb0=T * Tp, sb1=H * T * Tp)
+    bv = View(qkv, Dh, T, 1, cs=s_t, sb0=Dh, sb1=s_b, offset=2 * inner)
+    G.gemm(a, bv, dqkv, T, Dh, T, nb0=H, nb1=B, ldc=s_t, c_sb0=Dh, c_sb1=s_b, c_offset=0, alpha=att.scaling)
+    # projections
+    kvq_w = [att.k_proj.weight, att.v_proj.weight, att.q_proj.weight]
+    kvq_b = [att.k_proj.bias, att.v_proj.bias, att.q_proj.bias]
+    if kvq_b[0].requires_grad:
+        o0 = plan.offsets[id(kvq_b[0])]
+        ops.epilogue_bwd(dqkv, M, 3 * inner, dbias=plan.garena[o0:o0 + 3 * inner])
+    xin = rec["xin"]
+    if kvq_w[0].requires_grad:
+        o0 = plan.offsets[id(kvq_w[0])]
+        gw = plan.garena[o0:o0 + 3 * inner * D].view(3 * inner, D)
+        G.gemm(G.mat_t(dqkv), G.mat_t(xin), gw, 3 * inner, D, M, atomic=True, ksplit=_ksplit(3 * inner, D, M))
+    dx = A(tag + "att_dx", (M, D), dt)
+    G.gemm(G.mat(dqkv), G.mat_t(plan.wcat(kvq_w, dt)), dx, M, D, 3 * inner, residual=dresid)
+    if dgate is not None:
+        lin = att.gru_rel_pos_linear
+        ops.wavlm_gate_bwd(xin, plan.view(lin.weight), plan.view(att.gru_rel_pos_const), rec["ga"], rec["gb"], dgate, dx,
+                           plan.gview(lin.weight), plan.gview(lin.bias), plan.gview(att.gru_rel_pos_const), B, T,
+                           att.total_num_heads, D // att.total_num_heads)
+    return dx
+
+
+def _acc(total, extra, n):
+    """total += extra (same dtype, n elements); either may be None. Returns the combined buffer."""
+    if extra is None:
+        return total
+    if total is None:
+        return extra
+    ops.axpy(total, extra, n)
+    return total
+
+
+def encoder_bwd(plan: Plan, st, dh, dmasks, A):
+    """dh: list (len n_hidden) of gradients wrt the returned hidden states ((M, D) compute dtype, or None).
+    Returns the gradient wrt the extractor features (B, T, C). NOTE: buffers in `dh` may be modified in place."""
+    model = plan.model
+    enc = model.encoder
+    tr = enc.transformer
+    fp = enc.feature_projection
+    B, T = st["B"], st["T"]
+    M = B * T
+    feat = st["feat"]
+    C = feat.shape[2]
+    D = fp.projection.out_features
+    dt = feat.dtype
+    dh = list(dh)
+    g = None  # gradient flowing back from later layers wrt the current layer output
+    idx = st["n_hidden"] - 1
+    if "final_ln" in st:
+        g = _ln_bwd(plan, st["final_ln"], dh[idx], None, A, "final_ln_")
+        idx -= 1
+    n_run = sum(1 for r in st["layers"] if r is not None)
+    assert idx == n_run
+    wl = st.get("wl")
+    for li in range(len(st["layers"]) - 1, -1, -1):
+        rec = st["layers"][li]
+        if rec is None:
+            continue
+        layer = rec["layer"]
+        tag = "L%d_" % li
+        d_out, d_head = g, dh[idx]
+        idx -= 1
+        if d_out is None and d_head is None:
+            g = None
+            # nothing downstream depends on this layer's output (e.g. num_layers cut) -> no gradient
+            continue
+        if layer.layer_norm_first:
+            d2 = _acc(d_out, d_head, M * D)
+            if "ff" in rec:
+                dxf = _ffn_bwd(plan, rec["ff"], d2, None, dmasks, A, tag)
+                dx1 = _ln_bwd(plan, rec["ln2"], dxf, None, A, tag + "ln2_")
+                ops.axpy(dx1, d2, M * D)
+            else:
+                dx1 = d2
+            if "att" in rec:
+                dxa = _attention_bwd(plan, rec["att"], dx1, None, B, T, dmasks, A, tag, wl)
+                g = _ln_bwd(plan, rec["ln1"], dxa, None, A, tag + "ln1_")
+                ops.axpy(g, dx1, M * D)
+            else:
+                g = dx1
+        else:
+            if d_out is None:
+                d_out, d_head = d_head, None
+            ds = _ln_bwd(plan, rec["ln2"], d_out, d_head, A, tag + "ln2_")
+            dxl = _ffn_bwd(plan, rec["ff"], ds, ds, dmasks, A, tag) if "ff" in rec else ds
+            dx1 = _ln_bwd(plan, rec["ln1"], dxl, None, A, tag + "ln1_")
+            g = _attention_bwd(plan, rec["att"], dx1, dx1, B, T, dmasks, A, tag, wl) if "att" in rec else dx1
+    assert idx == 0
+    d_h0_head = dh[0]
+    if g is not None:
+        # ---- transformer pre-processing
+        if "tr_ln" in st:
+            dxpre = _ln_bwd(plan, st["tr_ln"], g, None, A, "tr_ln_")
+        elif "tr_drop" in st:
+            dxpre = A("tr_drop_d", (M, D), dt)
+            ops.epilogue_bwd(g, M, D, dout=dxpre, drop_p=st["tr_drop"]["p"], seed=st["tr_drop"]["seed"])
+        else:
+            dxpre = g
+        # ---- positional conv: xpre = h0 + GELU(conv(h0) + bias)
+        pcr = st["pc"]
+        pc = pcr["pc"]
+        _, K, Gn, Cg, Cgp = _posconv_geometry(pc, dt)
+        Wd = Gn * Cgp
+        front, pad, rows = pcr["front"], pcr["pad"], pcr["rows"]
+        dz = A("pos_dz", (M, D), dt)
+        ops.epilogue_bwd(dxpre, M, D, z=pcr["zpc"], dout=dz, dbias=_gb(plan, pc.conv.bias), act=1)
+        dzp = A("pos_dzp", (rows, Wd), dt, zero=True)
+        ops.posconv_pad(dz, dzp, B, T, Gn, Cg, Cgp, front, pad)
+        norm, _, wdp, _ = plan.pos_w
+        dh0 = A("dh0", (M, D), dt)
+        off = front - (K - 1 - K // 2)
+        a = View(dzp, T, K * Cgp, Wd, kin=Cgp, kxs=Wd, sb0=Cgp, sb1=(T + pad) * Wd, offset=off * Wd)
+        bv = View(wdp, Cg, K * Cgp, K * Cgp, kin=Cgp, kxs=Cgp, sb0=Cg * K * Cgp)
+        G.gemm(a, bv, dh0, T, Cg, K * Cgp, nb0=Gn, nb1=B, ldc=D, c_sb0=Cg, c_sb1=T * D, residual=dxpre, ldr=D, r_sb0=Cg,
+               r_sb1=T * D)
+        if pc.conv.weight_v.requires_grad:
+            Kext = B * (T + pad)
+            dwp = A("pos_dwp", (Gn, Cgp, K, Cgp), torch.float32)
+            a = View(dzp, Cgp, Kext, 1, cs=Wd, sb0=Cgp, offset=front * Wd)
+            bv = View(pcr["xp"], Cgp, Kext, 1, cs=Wd, sb0=Cgp, sb1=Wd)
+            G.gemm(a, bv, dwp, Cgp, Cgp, Kext, nb0=Gn, nb1=K, ldc=K * Cgp, c_sb0=Cgp * K * Cgp, c_sb1=Cgp)
+            scratch = A("pos_wb_scratch", (K,), torch.float32)
+            ops.posconv_weight_bwd(dwp, plan.view(pc.conv.weight_v), plan.view(pc.conv.weight_g), norm, scratch,
+                                   plan.gview(pc.conv.weight_v), plan.gview(pc.conv.weight_g), D, Gn, Cg, Cgp, Cgp, K)
+        dh0 = _acc(dh0, d_h0_head, M * D)
+    else:
+        dh0 = d_h0_head
+    if dh0 is None:
+        return None
+    # ---- feature projection
+    if st["lengths"] is not None:
+        ops.pad_rows_zero(dh0, st["lengths"], B, T, D)
+    fpr = st["fp"]
+    gp = _out_proj_bwd(plan, dh0, None, None, None, fp.projection.bias, fpr["p_in"], fpr["seed_in"], dmasks, A, "fp_", M, D)
+    dxn = A("fp_dxn", (M, C), dt)
+    G.gemm(G.mat(gp), G.mat_t(plan.W(fp.projection.weight, dt)), dxn, M, C, D)
+    _wgrad(plan, gp, fpr["xn"], fp.projection.weight, D, C, M)
+    dfeat = _ln_bwd(plan, fpr["ln"], dxn, None, A, "fp_ln_")
+    return dfeat.view(B, T, C)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# Whole-model forward / backward (no autograd inside: plain sequences of C-ABI launches)
+# ----------------------------------------------------------------------------------------------------------------
+def _out_lengths(model, lengths):
+    """Integer frame arithmetic of ConvLayerBlock.forward (components.py:116-119)."""
+    if lengths is None:
+        return None
+    for blk in model.feature_extractor.conv_layers:
+        lengths = torch.div(lengths - blk.kernel_size, blk.stride, rounding_mode="floor") + 1
+        lengths = torch.clamp(lengths, min=0)
+    return lengths
+
+
+def forward_core(plan: Plan, wave, lengths, masks, A, train, save=True, num_layers=None, final_norm=False,
+                 layer_keep=None):
+    """Returns (hiddens [(B,T,D)], frame lengths, state). `masks`: {id(HardConcrete): fp32 mask tensor}."""
+    model = plan.model
+    _require_cuda(wave, "waveforms")
+    if wave.dim() != 2:
+        raise ValueError("Expected the input Tensor to be 2D (batch, time), but received %s" % list(wave.shape))
+    dt = model.compute_dtype
+    plan.refresh(dt)
+    B, T0 = wave.shape
+    if wave.dtype != torch.float32:
+        raise _lib.DphError("waveforms must be float32")
+    if lengths is not None:
+        lengths = lengths.to(device=wave.device, dtype=torch.int64)
+    if model.normalize_waveform:
+        wn = A("wave_norm", (B, T0), torch.float32)
+        ops.wave_norm(wave.contiguous(), wn, lengths, B, T0)
+        wave = wn
+    feat, st_conv = conv_stack_fwd(plan, wave, masks, save, A)
+    flen = _out_lengths(model, lengths)
+    if flen is not None:
+        flen = flen.contiguous()
+    hiddens, st_enc = encoder_fwd(plan, feat, flen, masks, A, train, num_layers=num_layers, final_norm=final_norm,
+                                  layer_keep=layer_keep)
+    return hiddens, flen, {"conv": st_conv, "enc": st_enc}
+
+
+def backward_core(plan: Plan, st, dh, dmasks, A):
+    """dh: per-hidden gradients ((M, D) / (B, T, D) compute dtype or None). Parameter gradients are accumulated into
+    the gradient arena, HardConcrete mask gradients into `dmasks`."""
+    plan.prepare_backward()
+    enc = st["enc"]
+    M = enc["B"] * enc["T"]
+    dh = [None if g is None else g.view(M, -1) for g in dh]
+    dfeat = encoder_bwd(plan, enc, dh, dmasks, A)
+    if dfeat is not None:
+        conv_stack_bwd(plan, st["conv"], dfeat, dmasks, A)
+
+
+class _ModelFn(torch.autograd.Function):
+    """Autograd bridge for the module API: inputs are the mask vector (so that gradients reach `log_alpha` through the
+    sampling node) — parameter gradients are written straight into `p.grad` (views of the gradient arena)."""
+
+    @staticmethod
+    def forward(ctx, plan, wave, lengths, mask_flat, masks, opts, anchor):
+        A = FreshAlloc(plan.device)
+        train = plan.model.training
+        hiddens, flen, st = forward_core(plan, wave, lengths, masks, A, train, save=True, **opts)
+        ctx.plan, ctx.st = plan, st
+        ctx.has_masks = mask_flat is not None
+        ctx.mark_non_differentiable(*([flen] if flen is not None else []))
+        return tuple(hiddens) + ((flen,) if flen is not None else ())
+
+    @staticmethod
+    def backward(ctx, *grads):
+        plan, st = ctx.plan, ctx.st
+        n = st["enc"]["n_hidden"]
+        dt = plan.model.compute_dtype
+        dh = [None if g is None else g.to(dt).contiguous().clone() for g in grads[:n]]
+        A = FreshAlloc(plan.device)
+        dmasks = ops.zeros((max(plan.la_n, 1),), torch.float32, plan.device)
+        backward_core(plan, st, dh, dmasks, A)
+        ctx.st = None
+        return None, None, None, (dmasks if ctx.has_masks else None), None, None, None
+
+
+def _anchor(plan):
+    """a differentiable scalar so autograd always runs our backward when any parameter requires grad"""
+    for p in plan.params:
+        if p.requires_grad:
+            return p
+    return None
+
+
+def model_extract_features(model, waveforms, lengths=None, num_layers=None, _final=False):
+    _require_cuda(waveforms, "waveforms")
+    plan = get_plan(model)
+    grad_on = torch.is_grad_enabled() and plan.any_grad
+    tb = hc_tables(plan)
+    opts = {"num_layers": num_layers, "final_norm": _final}
+    if _final:
+        tr = model.encoder.transformer
+        if model.training and tr.layer_drop > 0:
+            # LayerDrop: same host-side draw as the reference (components.py:902)
+            opts["layer_keep"] = [not (torch.rand(1).item() <= tr.layer_drop) for _ in tr.layers]
+    if not grad_on:
+        masks = sample_masks(plan) if tb.nseg else {}
+        masks = {k: v.detach() for k, v in masks.items()}
+        A = FreshAlloc(plan.device)
+        with torch.no_grad():
+            hiddens, flen, _ = forward_core(plan, waveforms, lengths, masks, A, model.training, save=False, **opts)
+        return list(hiddens), flen
+    mask_flat = None
+    masks = {}
+    if tb.nseg:
+        masks = sample_masks(plan)
+        mask_flat = _flat_masks(plan, masks)
+        masks = {k: v.detach() for k, v in masks.items()}
+    outs = _ModelFn.apply(plan, waveforms, lengths, mask_flat, masks, opts, _anchor(plan))
+    n = len(outs) - (1 if lengths is not None else 0)
+    return list(outs[:n]), (outs[n] if lengths is not None else None)
+
+
+def _flat_masks(plan, masks):
+    """the (la_n,) tensor all mask views were sliced from (training: the sampling node's output)"""
+    tb = hc_tables(plan)
+    if plan.model.training:
+        any_view = next(iter(masks.values()))
+        base = any_view._base if any_view._base is not None else any_view
+        return base
+    flat = torch.zeros(plan.la_n, dtype=torch.float32, device=plan.device)
+    return flat
+
+
+def model_forward(model, waveforms, lengths=None):
+    hiddens, flen = model_extract_features(model, waveforms, lengths, None, _final=True)
+    x = hiddens[-1]
+    if model.aux is not None:
+        B, T, D = x.shape
+        plan = get_plan(model)
+        out = torch.empty(B * T, model.aux.out_features, dtype=x.dtype, device=x.device)
+        xd = x.detach().contiguous().view(B * T, D)
+        G.gemm(G.mat(xd), G.mat(plan.W(model.aux.weight, x.dtype)), out, B * T, model.aux.out_features, D,
+               bias=plan.view(model.aux.bias))
+        x = out.view(B, T, -1)
+    return x, flen

@@ -52,6 +52,18 @@ def transpose(src, dst, B, R, C):
     return dst
 
 
+def axpy(dst, src, n=None):
+    """dst += src (same dtype)"""
+    n = dst.numel() if n is None else n
+    check(_L().dph_axpy(ptr(dst), ptr(src), n, dtype_code(dst), stream_ptr()), "dph_axpy")
+    return dst
+
+
+def group_mask_bwd(dy, z, mask, dout, dmask, rows, C, group):
+    check(_L().dph_group_mask_bwd(ptr(dy), ptr(z), ptr(mask), ptr(dout), ptr(dmask), rows, C, group, dtype_code(dy),
+                                  stream_ptr()), "dph_group_mask_bwd")
+
+
 # ----------------------------------------------------------------------------------------------------------------
 # norms / elementwise
 # ----------------------------------------------------------------------------------------------------------------
@@ -104,6 +116,12 @@ def conv0_bwd(wave, w, bias, gamma, beta, mean, rstd, mask, dy, scratch, dW, dbi
     check(_L().dph_conv0_bwd(ptr(wave), wave.stride(0), ptr(w), ptr(bias), ptr(gamma), ptr(beta), ptr(mean), ptr(rstd),
                              ptr(mask), ptr(dy), ptr(scratch), ptr(dW), ptr(dbias), ptr(dgamma), ptr(dbeta), ptr(dmask),
                              B, C, k, stride, T1, norm, act, dtype_code(dy), stream_ptr()), "dph_conv0_bwd")
+
+
+def wave_norm(wave, out, lengths, B, T0, eps=1e-5):
+    check(_L().dph_wave_norm(ptr(wave), wave.stride(0), ptr(out), out.stride(0), ptr(lengths), B, T0, eps, stream_ptr()),
+          "dph_wave_norm")
+    return out
 
 
 # ----------------------------------------------------------------------------------------------------------------
@@ -236,6 +254,14 @@ def next_seed():
     """Host-side stream of kernel RNG seeds, re-seeded from torch's generator so torch.manual_seed controls it."""
     _seed_counter[0] = (_seed_counter[0] * 6364136223846793005 + 1442695040888963407) & 0xFFFFFFFFFFFFFFFF
     return _seed_counter[0] >> 1
+
+
+def rng_set(value):
+    check(_L().dph_rng_set(int(value) & 0xFFFFFFFFFFFFFFFF, stream_ptr()), "dph_rng_set")
+
+
+def rng_advance():
+    check(_L().dph_rng_advance(stream_ptr()), "dph_rng_advance")
 
 
 def manual_seed(seed):
