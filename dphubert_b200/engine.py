@@ -185,22 +185,30 @@ class Plan:
         key = self._vkey()
         if not self.dirty and self.dtype == dtype and key == self.version_key:
             return
+        self.rebuild_derived(dtype, cast_lin=True)
+        self.version_key = key
+
+    def rebuild_derived(self, dtype, cast_lin=True):
+        """bf16 copy of the Linear weights, tap-major conv weights, weight-normalised positional conv weights."""
         model = self.model
         dev = self.device
         bf = dtype == torch.bfloat16
         if bf:
             if self.lin16 is None:
                 self.lin16 = torch.empty(self.lin_total, dtype=torch.bfloat16, device=dev)
-            ops.cast(self.arena[: self.lin_total], self.lin16)
+                cast_lin = True
+            if cast_lin:
+                ops.cast(self.arena[: self.lin_total], self.lin16)
             for i, blk in enumerate(model.feature_extractor.conv_layers):
                 if i == 0:
                     continue
                 w = blk.conv.weight
                 Cout, Cin, k = w.shape
-                if Cin % 8 or Cout % 8:
+                if Cin % 64 or Cout % 8:
                     raise DphShapeError(
-                        "bf16 tensor-core mode needs conv channel counts that are multiples of 8 (layer %d has "
-                        "%d -> %d); use compute dtype float32 for ragged pruned models" % (i, Cin, Cout))
+                        "bf16 tensor-core mode needs conv input channels in multiples of 64 and output channels in "
+                        "multiples of 8 (layer %d has %d -> %d); use compute dtype float32 for ragged pruned models"
+                        % (i, Cin, Cout))
                 if i not in self.conv_w or self.conv_w[i][0].dtype != dtype or self.conv_w[i][0].numel() != w.numel():
                     self.conv_w[i] = (torch.empty(Cout, k, Cin, dtype=dtype, device=dev),
                                       torch.empty(k, Cin, Cout, dtype=dtype, device=dev))
@@ -220,7 +228,6 @@ class Plan:
         ops.posconv_weight_prep(self.view(v), self.view(g), norm, None, wp, wdp, D, Gn, Cg, Cgp, K)
         self.dtype = dtype
         self.dirty = False
-        self.version_key = key
 
     def w16(self, p):
         """bf16 copy of a Linear weight (view into the bf16 arena)."""
