@@ -1,0 +1,353 @@
+"""Headline benchmark: audio-seconds/second of the joint distill-and-prune training step (BASELINE.json configs[2]:
+HuBERT Base teacher -> HardConcrete-masked student, L1 + cosine layer-wise loss + L0 Lagrangian, target sparsity 0.75,
+bf16, 8 x 10 s of 16 kHz audio per GPU), synthetic waveforms and random-init weights.
+
+    python bench.py --gpus 1 --steps 20 --warmup 5              # our arm (CUDA, C-ABI kernels, CUDA graph)
+    python bench.py --impl reference --steps 2 --warmup 1       # the reference algorithm on the host cores (oracle)
+    torchrun --nproc-per-node N ... bench.py --gpus N ...       # data parallel, weak scaling
+
+Prints ONE JSON line (see the keys at the bottom).  A "step" = teacher forward + student forward + distillation heads +
+loss + Lagrangian + backward + gradient all-reduce + clip + AdamW on one batch.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "oracle")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import torch  # noqa: E402
+
+SR = 16000
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="prune", choices=["prune", "distill", "wavlm", "large"])
+    ap.add_argument("--batch", type=int, default=8)
+    ap.add_argument("--seconds", type=float, default=0.0, help="audio seconds per utterance (default 10; large: 15)")
+    ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-roofline", action="store_true")
+    return ap.parse_args()
+
+
+def model_configs(workload):
+    from dphubert_b200.wav2vec2.model import hubert_base_config, hubert_large_config, wavlm_base_plus_config
+
+    if workload == "large":
+        cfg, layers, name = hubert_large_config(), [0, 4, 8, 12, 16, 20, 24], "HuBERT Large 24L/1024d"
+    elif workload == "wavlm":
+        cfg, layers, name = wavlm_base_plus_config(), [0, 4, 8, 12], "WavLM Base+ 12L/768d"
+    else:
+        cfg, layers, name = hubert_base_config(), [0, 4, 8, 12], "HuBERT Base 12L/768d"
+    scfg = dict(cfg)
+    if workload != "distill":
+        scfg.update(extractor_prune_conv_channels=True, encoder_prune_attention_heads=True,
+                    encoder_prune_feed_forward_intermediate=True)  # run.sh:32 pruning_units=conv,head,interm
+    return cfg, scfg, layers, name
+
+
+def build_models(workload, device, dtype):
+    """teacher (frozen, eval) + student (teacher weights + fresh log_alpha, train) + identity-initialised shared heads
+    (distill.py:24-26,54-109)."""
+    from dphubert_b200.wav2vec2.model import wav2vec2_model
+
+    cfg, scfg, layers, name = model_configs(workload)
+    torch.manual_seed(0)
+    teacher = wav2vec2_model(**cfg)
+    for p in teacher.parameters():
+        p.requires_grad = False
+    teacher.eval()
+    student = wav2vec2_model(**scfg)
+    student.load_state_dict(teacher.state_dict(), strict=False)
+    student.train()
+    D = cfg["encoder_embed_dim"]
+    first, shared = torch.nn.Linear(D, D), torch.nn.Linear(D, D)
+    for lin in (first, shared):
+        with torch.no_grad():
+            lin.weight.copy_(torch.eye(D))
+            lin.bias.zero_()
+    projs = [first] + [shared] * (len(layers) - 1)  # run.sh:21 "0.4,8,12": group {0}, group {4,8,12}
+    if device is not None:
+        teacher.to(device)
+        student.to(device)
+        for lin in (first, shared):
+            lin.to(device)
+        teacher.set_compute_dtype(dtype)
+        student.set_compute_dtype(dtype)
+    return teacher, student, projs, layers, cfg, scfg, name
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region"""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.sm, self.reasons, self.max_mhz = index, False, [], set(), None
+
+    def run(self):
+        q = "clocks.sm,clocks.max.sm,clocks_throttle_reasons.active"
+        names = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip().split(",")
+                self.sm.append(float(out[0]))
+                self.max_mhz = float(out[1])
+                bits = int(out[2].strip(), 16)
+                for b, n in names.items():
+                    if bits & b:
+                        self.reasons.add(n)
+            except Exception:  # noqa: BLE001
+                pass
+            time.sleep(0.05)
+
+    def result(self):
+        sm = sorted(self.sm)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+def run_reference(args, rank):
+    """The reference algorithm on the host cores: the CPU oracle (functional restatement of the reference's PyTorch
+    code, pinned against it by tests/golden) — the reference itself is Python and does not travel to the GPU box.
+    Each step = one full forward + backward of the same training step on a bounded sample of the workload."""
+    import dphubert_oracle as O
+
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    teacher, student, projs, layers, cfg, scfg, name = build_models(args.workload, None, None)
+    B, secs = 2, 4.0
+    T0 = int(secs * SR)
+    t_sd = {k: v.detach() for k, v in teacher.state_dict().items()}
+    s_sd = {k: v.detach().clone().requires_grad_(v.is_floating_point() and "dummy" not in k)
+            for k, v in student.state_dict().items()}
+    heads = [(p.weight.detach().clone().requires_grad_(True), p.bias.detach().clone().requires_grad_(True)) for p in projs]
+    lam = [torch.tensor(0.0, requires_grad=True), torch.tensor(0.0, requires_grad=True)] if args.workload != "distill" else None
+    n0 = sum(p.numel() for p in teacher.parameters())
+    g = torch.Generator().manual_seed(2022)
+
+    def one():
+        wave = 0.1 * torch.randn(B, T0, generator=g)
+        lengths = torch.full((B,), T0)
+        noise = {k: torch.empty(s_sd[k + ".log_alpha"].shape).uniform_(1e-6, 1 - 1e-6, generator=g) for k in O.gate_keys(s_sd)}
+        loss, _ = O.distill_step_loss(t_sd, cfg, s_sd, scfg, heads, layers, wave, lengths, noise, lam, 0.75, n0,
+                                      (0.0, 1.0, 1.0), "raw")
+        loss.backward()
+        for v in s_sd.values():
+            v.grad = None
+        return float(loss.detach())
+
+    for _ in range(args.warmup):
+        one()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        one()
+    dt = (time.perf_counter() - t0) / args.steps
+    val = B * secs / dt
+    sample = "%d x %.0f s utterances per step, fp32, forward+backward (no optimizer), %d steps" % (B, secs, args.steps)
+    line = {"impl": "reference", "metric": "prune-step audio-sec/sec", "value": val, "unit": "audio-s/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "%s teacher -> student, %s step" % (name, args.workload), "sample": sample},
+            "cpu_baseline": {"value": val, "unit": "audio-s/s", "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def cpu_baseline(args):
+    """Bounded CPU sample of the same step through the oracle (reported baseline, not the target)."""
+    import dphubert_oracle as O
+
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    teacher, student, projs, layers, cfg, scfg, name = build_models(args.workload, None, None)
+    B, secs = 2, 4.0
+    T0 = int(secs * SR)
+    t_sd = {k: v.detach() for k, v in teacher.state_dict().items()}
+    s_sd = {k: v.detach().clone().requires_grad_(v.is_floating_point() and "dummy" not in k)
+            for k, v in student.state_dict().items()}
+    heads = [(p.weight.detach().clone().requires_grad_(True), p.bias.detach().clone().requires_grad_(True)) for p in projs]
+    lam = [torch.tensor(0.0, requires_grad=True), torch.tensor(0.0, requires_grad=True)] if args.workload != "distill" else None
+    n0 = sum(p.numel() for p in teacher.parameters())
+    g = torch.Generator().manual_seed(2022)
+    times = []
+    for i in range(3):
+        wave = 0.1 * torch.randn(B, T0, generator=g)
+        noise = {k: torch.empty(s_sd[k + ".log_alpha"].shape).uniform_(1e-6, 1 - 1e-6, generator=g) for k in O.gate_keys(s_sd)}
+        t0 = time.perf_counter()
+        loss, _ = O.distill_step_loss(t_sd, cfg, s_sd, scfg, heads, layers, wave, torch.full((B,), T0), noise, lam, 0.75, n0,
+                                      (0.0, 1.0, 1.0), "raw")
+        loss.backward()
+        times.append(time.perf_counter() - t0)
+    dt = min(times[1:])
+    return {"value": B * secs / dt, "unit": "audio-s/s", "cores": threads, "kind": "port",
+            "sample": "oracle forward+backward of the same step on %d x %.0f s, fp32, best of 2 after 1 warm-up" % (B, secs)}
+
+
+def run_ours(args, rank, world, local_rank):
+    from dphubert_b200 import _lib, ops
+    from dphubert_b200 import gemm as G
+    from dphubert_b200.trainer import NativeDistillStep
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py (impl=ours) needs a GPU: the product has no CPU fallback")
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=dev)
+    dtype = torch.bfloat16 if args.dtype == "bf16" else torch.float32
+    secs = args.seconds or (15.0 if args.workload == "large" else 10.0)
+    B, T0 = args.batch, int(secs * SR)
+    teacher, student, projs, layers, cfg, scfg, name = build_models(args.workload, dev, dtype)
+    step = NativeDistillStep(teacher, student, layers, projs, "layer2layer", 0.0, 1.0, 1.0, "raw",
+                             use_reg=args.workload != "distill", learning_rate=2e-4, reg_learning_rate=0.02,
+                             warmup_updates=15000, max_updates=50000, target_sparsity=0.75, sparsity_warmup_updates=5000,
+                             clip_norm=10.0)
+    step.global_step = 5000  # full target sparsity
+    ops.rng_set(2022 + rank)
+    # synthetic 16 kHz waveforms: a ring of pinned host batches, one static device input buffer
+    gen = torch.Generator().manual_seed(2022 + rank)
+    host = [(0.1 * torch.randn(B, T0, generator=gen)).pin_memory() for _ in range(4)]
+    wave = torch.empty(B, T0, device=dev)
+    lengths = torch.full((B,), T0, device=dev, dtype=torch.int64)
+    wave.copy_(host[0])
+    out_host = torch.zeros(16).pin_memory()
+
+    n_before = _lib.launch_count()
+    if args.no_graph:
+        step.run_step(wave, lengths)
+        launches_per_step = _lib.launch_count() - n_before
+        do_step = lambda: step.run_step(wave, lengths)  # noqa: E731
+    else:
+        step.capture(wave, lengths)
+        launches_per_step = (_lib.launch_count() - n_before) // 2  # warm-up pass + captured pass
+        do_step = step.replay
+    torch.cuda.synchronize()
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(n, e2e):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record()
+        for i in range(n):
+            if e2e:
+                wave.copy_(host[i % len(host)], non_blocking=True)
+            out = do_step()
+            if e2e:
+                out_host.copy_(out, non_blocking=True)
+                torch.cuda.current_stream().synchronize()  # the user reads the loss every step
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if dist is not None:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t)
+        return ms
+
+    timed(max(args.warmup, 3), False)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ms_dev = timed(args.steps, False)
+    ms_e2e = timed(args.steps, True)
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+    terms = step.loss_terms()
+    audio = world * B * secs * args.steps
+    line = {
+        "metric": "prune-step audio-sec/sec", "value": audio / (ms_dev / 1e3), "unit": "audio-s/s", "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+        "config": {"workload": "%s teacher -> %s student, %s step (teacher fwd + student fwd/bwd + heads + loss%s + "
+                               "clip + AdamW%s)" % (name, "HardConcrete-masked" if args.workload != "distill" else "un-masked",
+                                                    args.workload, " + L0 Lagrangian" if args.workload != "distill" else "",
+                                                    " + NCCL grad all-reduce" if world > 1 else ""),
+                   "batch_per_gpu": B, "seconds_per_utt": secs, "global_batch": B * world, "parallelism": "dp%d" % world,
+                   "cuda_graph": not args.no_graph,
+                   "l2_policy": "inputs larger than L2: one step touches > 10 GB of activations / weights / optimizer state"},
+        "e2e": {"value": audio / (ms_e2e / 1e3), "unit": "audio-s/s", "h2d_bytes_per_step": B * T0 * 4,
+                "d2h_bytes_per_step": 64, "ms_per_step": ms_e2e / args.steps},
+        "gpu_launches": int(launches_per_step * args.steps),
+        "clocks": sampler.result(),
+        "loss": terms["loss"],
+    }
+    if rank == 0 and not args.no_roofline and dtype == torch.bfloat16:
+        line["roofline"] = roofline(step, wave, lengths, G, dev)
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(args)
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def roofline(step, wave, lengths, G, dev):
+    """Dominant kernel = the tcgen05 GEMM (every Linear / conv / attention product): re-issue exactly the GEMM launches
+    of one step back to back and time them with CUDA events -> algorithmic TFLOP/s against the measured bf16 peak."""
+    G.TRACE = []
+    step._push_scalars()
+    step._body(wave, lengths)
+    trace, G.TRACE = G.TRACE, None
+    step.zero_grad()
+    torch.cuda.synchronize()
+    flops = sum(f for _, f in trace)
+    for _ in range(2):
+        G.replay(trace)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    reps = 3
+    for _ in range(reps):
+        G.replay(trace)
+    e1.record()
+    torch.cuda.synchronize()
+    step.zero_grad()
+    ms = e0.elapsed_time(e1) / reps
+    peak, src = 1423.1, "fallback"
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            mp = json.load(f)
+        peak, src = float(mp["bf16_tflops_sustained"]), "MEASURED_PEAKS.json bf16_tflops_sustained"
+    except Exception:  # noqa: BLE001
+        pass
+    ach = flops / (ms / 1e3) / 1e12
+    return {"bound": "tensor", "kernel": "gemm_bf16_kernel (tcgen05)", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
+            "frac": ach / peak, "traffic": None, "launches_per_step": len(trace), "ms_per_step_in_kernel": ms,
+            "avg_launch_us": ms * 1e3 / max(len(trace), 1), "algorithmic_flops_per_step": flops, "peak_source": src}
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -31,6 +31,10 @@ class DphShapeError(_lib.DphError):
     pass
 
 
+def _is_native(t):
+    return t.is_cuda
+
+
 def _require_cuda(t, what):
     if not t.is_cuda:
         raise _lib.DphError(
@@ -455,7 +459,7 @@ def fused_num_params(model):
     """Expected size through the fused kernels when the model has gates and lives on a GPU; None otherwise (the
     caller then falls back to the exact integer bookkeeping, which involves no tensor math)."""
     p0 = next(model.parameters())
-    if not p0.is_cuda:
+    if not _is_native(p0):
         return None
     plan = get_plan(model)
     tb = hc_tables(plan)

@@ -13,6 +13,10 @@ from ._lib import GemmDesc, GemmF32Desc, Operand, OperandF32
 BF16 = 0
 F32 = 1
 
+# When set to a list, every tensor-core GEMM launch appends (descriptor, algorithmic flops): bench.py replays exactly
+# these launches to time the dominant kernel in isolation for the roofline figure.
+TRACE = None
+
 
 def dtype_code(t):
     if t.dtype == torch.bfloat16:
@@ -115,6 +119,8 @@ def gemm(a, b, c, M, N, K, *, ldc=None, nb0=1, nb1=1, c_sb0=0, c_sb1=0, c_offset
         d.ldr, d.r_sb0, d.r_sb1 = ldr, r_sb0, r_sb1
         d.drop_p, d.seed = drop_p, seed
         d.vec_sb0, d.scalar_sb0 = vec_sb0, scalar_sb0
+        if TRACE is not None:
+            TRACE.append((d, 2.0 * M * N * K * nb0 * nb1))
         _lib.check(L.dph_gemm_bf16(ctypes.byref(d), _lib.stream_ptr()), "dph_gemm_bf16")
     else:
         assert a.t.dtype == torch.float32 and b.t.dtype == torch.float32 and c.dtype == torch.float32
@@ -137,3 +143,11 @@ def gemm(a, b, c, M, N, K, *, ldc=None, nb0=1, nb1=1, c_sb0=0, c_sb1=0, c_offset
         d.vec_sb0, d.scalar_sb0 = vec_sb0, scalar_sb0
         _lib.check(L.dph_gemm_f32(ctypes.byref(d), _lib.stream_ptr()), "dph_gemm_f32")
     return c
+
+
+def replay(trace):
+    """Re-issue traced tensor-core GEMM launches (same descriptors, same buffers)."""
+    L = _lib.lib()
+    sp = _lib.stream_ptr()
+    for d, _ in trace:
+        _lib.check(L.dph_gemm_bf16(ctypes.byref(d), sp), "dph_gemm_bf16")

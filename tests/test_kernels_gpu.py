@@ -1,0 +1,276 @@
+"""Every C-ABI kernel against its torch restatement (tests/emu.py) on random inputs — runs on the B200 box.
+Each case calls the real entry point through ctypes on CUDA tensors, the restatement on CPU copies, and compares every
+tensor argument afterwards (outputs are written in place)."""
+import pytest
+import torch
+
+import emu
+from dphubert_b200 import gemm as G
+from dphubert_b200 import ops
+
+pytestmark = pytest.mark.gpu
+DEV = torch.device("cuda:0")
+F32, BF16 = torch.float32, torch.bfloat16
+
+
+def _cpu(x):
+    if torch.is_tensor(x):
+        return x.detach().cpu().clone()
+    if isinstance(x, (tuple, list)):
+        return type(x)(_cpu(v) for v in x)
+    if isinstance(x, G.View):
+        v = G.View(_cpu(x.t), x.rows, x.K, x.rs, x.cs, x.kin, x.kxs, x.sb0, x.sb1, x.offset)
+        return v
+    return x
+
+
+def _flatten(x, out):
+    if torch.is_tensor(x):
+        out.append(x)
+    elif isinstance(x, (tuple, list)):
+        for v in x:
+            _flatten(v, out)
+    elif isinstance(x, dict):
+        for v in x.values():
+            _flatten(v, out)
+    elif isinstance(x, G.View):
+        out.append(x.t)
+
+
+def both(name, args, kwargs=None, tol=None, fn=None, ref=None, ignore=()):
+    kwargs = kwargs or {}
+    cargs, ckw = _cpu(list(args)), {k: _cpu(v) for k, v in kwargs.items()}
+    (fn or getattr(ops, name))(*args, **kwargs)
+    torch.cuda.synchronize()
+    (ref or getattr(emu, name))(*cargs, **ckw)
+    a, b = [], []
+    _flatten(list(args), a)
+    _flatten(kwargs, a)
+    _flatten(cargs, b)
+    _flatten(ckw, b)
+    assert len(a) == len(b)
+    for i, (x, y) in enumerate(zip(a, b)):
+        if any(x is t for t in ignore):
+            continue
+        if not x.is_floating_point():
+            assert torch.equal(x.cpu(), y), "%s: integer tensor #%d differs" % (name, i)
+            continue
+        t = tol if tol is not None else (2e-2 if x.dtype == BF16 else 2e-5)
+        xf, yf = x.detach().float().cpu(), y.float()
+        assert torch.isfinite(xf).all(), "%s: tensor #%d has non-finite values" % (name, i)
+        err = (xf - yf).abs().max().item() / max(yf.abs().max().item(), 1e-6)
+        assert err < t, "%s: tensor #%d rel err %.3e (tol %.1e)" % (name, i, err, t)
+
+
+def rnd(*shape, dtype=F32, scale=1.0):
+    return (torch.randn(*shape, device=DEV) * scale).to(dtype)
+
+
+def zer(*shape, dtype=F32):
+    return torch.zeros(*shape, device=DEV, dtype=dtype)
+
+
+@pytest.fixture(autouse=True)
+def _seed():
+    torch.manual_seed(1234)
+    ops.rng_set(0)
+
+
+# ---------------------------------------------------------------------------------------------- elementwise / norms
+@pytest.mark.parametrize("dt", [F32, BF16])
+@pytest.mark.parametrize("D", [512, 768, 1024, 104])
+def test_layernorm_fwd_bwd(dt, D):
+    rows = 333
+    x, w, b = rnd(rows, D, dtype=dt), rnd(D) * 0.2 + 1, rnd(D) * 0.1
+    cm = torch.rand(D, device=DEV)
+    for act, colmask in ((0, None), (1, cm)):
+        y, ypre, mean, rstd = zer(rows, D, dtype=dt), zer(rows, D, dtype=dt), zer(rows), zer(rows)
+        both("layernorm_fwd", (x, w, b, y, rows, D, 1e-5), dict(mean=mean, rstd=rstd, y_pre=ypre, colmask=colmask, act=act))
+        dy, dy2 = rnd(rows, D, dtype=dt), rnd(rows, D, dtype=dt)
+        dx, dw, db, dm = zer(rows, D, dtype=dt), zer(D), zer(D), zer(D)
+        both("layernorm_bwd", (dy, x, w, b, mean, rstd, dx, dw, db, rows, D),
+             dict(dy2=dy2, colmask=colmask, dmask=dm if colmask is not None else None, act=act),
+             tol=3e-2 if dt == BF16 else 2e-4)
+    # padded per-batch output layout (conv dgrad staging)
+    Bn, Tn, padr = 3, 111, 3
+    dzp = zer(Bn, Tn + 2 * padr, D, dtype=dt)
+    dy = rnd(Bn * Tn, D, dtype=dt)
+    mean, rstd = rnd(Bn * Tn) * 0.1, torch.rand(Bn * Tn, device=DEV) + 0.5
+    xx = rnd(Bn * Tn, D, dtype=dt)
+    both("layernorm_bwd", (dy, xx, w, b, mean, rstd, dzp, zer(D), zer(D), Bn * Tn, D),
+         dict(rows_per_batch=Tn, out_bs=(Tn + 2 * padr) * D, out_row_off=padr), tol=3e-2 if dt == BF16 else 2e-4)
+
+
+@pytest.mark.parametrize("dt", [F32, BF16])
+@pytest.mark.parametrize("C", [768, 3072, 100])
+def test_epilogue_bwd(dt, C):
+    rows = 517
+    dy, z = rnd(rows, C, dtype=dt), rnd(rows, C, dtype=dt)
+    cm, sc = torch.rand(C, device=DEV), torch.rand(1, device=DEV) + 0.5
+    tol = 3e-2 if dt == BF16 else 3e-4
+    both("epilogue_bwd", (dy, rows, C), dict(z=z, colmask=cm, scalar=sc, dout=zer(rows, C, dtype=dt), dmask=zer(C),
+                                             dbias=zer(C), dscalar=zer(1), act=1), tol=tol)
+    both("epilogue_bwd", (dy, rows, C), dict(dbias=zer(C)), tol=tol)
+    both("epilogue_bwd", (dy, rows, C), dict(z=z, scalar=sc, dout=zer(rows, C, dtype=dt), dbias=zer(C), dscalar=zer(1)),
+         tol=tol)
+    Bn, Tn, padr = 2, 100, 3
+    both("epilogue_bwd", (dy[: Bn * Tn], Bn * Tn, C),
+         dict(z=z[: Bn * Tn], colmask=cm, dout=zer(Bn, Tn + 2 * padr, C, dtype=dt), dmask=zer(C), dbias=zer(C), act=1,
+              rows_per_batch=Tn, out_bs=(Tn + 2 * padr) * C, out_row_off=padr), tol=tol)
+
+
+@pytest.mark.parametrize("dt", [F32, BF16])
+def test_small_elementwise(dt):
+    a, b = rnd(1000, 96, dtype=dt), rnd(1000, 96, dtype=dt)
+    both("axpy", (a, b))
+    both("axpy", (a.view(-1)[1:], b.view(-1)[1:], 95999))  # unaligned path
+    M, H, Dh = 300, 12, 64
+    both("group_mask_bwd", (rnd(M, H * Dh, dtype=dt), rnd(M, H * Dh, dtype=dt), torch.rand(H, device=DEV),
+                            zer(M, H * Dh, dtype=dt), zer(H), M, H * Dh, Dh), tol=3e-2 if dt == BF16 else 2e-4)
+    x = rnd(3, 50, 40, dtype=dt)
+    lengths = torch.tensor([50, 20, 0], device=DEV)
+    both("pad_rows_zero", (x, lengths, 3, 50, 40))
+    Bn, Tn, Gn, Cg, Cgp, front, pad = 2, 37, 4, 48, 64, 8, 16
+    xp = zer(front + Bn * (Tn + pad) + 16, Gn * Cgp, dtype=dt)
+    both("posconv_pad", (rnd(Bn, Tn, Gn * Cg, dtype=dt), xp, Bn, Tn, Gn, Cg, Cgp, front, pad))
+    src = rnd(777)
+    both("cast", (src, zer(777, dtype=BF16)))
+    both("vec_mul", (rnd(100), rnd(100), rnd(100), 0.5, 1.0))
+
+
+def test_wave_norm():
+    wave = rnd(3, 50000) * 0.3 + 0.05
+    lengths = torch.tensor([50000, 31234, 1000], device=DEV)
+    both("wave_norm", (wave, zer(3, 50000), lengths, 3, 50000), tol=2e-5)
+    both("wave_norm", (wave, zer(3, 50000), None, 3, 50000), tol=2e-5)
+
+
+# ---------------------------------------------------------------------------------------------- conv layer 0
+@pytest.mark.parametrize("dt", [F32, BF16])
+@pytest.mark.parametrize("C,bias", [(512, False), (64, True)])
+def test_conv0(dt, C, bias):
+    Bn, T0, k, s = 2, 16005, 10, 5
+    T1 = (T0 - k) // s + 1
+    wave = rnd(Bn, T0) * 0.1
+    w = rnd(C, 1, k) * 0.3
+    bs = rnd(C) * 0.1 if bias else None
+    gamma, beta, mask = rnd(C) * 0.2 + 1, rnd(C) * 0.1, torch.rand(C, device=DEV)
+    mean, rstd = zer(Bn * C), zer(Bn * C)
+    ops.conv0_stats(wave, w, bs, torch.zeros(Bn * 65, device=DEV, dtype=torch.float64), mean, rstd, Bn, C, k, s, T1, 1e-5)
+    cm, cr = zer(Bn * C).cpu(), zer(Bn * C).cpu()
+    emu.conv0_stats(wave.cpu(), w.cpu(), None if bs is None else bs.cpu(), None, cm, cr, Bn, C, k, s, T1, 1e-5)
+    assert (mean.cpu() - cm).abs().max() < 1e-5 * max(cm.abs().max().item(), 1e-3)
+    assert ((rstd.cpu() - cr).abs() / cr).max() < 1e-4
+    tol = 3e-2 if dt == BF16 else 3e-4
+    for norm, act in ((1, 1), (0, 1), (0, 0)):
+        y = zer(Bn, T1, C, dtype=dt)
+        both("conv0_fwd", (wave, w, bs, gamma, beta, mean, rstd, mask, y, Bn, C, k, s, T1, norm, act), tol=tol)
+        dy = rnd(Bn, T1, C, dtype=dt)
+        scratch = zer(2 * Bn * C)
+        both("conv0_bwd", (wave, w, bs, gamma, beta, mean, rstd, mask, dy, scratch, zer(C, 1, k),
+                           zer(C) if bias else None, zer(C), zer(C), zer(C), Bn, C, k, s, T1, norm, act),
+             tol=5e-2 if dt == BF16 else 2e-3, ignore=(scratch,))
+
+
+# ---------------------------------------------------------------------------------------------- attention pieces
+@pytest.mark.parametrize("dt", [F32, BF16])
+@pytest.mark.parametrize("T", [199, 64, 499])
+def test_softmax(dt, T):
+    Bn, H = 2, 3
+    Tp = (T + 7) // 8 * 8
+    S = rnd(Bn, H, T, Tp) * 2
+    lengths = torch.tensor([T, T - 17], device=DEV)
+    tol = 2e-2 if dt == BF16 else 1e-4
+    P = zer(Bn, H, T, Tp, dtype=dt)
+    both("softmax_fwd", (S, Tp, P, None, Tp, lengths, Bn, H, T), tol=tol)
+    both("softmax_fwd", (S, Tp, zer(Bn, H, T, Tp, dtype=dt), zer(Bn, H, T, Tp, dtype=dt), Tp, None, Bn, H, T), tol=tol)
+    dP = rnd(Bn, H, T, Tp)
+    both("softmax_bwd", (P, dP, Tp, zer(Bn, H, T, Tp, dtype=dt), Tp, Bn, H, T), tol=3e-2 if dt == BF16 else 2e-4)
+
+
+@pytest.mark.parametrize("dt", [F32, BF16])
+def test_softmax_wavlm_bias_and_gate(dt):
+    Bn, Htot, T, Dh, nb = 2, 4, 70, 32, 32
+    heads = [0, 2, 3]
+    H = len(heads)
+    Tp = (T + 7) // 8 * 8
+    x = rnd(Bn, T, Htot * Dh, dtype=dt)
+    Wg, bg, cst = rnd(8, Dh) * 0.2, rnd(8) * 0.1, rnd(1, Htot, 1, 1) * 0.1 + 1
+    gate, ga, gb = zer(Bn, Htot, T), zer(Bn, Htot, T), zer(Bn, Htot, T)
+    both("wavlm_gate_fwd", (x, Wg, bg, cst, gate, ga, gb, Bn, T, Htot, Dh), tol=2e-2 if dt == BF16 else 1e-4)
+    rt = torch.randint(0, nb, (2 * T - 1,), device=DEV, dtype=torch.int32)
+    emb = rnd(nb, Htot)
+    hidx = torch.tensor(heads, device=DEV, dtype=torch.int32)
+    wl = (rt, emb, gate, hidx, Htot)
+    S = rnd(Bn, H, T, Tp)
+    P = zer(Bn, H, T, Tp, dtype=dt)
+    tol = 2e-2 if dt == BF16 else 1e-4
+    both("softmax_fwd", (S, Tp, P, None, Tp, None, Bn, H, T), dict(wavlm=wl), tol=tol)
+    dgate, demb = zer(Bn, Htot, T), zer(nb, Htot)
+    both("softmax_bwd", (P, rnd(Bn, H, T, Tp), Tp, zer(Bn, H, T, Tp, dtype=dt), Tp, Bn, H, T),
+         dict(wavlm=wl, dgate=dgate, demb=demb, num_buckets=nb), tol=3e-2 if dt == BF16 else 5e-4)
+    dx = rnd(Bn, T, Htot * Dh, dtype=dt)
+    both("wavlm_gate_bwd", (x, Wg, cst, ga, gb, rnd(Bn, Htot, T), dx, zer(8, Dh), zer(8), zer(1, Htot, 1, 1), Bn, T, Htot,
+                            Dh), tol=3e-2 if dt == BF16 else 5e-4)
+
+
+# ---------------------------------------------------------------------------------------------- loss / gates / optimizer
+@pytest.mark.parametrize("dt", [F32, BF16])
+@pytest.mark.parametrize("cos_type", [0, 1])
+def test_distill_loss(dt, cos_type):
+    rows, D = 1001, 768
+    a, b = rnd(rows, D, dtype=dt), rnd(rows, D, dtype=dt)
+    rowstat, acc, out = zer(rows * 3), zer(4), zer(16)
+    both("distill_loss_fwd", (a, b, rowstat, acc, out, rows, D, 0.5, 1.0, 1.0, cos_type, True, False, 2 * rows), tol=1e-4)
+    both("distill_loss_fwd", (b, a, zer(rows * 3), acc, out, rows, D, 0.5, 1.0, 1.0, cos_type, False, True, 2 * rows),
+         tol=1e-4)
+    both("distill_loss_bwd", (a, b, rowstat, None, zer(rows, D, dtype=dt), rows, 2 * rows, D, 0.5, 1.0, 1.0, cos_type),
+         tol=2e-2 if dt == BF16 else 1e-4)
+
+
+def test_hardconcrete_and_size():
+    n = 4000
+    la, u = rnd(n) * 2 + 1, torch.rand(n, device=DEV).clamp(1e-6, 1 - 1e-6)
+    beta, l, r = 2 / 3, -0.1, 1.1
+    mask = zer(n)
+    both("hardconcrete_fwd", (la, u, None, mask, n, beta, l, r, 1e-6, 0), tol=1e-5)
+    both("hardconcrete_bwd", (la, u, rnd(n), zer(n), n, beta, l, r), tol=1e-4)
+    # device-generated noise: right range, right moments, new draw after the epoch advances
+    u1, u2 = zer(n), zer(n)
+    ops.hardconcrete_fwd(la, None, u1, mask, n, beta, l, r, 1e-6, 77)
+    ops.rng_advance()
+    ops.hardconcrete_fwd(la, None, u2, mask, n, beta, l, r, 1e-6, 77)
+    assert u1.min() >= 1e-6 and u1.max() <= 1 - 1e-6 and abs(u1.mean().item() - 0.5) < 0.03
+    assert (u1 != u2).float().mean() > 0.99
+    seg_off = torch.tensor([0, 512, 1024, 1040], device=DEV)
+    seg_len = torch.tensor([512, 512, 12, 2960], device=DEV, dtype=torch.int32)
+    norms = zer(4)
+    both("l0_norms", (la, seg_off, seg_len, 4, 1.6, norms), tol=1e-5)
+    both("l0_norms_bwd", (la, zer(n), seg_off, seg_len, 4, 1.6, rnd(4), None, torch.tensor([0.3], device=DEV)), tol=1e-4)
+    both("lagrangian", (torch.tensor([8.0e7], device=DEV), torch.tensor([0.3, 0.2], device=DEV), 9.4e7,
+                        torch.tensor([0.75], device=DEV), zer(8)), tol=1e-5)
+
+
+def test_adamw_and_sumsq():
+    n = 100003
+    p, g, m, v = rnd(n), rnd(n) * 0.1, rnd(n) * 0.01, torch.rand(n, device=DEV) * 1e-3
+    gn = torch.zeros(1, device=DEV, dtype=torch.float64)
+    both("sumsq", (g[:100000], gn), tol=1e-6)
+    lr, step = torch.tensor([-0.01], device=DEV), torch.tensor([3], device=DEV, dtype=torch.int32)
+    both("adamw", (p, g, m, v, lr, 0.9, 0.999, 1e-8, 0.01, step, gn, 1.0, zer(n, dtype=BF16), True), tol=1e-5)
+    both("counter_inc", (step,))
+
+
+def test_weight_prep():
+    Cout, Cin, k = 64, 128, 3
+    w = rnd(Cout, Cin, k)
+    both("conv_weight_prep", (w, zer(Cout, k, Cin, dtype=BF16), zer(k, Cin, Cout, dtype=BF16), Cout, Cin, k, [1, 2, 0]))
+    both("conv_wgrad_unpermute", (rnd(Cout, k * Cin), zer(Cout, Cin, k), Cout, Cin, k))
+    D, Gn, Cg, Cgp, K = 192, 4, 48, 64, 16
+    v, g = rnd(D, Cg, K), rnd(1, 1, K) + 2
+    norm = zer(K)
+    both("posconv_weight_prep", (v, g, norm, zer(D, Cg, K), zer(Gn, Cg, K, Cgp, dtype=BF16), zer(Gn, Cg, K, Cgp, dtype=BF16),
+                                 D, Gn, Cg, Cgp, K))
+    scratch = zer(K)
+    both("posconv_weight_bwd", (rnd(Gn, Cgp, K, Cgp), v, g, norm, scratch, zer(D, Cg, K), zer(1, 1, K), D, Gn, Cg, Cgp, Cgp,
+                                K), tol=2e-4, ignore=(scratch,))
