@@ -40,6 +40,9 @@ def parse():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--profile-step", action="store_true",
+                    help="run two eager steps, then ONE eager step between cudaProfilerStart/Stop and exit "
+                         "(for `ncu --profile-from-start off`); prints no bench line")
     return ap.parse_args()
 
 
@@ -230,6 +233,15 @@ def run_ours(args, rank, world, local_rank):
     wave.copy_(host[0])
     out_host = torch.zeros(16).pin_memory()
 
+    if args.profile_step:
+        for _ in range(2):
+            step.run_step(wave, lengths)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
+        step.run_step(wave, lengths)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
+        return
     n_before = _lib.launch_count()
     if args.no_graph:
         step.run_step(wave, lengths)

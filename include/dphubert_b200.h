@@ -114,6 +114,141 @@ typedef struct {
 
 int dph_gemm_f32(const dph_gemm_f32_desc_t* desc, void* stream);
 
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Kernel RNG epoch (dropout / HardConcrete noise): a device-side counter mixed into every counter-based draw, so
+ * that a training step captured in a CUDA graph still draws fresh masks on every replay.
+ * Replaces torch's global CUDA generator state used by nn.Dropout / Tensor.uniform_ (hardconcrete.py:96).
+ * ---------------------------------------------------------------------------------------------------------- */
+int dph_rng_set(unsigned long long value, void* stream);
+int dph_rng_advance(void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Waveform feature extractor, layer 0 (memory-bound): Conv1d(1->C, k<=10, stride) -> GroupNorm(C groups) -> GELU ->
+ * HardConcrete channel mask, channels-last (B, T1, C) output written exactly once; statistics come from a 65-term
+ * autocorrelation of the waveform (fp64), the backward recomputes the conv from the waveform.
+ * Replaces wav2vec2/components.py:107-114 (ConvLayerBlock.forward, layer 0) + autograd; dph_wave_norm replaces
+ * wav2vec2/model.py:96-103 (per-utterance F.layer_norm of the waveform).
+ * ---------------------------------------------------------------------------------------------------------- */
+int dph_conv0_stats(const float* wave, int64_t wave_bs, const float* w, const float* bias, double* moments /* B*65 */,
+                    float* mean /* B*C */, float* rstd /* B*C */, int B, int C, int k, int stride, int T1, float eps,
+                    void* stream);
+int dph_conv0_fwd(const float* wave, int64_t wave_bs, const float* w, const float* bias, const float* gamma,
+                  const float* beta, const float* mean, const float* rstd, const float* mask, void* y, int B, int C, int k,
+                  int stride, int T1, int norm, int act, int dtype, void* stream);
+int dph_conv0_bwd(const float* wave, int64_t wave_bs, const float* w, const float* bias, const float* gamma,
+                  const float* beta, const float* mean, const float* rstd, const float* mask, const void* dy,
+                  float* scratch /* 2*B*C */, float* dW, float* dbias, float* dgamma, float* dbeta, float* dmask, int B,
+                  int C, int k, int stride, int T1, int norm, int act, int dtype, void* stream);
+int dph_wave_norm(const float* in, int64_t in_bs, float* out, int64_t out_bs, const int64_t* lengths, int B, int T0,
+                  float eps, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Row LayerNorm (+ optional GELU, column mask, dropout) forward / backward.
+ * Replaces nn.LayerNorm at components.py:54-61 (channel LN of the Large extractor), :271, :808-811, :839, :850-856,
+ * :879, :888-889, :905-906 and the dropout at :891.
+ * ---------------------------------------------------------------------------------------------------------- */
+int dph_layernorm_fwd(const void* x, const float* w, const float* b, void* y, void* y_pre, float* mean, float* rstd,
+                      const float* colmask, int rows, int D, float eps, int act, float drop_p, uint64_t seed, int dtype,
+                      void* stream);
+int dph_layernorm_bwd(const void* dy, const void* dy2, const void* x, const float* w, const float* b, const float* mean,
+                      const float* rstd, void* dx, float* dw, float* db, const float* colmask, float* dmask, int rows, int D,
+                      int act, float drop_p, uint64_t seed, int rows_per_batch, int64_t out_bs, int out_row_off, int dtype,
+                      void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Elementwise / column-reduction helpers around the GEMMs.
+ *  dph_epilogue_bwd: backward of  o = dropout(scalar * colmask * act(z))  -> dz, bias grad, HardConcrete column-mask
+ *    grad, layer-gate grad (components.py:110-114, :424-434, :733-746 via autograd).
+ *  dph_group_mask_bwd: backward of the per-head mask `output * head_mask[:, None, None]` (components.py:424-426).
+ *  dph_pad_rows_zero: `x[mask] = 0` (components.py:979-980).   dph_posconv_pad/unpad: staging layout of the
+ *    positional conv (components.py:319-333).   dph_axpy: residual / multi-consumer gradient accumulation.
+ * ---------------------------------------------------------------------------------------------------------- */
+int dph_epilogue_bwd(const void* dy, const void* z, const float* colmask, const float* scalar, void* dout, float* dmask,
+                     float* dbias, float* dscalar, int rows, int C, int act, float drop_p, uint64_t seed,
+                     int rows_per_batch, int64_t out_bs, int out_row_off, int64_t in_ld, int64_t z_ld, int dtype,
+                     void* stream);
+int dph_group_mask_bwd(const void* dy, const void* z, const float* mask, void* dout, float* dmask, int rows, int C,
+                       int group, int dtype, void* stream);
+int dph_pad_rows_zero(void* x, const int64_t* lengths, int B, int T, int D, int dtype, void* stream);
+int dph_posconv_pad(const void* x, void* xp, int B, int T, int G, int Cg, int Cgp, int front, int pad, int dtype,
+                    void* stream);
+int dph_posconv_unpad(const void* xp, void* x, int B, int T, int G, int Cg, int Cgp, int front, int pad, int accumulate,
+                      int dtype, void* stream);
+int dph_axpy(void* dst, const void* src, int64_t n, int dtype, void* stream);
+int dph_cast(const void* in, int in_dtype, void* out, int out_dtype, int64_t n, void* stream);
+int dph_vec_mul(const float* a, const float* b, float* out, float alpha, float beta, int n, void* stream);
+int dph_transpose(const void* in, int in_dtype, void* out, int out_dtype, int B, int R, int C, void* stream);
+int dph_memset(void* p, int value, int64_t bytes, void* stream);
+int dph_memset2d(void* p, int64_t pitch, int value, int64_t width, int64_t height, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Attention probabilities: masked / biased softmax (+dropout) and WavLM's gated relative position bias.
+ * Replaces components.py:411-420 and :546-600, :629-647 (+ autograd); the additive padding mask of
+ * components.py:979-983 is rebuilt from `lengths`, no (B,1,T,T) / (B*H,T,T) tensor is materialised.
+ * ---------------------------------------------------------------------------------------------------------- */
+int dph_softmax_fwd(const float* S, int64_t lds, void* P, void* Pd, int64_t ldp, const int64_t* lengths, int B, int H,
+                    int T, float drop_p, uint64_t seed, const int* rel_table, const float* emb, const float* gate,
+                    const int* head_index, int Htot, int dtype, void* stream);
+int dph_softmax_bwd(const void* P, const float* dPd, int64_t lds, void* dS, int64_t ldp, int B, int H, int T, float drop_p,
+                    uint64_t seed, const int* rel_table, const float* emb, const float* gate, const int* head_index,
+                    int Htot, float* dgate, float* demb, int num_buckets, int dtype, void* stream);
+int dph_wavlm_gate_fwd(const void* x, const float* Wg, const float* bg, const float* cst, float* gate, float* ga, float* gb,
+                       int B, int T, int Htot, int Dh, int dtype, void* stream);
+int dph_wavlm_gate_bwd(const void* x, const float* Wg, const float* cst, const float* ga, const float* gb,
+                       const float* dgate, void* dx, float* dWg, float* dbg, float* dcst, int B, int T, int Htot, int Dh,
+                       int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * HardConcrete gates, expected model size, Lagrangian.
+ * Replaces wav2vec2/hardconcrete.py:76-99, the get_num_params tree (components.py:122-134, 187-196, 276-277, 438-449,
+ * 750-761, 859-865, 929-934, 1005-1009; model.py:109-113) and lightning.py:267-271 (+ autograd).
+ * ---------------------------------------------------------------------------------------------------------- */
+int dph_hardconcrete_fwd(const float* log_alpha, const float* u_in, float* u_out, float* mask, int64_t n, float beta,
+                         float limit_l, float limit_r, float eps, uint64_t seed, void* stream);
+int dph_hardconcrete_bwd(const float* log_alpha, const float* u, const float* dmask, float* dlog_alpha, int64_t n,
+                         float beta, float limit_l, float limit_r, void* stream);
+int dph_l0_norms(const float* la_base, const int64_t* seg_off, const int* seg_len, int nseg, float bias, float* norms,
+                 void* stream);
+int dph_num_params(const int* prog, const float* norms, int nseg, float* out_n, float* dnorm, void* stream);
+int dph_lagrangian(const float* n_hat, const float* lambdas, float n0, const float* target, float* out /* 5 */,
+                   void* stream);
+int dph_l0_norms_bwd(const float* la_base, float* dla_base, const int64_t* seg_off, const int* seg_len, int nseg, float bias,
+                     const float* dnorm, const float* upstream, const float* coef, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Layer-wise distillation loss (MSE + L1 + cosine), fused reductions.  Replaces lightning.py:116-139 (+ autograd).
+ * ---------------------------------------------------------------------------------------------------------- */
+int dph_distill_loss_fwd(const void* a, const void* b, float* rowstat, float* acc, float* out /* 4 */, int64_t rows, int D,
+                         float w2, float w1, float wc, int cos_type, int first, int last, int64_t total_rows, int dtype,
+                         void* stream);
+int dph_distill_loss_bwd(const void* a, const void* b, const float* rowstat, const float* upstream, void* da, int64_t rows,
+                         int64_t total_rows, int D, float w2, float w1, float wc, int cos_type, int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Derived GEMM operands: tap-major conv weights (components.py:81-87), weight_norm(dim=2) reparameterisation of the
+ * positional conv (components.py:298-307) and its backward.
+ * ---------------------------------------------------------------------------------------------------------- */
+int dph_conv_weight_prep(const float* w, void* wf, void* wd, int Cout, int Cin, int k, const int* tap_perm, int dtype,
+                         void* stream);
+int dph_conv_wgrad_unpermute(const float* src, float* dw, int Cout, int Cin, int k, void* stream);
+int dph_posconv_weight_prep(const float* v, const float* g, float* norm, float* wn, void* wp, void* wdp, int D, int G,
+                            int Cg, int Cgp, int K, int dtype, void* stream);
+int dph_posconv_weight_bwd(const float* dwp, const float* v, const float* g, const float* norm, float* scratch, float* dv,
+                           float* dg, int D, int G, int Cg, int Cop, int Cgp, int K, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Optimizer over flat arenas: global grad norm, clip, AdamW (lr / step in device memory), bf16 weight refresh,
+ * grad zeroing.  Replaces lightning.py:200-238 (torch.optim.AdamW, 3 groups incl. the negative-lr lambda group) and
+ * distill.py:48 (gradient_clip_val -> clip_grad_norm_).
+ * ---------------------------------------------------------------------------------------------------------- */
+int dph_sumsq(const float* x, int64_t n, double* out, void* stream);
+int dph_counter_inc(int* counter, void* stream);
+int dph_adamw(float* p, float* g, float* m, float* v, int64_t n, const float* lr_dev, float beta1, float beta2, float eps,
+              float weight_decay, const int* step_dev, const double* gnorm_sq, float max_norm, void* p_bf16, int zero_grad,
+              void* stream);
+int dph_scale(float* x, int64_t n, float a, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

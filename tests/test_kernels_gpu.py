@@ -167,8 +167,9 @@ def test_conv0(dt, C, bias):
         both("conv0_fwd", (wave, w, bs, gamma, beta, mean, rstd, mask, y, Bn, C, k, s, T1, norm, act), tol=tol)
         dy = rnd(Bn, T1, C, dtype=dt)
         scratch = zer(2 * Bn * C)
+        # with GroupNorm the conv-bias gradient is analytically zero (the norm removes the mean): skip it there
         both("conv0_bwd", (wave, w, bs, gamma, beta, mean, rstd, mask, dy, scratch, zer(C, 1, k),
-                           zer(C) if bias else None, zer(C), zer(C), zer(C), Bn, C, k, s, T1, norm, act),
+                           zer(C) if (bias and not norm) else None, zer(C), zer(C), zer(C), Bn, C, k, s, T1, norm, act),
              tol=5e-2 if dt == BF16 else 2e-3, ignore=(scratch,))
 
 
@@ -257,7 +258,9 @@ def test_adamw_and_sumsq():
     gn = torch.zeros(1, device=DEV, dtype=torch.float64)
     both("sumsq", (g[:100000], gn), tol=1e-6)
     lr, step = torch.tensor([-0.01], device=DEV), torch.tensor([3], device=DEV, dtype=torch.int32)
-    both("adamw", (p, g, m, v, lr, 0.9, 0.999, 1e-8, 0.01, step, gn, 1.0, zer(n, dtype=BF16), True), tol=1e-5)
+    p16 = zer(n, dtype=BF16)
+    both("adamw", (p, g, m, v, lr, 0.9, 0.999, 1e-8, 0.01, step, gn, 1.0, p16, True), tol=1e-5, ignore=(p16,))
+    assert (p16.float() - p).abs().max() <= p.abs().max() * 2 ** -8
     both("counter_inc", (step,))
 
 
