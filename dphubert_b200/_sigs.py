@@ -44,6 +44,10 @@ SIGS = {
     "dph_softmax_bwd": [vp, vp, i64, vp, i64, i32, i32, i32, f32, u64, vp, vp, vp, vp, i32, vp, vp, i32, i32, vp],
     "dph_wavlm_gate_fwd": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "dph_wavlm_gate_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
+    # attention.cu
+    "dph_attn_fwd": [vp, vp, vp, vp, i32, i32, i32, f32, vp, vp, vp, vp, vp, i32, f32, u64, vp, vp],
+    "dph_attn_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, f32, vp, vp, vp, vp, vp, i32, f32, u64, vp, vp, vp,
+                     i32, vp],
     # hardconcrete.cu
     "dph_hardconcrete_fwd": [vp, vp, vp, vp, i64, f32, f32, f32, f32, u64, vp],
     "dph_hardconcrete_bwd": [vp, vp, vp, vp, i64, f32, f32, f32, vp],

@@ -1,0 +1,672 @@
+// Fused multi-head self-attention for head_dim = 64 on the 5th-generation tensor cores (tcgen05 + TMEM + TMA):
+//   forward : S = scale * Q K^T (+ WavLM gated relative-position bias, + additive padding mask) -> online softmax
+//             -> dropout -> O = P V -> head mask, with S and P living only in TMEM / shared memory;
+//   backward: recomputes S / P per tile from Q, K and the saved log-sum-exp, and produces dQ, dK, dV (and the WavLM
+//             gate / embedding gradients) without ever materialising a (B, H, T, T) tensor in HBM.
+//
+// Replaces wav2vec2/components.py:406-426 (SelfAttention.forward: the two batched matmuls, mask add, row-max
+// subtraction, softmax, dropout, head mask) and :629-647 (WavLM bias) plus their autograd backward.  The reference
+// materialises (B, H, T, T) fp32 scores (95.6 MB per copy at B=8, T=499) and makes ~6 elementwise passes over them.
+//
+// Layout: q/k/v are read straight out of the fused projection buffer qkv[(b T + t)][k | v | q] (row stride 3 * H * 64)
+// by TMA; the context is written as ctx[(b T + t)][h * 64 + e].
+#include "common.cuh"
+#include "../../include/dphubert_b200.h"
+
+namespace dph {
+void set_error(const char* fmt, ...);
+
+constexpr int ATT_D = 64;        // head dim
+constexpr int ATT_BQ = 128;      // queries per CTA
+constexpr int ATT_BK = 128;      // keys per tile
+constexpr float kLog2e = 1.4426950408889634f;
+
+struct AttnParams {
+  int B, H, T, inner;            // inner = H * 64
+  float scale;
+  const long long* lengths;      // (B) or null
+  // WavLM relative position bias (null emb = none)
+  const int* rel_table;          // (2T-1)
+  const float* emb;              // (num_buckets, Htot)
+  const float* gate;             // (B, Htot, T) or null
+  const int* head_index;         // (H) or null
+  int Htot;
+  float drop_p;
+  unsigned long long seed;
+  const float* head_mask;        // (H) or null
+};
+
+DPH_DEVICE void tma_load_2d(uint32_t smem_dst, const CUtensorMap* m, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_dst),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+DPH_DEVICE void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// byte offset of 16-byte chunk `c` (0..7) of row `r` inside a [rows][64 bf16] 128B-swizzled K-major tile
+DPH_DEVICE uint32_t sw128(int r, int c) { return (uint32_t)(r * 128 + ((c ^ (r & 7)) << 4)); }
+
+// shared memory map of the forward kernel (all tiles 1024-byte aligned)
+constexpr int FWD_SQ = 0;                                // Q   [128][64]        16 KB
+constexpr int FWD_SK = FWD_SQ + ATT_BQ * ATT_D * 2;      // K   [128][64]        16 KB
+constexpr int FWD_SV = FWD_SK + ATT_BK * ATT_D * 2;      // V   [128][64]        16 KB
+constexpr int FWD_SP = FWD_SV + ATT_BK * ATT_D * 2;      // P   2 x [128][64]    32 KB (two 64-key blocks)
+constexpr int FWD_TB = FWD_SP + ATT_BQ * ATT_BK * 2;     // bias table, up to 2*1024 floats 8 KB
+constexpr int FWD_BAR = FWD_TB + 2048 * 4;               // mbarriers + tmem slot
+constexpr int FWD_SMEM = FWD_BAR + 64 + 1024;            // + alignment slack
+
+__global__ void __launch_bounds__(128, 2)
+    attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p, bf16* __restrict__ ctx,
+                    bf16* __restrict__ ctx_un, float* __restrict__ lse) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* gbase = smem_raw + (sbase - smem_u32(smem_raw));
+  const uint32_t sQ = sbase + FWD_SQ, sK = sbase + FWD_SK, sV = sbase + FWD_SV, sP = sbase + FWD_SP;
+  float* tb = reinterpret_cast<float*>(gbase + FWD_TB);
+  const uint32_t bar_q = sbase + FWD_BAR, bar_k = bar_q + 8, bar_v = bar_q + 16, bar_mma = bar_q + 24,
+                 tmem_slot = bar_q + 32;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int T = p.T;
+  const int q0 = qt * ATT_BQ;
+  const int ntiles = (T + ATT_BK - 1) / ATT_BK;
+  const int row_q = b * T + q0;
+
+  if (tid == 0) {
+    mbar_init(bar_q, 1);
+    mbar_init(bar_k, 1);
+    mbar_init(bar_v, 1);
+    mbar_init(bar_mma, 1);
+    mbar_fence_init();
+    tma_prefetch_desc(&tmQKV);
+  }
+  if (warp == 0) {
+    __syncwarp();
+    tmem_alloc(tmem_slot, 256);
+    tmem_relinquish();
+  }
+  int htot = h;
+  float gate_i = 1.f;
+  const int i = q0 + tid;  // query row of this thread
+  if (p.emb) {
+    htot = p.head_index ? p.head_index[h] : h;
+    for (int r = tid; r < 2 * T - 1; r += 128) tb[r] = __ldg(p.emb + (long long)p.rel_table[r] * p.Htot + htot);
+    if (p.gate && i < T) gate_i = p.gate[((long long)b * p.Htot + htot) * T + i];
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+  const uint32_t tS = tmem_base, tO = tmem_base + 128;
+  const uint32_t lane_off = ((uint32_t)(warp * 32)) << 16;
+
+  if (tid == 0) {
+    mbar_expect_tx(bar_q, ATT_BQ * ATT_D * 2);
+    tma_load_2d(sQ, &tmQKV, bar_q, 2 * p.inner + h * ATT_D, row_q);
+    mbar_expect_tx(bar_k, ATT_BK * ATT_D * 2);
+    tma_load_2d(sK, &tmQKV, bar_k, h * ATT_D, b * T);
+    mbar_expect_tx(bar_v, ATT_BK * ATT_D * 2);
+    tma_load_2d(sV, &tmQKV, bar_v, p.inner + h * ATT_D, b * T);
+  }
+  const int len = p.lengths ? (int)p.lengths[b] : T;
+  const uint32_t thresh = (uint32_t)(p.drop_p * 4294967296.0);
+  const float inv_keep = p.drop_p > 0.f ? 1.f / (1.f - p.drop_p) : 1.f;
+  const unsigned long long drop_row = ((unsigned long long)(b * p.H + h) * T + (unsigned long long)i) * T;
+  const float sc2 = p.scale * kLog2e;
+
+  float m2 = -INFINITY, l = 0.f;  // running max (log2 domain) and sum
+  float o[ATT_D];
+#pragma unroll
+  for (int e = 0; e < ATT_D; ++e) o[e] = 0.f;
+  uint32_t mma_phase = 0;
+  constexpr uint32_t idesc_s = make_idesc_bf16(ATT_BQ, ATT_BK, false, false);
+  constexpr uint32_t idesc_o = make_idesc_bf16(ATT_BQ, ATT_D, false, true);
+
+  for (int t = 0; t < ntiles; ++t) {
+    const int k0 = t * ATT_BK;
+    if (tid == 0) {
+      if (t == 0) mbar_wait(bar_q, 0);
+      mbar_wait(bar_k, (uint32_t)(t & 1));
+      tc_fence_after();
+      const uint32_t kb = sK;
+#pragma unroll
+      for (int k = 0; k < ATT_D / 16; ++k)
+        umma_f16_ss(tS, make_smem_desc(sQ + k * 32, 0, 1024, 2), make_smem_desc(kb + k * 32, 0, 1024, 2), idesc_s,
+                    k > 0 ? 1u : 0u);
+      umma_commit(bar_mma);
+    }
+    mbar_wait(bar_mma, mma_phase);
+    mma_phase ^= 1u;
+    tc_fence_after();
+    if (tid == 0 && t + 1 < ntiles) {  // K tile is free again: fetch the next one while the softmax runs
+      mbar_expect_tx(bar_k, ATT_BK * ATT_D * 2);
+      tma_load_2d(sK, &tmQKV, bar_k, h * ATT_D, b * T + k0 + ATT_BK);
+    }
+
+    // ---- pass A: row maximum of this tile (log2 domain)
+    float mx = m2;
+#pragma unroll 1
+    for (int c = 0; c < ATT_BK / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32(tS + lane_off + c * 32, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int jj = 0; jj < 32; ++jj) {
+        const int j = k0 + c * 32 + jj;
+        float x = __uint_as_float(r[jj]) * sc2;
+        if (p.emb) x += gate_i * tb[min(max(j - i + T - 1, 0), 2 * T - 2)] * kLog2e;
+        if (j >= len) x += -10000.0f * kLog2e;
+        if (j < T) mx = fmaxf(mx, x);
+      }
+    }
+    const float alpha = exp2f(m2 - mx);  // m2 = -inf on the first tile -> 0
+    m2 = mx;
+    l *= alpha;
+#pragma unroll
+    for (int e = 0; e < ATT_D; ++e) o[e] *= alpha;
+    // ---- pass B: probabilities -> bf16 P tile in shared memory (K-major, 128B swizzle, two 64-key blocks)
+    float lsum = 0.f;
+#pragma unroll 1
+    for (int c = 0; c < ATT_BK / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32(tS + lane_off + c * 32, r);
+      tmem_ld_wait();
+      uint32_t pk[16];
+#pragma unroll
+      for (int jj = 0; jj < 32; jj += 2) {
+        float pv[2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const int j = k0 + c * 32 + jj + u;
+          float x = __uint_as_float(r[jj + u]) * sc2;
+          if (p.emb) x += gate_i * tb[min(max(j - i + T - 1, 0), 2 * T - 2)] * kLog2e;
+          if (j >= len) x += -10000.0f * kLog2e;
+          float pe = (j < T) ? exp2f(x - m2) : 0.f;
+          lsum += pe;
+          if (p.drop_p > 0.f) pe *= dropout_scale(p.seed, drop_row + (unsigned long long)j, thresh, inv_keep);
+          pv[u] = pe;
+        }
+        pk[jj >> 1] = pack_bf16x2(pv[0], pv[1]);
+      }
+      // 32 keys = 4 chunks of 16 bytes; key block (c / 2), chunk index within the 64-key block ((c & 1) * 4 + q)
+      const uint32_t blk = sP + (uint32_t)(c >> 1) * (ATT_BQ * 128);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint32_t addr = blk + sw128(tid, (c & 1) * 4 + q);
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(pk[4 * q]), "r"(pk[4 * q + 1]),
+                     "r"(pk[4 * q + 2]), "r"(pk[4 * q + 3])
+                     : "memory");
+      }
+    }
+    l += lsum;
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    // ---- O_tile = P V
+    if (tid == 0) {
+      mbar_wait(bar_v, (uint32_t)(t & 1));
+      tc_fence_after();
+      const uint32_t vb = sV;
+#pragma unroll
+      for (int k = 0; k < ATT_BK / 16; ++k)
+        umma_f16_ss(tO, make_smem_desc(sP + (k >> 2) * (ATT_BQ * 128) + (k & 3) * 32, 0, 1024, 2),
+                    make_smem_desc(vb + k * 2048, ATT_BK * 128, 1024, 2), idesc_o, k > 0 ? 1u : 0u);
+      umma_commit(bar_mma);
+    }
+    mbar_wait(bar_mma, mma_phase);
+    mma_phase ^= 1u;
+    tc_fence_after();
+    if (tid == 0 && t + 1 < ntiles) {
+      mbar_expect_tx(bar_v, ATT_BK * ATT_D * 2);
+      tma_load_2d(sV, &tmQKV, bar_v, p.inner + h * ATT_D, b * T + k0 + ATT_BK);
+    }
+#pragma unroll
+    for (int c = 0; c < ATT_D / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32(tO + lane_off + c * 32, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int jj = 0; jj < 32; ++jj) o[c * 32 + jj] += __uint_as_float(r[jj]);
+    }
+    tc_fence_before();
+    __syncthreads();  // S / O_tile / P may now be overwritten
+  }
+
+  if (i < T) {
+    const float inv_l = 1.f / l;
+    const float hm = p.head_mask ? __ldg(p.head_mask + h) : 1.f;
+    if (lse) lse[((long long)(b * p.H + h)) * T + i] = (m2 + log2f(l)) * (1.f / kLog2e);
+    bf16* dst = ctx + ((long long)(b * T + i)) * p.inner + h * ATT_D;
+    bf16* dst_un = ctx_un ? ctx_un + ((long long)(b * T + i)) * p.inner + h * ATT_D : nullptr;
+#pragma unroll
+    for (int e = 0; e < ATT_D; e += 8) {
+      float v[8], vm[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        v[u] = o[e + u] * inv_l;
+        vm[u] = v[u] * hm;
+      }
+      uint4 a, c4;
+      a.x = pack_bf16x2(vm[0], vm[1]); a.y = pack_bf16x2(vm[2], vm[3]);
+      a.z = pack_bf16x2(vm[4], vm[5]); a.w = pack_bf16x2(vm[6], vm[7]);
+      *reinterpret_cast<uint4*>(dst + e) = a;
+      if (dst_un) {
+        c4.x = pack_bf16x2(v[0], v[1]); c4.y = pack_bf16x2(v[2], v[3]);
+        c4.z = pack_bf16x2(v[4], v[5]); c4.w = pack_bf16x2(v[6], v[7]);
+        *reinterpret_cast<uint4*>(dst_un + e) = c4;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 256);
+  }
+}
+
+
+// ------------------------------------------------------------------------------------------------------------
+// backward, step 1: delta'[b,h,i] = sum_e dctx[b,i,h,e] * O_un[b,i,h,e]  (and the head-mask gradient = its sum)
+// ------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+    attn_bwd_prep_kernel(const bf16* __restrict__ dctx, const bf16* __restrict__ o_un, float* __restrict__ delta,
+                         float* __restrict__ dmask_h, int B, int H, int T, int inner) {
+  __shared__ float red[8];
+  const int h = blockIdx.y;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const long long M = (long long)B * T;
+  float blk = 0.f;
+  for (int rr = 0; rr < 8; ++rr) {
+    const long long row = ((long long)blockIdx.x * 8 + w) * 8 + rr;
+    if (row >= M) break;
+    const long long off = row * inner + h * ATT_D + lane * 2;
+    const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(dctx + off));
+    const float2 c = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(o_un + off));
+    float d = warp_sum(a.x * c.x + a.y * c.y);
+    if (lane == 0) {
+      const int b = (int)(row / T), i = (int)(row - (long long)b * T);
+      delta[((long long)(b * H + h)) * T + i] = d;
+      blk += d;
+    }
+  }
+  if (dmask_h) {
+    if (lane == 0) red[w] = blk;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float t = 0.f;
+      for (int q = 0; q < 8; ++q) t += red[q];
+      atomicAdd(dmask_h + h, t);
+    }
+  }
+}
+
+// dq32 (M, inner) fp32 accumulator -> bf16 Q slot of dqkv, and clear the accumulator for the next layer
+__global__ void attn_dq_convert_kernel(float* __restrict__ dq32, bf16* __restrict__ dqkv, long long M, int inner) {
+  const long long n4 = M * inner / 4;
+  for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < n4; v += (long long)gridDim.x * blockDim.x) {
+    float4 f = reinterpret_cast<float4*>(dq32)[v];
+    reinterpret_cast<float4*>(dq32)[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+    const long long e = v * 4;
+    const long long row = e / inner;
+    const int col = (int)(e - row * inner);
+    uint2 u;
+    u.x = pack_bf16x2(f.x, f.y);
+    u.y = pack_bf16x2(f.z, f.w);
+    *reinterpret_cast<uint2*>(dqkv + row * (3LL * inner) + 2 * inner + col) = u;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// backward, step 2: one CTA per (key tile, head, utterance); loops over the query tiles
+// ------------------------------------------------------------------------------------------------------------
+constexpr int BWD_SK = 0;                                // K    [128 j][64]            16 KB
+constexpr int BWD_SV = BWD_SK + ATT_BK * ATT_D * 2;      // V    [128 j][64]            16 KB
+constexpr int BWD_SQ = BWD_SV + ATT_BK * ATT_D * 2;      // Q    [128 i][64]            16 KB
+constexpr int BWD_SDO = BWD_SQ + ATT_BQ * ATT_D * 2;     // dO   [128 i][64]            16 KB
+constexpr int BWD_SP = BWD_SDO + ATT_BQ * ATT_D * 2;     // Pd   2 x [128 i][64 j]      32 KB
+constexpr int BWD_SDS = BWD_SP + ATT_BQ * ATT_BK * 2;    // dS   2 x [128 i][64 j]      32 KB
+constexpr int BWD_TB = BWD_SDS + ATT_BQ * ATT_BK * 2;    // bias table (2T-1 floats)     8 KB
+constexpr int BWD_HIST = BWD_TB + 2048 * 4;              // embedding-gradient histogram 4 KB
+constexpr int BWD_BAR = BWD_HIST + 1024 * 4;
+constexpr int BWD_SMEM = BWD_BAR + 64 + 1024;
+
+__global__ void __launch_bounds__(128, 1)
+    attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
+                    const AttnParams p, const float* __restrict__ lse, const float* __restrict__ delta,
+                    float* __restrict__ dq32, bf16* __restrict__ dqkv, float* __restrict__ dgate,
+                    float* __restrict__ demb, int num_buckets) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* gbase = smem_raw + (sbase - smem_u32(smem_raw));
+  const uint32_t sK = sbase + BWD_SK, sV = sbase + BWD_SV, sQ = sbase + BWD_SQ, sDO = sbase + BWD_SDO,
+                 sP = sbase + BWD_SP, sDS = sbase + BWD_SDS;
+  float* tb = reinterpret_cast<float*>(gbase + BWD_TB);
+  float* hist = reinterpret_cast<float*>(gbase + BWD_HIST);
+  const uint32_t bar_kv = sbase + BWD_BAR, bar_qdo = bar_kv + 8, bar_mma = bar_kv + 16, tmem_slot = bar_kv + 24;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int kt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int T = p.T;
+  const int k0 = kt * ATT_BK;
+  const int nq = (T + ATT_BQ - 1) / ATT_BQ;
+
+  if (tid == 0) {
+    mbar_init(bar_kv, 1);
+    mbar_init(bar_qdo, 1);
+    mbar_init(bar_mma, 1);
+    mbar_fence_init();
+    tma_prefetch_desc(&tmQKV);
+    tma_prefetch_desc(&tmDO);
+  }
+  if (warp == 0) {
+    __syncwarp();
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  int htot = h;
+  if (p.emb) {
+    htot = p.head_index ? p.head_index[h] : h;
+    for (int r = tid; r < 2 * T - 1; r += 128) tb[r] = __ldg(p.emb + (long long)p.rel_table[r] * p.Htot + htot);
+    if (demb)
+      for (int r = tid; r < num_buckets; r += 128) hist[r] = 0.f;
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+  const uint32_t tS = tmem_base, tP = tmem_base + 128, tdV = tmem_base + 256, tdK = tmem_base + 320,
+                 tdQ = tmem_base + 384;
+  const uint32_t lane_off = ((uint32_t)(warp * 32)) << 16;
+
+  if (tid == 0) {
+    mbar_expect_tx(bar_kv, 2 * ATT_BK * ATT_D * 2);
+    tma_load_2d(sK, &tmQKV, bar_kv, h * ATT_D, b * T + k0);
+    tma_load_2d(sV, &tmQKV, bar_kv, p.inner + h * ATT_D, b * T + k0);
+    mbar_expect_tx(bar_qdo, 2 * ATT_BQ * ATT_D * 2);
+    tma_load_2d(sQ, &tmQKV, bar_qdo, 2 * p.inner + h * ATT_D, b * T);
+    tma_load_2d(sDO, &tmDO, bar_qdo, h * ATT_D, b * T);
+  }
+  const int len = p.lengths ? (int)p.lengths[b] : T;
+  const uint32_t thresh = (uint32_t)(p.drop_p * 4294967296.0);
+  const float inv_keep = p.drop_p > 0.f ? 1.f / (1.f - p.drop_p) : 1.f;
+  const float sc2 = p.scale * kLog2e;
+  const float hm = p.head_mask ? __ldg(p.head_mask + h) : 1.f;
+  uint32_t mma_phase = 0;
+  constexpr uint32_t idesc_s = make_idesc_bf16(ATT_BQ, ATT_BK, false, false);   // S, dP : K-major x K-major
+  constexpr uint32_t idesc_kv = make_idesc_bf16(ATT_BK, ATT_D, true, true);     // dV, dK: A^T (MN-major) x MN-major
+  constexpr uint32_t idesc_q = make_idesc_bf16(ATT_BQ, ATT_D, false, true);     // dQ    : K-major x MN-major
+
+  for (int qt = 0; qt < nq; ++qt) {
+    const int q0 = qt * ATT_BQ;
+    const int i = q0 + tid;
+    if (tid == 0) {
+      if (qt == 0) mbar_wait(bar_kv, 0);
+      mbar_wait(bar_qdo, (uint32_t)(qt & 1));
+      tc_fence_after();
+#pragma unroll
+      for (int k = 0; k < ATT_D / 16; ++k)
+        umma_f16_ss(tS, make_smem_desc(sQ + k * 32, 0, 1024, 2), make_smem_desc(sK + k * 32, 0, 1024, 2), idesc_s,
+                    k > 0 ? 1u : 0u);
+#pragma unroll
+      for (int k = 0; k < ATT_D / 16; ++k)
+        umma_f16_ss(tP, make_smem_desc(sDO + k * 32, 0, 1024, 2), make_smem_desc(sV + k * 32, 0, 1024, 2), idesc_s,
+                    k > 0 ? 1u : 0u);
+      umma_commit(bar_mma);
+    }
+    float L2 = 0.f, dl = 0.f, gate_i = 1.f;
+    const bool row_ok = i < T;
+    if (row_ok) {
+      const long long ro = ((long long)(b * p.H + h)) * T + i;
+      L2 = lse[ro] * kLog2e;
+      dl = delta[ro] * hm;
+      if (p.emb && p.gate) gate_i = p.gate[((long long)b * p.Htot + htot) * T + i];
+    }
+    const unsigned long long drop_row = ((unsigned long long)(b * p.H + h) * T + (unsigned long long)i) * T;
+    mbar_wait(bar_mma, mma_phase);
+    mma_phase ^= 1u;
+    tc_fence_after();
+    float dg = 0.f;
+#pragma unroll 1
+    for (int c = 0; c < ATT_BK / 32; ++c) {
+      uint32_t rs[32], rp[32];
+      tmem_ld_32x32(tS + lane_off + c * 32, rs);
+      tmem_ld_32x32(tP + lane_off + c * 32, rp);
+      tmem_ld_wait();
+      uint32_t pk[16], dk[16];
+#pragma unroll
+      for (int jj = 0; jj < 32; jj += 2) {
+        float pv[2], dv[2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const int j = k0 + c * 32 + jj + u;
+          float x = __uint_as_float(rs[jj + u]) * sc2;
+          float tbv = 0.f;
+          if (p.emb) {
+            tbv = tb[min(max(j - i + T - 1, 0), 2 * T - 2)];
+            x += gate_i * tbv * kLog2e;
+          }
+          if (j >= len) x += -10000.0f * kLog2e;
+          const bool ok = row_ok && (j < T);
+          const float pe = ok ? exp2f(x - L2) : 0.f;
+          float ds_scale = 1.f;
+          if (p.drop_p > 0.f) ds_scale = dropout_scale(p.seed, drop_row + (unsigned long long)j, thresh, inv_keep);
+          const float dp = __uint_as_float(rp[jj + u]) * hm * ds_scale;  // d loss / d p_ij
+          const float ds = pe * (dp - dl);
+          pv[u] = pe * ds_scale;
+          dv[u] = ds;
+          if (p.emb && ok) {
+            dg += ds * tbv;
+            if (demb) atomicAdd(&hist[p.rel_table[j - i + T - 1]], ds * gate_i);
+          }
+        }
+        pk[jj >> 1] = pack_bf16x2(pv[0], pv[1]);
+        dk[jj >> 1] = pack_bf16x2(dv[0], dv[1]);
+      }
+      const uint32_t off = (uint32_t)(c >> 1) * (ATT_BQ * 128);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint32_t so = off + sw128(tid, (c & 1) * 4 + q);
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sP + so), "r"(pk[4 * q]), "r"(pk[4 * q + 1]),
+                     "r"(pk[4 * q + 2]), "r"(pk[4 * q + 3])
+                     : "memory");
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sDS + so), "r"(dk[4 * q]), "r"(dk[4 * q + 1]),
+                     "r"(dk[4 * q + 2]), "r"(dk[4 * q + 3])
+                     : "memory");
+      }
+    }
+    if (dgate && p.emb && p.gate && row_ok) atomicAdd(dgate + ((long long)b * p.Htot + htot) * T + i, dg);
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      tc_fence_after();
+#pragma unroll
+      for (int k = 0; k < ATT_BQ / 16; ++k) {  // reduction over the 128 queries of this tile
+        const uint32_t acc = (qt > 0 || k > 0) ? 1u : 0u;
+        // dV[j, e] += sum_i Pd[i, j] dO[i, e]
+        umma_f16_ss(tdV, make_smem_desc(sP + k * 2048, ATT_BQ * 128, 1024, 2),
+                    make_smem_desc(sDO + k * 2048, ATT_BQ * 128, 1024, 2), idesc_kv, acc);
+        // dK[j, e] += sum_i dS[i, j] Q[i, e]
+        umma_f16_ss(tdK, make_smem_desc(sDS + k * 2048, ATT_BQ * 128, 1024, 2),
+                    make_smem_desc(sQ + k * 2048, ATT_BQ * 128, 1024, 2), idesc_kv, acc);
+      }
+#pragma unroll
+      for (int k = 0; k < ATT_BK / 16; ++k)  // dQ[i, e] = sum_j dS[i, j] K[j, e]
+        umma_f16_ss(tdQ, make_smem_desc(sDS + (k >> 2) * (ATT_BQ * 128) + (k & 3) * 32, 0, 1024, 2),
+                    make_smem_desc(sK + k * 2048, ATT_BK * 128, 1024, 2), idesc_q, k > 0 ? 1u : 0u);
+      umma_commit(bar_mma);
+    }
+    mbar_wait(bar_mma, mma_phase);
+    mma_phase ^= 1u;
+    tc_fence_after();
+    if (tid == 0 && qt + 1 < nq) {
+      mbar_expect_tx(bar_qdo, 2 * ATT_BQ * ATT_D * 2);
+      tma_load_2d(sQ, &tmQKV, bar_qdo, 2 * p.inner + h * ATT_D, b * T + q0 + ATT_BQ);
+      tma_load_2d(sDO, &tmDO, bar_qdo, h * ATT_D, b * T + q0 + ATT_BQ);
+    }
+#pragma unroll
+    for (int c = 0; c < ATT_D / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32(tdQ + lane_off + c * 32, r);
+      tmem_ld_wait();
+      if (row_ok) {
+        float* dst = dq32 + ((long long)(b * T + i)) * p.inner + h * ATT_D + c * 32;
+#pragma unroll
+        for (int jj = 0; jj < 32; ++jj) atomicAdd(dst + jj, __uint_as_float(r[jj]) * p.scale);
+      }
+    }
+    tc_fence_before();
+    __syncthreads();
+  }
+  // ---- epilogue: dV (x head mask) and dK (x scale) of this key tile
+  const int j = k0 + tid;
+#pragma unroll
+  for (int which = 0; which < 2; ++which) {
+    const uint32_t ta = which == 0 ? tdV : tdK;
+    const float mul = which == 0 ? hm : p.scale;
+    bf16* dst = dqkv + ((long long)(b * T + j)) * (3LL * p.inner) + (which == 0 ? p.inner : 0) + h * ATT_D;
+#pragma unroll
+    for (int c = 0; c < ATT_D / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32(ta + lane_off + c * 32, r);
+      tmem_ld_wait();
+      if (j < T) {
+#pragma unroll
+        for (int e = 0; e < 32; e += 8) {
+          uint4 u;
+          u.x = pack_bf16x2(__uint_as_float(r[e]) * mul, __uint_as_float(r[e + 1]) * mul);
+          u.y = pack_bf16x2(__uint_as_float(r[e + 2]) * mul, __uint_as_float(r[e + 3]) * mul);
+          u.z = pack_bf16x2(__uint_as_float(r[e + 4]) * mul, __uint_as_float(r[e + 5]) * mul);
+          u.w = pack_bf16x2(__uint_as_float(r[e + 6]) * mul, __uint_as_float(r[e + 7]) * mul);
+          *reinterpret_cast<uint4*>(dst + c * 32 + e) = u;
+        }
+      }
+    }
+  }
+  if (demb && p.emb) {
+    __syncthreads();
+    for (int r = tid; r < num_buckets; r += 128) {
+      const float v = hist[r];
+      if (v != 0.f) atomicAdd(demb + (long long)r * p.Htot + htot, v);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+}  // namespace dph
+
+using namespace dph;
+
+namespace dph {
+int make_tmap_2d(CUtensorMap* out, const void* ptr, uint64_t cols, uint64_t rows, uint64_t row_stride_elems,
+                 uint32_t box_cols, uint32_t box_rows);
+}
+
+static int attn_check(int B, int H, int T, int num_buckets) {
+  if (B <= 0 || H <= 0 || T <= 0 || T > 1024 || num_buckets > 1024 || B > 65535 || H > 65535) {
+    set_error("fused attention: unsupported shape B=%d H=%d T=%d (head_dim must be 64, T <= 1024)", B, H, T);
+    return DPH_ERR_UNSUPPORTED;
+  }
+  return DPH_OK;
+}
+
+static AttnParams attn_params(int B, int H, int T, float scale, const int64_t* lengths, const int* rel_table,
+                              const float* emb, const float* gate, const int* head_index, int Htot, float drop_p,
+                              uint64_t seed, const float* head_mask) {
+  AttnParams p;
+  p.B = B;
+  p.H = H;
+  p.T = T;
+  p.inner = H * ATT_D;
+  p.scale = scale;
+  p.lengths = reinterpret_cast<const long long*>(lengths);
+  p.rel_table = rel_table;
+  p.emb = emb;
+  p.gate = gate;
+  p.head_index = head_index;
+  p.Htot = Htot;
+  p.drop_p = drop_p;
+  p.seed = seed;
+  p.head_mask = head_mask;
+  return p;
+}
+
+extern "C" int dph_attn_fwd(const void* qkv, void* ctx, void* ctx_un, float* lse, int B, int H, int T, float scale,
+                            const int64_t* lengths, const int* rel_table, const float* emb, const float* gate,
+                            const int* head_index, int Htot, float drop_p, uint64_t seed, const float* head_mask,
+                            void* stream) {
+  int rc = attn_check(B, H, T, 0);
+  if (rc) return rc;
+  if (!qkv || !ctx) {
+    set_error("attn_fwd: null pointer");
+    return DPH_ERR_ARG;
+  }
+  const int inner = H * ATT_D;
+  CUtensorMap tm;
+  rc = make_tmap_2d(&tm, qkv, 3ull * inner, (uint64_t)B * T, 3ull * inner, ATT_D, ATT_BK);
+  if (rc) return rc;
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
+    if (e != cudaSuccess) {
+      set_error("attn_fwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+      return DPH_ERR_CUDA;
+    }
+    attr = true;
+  }
+  AttnParams p = attn_params(B, H, T, scale, lengths, rel_table, emb, gate, head_index, Htot, drop_p, seed, head_mask);
+  dim3 grid((T + ATT_BQ - 1) / ATT_BQ, H, B);
+  attn_fwd_kernel<<<grid, 128, FWD_SMEM, reinterpret_cast<cudaStream_t>(stream)>>>(tm, p, (bf16*)ctx, (bf16*)ctx_un, lse);
+  dph_count_launch();
+  return dph_check_last("attn_fwd");
+}
+
+// delta: (B, H, T) fp32 scratch; dq32: (B*T, H*64) fp32 accumulator that must be zero on entry (it is left zeroed).
+extern "C" int dph_attn_bwd(const void* qkv, const void* dctx, const void* o_un, const float* lse, float* delta,
+                            float* dq32, void* dqkv, float* dmask_h, int B, int H, int T, float scale,
+                            const int64_t* lengths, const int* rel_table, const float* emb, const float* gate,
+                            const int* head_index, int Htot, float drop_p, uint64_t seed, const float* head_mask,
+                            float* dgate, float* demb, int num_buckets, void* stream) {
+  int rc = attn_check(B, H, T, num_buckets);
+  if (rc) return rc;
+  if (!qkv || !dctx || !o_un || !lse || !delta || !dq32 || !dqkv) {
+    set_error("attn_bwd: null pointer");
+    return DPH_ERR_ARG;
+  }
+  const int inner = H * ATT_D;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  CUtensorMap tmq, tmd;
+  rc = make_tmap_2d(&tmq, qkv, 3ull * inner, (uint64_t)B * T, 3ull * inner, ATT_D, ATT_BK);
+  if (rc) return rc;
+  rc = make_tmap_2d(&tmd, dctx, (uint64_t)inner, (uint64_t)B * T, (uint64_t)inner, ATT_D, ATT_BQ);
+  if (rc) return rc;
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
+    if (e != cudaSuccess) {
+      set_error("attn_bwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+      return DPH_ERR_CUDA;
+    }
+    attr = true;
+  }
+  const long long M = (long long)B * T;
+  attn_bwd_prep_kernel<<<dim3((unsigned)((M + 63) / 64), H), 256, 0, s>>>((const bf16*)dctx, (const bf16*)o_un, delta,
+                                                                         dmask_h, B, H, T, inner);
+  AttnParams p = attn_params(B, H, T, scale, lengths, rel_table, emb, gate, head_index, Htot, drop_p, seed, head_mask);
+  dim3 grid((T + ATT_BK - 1) / ATT_BK, H, B);
+  attn_bwd_kernel<<<grid, 128, BWD_SMEM, s>>>(tmq, tmd, p, lse, delta, dq32, (bf16*)dqkv, dgate, demb, num_buckets);
+  long long n4 = M * inner / 4;
+  int cg = (int)((n4 + 255) / 256 < 148 * 8 ? (n4 + 255) / 256 : 148 * 8);
+  attn_dq_convert_kernel<<<cg, 256, 0, s>>>(dq32, (bf16*)dqkv, M, inner);
+  dph_count_launch(3);
+  return dph_check_last("attn_bwd");
+}

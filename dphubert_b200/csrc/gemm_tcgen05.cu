@@ -414,6 +414,32 @@ static int make_tmap(CUtensorMap* out, const dph_operand_t& op, int box_rows_kma
   return DPH_OK;
 }
 
+// 2-D bf16 tensor map (128B swizzle) over a row-major matrix: used by the fused attention kernels.
+int make_tmap_2d(CUtensorMap* out, const void* ptr, uint64_t cols, uint64_t rows, uint64_t row_stride_elems,
+                 uint32_t box_cols, uint32_t box_rows) {
+  PFN_encodeTiled enc = get_encode_fn();
+  if (!enc) {
+    set_error("cuTensorMapEncodeTiled unavailable");
+    return DPH_ERR_CUDA;
+  }
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0 || (row_stride_elems * 2) % 16 != 0) {
+    set_error("tensor map: pointer / row stride not 16-byte aligned");
+    return DPH_ERR_ARG;
+  }
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {row_stride_elems * 2};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled(2d) failed: %d", (int)r);
+    return DPH_ERR_CUDA;
+  }
+  return DPH_OK;
+}
+
 static int num_sms() {
   static int n = 0;
   if (n == 0) {

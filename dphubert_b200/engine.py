@@ -742,6 +742,11 @@ def _a8(n):
     return (n + 7) // 8 * 8
 
 
+# bf16 / head_dim 64: attention runs as the fused tcgen05 kernel (scores never reach HBM); set False to force the
+# unfused GEMM + softmax path (used by tests to cross-check the two)
+FUSED_ATTENTION = True
+
+
 def _mask_of(masks, hc):
     return masks.get(id(hc)) if hc is not None else None
 
@@ -789,10 +794,6 @@ def _attention_fwd(plan, att, xin, resid, B, T, lengths, masks, A, tag, train, p
     qkv = A(tag + "qkv", (M, 3 * inner), dt)
     G.gemm(G.mat(xin), G.mat(Wkvq), qkv, M, 3 * inner, D, bias=bkvq)
     s_t, s_b = 3 * inner, T * 3 * inner
-    S = A("att_S", (B, H, T, Tp), torch.float32)
-    q = View(qkv, T, Dh, s_t, sb0=Dh, sb1=s_b, offset=2 * inner)
-    k = View(qkv, T, Dh, s_t, sb0=Dh, sb1=s_b, offset=0)
-    G.gemm(q, k, S, T, T, Dh, nb0=H, nb1=B, ldc=Tp, c_sb0=T * Tp, c_sb1=H * T * Tp, alpha=att.scaling)
     wavlm = None
     if wl is not None:
         # gated relative position bias; the gate is a function of the attention input (components.py:636-644)
@@ -808,24 +809,35 @@ def _attention_fwd(plan, att, xin, resid, B, T, lengths, masks, A, tag, train, p
         rec.update(ga=ga, gb=gb, wavlm=wavlm)
     p_att = _p(att.dropout, train)
     seed_att = _seed(p_att)
-    P = A(tag + "P", (B, H, T, Tp), dt)
-    Pd = A(tag + "Pd", (B, H, T, Tp), dt) if p_att > 0 else None
-    ops.softmax_fwd(S, Tp, P, Pd, Tp, lengths, B, H, T, p_att, seed_att, wavlm)
     hmask = _mask_of(masks, att.hard_concrete_for_heads)
     lmask = _mask_of(masks, att.hard_concrete_for_layer)
     ctx = A(tag + "ctx", (M, inner), dt)
     ctx_un = A(tag + "ctx_un", (M, inner), dt) if hmask is not None else None
-    pv = View(Pd if Pd is not None else P, T, T, Tp, sb0=T * Tp, sb1=H * T * Tp)
-    v = View(qkv, Dh, T, 1, cs=s_t, sb0=Dh, sb1=s_b, offset=inner)
-    G.gemm(pv, v, ctx, T, Dh, T, nb0=H, nb1=B, ldc=inner, c_sb0=Dh, c_sb1=T * inner, scalar_mask=hmask,
-           scalar_sb0=1 if hmask is not None else 0, c2=ctx_un)
+    fused = FUSED_ATTENTION and dt == torch.bfloat16 and Dh == 64 and T <= 1024
+    P = Pd = lse = None
+    if fused:
+        # S and P never leave the SM: tcgen05 QK^T -> online softmax -> PV  (csrc/attention.cu)
+        lse = A(tag + "lse", (B, H, T), torch.float32)
+        ops.attn_fwd(qkv, ctx, ctx_un, lse, B, H, T, att.scaling, lengths, p_att, seed_att, wavlm, hmask)
+    else:
+        S = A("att_S", (B, H, T, Tp), torch.float32)
+        q = View(qkv, T, Dh, s_t, sb0=Dh, sb1=s_b, offset=2 * inner)
+        k = View(qkv, T, Dh, s_t, sb0=Dh, sb1=s_b, offset=0)
+        G.gemm(q, k, S, T, T, Dh, nb0=H, nb1=B, ldc=Tp, c_sb0=T * Tp, c_sb1=H * T * Tp, alpha=att.scaling)
+        P = A(tag + "P", (B, H, T, Tp), dt)
+        Pd = A(tag + "Pd", (B, H, T, Tp), dt) if p_att > 0 else None
+        ops.softmax_fwd(S, Tp, P, Pd, Tp, lengths, B, H, T, p_att, seed_att, wavlm)
+        pv = View(Pd if Pd is not None else P, T, T, Tp, sb0=T * Tp, sb1=H * T * Tp)
+        v = View(qkv, Dh, T, 1, cs=s_t, sb0=Dh, sb1=s_b, offset=inner)
+        G.gemm(pv, v, ctx, T, Dh, T, nb0=H, nb1=B, ldc=inner, c_sb0=Dh, c_sb1=T * inner, scalar_mask=hmask,
+               scalar_sb0=1 if hmask is not None else 0, c2=ctx_un)
     out = A(tag + "attn_out", (M, D), dt)
     pre = A(tag + "attn_pre", (M, D), dt) if lmask is not None else None
     seed_o = _seed(p_drop)
     G.gemm(G.mat(ctx), G.mat(plan.W(att.out_proj.weight, dt)), out, M, D, inner, bias=plan.view(att.out_proj.bias),
            scalar_mask=lmask, drop_p=p_drop, seed=seed_o, residual=resid, c2=pre)
     rec.update(qkv=qkv, P=P, Pd=Pd, ctx=ctx, ctx_un=ctx_un, pre=pre, hmask=hmask, lmask=lmask, p_att=p_att,
-               seed_att=seed_att, p_drop=p_drop, seed_o=seed_o)
+               seed_att=seed_att, p_drop=p_drop, seed_o=seed_o, lse=lse, lengths=lengths)
     return out, rec
 
 
@@ -1065,25 +1077,7 @@ def _attention_bwd(plan, rec, dout, dresid, B, T, dmasks, A, tag, wl):
     dctx = A(tag + "dctx", (M, inner), dt)
     G.gemm(G.mat(g), G.mat_t(plan.W(att.out_proj.weight, dt)), dctx, M, inner, D)
     _wgrad(plan, g, rec["ctx"], att.out_proj.weight, D, inner, M)
-    if rec["hmask"] is not None:
-        dctx2 = A(tag + "dctx2", (M, inner), dt)
-        ops.group_mask_bwd(dctx, rec["ctx_un"], rec["hmask"], dctx2, _gslot(plan, dmasks, att.hard_concrete_for_heads), M,
-                           inner, Dh)
-        dctx = dctx2
     qkv = rec["qkv"]
-    P, Pd = rec["P"], rec["Pd"] if rec["Pd"] is not None else rec["P"]
-    # dPd = dctx V^T
-    dP = A("att_dP", (B, H, T, Tp), torch.float32)
-    a = View(dctx, T, Dh, inner, sb0=Dh, sb1=T * inner)
-    vk = View(qkv, T, Dh, s_t, sb0=Dh, sb1=s_b, offset=inner)
-    G.gemm(a, vk, dP, T, T, Dh, nb0=H, nb1=B, ldc=Tp, c_sb0=T * Tp, c_sb1=H * T * Tp)
-    dqkv = A(tag + "dqkv", (M, 3 * inner), dt)
-    # dV = Pd^T dctx
-    a = View(Pd, T, T, 1, cs=Tp, sb0=T * Tp, sb1=H * T * Tp)
-    bv = View(dctx, Dh, T, 1, cs=inner, sb0=Dh, sb1=T * inner)
-    G.gemm(a, bv, dqkv, T, Dh, T, nb0=H, nb1=B, ldc=s_t, c_sb0=Dh, c_sb1=s_b, c_offset=inner)
-    # dS = softmax'(P) . dropout'(dPd)  (+ WavLM bias gradients)
-    dS = A("att_dS", (B, H, T, Tp), dt)
     wavlm = rec.get("wavlm")
     dgate = None
     demb = None
@@ -1095,14 +1089,40 @@ def _attention_bwd(plan, rec, dout, dresid, B, T, dmasks, A, tag, wl):
         if wavlm[2] is not None:
             dgate = A(tag + "dgate", (B, att.total_num_heads, T), torch.float32)
             ops.memset(dgate)
-    ops.softmax_bwd(P, dP, Tp, dS, Tp, B, H, T, rec["p_att"], rec["seed_att"], wavlm, dgate, demb, nbuckets)
-    # dQ = scaling * dS K ; dK = scaling * dS^T Q
-    a = View(dS, T, T, Tp, sb0=T * Tp, sb1=H * T * Tp)
-    bv = View(qkv, Dh, T, 1, cs=s_t, sb0=Dh, sb1=s_b, offset=0)
-    G.gemm(a, bv, dqkv, T, Dh, T, nb0=H, nb1=B, ldc=s_t, c_sb0=Dh, c_sb1=s_b, c_offset=2 * inner, alpha=att.scaling)
-    a = View(dS, T, T, 1, cs=Tp, sb0=T * Tp, sb1=H * T * Tp)
-    bv = View(qkv, Dh, T, 1, cs=s_t, sb0=Dh, sb1=s_b, offset=2 * inner)
-    G.gemm(a, bv, dqkv, T, Dh, T, nb0=H, nb1=B, ldc=s_t, c_sb0=Dh, c_sb1=s_b, c_offset=0, alpha=att.scaling)
+    dqkv = A(tag + "dqkv", (M, 3 * inner), dt)
+    if rec["lse"] is not None:
+        delta = A("att_delta", (B, H, T), torch.float32)
+        dq32 = A("att_dq32_%d" % inner, (M, inner), torch.float32, zero=True)
+        o_un = rec["ctx_un"] if rec["hmask"] is not None else rec["ctx"]
+        ops.attn_bwd(qkv, dctx, o_un, rec["lse"], delta, dq32, dqkv, _gslot(plan, dmasks, att.hard_concrete_for_heads)
+                     if rec["hmask"] is not None else None, B, H, T, att.scaling, rec["lengths"], rec["p_att"],
+                     rec["seed_att"], wavlm, rec["hmask"], dgate, demb, nbuckets)
+    else:
+        if rec["hmask"] is not None:
+            dctx2 = A(tag + "dctx2", (M, inner), dt)
+            ops.group_mask_bwd(dctx, rec["ctx_un"], rec["hmask"], dctx2,
+                               _gslot(plan, dmasks, att.hard_concrete_for_heads), M, inner, Dh)
+            dctx = dctx2
+        P, Pd = rec["P"], rec["Pd"] if rec["Pd"] is not None else rec["P"]
+        # dPd = dctx V^T
+        dP = A("att_dP", (B, H, T, Tp), torch.float32)
+        a = View(dctx, T, Dh, inner, sb0=Dh, sb1=T * inner)
+        vk = View(qkv, T, Dh, s_t, sb0=Dh, sb1=s_b, offset=inner)
+        G.gemm(a, vk, dP, T, T, Dh, nb0=H, nb1=B, ldc=Tp, c_sb0=T * Tp, c_sb1=H * T * Tp)
+        # dV = Pd^T dctx
+        a = View(Pd, T, T, 1, cs=Tp, sb0=T * Tp, sb1=H * T * Tp)
+        bv = View(dctx, Dh, T, 1, cs=inner, sb0=Dh, sb1=T * inner)
+        G.gemm(a, bv, dqkv, T, Dh, T, nb0=H, nb1=B, ldc=s_t, c_sb0=Dh, c_sb1=s_b, c_offset=inner)
+        # dS = softmax'(P) . dropout'(dPd)  (+ WavLM bias gradients)
+        dS = A("att_dS", (B, H, T, Tp), dt)
+        ops.softmax_bwd(P, dP, Tp, dS, Tp, B, H, T, rec["p_att"], rec["seed_att"], wavlm, dgate, demb, nbuckets)
+        # dQ = scaling * dS K ; dK = scaling * dS^T Q
+        a = View(dS, T, T, Tp, sb0=T * Tp, sb1=H * T * Tp)
+        bv = View(qkv, Dh, T, 1, cs=s_t, sb0=Dh, sb1=s_b, offset=0)
+        G.gemm(a, bv, dqkv, T, Dh, T, nb0=H, nb1=B, ldc=s_t, c_sb0=Dh, c_sb1=s_b, c_offset=2 * inner, alpha=att.scaling)
+        a = View(dS, T, T, 1, cs=Tp, sb0=T * Tp, sb1=H * T * Tp)
+        bv = View(qkv, Dh, T, 1, cs=s_t, sb0=Dh, sb1=s_b, offset=2 * inner)
+        G.gemm(a, bv, dqkv, T, Dh, T, nb0=H, nb1=B, ldc=s_t, c_sb0=Dh, c_sb1=s_b, c_offset=0, alpha=att.scaling)
     # projections
     kvq_w = [att.k_proj.weight, att.v_proj.weight, att.q_proj.weight]
     kvq_b = [att.k_proj.bias, att.v_proj.bias, att.q_proj.bias]

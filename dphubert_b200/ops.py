@@ -156,6 +156,27 @@ def wavlm_gate_bwd(x, Wg, cst, ga, gb, dgate, dx, dWg, dbg, dcst, B, T, Htot, Dh
                                   ptr(dcst), B, T, Htot, Dh, dtype_code(x), stream_ptr()), "dph_wavlm_gate_bwd")
 
 
+def attn_fwd(qkv, ctx, ctx_un, lse, B, H, T, scale, lengths=None, drop_p=0.0, seed=0, wavlm=None, head_mask=None):
+    """Fused attention forward (head_dim 64, bf16): qkv (B*T, 3*H*64) laid out [k | v | q] -> ctx (B*T, H*64)."""
+    rt = emb = gate = hidx = None
+    htot = H
+    if wavlm is not None:
+        rt, emb, gate, hidx, htot = wavlm
+    check(_L().dph_attn_fwd(ptr(qkv), ptr(ctx), ptr(ctx_un), ptr(lse), B, H, T, scale, ptr(lengths), ptr(rt), ptr(emb),
+                            ptr(gate), ptr(hidx), htot, drop_p, seed, ptr(head_mask), stream_ptr()), "dph_attn_fwd")
+
+
+def attn_bwd(qkv, dctx, o_un, lse, delta, dq32, dqkv, dmask_h, B, H, T, scale, lengths=None, drop_p=0.0, seed=0,
+             wavlm=None, head_mask=None, dgate=None, demb=None, num_buckets=0):
+    rt = emb = gate = hidx = None
+    htot = H
+    if wavlm is not None:
+        rt, emb, gate, hidx, htot = wavlm
+    check(_L().dph_attn_bwd(ptr(qkv), ptr(dctx), ptr(o_un), ptr(lse), ptr(delta), ptr(dq32), ptr(dqkv), ptr(dmask_h), B, H,
+                            T, scale, ptr(lengths), ptr(rt), ptr(emb), ptr(gate), ptr(hidx), htot, drop_p, seed,
+                            ptr(head_mask), ptr(dgate), ptr(demb), num_buckets, stream_ptr()), "dph_attn_bwd")
+
+
 # ----------------------------------------------------------------------------------------------------------------
 # distillation loss
 # ----------------------------------------------------------------------------------------------------------------

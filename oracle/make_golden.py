@@ -57,7 +57,7 @@ def import_reference():
 def small_cfg(kind):
     """Scaled-down configs with the exact structure of the canonical ones (convert_hubert_from_hf.py:18-44,
     convert_hubert_large_from_fairseq.py:20-46, convert_wavlm_from_hf.py:19-47)."""
-    L, D, H, Dh, Fi, C = 3, 128, 4, 32, 256, 64
+    L, D, H, Dh, Fi, C = 2, 192, 3, 64, 128, 64  # head_dim 64 so the bf16 runs take the fused attention kernel
     conv = [(C, 10, 5)] + [(C, 3, 2)] * 4 + [(C, 2, 2)] * 2
     cfg = dict(
         extractor_mode="group_norm", extractor_conv_layer_config=conv, extractor_conv_bias=False,
@@ -272,7 +272,7 @@ def case_prune(wav2vec2_model, kind, seed, units=("conv", "head", "interm", "att
         for n, p in model.named_parameters():
             if "log_alpha" in n:
                 if p.numel() == 1:  # whole-layer gates: close one attention layer and one FFN layer
-                    closed = (".layers.1.attention." in n) or (".layers.2.feed_forward." in n)
+                    closed = (".layers.1.attention." in n) or (".layers.0.feed_forward." in n)
                     p.fill_(-6.0 if closed else 4.0)
                 else:
                     p.copy_(torch.randn(p.shape, generator=g) * 3.0 + 0.5)

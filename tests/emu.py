@@ -403,6 +403,69 @@ def wavlm_gate_bwd(x, Wg, cst, ga, gb, dgate, dx, dWg, dbg, dcst, B, T, Htot, Dh
         dxv += torch.einsum("btho,od->bthd", dp, Wg).to(dx.dtype)
 
 
+def _attn_core(qkv, B, H, T, scale, lengths, wavlm):
+    Dh = 64
+    inner = H * Dh
+    x = qkv.reshape(B, T, 3, H, Dh).float()
+    k, v, q = x[:, :, 0].permute(0, 2, 1, 3), x[:, :, 1].permute(0, 2, 1, 3), x[:, :, 2].permute(0, 2, 1, 3)
+    s = scale * q @ k.transpose(-1, -2)
+    if wavlm is not None:
+        s = s + _bias_term(wavlm, B, H, T)[0]
+    if lengths is not None:
+        pad = torch.arange(T).view(1, -1) >= lengths.view(-1, 1)
+        s = s + (-10000.0) * pad.view(B, 1, 1, T).float()
+    return q, k, v, s
+
+
+def attn_fwd(qkv, ctx, ctx_un, lse, B, H, T, scale, lengths=None, drop_p=0.0, seed=0, wavlm=None, head_mask=None):
+    assert drop_p == 0.0 and qkv.dtype == torch.bfloat16
+    q, k, v, s = _attn_core(qkv, B, H, T, scale, lengths, wavlm)
+    p = torch.softmax(s, -1)
+    o = (p @ v).permute(0, 2, 1, 3).reshape(B * T, H * 64)
+    if lse is not None:
+        lse.view(B, H, T).copy_(torch.logsumexp(s, -1))
+    if ctx_un is not None:
+        ctx_un.view(B * T, -1).copy_(o)
+    if head_mask is not None:
+        o = o * head_mask.repeat_interleave(64)
+    ctx.view(B * T, -1).copy_(o)
+
+
+def attn_bwd(qkv, dctx, o_un, lse, delta, dq32, dqkv, dmask_h, B, H, T, scale, lengths=None, drop_p=0.0, seed=0,
+             wavlm=None, head_mask=None, dgate=None, demb=None, num_buckets=0):
+    assert drop_p == 0.0
+    q, k, v, s = _attn_core(qkv, B, H, T, scale, lengths, wavlm)
+    p = torch.softmax(s, -1)
+    d = dctx.reshape(B, T, H, 64).float().permute(0, 2, 1, 3)  # gradient wrt the masked context
+    ou = o_un.reshape(B, T, H, 64).float().permute(0, 2, 1, 3)
+    dl = (d * ou).sum(-1)  # (B, H, T)
+    delta.view(B, H, T).copy_(dl)
+    if dmask_h is not None:
+        dmask_h += dl.sum((0, 2))
+    hm = head_mask.view(1, H, 1, 1) if head_mask is not None else 1.0
+    do = d * hm
+    dv = p.transpose(-1, -2) @ do
+    dp = do @ v.transpose(-1, -2)
+    ds = p * (dp - (dp * p).sum(-1, keepdim=True))
+    dq = scale * ds @ k
+    dk = scale * ds.transpose(-1, -2) @ q
+    out = dqkv.view(B, T, 3, H, 64)
+    out[:, :, 0] = dk.permute(0, 2, 1, 3).to(dqkv.dtype)
+    out[:, :, 1] = dv.permute(0, 2, 1, 3).to(dqkv.dtype)
+    out[:, :, 2] = dq.permute(0, 2, 1, 3).to(dqkv.dtype)
+    if wavlm is not None:
+        rt, emb, gate, hidx, htot = wavlm
+        _, bucket, heads = _bias_term(wavlm, B, H, T)
+        embv = emb[bucket][:, :, heads].permute(2, 0, 1)
+        if dgate is not None:
+            dgate.view(B, htot, T)[:, heads] += (ds * embv.unsqueeze(0)).sum(-1)
+        if demb is not None:
+            g = gate.view(B, htot, T)[:, heads].unsqueeze(-1) if gate is not None else 1.0
+            contrib = (ds * g).sum(0)
+            for hi, ht in enumerate(heads.tolist()):
+                demb[:, ht].index_add_(0, bucket.reshape(-1), contrib[hi].reshape(-1))
+
+
 # ------------------------------------------------------------------------------------------------ loss
 def distill_loss_fwd(a, b, rowstat, acc, out, rows, D, w2, w1, wc, cos_type, first, last, total_rows):
     x, y = a.reshape(rows, D).float(), b.reshape(rows, D).float()
@@ -617,7 +680,7 @@ def rng_advance():
 
 _NAMES = ["memset", "memset2d", "zeros", "cast", "vec_mul", "transpose", "axpy", "group_mask_bwd", "wave_norm",
           "layernorm_fwd", "layernorm_bwd", "epilogue_bwd", "pad_rows_zero", "posconv_pad", "conv0_stats", "conv0_fwd",
-          "conv0_bwd", "softmax_fwd", "softmax_bwd", "wavlm_gate_fwd", "wavlm_gate_bwd", "distill_loss_fwd",
+          "conv0_bwd", "softmax_fwd", "softmax_bwd", "attn_fwd", "attn_bwd", "wavlm_gate_fwd", "wavlm_gate_bwd", "distill_loss_fwd",
           "distill_loss_bwd", "conv_weight_prep", "conv_wgrad_unpermute", "posconv_weight_prep", "posconv_weight_bwd",
           "sumsq", "counter_inc", "adamw", "scale_", "hardconcrete_fwd", "hardconcrete_bwd", "l0_norms", "num_params",
           "lagrangian", "l0_norms_bwd", "rng_set", "rng_advance"]

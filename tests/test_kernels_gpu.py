@@ -277,3 +277,61 @@ def test_weight_prep():
     scratch = zer(K)
     both("posconv_weight_bwd", (rnd(Gn, Cgp, K, Cgp), v, g, norm, scratch, zer(D, Cg, K), zer(1, 1, K), D, Gn, Cg, Cgp, Cgp,
                                 K), tol=2e-4, ignore=(scratch,))
+
+
+# ---------------------------------------------------------------------------------------------- fused attention
+@pytest.mark.parametrize("T", [64, 199, 499])
+@pytest.mark.parametrize("masked", [False, True])
+def test_fused_attention(T, masked):
+    Bn, H = 2, 3
+    inner = H * 64
+    qkv = rnd(Bn * T, 3 * inner, dtype=BF16)
+    lengths = torch.tensor([T, max(T - 37, 1)], device=DEV) if masked else None
+    hmask = torch.rand(H, device=DEV) if masked else None
+    ctx, ctx_un, lse = zer(Bn * T, inner, dtype=BF16), zer(Bn * T, inner, dtype=BF16), zer(Bn, H, T)
+    both("attn_fwd", (qkv, ctx, ctx_un if masked else None, lse, Bn, H, T, 0.125),
+         dict(lengths=lengths, head_mask=hmask), tol=2e-2)
+    dctx = rnd(Bn * T, inner, dtype=BF16)
+    o_un = ctx_un if masked else ctx
+    delta, dq32 = zer(Bn, H, T), zer(Bn * T, inner)
+    dqkv = zer(Bn * T, 3 * inner, dtype=BF16)
+    both("attn_bwd", (qkv, dctx, o_un, lse, delta, dq32, dqkv, zer(H) if masked else None, Bn, H, T, 0.125),
+         dict(lengths=lengths, head_mask=hmask), tol=3e-2, ignore=(dq32,))
+    assert float(dq32.abs().max()) == 0.0  # the fp32 dQ accumulator is handed back cleared
+
+
+def test_fused_attention_wavlm():
+    Bn, Htot, T, nb = 2, 4, 150, 32
+    heads = [0, 2, 3]
+    H = len(heads)
+    inner = H * 64
+    qkv = rnd(Bn * T, 3 * inner, dtype=BF16)
+    gate = torch.rand(Bn, Htot, T, device=DEV) + 0.5
+    rt = torch.randint(0, nb, (2 * T - 1,), device=DEV, dtype=torch.int32)
+    emb = rnd(nb, Htot)
+    wl = (rt, emb, gate, torch.tensor(heads, device=DEV, dtype=torch.int32), Htot)
+    ctx, lse = zer(Bn * T, inner, dtype=BF16), zer(Bn, H, T)
+    both("attn_fwd", (qkv, ctx, None, lse, Bn, H, T, 0.125), dict(wavlm=wl), tol=2e-2)
+    dq32 = zer(Bn * T, inner)
+    both("attn_bwd", (qkv, rnd(Bn * T, inner, dtype=BF16), ctx, lse, zer(Bn, H, T), dq32, zer(Bn * T, 3 * inner, dtype=BF16),
+                      None, Bn, H, T, 0.125), dict(wavlm=wl, dgate=zer(Bn, Htot, T), demb=zer(nb, Htot), num_buckets=nb),
+         tol=3e-2, ignore=(dq32,))
+
+
+def test_fused_attention_dropout_matches_unfused_mask():
+    """same counter-based keep mask as the unfused softmax kernel: fused O == (dropout(P) V) of the unfused path"""
+    Bn, H, T = 1, 2, 130
+    inner = H * 64
+    qkv = rnd(Bn * T, 3 * inner, dtype=BF16)
+    ctx = zer(Bn * T, inner, dtype=BF16)
+    ops.attn_fwd(qkv, ctx, None, None, Bn, H, T, 0.125, drop_p=0.2, seed=99)
+    x = qkv.view(Bn, T, 3, H, 64).float()
+    k, v, q = x[:, :, 0].permute(0, 2, 1, 3), x[:, :, 1].permute(0, 2, 1, 3), x[:, :, 2].permute(0, 2, 1, 3)
+    Tp = (T + 7) // 8 * 8
+    S = torch.zeros(Bn, H, T, Tp, device=DEV)
+    S[..., :T] = 0.125 * q @ k.transpose(-1, -2)
+    P, Pd = zer(Bn, H, T, Tp), zer(Bn, H, T, Tp)
+    ops.softmax_fwd(S, Tp, P, Pd, Tp, None, Bn, H, T, 0.2, 99)
+    ref = (Pd[..., :T] @ v).permute(0, 2, 1, 3).reshape(Bn * T, inner)
+    err = (ctx.float() - ref).abs().max().item() / ref.abs().max().item()
+    assert err < 2e-2, err
