@@ -13,15 +13,20 @@
 namespace dph {
 void set_error(const char* fmt, ...);
 
+// Thread block = 32 column groups (VEC columns each) x 8 row lanes; a block owns a strip of 32*VEC columns and a
+// contiguous chunk of rows.  Column partial sums are reduced across the 8 row lanes in shared memory and leave the
+// block as ONE line-wide RED per column (same-address float atomics serialise in L2: keep them few and coalesced).
 template <typename T, int VEC>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(256)
     epilogue_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ z, const float* __restrict__ colmask,
                         const float* __restrict__ scalar, T* __restrict__ dout, float* __restrict__ dmask,
                         float* __restrict__ dbias, float* __restrict__ dscalar, int rows, int C, int rows_per_blk,
                         int act, float drop_p, unsigned long long seed, int rows_per_batch, long long out_bs,
                         int out_row_off, long long in_ld, long long z_ld) {
-  __shared__ float red[32];
-  const int c0 = (blockIdx.x * blockDim.x + threadIdx.x) * VEC;
+  __shared__ float red[2][8][32 * VEC + 1];
+  __shared__ float red_s[32];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c0 = (blockIdx.x * 32 + tx) * VEC;
   const int r0 = blockIdx.y * rows_per_blk;
   const int r1 = min(rows, r0 + rows_per_blk);
   const bool active = c0 < C;
@@ -38,7 +43,8 @@ __global__ void __launch_bounds__(128)
   const float inv_keep = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
   const bool need_z = (z != nullptr);
   if (active) {
-    for (int r = r0; r < r1; ++r) {
+#pragma unroll 2
+    for (int r = r0 + ty; r < r1; r += 8) {
       float d[VEC], zz[VEC];
       const long long ioff = (long long)r * in_ld + c0;
       if constexpr (VEC > 1) {
@@ -71,16 +77,30 @@ __global__ void __launch_bounds__(128)
         }
       }
     }
+  }
+  if (dmask || dbias) {
 #pragma unroll
     for (int j = 0; j < VEC; ++j) {
-      if (c0 + j < C) {
-        if (dmask) atomicAdd(dmask + c0 + j, a_mask[j]);
-        if (dbias) atomicAdd(dbias + c0 + j, a_bias[j]);
+      red[0][ty][tx * VEC + j] = a_mask[j];
+      red[1][ty][tx * VEC + j] = a_bias[j];
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < 32 * VEC; c += 256) {
+      const int col = blockIdx.x * 32 * VEC + c;
+      if (col < C) {
+        float m = 0.f, bsum = 0.f;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          m += red[0][q][c];
+          bsum += red[1][q][c];
+        }
+        if (dmask) atomicAdd(dmask + col, m);
+        if (dbias) atomicAdd(dbias + col, bsum);
       }
     }
   }
   if (dscalar) {
-    float tot = block_sum(a_scalar, red);
+    float tot = block_sum(a_scalar, red_s);
     if (threadIdx.x == 0) atomicAdd(dscalar, tot);
   }
 }
@@ -249,15 +269,18 @@ extern "C" int dph_epilogue_bwd(const void* dy, const void* z, const float* colm
   const bool vec_ok = (C % vecw == 0) && (in_ld % vecw == 0) && (z_ld % vecw == 0) && al(dy) && al(z) && al(dout) &&
                       (out_bs % vecw == 0);
   const int VECW = vec_ok ? vecw : 1;
-  const int cols_per_blk = 128 * VECW;
+  const int cols_per_blk = 32 * VECW;
   const int gx = (C + cols_per_blk - 1) / cols_per_blk;
-  int target_y = (148 * 8 + gx - 1) / gx;
-  int rows_per_blk = (rows + target_y - 1) / target_y;
-  if (rows_per_blk < 8) rows_per_blk = 8;
-  const int gy = (rows + rows_per_blk - 1) / rows_per_blk;
+  int gy = (148 * 3 + gx - 1) / gx;          // ~3 CTAs of 256 threads per SM
+  const int max_gy = (rows + 15) / 16;       // at least 16 rows per CTA
+  if (gy > max_gy) gy = max_gy;
+  if (gy < 1) gy = 1;
+  if (gy > 65535) gy = 65535;
+  const int rows_per_blk = (rows + gy - 1) / gy;
+  gy = (rows + rows_per_blk - 1) / rows_per_blk;
   dim3 grid(gx, gy);
 #define EB_LAUNCH(T, V)                                                                                             \
-  epilogue_bwd_kernel<T, V><<<grid, 128, 0, s>>>((const T*)dy, (const T*)z, colmask, scalar, (T*)dout, dmask, dbias, \
+  epilogue_bwd_kernel<T, V><<<grid, 256, 0, s>>>((const T*)dy, (const T*)z, colmask, scalar, (T*)dout, dmask, dbias, \
                                                  dscalar, rows, C, rows_per_blk, act, drop_p, seed, rows_per_batch,  \
                                                  out_bs, out_row_off, in_ld, z_ld)
   if (dtype == DPH_DTYPE_BF16) {

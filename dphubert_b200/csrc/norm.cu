@@ -8,6 +8,7 @@
 // dropout after the norm (components.py:891), second upstream gradient added in the backward (hidden states that
 // feed both the next layer and a distillation head).
 #include "common.cuh"
+#include "vec.cuh"
 #include "../../include/dphubert_b200.h"
 
 namespace dph {
@@ -151,6 +152,144 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// Vectorised variants for the hot shapes (D a multiple of 32 * VEC, plain LayerNorm with optional dropout):
+// 128-bit accesses, one warp per row, persistent grid; the backward reduces dw / db across the warps of a CTA in
+// shared memory (no shared-memory atomics) and issues one coalesced RED per column per CTA.
+// ---------------------------------------------------------------------------------------------------------------
+template <typename T, int Q>
+__global__ void __launch_bounds__(256)
+    layernorm_fwd_vec_kernel(const T* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
+                             T* __restrict__ y, float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows,
+                             int D, float eps, float drop_p, unsigned long long seed) {
+  constexpr int VEC = VecOf<T>::N;
+  const int lane = threadIdx.x & 31;
+  const int warps_per_blk = blockDim.x >> 5;
+  const uint32_t thresh = (uint32_t)(drop_p * 4294967296.0);
+  const float inv_keep = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+  for (int row = blockIdx.x * warps_per_blk + (threadIdx.x >> 5); row < rows; row += gridDim.x * warps_per_blk) {
+    const T* xr = x + (long long)row * D;
+    float v[Q][VEC];
+    float s = 0.f;
+#pragma unroll
+    for (int q = 0; q < Q; ++q) {
+      load_vec(xr + (lane + 32 * q) * VEC, v[q]);
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) s += v[q][j];
+    }
+    const float mean = warp_sum(s) / D;
+    float qs = 0.f;
+#pragma unroll
+    for (int q = 0; q < Q; ++q)
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) {
+        const float d = v[q][j] - mean;
+        qs += d * d;
+      }
+    const float rstd = rsqrtf(warp_sum(qs) / D + eps);
+    if (lane == 0) {
+      if (mean_out) mean_out[row] = mean;
+      if (rstd_out) rstd_out[row] = rstd;
+    }
+    T* yr = y + (long long)row * D;
+#pragma unroll
+    for (int q = 0; q < Q; ++q) {
+      const int c0 = (lane + 32 * q) * VEC;
+      float wv[VEC], bv[VEC], o[VEC];
+      load_vec_f32(w + c0, wv);
+      load_vec_f32(b + c0, bv);
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) {
+        o[j] = (v[q][j] - mean) * rstd * wv[j] + bv[j];
+        if (drop_p > 0.f) o[j] *= dropout_scale(seed, (unsigned long long)row * D + c0 + j, thresh, inv_keep);
+      }
+      store_vec(yr + c0, o);
+    }
+  }
+}
+
+constexpr int LNB_WARPS = 16;
+
+template <typename T, int Q>
+__global__ void __launch_bounds__(LNB_WARPS * 32, 1)
+    layernorm_bwd_vec_kernel(const T* __restrict__ dy, const T* __restrict__ dy2, const T* __restrict__ x,
+                             const float* __restrict__ w, const float* __restrict__ mean_in,
+                             const float* __restrict__ rstd_in, T* __restrict__ dx, float* __restrict__ dw,
+                             float* __restrict__ db, int rows, int D, float drop_p, unsigned long long seed) {
+  constexpr int VEC = VecOf<T>::N;
+  extern __shared__ float sh[];  // [LNB_WARPS][D]
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const uint32_t thresh = (uint32_t)(drop_p * 4294967296.0);
+  const float inv_keep = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+  float a_dw[Q][VEC], a_db[Q][VEC], wv[Q][VEC];
+#pragma unroll
+  for (int q = 0; q < Q; ++q) {
+    load_vec_f32(w + (lane + 32 * q) * VEC, wv[q]);
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) a_dw[q][j] = a_db[q][j] = 0.f;
+  }
+  for (int row = blockIdx.x * LNB_WARPS + wid; row < rows; row += gridDim.x * LNB_WARPS) {
+    const long long off = (long long)row * D;
+    const float mean = mean_in[row], rstd = rstd_in[row];
+    float g[Q][VEC], xh[Q][VEC];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int q = 0; q < Q; ++q) {
+      const int c0 = (lane + 32 * q) * VEC;
+      load_vec(dy + off + c0, g[q]);
+      load_vec(x + off + c0, xh[q]);
+      if (dy2) {
+        float t[VEC];
+        load_vec(dy2 + off + c0, t);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) g[q][j] += t[j];
+      }
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) {
+        float d = g[q][j];
+        if (drop_p > 0.f) d *= dropout_scale(seed, (unsigned long long)off + c0 + j, thresh, inv_keep);
+        const float xhat = (xh[q][j] - mean) * rstd;
+        a_dw[q][j] += d * xhat;
+        a_db[q][j] += d;
+        const float gg = d * wv[q][j];
+        g[q][j] = gg;
+        xh[q][j] = xhat;
+        s1 += gg;
+        s2 += gg * xhat;
+      }
+    }
+    s1 = warp_sum(s1) / D;
+    s2 = warp_sum(s2) / D;
+#pragma unroll
+    for (int q = 0; q < Q; ++q) {
+      float o[VEC];
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) o[j] = rstd * (g[q][j] - s1 - xh[q][j] * s2);
+      store_vec(dx + off + (lane + 32 * q) * VEC, o);
+    }
+  }
+  // cross-warp reduction of the parameter gradients, one quantity at a time through [warps][D] shared memory
+#pragma unroll
+  for (int which = 0; which < 2; ++which) {
+    float* outp = which == 0 ? dw : db;
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < Q; ++q)
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) sh[wid * D + (lane + 32 * q) * VEC + j] = which == 0 ? a_dw[q][j] : a_db[q][j];
+    __syncthreads();
+    if (outp) {
+      for (int c = threadIdx.x; c < D; c += blockDim.x) {
+        float t = 0.f;
+#pragma unroll
+        for (int q = 0; q < LNB_WARPS; ++q) t += sh[q * D + c];
+        atomicAdd(outp + c, t);
+      }
+    }
+  }
+}
+
 }  // namespace dph
 
 using namespace dph;
@@ -164,6 +303,27 @@ extern "C" int dph_layernorm_fwd(const void* x, const float* w, const float* b, 
   }
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   const int warps_per_blk = 8;
+  {
+    // vectorised fast path
+    const int vec = dtype == DPH_DTYPE_BF16 ? 8 : 4;
+    const bool al = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(w) |
+                      reinterpret_cast<uintptr_t>(b)) & 15) == 0;
+    const int q = D / (32 * vec);
+    if (al && !y_pre && !colmask && act == 0 && D % (32 * vec) == 0 && q >= 1 && q <= 4) {
+      int g = (rows + warps_per_blk - 1) / warps_per_blk;
+      if (g > 148 * 8) g = 148 * 8;
+#define LN_FV(T, Q)                                                                                                  \
+  layernorm_fwd_vec_kernel<T, Q><<<g, 256, 0, s>>>((const T*)x, w, b, (T*)y, mean, rstd, rows, D, eps, drop_p, seed)
+      if (dtype == DPH_DTYPE_BF16) {
+        if (q == 1) LN_FV(bf16, 1); else if (q == 2) LN_FV(bf16, 2); else if (q == 3) LN_FV(bf16, 3); else LN_FV(bf16, 4);
+      } else {
+        if (q == 1) LN_FV(float, 1); else if (q == 2) LN_FV(float, 2); else if (q == 3) LN_FV(float, 3); else LN_FV(float, 4);
+      }
+#undef LN_FV
+      dph_count_launch();
+      return dph_check_last("layernorm_fwd_vec");
+    }
+  }
   const int grid = (rows + warps_per_blk - 1) / warps_per_blk;
 #define LN_FWD(NPL)                                                                                              \
   do {                                                                                                           \
@@ -199,6 +359,38 @@ extern "C" int dph_layernorm_bwd(const void* dy, const void* dy2, const void* x,
   }
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   const int warps_per_blk = 8;
+  {
+    const int vec = dtype == DPH_DTYPE_BF16 ? 8 : 4;
+    const bool al = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(dx) |
+                      reinterpret_cast<uintptr_t>(dy2) | reinterpret_cast<uintptr_t>(w)) & 15) == 0;
+    const int q = D / (32 * vec);
+    const bool fp32_ok = dtype == DPH_DTYPE_BF16 || q <= 4;
+    if (al && !colmask && !dmask && act == 0 && rows_per_batch == rows && out_row_off == 0 && D % (32 * vec) == 0 &&
+        q >= 1 && q <= (dtype == DPH_DTYPE_BF16 ? 4 : 8) && fp32_ok) {
+      int g = (rows + LNB_WARPS - 1) / LNB_WARPS;
+      if (g > 148) g = 148;
+      const size_t smem = (size_t)LNB_WARPS * D * sizeof(float);
+#define LN_BV(T, Q)                                                                                                   \
+  do {                                                                                                                \
+    static bool attr = false;                                                                                         \
+    if (!attr) {                                                                                                      \
+      cudaFuncSetAttribute(layernorm_bwd_vec_kernel<T, Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);   \
+      attr = true;                                                                                                    \
+    }                                                                                                                 \
+    layernorm_bwd_vec_kernel<T, Q><<<g, LNB_WARPS * 32, smem, s>>>((const T*)dy, (const T*)dy2, (const T*)x, w, mean, \
+                                                                   rstd, (T*)dx, dw, db, rows, D, drop_p, seed);      \
+  } while (0)
+      if (dtype == DPH_DTYPE_BF16) {
+        if (q == 1) LN_BV(bf16, 1); else if (q == 2) LN_BV(bf16, 2); else if (q == 3) LN_BV(bf16, 3); else LN_BV(bf16, 4);
+      } else {
+        if (q == 1) LN_BV(float, 1); else if (q == 2) LN_BV(float, 2); else if (q == 3) LN_BV(float, 3);
+        else if (q == 4) LN_BV(float, 4); else if (q == 6) LN_BV(float, 6); else LN_BV(float, 8);
+      }
+#undef LN_BV
+      dph_count_launch();
+      return dph_check_last("layernorm_bwd_vec");
+    }
+  }
   // ~4 CTAs per SM worth of work; each warp walks rows_per_warp consecutive rows
   int target_warps = 148 * 4 * warps_per_blk;
   int rows_per_warp = (rows + target_warps - 1) / target_warps;
