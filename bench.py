@@ -40,6 +40,7 @@ def parse():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--gemm-table", default="", help="write a per-shape timing table of the step's tensor-core GEMMs here")
     ap.add_argument("--profile-step", action="store_true",
                     help="run two eager steps, then ONE eager step between cudaProfilerStart/Stop and exit "
                          "(for `ncu --profile-from-start off`); prints no bench line")
@@ -242,6 +243,9 @@ def run_ours(args, rank, world, local_rank):
         torch.cuda.synchronize()
         torch.cuda.profiler.stop()
         return
+    if args.gemm_table:
+        gemm_table(step, wave, lengths, G, args.gemm_table)
+        return
     n_before = _lib.launch_count()
     if args.no_graph:
         step.run_step(wave, lengths)
@@ -313,6 +317,52 @@ def run_ours(args, rank, world, local_rank):
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def gemm_table(step, wave, lengths, G, path):
+    """Group the tensor-core GEMM launches of one step by shape / operand majors / epilogue and time each group
+    (every member launched back to back, 5 repetitions, CUDA events)."""
+    G.TRACE = []
+    step._push_scalars()
+    step._body(wave, lengths)
+    trace, G.TRACE = G.TRACE, None
+    step.zero_grad()
+    torch.cuda.synchronize()
+    groups = {}
+    for d, f in trace:
+        key = (d.M, d.N, d.K, d.nb0 * d.nb1, int(d.a.major_mn), int(d.b.major_mn), d.act, int(bool(d.c2)), d.c_mode,
+               d.c_dtype, int(bool(d.residual)), int(d.drop_p > 0))
+        groups.setdefault(key, []).append((d, f))
+    rows = []
+    st = torch.cuda.Stream()
+    for key, members in groups.items():
+        # capture the group's launches in a CUDA graph so that host launch gaps do not count
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(st):
+            G.replay(members)
+            st.synchronize()
+            with torch.cuda.graph(g, stream=st):
+                G.replay(members)
+        torch.cuda.synchronize()
+        g.replay()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(5):
+            g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / 5
+        fl = sum(f for _, f in members)
+        rows.append((ms, len(members), fl, key))
+    step.zero_grad()
+    rows.sort(reverse=True)
+    with open(path, "w") as f:
+        f.write("# ms/step  launches  us/launch  TFLOP/s   M N K batch a_mn b_mn act c2 c_mode c_dtype residual dropout\n")
+        for ms, n, fl, key in rows:
+            f.write("%8.3f %5d %9.1f %8.1f   %s\n" % (ms, n, ms * 1e3 / n, fl / ms / 1e9, " ".join(str(k) for k in key)))
+        f.write("# total %.3f ms, %d launches, %.1f TFLOP/s\n" % (sum(r[0] for r in rows), len(trace),
+                                                                sum(r[2] for r in rows) / sum(r[0] for r in rows) / 1e9))
 
 
 def roofline(step, wave, lengths, G, dev):

@@ -61,6 +61,7 @@ class GemmDesc(ctypes.Structure):
         ("seed", ctypes.c_uint64),
         ("vec_sb0", ctypes.c_int64),
         ("scalar_sb0", ctypes.c_int64),
+        ("cta_group", ctypes.c_int),
     ]
 
 

@@ -40,6 +40,21 @@ DPH_DEVICE float gelu_erf_grad(float x) {
   float pdf = kInvSqrt2Pi * __expf(-0.5f * x * x);
   return cdf + x * pdf;
 }
+// Branch-free erf-GELU for the tensor-core GEMM epilogue (bf16 outputs): Abramowitz-Stegun 7.1.26 (|erf error| <=
+// 1.5e-7) evaluated so that the negative tail has no cancellation: with z = |x|/sqrt(2), t = 1/(1 + p z) and
+// q = poly(t) exp(-z^2) = 1 - erf(z):  gelu(x) = x >= 0 ? x - 0.5 x q : 0.5 x q.
+DPH_DEVICE float gelu_erf_fast(float x) {
+  const float z = fabsf(x) * 0.70710678118654752440f;
+  const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
+  float poly = fmaf(1.061405429f, t, -1.453152027f);
+  poly = fmaf(poly, t, 1.421413741f);
+  poly = fmaf(poly, t, -0.284496736f);
+  poly = fmaf(poly, t, 0.254829592f);
+  poly *= t;
+  const float e = exp2f(-1.4426950408889634f * z * z);
+  const float u = 0.5f * x * poly * e;
+  return x >= 0.0f ? x - u : u;
+}
 DPH_DEVICE float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
 
 DPH_DEVICE float warp_sum(float v) {
@@ -89,6 +104,12 @@ template <typename T> DPH_DEVICE T from_f(float v);
 template <> DPH_DEVICE float from_f<float>(float v) { return v; }
 template <> DPH_DEVICE bf16 from_f<bf16>(float v) { return __float2bfloat16_rn(v); }
 
+// 16-byte vector reduction (sm_90+): one L2 atomic transaction for four consecutive fp32 (16-byte aligned).
+DPH_DEVICE void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
+               : "memory");
+}
+
 DPH_DEVICE uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
@@ -123,6 +144,26 @@ DPH_DEVICE void mbar_wait(uint32_t bar, uint32_t parity) {
       : "memory");
 }
 
+// ---- thread-block cluster helpers (CTA pairs for tcgen05 cta_group::2) ----
+DPH_DEVICE uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+DPH_DEVICE void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cluster address of the same shared-memory offset in CTA `rank` of this cluster
+DPH_DEVICE uint32_t mapa_shared(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+DPH_DEVICE void mbar_arrive_cluster(uint32_t cluster_addr) {
+  // default semantics (release at CTA scope): a cluster-scope release would drain every outstanding global store
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+
 DPH_DEVICE bool elect_one() {
   uint32_t pred = 0;
   asm volatile(
@@ -150,9 +191,61 @@ DPH_DEVICE void tma_load_5d(uint32_t smem_dst, const CUtensorMap* m, uint32_t ba
       : "memory");
 }
 
+// CTA-pair variant: the data lands in this CTA's shared memory, the transaction bytes complete on `bar_cluster`
+// (a shared::cluster address, normally the leader CTA's barrier).
+DPH_DEVICE void tma_load_5d_2sm(uint32_t smem_dst, const CUtensorMap* m, uint32_t bar_cluster, int c0, int c1, int c2,
+                                int c3, int c4) {
+  asm volatile(
+      "cp.async.bulk.tensor.5d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6, %7}], [%2];" ::"r"(smem_dst),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(bar_cluster), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+      : "memory");
+}
+
 // ---------------------------------------------------------------------------------------------
 // tcgen05 / TMEM
 // ---------------------------------------------------------------------------------------------
+template <int CG> DPH_DEVICE void tmem_alloc_cg(uint32_t smem_dst, uint32_t ncols) {
+  if constexpr (CG == 1)
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst), "r"(ncols)
+                 : "memory");
+  else
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst), "r"(ncols)
+                 : "memory");
+}
+template <int CG> DPH_DEVICE void tmem_relinquish_cg() {
+  if constexpr (CG == 1)
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  else
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+template <int CG> DPH_DEVICE void tmem_dealloc_cg(uint32_t taddr, uint32_t ncols) {
+  if constexpr (CG == 1)
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+  else
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+// cta_group::2 MMA: issued by the leader CTA of a pair; A/B descriptors address the same shared-memory offsets in
+// both CTAs (A: 128 rows each, B: N/2 rows each), D is the same TMEM address in both.
+DPH_DEVICE void umma_f16_ss_2sm(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// Arrive (once) on the barrier at the same offset in every CTA of `cta_mask` when the MMAs issued so far complete.
+DPH_DEVICE void umma_commit_2sm(uint32_t bar, uint16_t cta_mask) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+      "h"(cta_mask)
+      : "memory");
+}
+
 DPH_DEVICE void tmem_alloc(uint32_t smem_dst, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst), "r"(ncols)
                : "memory");

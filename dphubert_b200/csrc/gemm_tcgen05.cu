@@ -1,14 +1,19 @@
 // bf16 GEMM on the 5th-generation tensor cores (tcgen05.mma, fp32 accumulators in TMEM, TMA-fed smem ring).
 //
-// One persistent CTA per SM, 6 warps:
+// Persistent kernel, one CTA per SM, 10 warps:
 //   warp 0      TMA producer   (one lane issues cp.async.bulk.tensor into a STAGES-deep smem ring)
 //   warp 1      MMA issuer     (one lane issues tcgen05.mma; owns the TMEM allocation)
-//   warps 2..5  epilogue       (tcgen05.ld TMEM -> registers -> fused epilogue -> global)
+//   warps 2..9  epilogue       (tcgen05.ld TMEM -> registers -> fused epilogue -> global; two warps per TMEM lane
+//                               quadrant, each taking half of the tile's columns)
 // Three mbarrier pipelines: smem full/empty (TMA <-> MMA), TMEM full/empty (MMA <-> epilogue, two accumulator
 // buffers so the epilogue of tile i overlaps the mainloop of tile i+1), and the static persistent tile walk.
 //
-// Tile = 128 x BN x 64 (BN in {64,128,192,256}); operands may be K-major or MN-major (the latter is what
-// weight-gradient and P*V / dS^T*Q products need: their reduction index is the slow memory dimension).
+// CG = 1: tile 128 x BN x 64 per CTA.
+// CG = 2: the two CTAs of a cluster (one TPC) work on one 256 x BN tile with tcgen05.mma.cta_group::2: each CTA
+//         stages its own 128 rows of A and only BN/2 rows of B, the leader CTA issues the MMAs for both, every CTA
+//         runs the epilogue of its own 128 rows.  Halves the B traffic from L2 and the smem reads per flop.
+// Operands may be K-major or MN-major (the latter is what weight-gradient products need: their reduction index is
+// the slow memory dimension).
 #include "common.cuh"
 #include "gemm.h"
 
@@ -16,12 +21,14 @@ namespace dph {
 
 constexpr int BM = 128;
 constexpr int BK = 64;
-constexpr int kGemmThreads = 192;
+constexpr int kEpiWarps = 8;
+constexpr int kGemmThreads = 64 + 32 * kEpiWarps;
 
-template <int BN>
+template <int BN, int CG>
 struct GemmCfg {
+  static constexpr int B_ROWS = BN / CG;  // rows of B staged by one CTA
   static constexpr int A_BYTES = BM * BK * 2;
-  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int B_BYTES = B_ROWS * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGES_RAW = (200 * 1024) / STAGE_BYTES;
   static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
@@ -33,6 +40,8 @@ struct TileCoord {
   int m0, n0, b0, b1, ks;
 };
 
+// m0 is the first row of the (128 * CG)-row tile; n0 is the N-tile index (multiplied by BN by the caller).
+template <int CG>
 DPH_DEVICE TileCoord decode_tile(const GemmParams& p, int t) {
   TileCoord c;
   c.ks = t % p.ksplit;
@@ -43,14 +52,15 @@ DPH_DEVICE TileCoord decode_tile(const GemmParams& p, int t) {
   t /= p.mtiles;
   c.b0 = t % p.nb0;
   c.b1 = t / p.nb0;
-  c.m0 = mb * BM;
-  c.n0 = 0;
-  c.n0 = nb;  // multiplied by BN by the caller (BN is a template parameter there)
+  c.m0 = mb * (BM * CG);
+  c.n0 = nb;
   return c;
 }
 
-template <int BN>
-DPH_DEVICE void epilogue_chunk(const GemmParams& p, const TileCoord& tc, int row, int col0, uint32_t (&r)[32]) {
+// Generic (ragged / unaligned) epilogue of one 32-column chunk: scalar accesses, any nvalid. Out of line so that its
+// dynamically indexed arrays do not force the fast path's registers onto the stack.
+__device__ __noinline__ void epilogue_chunk_generic(const GemmParams& p, const TileCoord& tc, int row, int col0,
+                                                    const uint32_t (&r)[32]) {
   // row: row index inside the batch (already checked < M); col0: first column of this 32-wide chunk.
   const int nvalid = min(32, p.N - col0);
   if (nvalid <= 0) return;
@@ -89,7 +99,7 @@ DPH_DEVICE void epilogue_chunk(const GemmParams& p, const TileCoord& tc, int row
   }
   if (p.act == 1) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+    for (int j = 0; j < 32; ++j) v[j] = gelu_erf_fast(v[j]);
   }
   if (p.colmask != nullptr) {
 #pragma unroll
@@ -155,7 +165,12 @@ DPH_DEVICE void epilogue_chunk(const GemmParams& p, const TileCoord& tc, int row
   } else {
     float* o = reinterpret_cast<float*>(p.C) + coff;
     if (p.c_mode == 1) {
-      for (int j = 0; j < nvalid; ++j) atomicAdd(o + j, v[j]);
+      if (full) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) red_add_v4(o + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
+      } else {
+        for (int j = 0; j < nvalid; ++j) atomicAdd(o + j, v[j]);
+      }
     } else if (full) {
 #pragma unroll
       for (int j = 0; j < 32; j += 4) {
@@ -175,12 +190,164 @@ DPH_DEVICE void epilogue_chunk(const GemmParams& p, const TileCoord& tc, int row
   }
 }
 
-template <int BN, bool A_MN, bool B_MN>
+
+DPH_DEVICE void unpack_bf16x8(const uint4& u, float* f) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    float2 t = __bfloat1622float2(h[q]);
+    f[2 * q] = t.x;
+    f[2 * q + 1] = t.y;
+  }
+}
+
+// Fast path: all 32 columns valid and every pointer 16-byte aligned (p.vec_ok). Every global load of the chunk
+// (bias, column mask, residual; all read-only in this kernel) is issued up front as an independent 16-byte load so
+// that their latencies overlap; no dynamically indexed arrays.
+DPH_DEVICE void epilogue_chunk(const GemmParams& p, const TileCoord& tc, int row, int col0, uint32_t (&r)[32]) {
+  if (!(p.vec_ok && col0 + 32 <= p.N)) {
+    if (col0 < p.N) epilogue_chunk_generic(p, tc, row, col0, r);
+    return;
+  }
+  const long long coff = (long long)tc.b0 * p.c_sb0 + (long long)tc.b1 * p.c_sb1 + (long long)row * p.ldc + col0;
+  float v[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
+
+  uint4 res[4];
+  const bool has_res16 = (p.residual != nullptr) && (p.r_dtype == 0);
+  if (has_res16) {
+    const long long roff = (long long)tc.b0 * p.r_sb0 + (long long)tc.b1 * p.r_sb1 + (long long)row * p.ldr + col0;
+    const uint4* rp = reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(p.residual) + roff);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) res[j] = __ldg(rp + j);
+  }
+  if (p.bias != nullptr) {
+    const float4* bp = reinterpret_cast<const float4*>(p.bias + tc.b0 * p.vec_sb0 + col0);
+    float4 bv[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) bv[j] = __ldg(bp + j);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      v[4 * j] += bv[j].x;
+      v[4 * j + 1] += bv[j].y;
+      v[4 * j + 2] += bv[j].z;
+      v[4 * j + 3] += bv[j].w;
+    }
+  }
+  if (p.C2 != nullptr) {
+    if (p.c_dtype == 0) {
+      uint4* o = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.C2) + coff);
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        o[j] = make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                          pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+    } else {
+      float4* o = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.C2) + coff);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    }
+  }
+  if (p.act == 1) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = gelu_erf_fast(v[j]);
+  }
+  if (p.colmask != nullptr) {
+    const float4* mp = reinterpret_cast<const float4*>(p.colmask + tc.b0 * p.vec_sb0 + col0);
+    float4 mv[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) mv[j] = __ldg(mp + j);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      v[4 * j] *= mv[j].x;
+      v[4 * j + 1] *= mv[j].y;
+      v[4 * j + 2] *= mv[j].z;
+      v[4 * j + 3] *= mv[j].w;
+    }
+  }
+  if (p.scalar_mask != nullptr) {
+    const float s = __ldg(p.scalar_mask + tc.b0 * p.scalar_sb0);
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] *= s;
+  }
+  if (p.drop_p > 0.0f) {
+    const uint32_t thresh = (uint32_t)(p.drop_p * 4294967296.0);
+    const float inv_keep = 1.0f / (1.0f - p.drop_p);
+    const unsigned long long base =
+        (((unsigned long long)tc.b1 * p.nb0 + tc.b0) * (unsigned long long)p.M + row) * (unsigned long long)p.N + col0;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] *= dropout_scale(p.seed, base + j, thresh, inv_keep);
+  }
+  if (has_res16) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float f[8];
+      unpack_bf16x8(res[j], f);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) v[8 * j + q] += f[q];
+    }
+  } else if (p.residual != nullptr) {
+    const long long roff = (long long)tc.b0 * p.r_sb0 + (long long)tc.b1 * p.r_sb1 + (long long)row * p.ldr + col0;
+    const float4* rp = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.residual) + roff);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float4 f = __ldg(rp + j);
+      v[4 * j] += f.x;
+      v[4 * j + 1] += f.y;
+      v[4 * j + 2] += f.z;
+      v[4 * j + 3] += f.w;
+    }
+  }
+  // ---- store ----
+  if (p.c_dtype == 0) {
+    uint4* o = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.C) + coff);
+    if (p.c_mode == 2) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float f[8];
+        const uint4 old = o[j];
+        unpack_bf16x8(old, f);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) v[8 * j + q] += f[q];
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      o[j] = make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                        pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+  } else {
+    float* o = reinterpret_cast<float*>(p.C) + coff;
+    if (p.c_mode == 1) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 4) red_add_v4(o + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
+    } else {
+      float4* o4 = reinterpret_cast<float4*>(o);
+      if (p.c_mode == 2) {
+        float4 old[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) old[j] = o4[j];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          v[4 * j] += old[j].x;
+          v[4 * j + 1] += old[j].y;
+          v[4 * j + 2] += old[j].z;
+          v[4 * j + 3] += old[j].w;
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o4[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    }
+  }
+}
+
+template <int BN, bool A_MN, bool B_MN, int CG>
 __global__ void __launch_bounds__(kGemmThreads, 1)
     gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                      const GemmParams p) {
-  using Cfg = GemmCfg<BN>;
+  using Cfg = GemmCfg<BN, CG>;
   constexpr int STAGES = Cfg::STAGES;
+  static_assert(CG == 1 || CG == 2, "CTA group is 1 or 2");
+  static_assert(!(B_MN && CG == 2) || (BN % 128 == 0), "MN-major B halves must be whole 64-column boxes");
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bar_base = smem_base + STAGES * Cfg::STAGE_BYTES;
@@ -193,6 +360,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const int rank = (CG == 2) ? (int)cluster_ctarank() : 0;  // 0 = leader (issues the MMAs)
+  const int unit = blockIdx.x / CG;                         // persistent work unit = CTA or CTA pair
+  const int nunits = gridDim.x / CG;
   const int total_tiles = p.nb1 * p.nb0 * p.mtiles * p.ntiles * p.ksplit;
 
   if (warp == 0 && lane == 0) {
@@ -202,57 +372,64 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
   if (warp == 1) {
     if (lane == 0) {
       for (int s = 0; s < STAGES; ++s) {
-        mbar_init(full_bar(s), 1);
-        mbar_init(empty_bar(s), 1);
+        mbar_init(full_bar(s), 1);   // leader: its own arrive.expect_tx (transaction bytes of both CTAs)
+        mbar_init(empty_bar(s), 1);  // one (multicast) tcgen05.commit
       }
       for (int a = 0; a < 2; ++a) {
         mbar_init(tfull_bar(a), 1);
-        mbar_init(tempty_bar(a), 4);
+        mbar_init(tempty_bar(a), kEpiWarps * CG);  // leader's barrier collects the epilogue warps of both CTAs
       }
       mbar_fence_init();
     }
     __syncwarp();
-    tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
-    tmem_relinquish();
+    tmem_alloc_cg<CG>(tmem_slot, Cfg::TMEM_COLS);
+    tmem_relinquish_cg<CG>();
   }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
   if (warp == 0) {
-    // ======================= TMA producer =======================
+    // ======================= TMA producer (both CTAs of a pair) =======================
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        TileCoord tc = decode_tile(p, t);
-        const int n0 = tc.n0 * BN;
+      for (int t = unit; t < total_tiles; t += nunits) {
+        TileCoord tc = decode_tile<CG>(p, t);
+        const int m0 = tc.m0 + rank * BM;                    // this CTA's rows of A
+        const int n0 = tc.n0 * BN + rank * Cfg::B_ROWS;      // this CTA's share of the B tile
         const int kb_begin = tc.ks * p.kb_per_split;
         const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
         for (int kb = kb_begin; kb < kb_end; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t sA = smem_base + stage * Cfg::STAGE_BYTES;
           const uint32_t sB = sA + Cfg::A_BYTES;
-          mbar_expect_tx(full_bar(stage), Cfg::STAGE_BYTES);
+          uint32_t fb = full_bar(stage);
+          if constexpr (CG == 2) {
+            if (rank == 0) mbar_expect_tx(fb, 2 * Cfg::STAGE_BYTES);
+            fb = mapa_shared(fb, 0);
+          } else {
+            mbar_expect_tx(fb, Cfg::STAGE_BYTES);
+          }
+          auto load = [&](uint32_t dst, const CUtensorMap* m, int c0, int c1, int c2, int c3, int c4) {
+            if constexpr (CG == 2) tma_load_5d_2sm(dst, m, fb, c0, c1, c2, c3, c4);
+            else tma_load_5d(dst, m, fb, c0, c1, c2, c3, c4);
+          };
           if constexpr (!A_MN) {
-            tma_load_5d(sA, &tmA, full_bar(stage), (kb % p.a_kdiv) * BK, tc.m0, kb / p.a_kdiv, tc.b0 * p.a_b0,
-                        tc.b1 * p.a_b1);
+            load(sA, &tmA, (kb % p.a_kdiv) * BK, m0, kb / p.a_kdiv, tc.b0 * p.a_b0, tc.b1 * p.a_b1);
           } else {
 #pragma unroll
             for (int j = 0; j < BM / 64; ++j)
-              tma_load_5d(sA + j * (BK * 128), &tmA, full_bar(stage), tc.m0 + 64 * j, kb * BK, tc.b0 * p.a_b0,
-                          tc.b1 * p.a_b1, 0);
+              load(sA + j * (BK * 128), &tmA, m0 + 64 * j, kb * BK, tc.b0 * p.a_b0, tc.b1 * p.a_b1, 0);
           }
           if constexpr (!B_MN) {
-            tma_load_5d(sB, &tmB, full_bar(stage), (kb % p.b_kdiv) * BK, n0, kb / p.b_kdiv, tc.b0 * p.b_b0,
-                        tc.b1 * p.b_b1);
+            load(sB, &tmB, (kb % p.b_kdiv) * BK, n0, kb / p.b_kdiv, tc.b0 * p.b_b0, tc.b1 * p.b_b1);
           } else {
 #pragma unroll
-            for (int j = 0; j < BN / 64; ++j)
-              tma_load_5d(sB + j * (BK * 128), &tmB, full_bar(stage), n0 + 64 * j, kb * BK, tc.b0 * p.b_b0,
-                          tc.b1 * p.b_b1, 0);
+            for (int j = 0; j < Cfg::B_ROWS / 64; ++j)
+              load(sB + j * (BK * 128), &tmB, n0 + 64 * j, kb * BK, tc.b0 * p.b_b0, tc.b1 * p.b_b1, 0);
           }
           if (++stage == STAGES) {
             stage = 0;
@@ -262,76 +439,91 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
       }
     }
   } else if (warp == 1) {
-    // ======================= MMA issuer =======================
-    constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN, B_MN);
-    int stage = 0;
-    uint32_t phase = 0;
-    int acc = 0;
-    uint32_t acc_phase = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-      TileCoord tc = decode_tile(p, t);
-      const int kb_begin = tc.ks * p.kb_per_split;
-      const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
-      mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
-      tc_fence_after();
-      const uint32_t tmem_d = tmem_base + (uint32_t)(acc * BN);
-      for (int kb = kb_begin; kb < kb_end; ++kb) {
-        mbar_wait(full_bar(stage), phase);
+    // ======================= MMA issuer (leader CTA only) =======================
+    if (rank == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM * CG, BN, A_MN, B_MN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int t = unit; t < total_tiles; t += nunits) {
+        TileCoord tc = decode_tile<CG>(p, t);
+        const int kb_begin = tc.ks * p.kb_per_split;
+        const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
+        mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
         tc_fence_after();
-        if (lane == 0) {
-          const uint32_t sA = smem_base + stage * Cfg::STAGE_BYTES;
-          const uint32_t sB = sA + Cfg::A_BYTES;
+        const uint32_t tmem_d = tmem_base + (uint32_t)(acc * BN);
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          if (lane == 0) {
+            const uint32_t sA = smem_base + stage * Cfg::STAGE_BYTES;
+            const uint32_t sB = sA + Cfg::A_BYTES;
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k) {
-            const uint64_t da = A_MN ? make_smem_desc(sA + k * 2048, BK * 128, 1024, 2)
-                                     : make_smem_desc(sA + k * 32, 0, 1024, 2);
-            const uint64_t db = B_MN ? make_smem_desc(sB + k * 2048, BK * 128, 1024, 2)
-                                     : make_smem_desc(sB + k * 32, 0, 1024, 2);
-            umma_f16_ss(tmem_d, da, db, idesc, (kb > kb_begin || k > 0) ? 1u : 0u);
+            for (int k = 0; k < BK / 16; ++k) {
+              const uint64_t da = A_MN ? make_smem_desc(sA + k * 2048, BK * 128, 1024, 2)
+                                       : make_smem_desc(sA + k * 32, 0, 1024, 2);
+              const uint64_t db = B_MN ? make_smem_desc(sB + k * 2048, BK * 128, 1024, 2)
+                                       : make_smem_desc(sB + k * 32, 0, 1024, 2);
+              const uint32_t accum = (kb > kb_begin || k > 0) ? 1u : 0u;
+              if constexpr (CG == 2) umma_f16_ss_2sm(tmem_d, da, db, idesc, accum);
+              else umma_f16_ss(tmem_d, da, db, idesc, accum);
+            }
+            if constexpr (CG == 2) {
+              umma_commit_2sm(empty_bar(stage), 3);
+              if (kb == kb_end - 1) umma_commit_2sm(tfull_bar(acc), 3);
+            } else {
+              umma_commit(empty_bar(stage));
+              if (kb == kb_end - 1) umma_commit(tfull_bar(acc));
+            }
           }
-          umma_commit(empty_bar(stage));
-          if (kb == kb_end - 1) umma_commit(tfull_bar(acc));
+          __syncwarp();
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1u;
+          }
         }
-        __syncwarp();
-        if (++stage == STAGES) {
-          stage = 0;
-          phase ^= 1u;
+        if (kb_end <= kb_begin && lane == 0) {
+          // empty split (cannot happen with the host-side split computation, kept for safety)
+          if constexpr (CG == 2) umma_commit_2sm(tfull_bar(acc), 3);
+          else umma_commit(tfull_bar(acc));
         }
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1u;
       }
-      if (kb_end <= kb_begin && lane == 0) {
-        // empty split (cannot happen with the host-side split computation, kept for safety)
-        umma_commit(tfull_bar(acc));
-      }
-      acc ^= 1;
-      if (acc == 0) acc_phase ^= 1u;
     }
   } else {
-    // ======================= epilogue warps =======================
-    const int q = warp & 3;  // TMEM lane quadrant this warp may access
+    // ======================= epilogue warps (both CTAs: own 128 rows, all BN columns) =======================
+    const int q = warp & 3;           // TMEM lane quadrant this warp may access
+    const int half = (warp - 2) >> 2; // which half of the tile's columns
+    constexpr int CHUNKS = BN / 64;   // 32-column chunks per warp
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-      TileCoord tc = decode_tile(p, t);
-      const int n0 = tc.n0 * BN;
+    for (int t = unit; t < total_tiles; t += nunits) {
+      TileCoord tc = decode_tile<CG>(p, t);
+      const int n0 = tc.n0 * BN + half * (BN / 2);
       const int kb_begin = tc.ks * p.kb_per_split;
       const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
-      const int row = tc.m0 + q * 32 + lane;
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
+      const int row = tc.m0 + rank * BM + q * 32 + lane;
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + half * (BN / 2));
       const bool row_ok = (row < p.M) && (kb_end > kb_begin);
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
+      for (int c = 0; c < CHUNKS; ++c) {
         uint32_t r[32];
         tmem_ld_32x32(taddr + c * 32, r);
         tmem_ld_wait();
-        if (c == BN / 32 - 1) {
-          // all TMEM reads of this accumulator are done: hand the buffer back to the MMA warp
+        if (c == CHUNKS - 1) {
+          // all TMEM reads of this accumulator are done: hand the buffer back to the (leader's) MMA warp
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(tempty_bar(acc));
+          if (lane == 0) {
+            if constexpr (CG == 2) mbar_arrive_cluster(mapa_shared(tempty_bar(acc), 0));
+            else mbar_arrive(tempty_bar(acc));
+          }
         }
-        if (row_ok) epilogue_chunk<BN>(p, tc, row, n0 + c * 32, r);
+        if (row_ok) epilogue_chunk(p, tc, row, n0 + c * 32, r);
       }
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1u;
@@ -339,10 +531,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
   }
 
   tc_fence_before();
-  __syncthreads();
+  if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+    tmem_dealloc_cg<CG>(tmem_base, Cfg::TMEM_COLS);
   }
 }
 
@@ -451,12 +643,12 @@ static int num_sms() {
   return n;
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, int CG>
 static int launch_inst(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid,
                        cudaStream_t stream) {
-  using Cfg = GemmCfg<BN>;
+  using Cfg = GemmCfg<BN, CG>;
   static bool attr_set = false;
-  auto kfn = gemm_bf16_kernel<BN, A_MN, B_MN>;
+  auto kfn = gemm_bf16_kernel<BN, A_MN, B_MN, CG>;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
     if (e != cudaSuccess) {
@@ -465,31 +657,57 @@ static int launch_inst(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
     }
     attr_set = true;
   }
-  kfn<<<grid, kGemmThreads, Cfg::SMEM_BYTES, stream>>>(ta, tb, p);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CG;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = (CG > 1) ? 1 : 0;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kfn, ta, tb, p);
+  if (e != cudaSuccess) {
+    set_error("gemm_bf16_kernel launch: %s", cudaGetErrorString(e));
+    return DPH_ERR_CUDA;
+  }
   dph_count_launch();
   return dph_check_last("gemm_bf16_kernel");
 }
 
-template <int BN>
+template <int BN, int CG>
 static int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, bool a_mn,
                      bool b_mn, cudaStream_t s) {
-  if (!a_mn && !b_mn) return launch_inst<BN, false, false>(ta, tb, p, grid, s);
-  if (!a_mn && b_mn) return launch_inst<BN, false, true>(ta, tb, p, grid, s);
-  if (a_mn && !b_mn) return launch_inst<BN, true, false>(ta, tb, p, grid, s);
-  return launch_inst<BN, true, true>(ta, tb, p, grid, s);
+  if (!a_mn && !b_mn) return launch_inst<BN, false, false, CG>(ta, tb, p, grid, s);
+  if (a_mn && !b_mn) return launch_inst<BN, true, false, CG>(ta, tb, p, grid, s);
+  if constexpr (CG == 1 || BN % 128 == 0) {
+    if (!a_mn && b_mn) return launch_inst<BN, false, true, CG>(ta, tb, p, grid, s);
+    return launch_inst<BN, true, true, CG>(ta, tb, p, grid, s);
+  } else {
+    set_error("gemm: MN-major B with a CTA pair needs block_n 128 or 256");
+    return DPH_ERR_ARG;
+  }
 }
 
-static int pick_block_n(int M, int N, int nbatch, int sms) {
-  // minimise (waves * tile cost) — cost of a tile is proportional to BN
+// A CTA pair cannot split an MN-major B tile of 64 or 192 columns into whole 64-column TMA boxes.
+static bool bn_legal(int bn, int cg, bool b_mn) { return !(cg == 2 && b_mn && (bn % 128) != 0); }
+
+static int pick_block_n(int M, int N, int nbatch, int units, int cg, bool b_mn) {
+  // minimise (waves * tile cost) -- cost of a tile is proportional to BN
   const int cands[4] = {256, 192, 128, 64};
   int best = 128;
   double best_cost = 1e30;
-  const long long mt = (M + BM - 1) / BM;
+  const long long mt = (M + BM * cg - 1) / (BM * cg);
   for (int i = 0; i < 4; ++i) {
     int bn = cands[i];
-    if (bn > 64 && N <= bn / 2 && N <= 128) continue;  // do not waste >50% of a tile on padding
+    if (!bn_legal(bn, cg, b_mn)) continue;
+    if (bn > 128 && N <= bn / 2) continue;                          // do not waste >50% of a tile on padding
+    if (bn == 128 && N <= 64 && bn_legal(64, cg, b_mn)) continue;
     long long tiles = mt * ((N + bn - 1) / bn) * nbatch;
-    long long waves = (tiles + sms - 1) / sms;
+    long long waves = (tiles + units - 1) / units;
     double cost = (double)waves * (bn + 24);  // +24: fixed per-tile overhead in "columns"
     if (cost < best_cost - 1e-9) {
       best_cost = cost;
@@ -513,10 +731,32 @@ int gemm_bf16_launch(const dph_gemm_desc_t* d, cudaStream_t stream) {
     return DPH_ERR_ARG;
   }
   const int sms = num_sms();
+  const bool a_mn = d->a.major_mn != 0, b_mn = d->b.major_mn != 0;
+  // CTA pairs (tcgen05 cta_group::2) whenever there is more than one 128-row tile to pair up.
+  int cg = d->cta_group;
+  if (cg == 0) cg = (d->M > BM && sms >= 2 && !(b_mn && d->block_n != 0 && d->block_n % 128 != 0)) ? 2 : 1;
+  if (cg != 1 && cg != 2) {
+    set_error("gemm: cta_group must be 0 (auto), 1 or 2");
+    return DPH_ERR_ARG;
+  }
+  const int units = cg == 2 ? sms / 2 : sms;  // persistent work units (CTAs or CTA pairs)
+  const bool auto_split = d->ksplit < 0;
+  if (auto_split && d->c_mode != 1) {
+    set_error("gemm: automatic split-K requires atomic output mode");
+    return DPH_ERR_ARG;
+  }
   int bn = d->block_n;
-  if (bn == 0) bn = pick_block_n(d->M, d->N, d->nb0 * d->nb1, sms);
-  if (bn != 64 && bn != 128 && bn != 192 && bn != 256) {
-    set_error("gemm: unsupported block_n %d", bn);
+  if (bn == 0) {
+    // long reductions into a small output: biggest tile (least operand traffic), parallelism comes from split-K
+    int big = d->N > 128 ? 256 : (d->N > 64 ? 128 : 64);
+    if (!bn_legal(big, cg, b_mn)) big = 128;
+    const long long tiles_big =
+        (long long)((d->M + BM * cg - 1) / (BM * cg)) * ((d->N + big - 1) / big) * d->nb0 * d->nb1;
+    if (auto_split && tiles_big * 2 <= units) bn = big;
+    else bn = pick_block_n(d->M, d->N, d->nb0 * d->nb1, units, cg, b_mn);
+  }
+  if ((bn != 64 && bn != 128 && bn != 192 && bn != 256) || !bn_legal(bn, cg, b_mn)) {
+    set_error("gemm: unsupported block_n %d (cta_group %d)", bn, cg);
     return DPH_ERR_ARG;
   }
   GemmParams p;
@@ -525,10 +765,16 @@ int gemm_bf16_launch(const dph_gemm_desc_t* d, cudaStream_t stream) {
   p.K = d->K;
   p.nb0 = d->nb0;
   p.nb1 = d->nb1;
-  p.mtiles = (d->M + BM - 1) / BM;
+  p.mtiles = (d->M + BM * cg - 1) / (BM * cg);
   p.ntiles = (d->N + bn - 1) / bn;
   p.num_kb = (d->K + BK - 1) / BK;
   int ksplit = d->ksplit > 1 ? d->ksplit : 1;
+  if (auto_split) {
+    const long long tiles = (long long)p.mtiles * p.ntiles * d->nb0 * d->nb1;
+    long long ks = units / (tiles > 0 ? tiles : 1);
+    if (ks > p.num_kb / 4) ks = p.num_kb / 4;  // at least 4 k-blocks of work per split
+    ksplit = ks < 1 ? 1 : (int)ks;
+  }
   if (ksplit > 1 && d->c_mode != 1) {
     set_error("gemm: split-K requires atomic output mode");
     return DPH_ERR_ARG;
@@ -563,6 +809,8 @@ int gemm_bf16_launch(const dph_gemm_desc_t* d, cudaStream_t stream) {
   p.c_sb1 = d->c_sb1;
   p.c_dtype = d->c_dtype;
   p.c_mode = d->c_mode;
+  // A single split whose batches do not alias one output needs no atomics: read-add-store with vector accesses.
+  if (p.c_mode == 1 && ksplit == 1 && (d->nb0 == 1 || d->c_sb0 != 0) && (d->nb1 == 1 || d->c_sb1 != 0)) p.c_mode = 2;
   p.alpha = d->alpha;
   p.bias = d->bias;
   p.act = d->act;
@@ -587,22 +835,31 @@ int gemm_bf16_launch(const dph_gemm_desc_t* d, cudaStream_t stream) {
     vec = vec && (d->ldr % relt == 0) && (d->r_sb0 % relt == 0) && (d->r_sb1 % relt == 0) &&
           ((reinterpret_cast<uintptr_t>(d->residual) & 15) == 0);
   }
+  if (d->bias) vec = vec && ((reinterpret_cast<uintptr_t>(d->bias) & 15) == 0) && (d->vec_sb0 % 4 == 0);
+  if (d->colmask) vec = vec && ((reinterpret_cast<uintptr_t>(d->colmask) & 15) == 0) && (d->vec_sb0 % 4 == 0);
   p.vec_ok = vec ? 1 : 0;
 
   CUtensorMap ta, tb;
   int rc = make_tmap(&ta, d->a, BM);
   if (rc != DPH_OK) return rc;
-  rc = make_tmap(&tb, d->b, bn);
+  rc = make_tmap(&tb, d->b, bn / cg);
   if (rc != DPH_OK) return rc;
 
   const long long total = (long long)p.nb1 * p.nb0 * p.mtiles * p.ntiles * p.ksplit;
-  const int grid = (int)(total < sms ? total : sms);
-  const bool a_mn = d->a.major_mn != 0, b_mn = d->b.major_mn != 0;
+  const int grid = (int)(total < units ? total : units) * cg;
+  if (cg == 2) {
+    switch (bn) {
+      case 64: return launch_bn<64, 2>(ta, tb, p, grid, a_mn, b_mn, stream);
+      case 128: return launch_bn<128, 2>(ta, tb, p, grid, a_mn, b_mn, stream);
+      case 192: return launch_bn<192, 2>(ta, tb, p, grid, a_mn, b_mn, stream);
+      default: return launch_bn<256, 2>(ta, tb, p, grid, a_mn, b_mn, stream);
+    }
+  }
   switch (bn) {
-    case 64: return launch_bn<64>(ta, tb, p, grid, a_mn, b_mn, stream);
-    case 128: return launch_bn<128>(ta, tb, p, grid, a_mn, b_mn, stream);
-    case 192: return launch_bn<192>(ta, tb, p, grid, a_mn, b_mn, stream);
-    default: return launch_bn<256>(ta, tb, p, grid, a_mn, b_mn, stream);
+    case 64: return launch_bn<64, 1>(ta, tb, p, grid, a_mn, b_mn, stream);
+    case 128: return launch_bn<128, 1>(ta, tb, p, grid, a_mn, b_mn, stream);
+    case 192: return launch_bn<192, 1>(ta, tb, p, grid, a_mn, b_mn, stream);
+    default: return launch_bn<256, 1>(ta, tb, p, grid, a_mn, b_mn, stream);
   }
 }
 

@@ -711,7 +711,7 @@ def conv_stack_bwd(plan: Plan, st, dfeat, dmasks, A):
                 ops.memset(wg)
                 a = View(dzp, Cout, Tout, 1, cs=Cout, sb0=rows_pb * Cout, offset=padr * Cout)
                 bv = View(x_in, k * Cin, Tout, 1, cs=s * Cin, sb0=Tin * Cin)
-                G.gemm(a, bv, wg, Cout, k * Cin, Tout, nb0=B, c_sb0=0, atomic=True)
+                G.gemm(a, bv, wg, Cout, k * Cin, Tout, nb0=B, c_sb0=0, atomic=True, ksplit=-1)
                 ops.conv_wgrad_unpermute(wg, plan.gview(conv.weight), Cout, Cin, k)
             # ---- input gradient, one GEMM per output phase (u = s t' + phase)
             _, phases = _conv_weight_views(plan, blk, i, dt)
@@ -997,10 +997,9 @@ def encoder_fwd(plan: Plan, feat, lengths, masks, A, train, num_layers=None, fin
 # Encoder backward
 # ----------------------------------------------------------------------------------------------------------------
 def _ksplit(Mo, No, K):
-    """Split-K factor for weight-gradient GEMMs (small outputs, long reductions): aim for >= one wave of CTAs."""
-    tiles = ((Mo + 127) // 128) * ((No + 255) // 256)
-    ks = max(1, min(148 // max(tiles, 1), K // 512))
-    return ks
+    """Split-K factor for weight-gradient GEMMs (small outputs, long reductions): -1 lets the library pick it from
+    the tile shape it chooses (bf16 tensor-core path); the fp32 path ignores it."""
+    return -1
 
 
 def _wgrad(plan, dy2d, x2d, param, Mo, No, Krows):

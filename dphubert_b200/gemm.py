@@ -88,7 +88,8 @@ def _operand_f32(v):
 
 def gemm(a, b, c, M, N, K, *, ldc=None, nb0=1, nb1=1, c_sb0=0, c_sb1=0, c_offset=0, alpha=1.0, bias=None, act=0,
          colmask=None, scalar_mask=None, residual=None, ldr=None, r_sb0=0, r_sb1=0, r_offset=0, c2=None,
-         accumulate=False, atomic=False, ksplit=1, drop_p=0.0, seed=0, block_n=0, vec_sb0=0, scalar_sb0=0):
+         accumulate=False, atomic=False, ksplit=1, drop_p=0.0, seed=0, block_n=0, vec_sb0=0, scalar_sb0=0,
+         cta_group=0):
     """C[b][m, n] = epilogue(alpha * sum_k a(m,k) b(n,k)).  `a`, `b` are `View`s; dtype of `a.t` selects the path:
     bf16 -> tcgen05 tensor-core kernel, fp32 -> CUDA-core kernel."""
     L = _lib.lib()
@@ -102,7 +103,7 @@ def gemm(a, b, c, M, N, K, *, ldc=None, nb0=1, nb1=1, c_sb0=0, c_sb1=0, c_offset
         d.a = _operand_bf16(a, nb0, nb1)
         d.b = _operand_bf16(b, nb0, nb1)
         d.M, d.N, d.K, d.nb0, d.nb1 = M, N, K, nb0, nb1
-        d.block_n, d.ksplit = block_n, ksplit
+        d.block_n, d.ksplit, d.cta_group = block_n, ksplit, cta_group
         d.c = c.data_ptr() + c_offset * c.element_size()
         d.c2 = None if c2 is None else c2.data_ptr() + c_offset * c2.element_size()
         d.ldc, d.c_sb0, d.c_sb1 = ldc, c_sb0, c_sb1

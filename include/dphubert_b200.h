@@ -57,7 +57,7 @@ typedef struct {
   int M, N, K;        /* per-batch problem size (rows of A, rows of B, reduction length)                        */
   int nb0, nb1;       /* batch extents (>= 1)                                                                  */
   int block_n;        /* 0 = auto, else one of 64 / 128 / 192 / 256                                            */
-  int ksplit;         /* >1: split the reduction over ksplit CTAs (requires c_mode == 1)                       */
+  int ksplit;         /* >1: split the reduction over ksplit CTAs (requires c_mode == 1); <0: library chooses    */
   /* output */
   void* c;            /* (rows, N) row-major with leading dimension ldc; batch offsets c_sb0 / c_sb1 (elements)*/
   void* c2;           /* optional second output holding the pre-activation value (same layout / dtype as c)    */
@@ -78,6 +78,7 @@ typedef struct {
   uint64_t seed;
   int64_t vec_sb0;          /* element offset added to bias / colmask per batch index b0 (grouped conv, heads) */
   int64_t scalar_sb0;       /* element offset added to scalar_mask per batch index b0 (per-head HardConcrete mask) */
+  int cta_group;            /* 0 = auto; 1 = one CTA per 128-row tile; 2 = CTA pair (tcgen05 cta_group::2) per 256-row tile */
 } dph_gemm_desc_t;
 
 int dph_gemm_bf16(const dph_gemm_desc_t* desc, void* stream);

@@ -55,7 +55,8 @@ def _gather(v, nb0, nb1):
 
 def gemm(a, b, c, M, N, K, *, ldc=None, nb0=1, nb1=1, c_sb0=0, c_sb1=0, c_offset=0, alpha=1.0, bias=None, act=0,
          colmask=None, scalar_mask=None, residual=None, ldr=None, r_sb0=0, r_sb1=0, r_offset=0, c2=None,
-         accumulate=False, atomic=False, ksplit=1, drop_p=0.0, seed=0, block_n=0, vec_sb0=0, scalar_sb0=0):
+         accumulate=False, atomic=False, ksplit=1, drop_p=0.0, seed=0, block_n=0, vec_sb0=0, scalar_sb0=0,
+         cta_group=0):
     assert drop_p == 0.0, "the emulator runs the dropout-free parity configuration"
     ldc = N if ldc is None else ldc
     ldr = ldc if ldr is None else ldr

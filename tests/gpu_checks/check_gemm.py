@@ -150,36 +150,89 @@ def case_conv():
     report("grouped pos-conv (tap-major K, group batch)", rel_err(y, ref), 2e-2)
 
 
+def _time(fn, n=20):
+    """Device time per call: n calls captured in a CUDA graph (no host launch gaps), replayed 5 times."""
+    for _ in range(2):
+        fn()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        fn()
+        st.synchronize()
+        with torch.cuda.graph(g, stream=st):
+            for _ in range(n):
+                fn()
+    torch.cuda.synchronize()
+    g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(5):
+        g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / (5 * n)
+
+
 def case_perf():
     for (M, N, K) in [(3992, 768, 768), (3992, 2304, 768), (3992, 3072, 768), (3992, 768, 3072), (8192, 8192, 8192),
                       (127992, 512, 1536)]:
         a, b = rnd(M, K), rnd(N, K)
         c = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
-        for bn in (0, 128, 192, 256):
-            for _ in range(3):
-                G.gemm(G.mat(a), G.mat(b), c, M, N, K, block_n=bn)
-            torch.cuda.synchronize()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            n = 20
-            e0.record()
-            for _ in range(n):
-                G.gemm(G.mat(a), G.mat(b), c, M, N, K, block_n=bn)
-            e1.record()
-            torch.cuda.synchronize()
-            ms = e0.elapsed_time(e1) / n
-            print("perf M=%d N=%d K=%d bn=%3d: %.3f ms  %.1f TFLOP/s" % (M, N, K, bn, ms, 2.0 * M * N * K / ms / 1e9), flush=True)
-        t0 = time.time()
-        for _ in range(3):
-            torch.matmul(a, b.t())
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(20):
-            torch.matmul(a, b.t())
-        e1.record()
-        torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1) / 20
+        bias = torch.randn(N, device=dev)
+        for cg in (1, 2):
+            for bn in (0, 128, 192, 256):
+                ms = _time(lambda: G.gemm(G.mat(a), G.mat(b), c, M, N, K, block_n=bn, cta_group=cg))
+                print("perf M=%d N=%d K=%d cg=%d bn=%3d: %.3f ms  %.1f TFLOP/s" % (M, N, K, cg, bn, ms, 2.0 * M * N * K / ms / 1e9), flush=True)
+            ms = _time(lambda: G.gemm(G.mat(a), G.mat(b), c, M, N, K, bias=bias, act=1, cta_group=cg))
+            print("perf M=%d N=%d K=%d cg=%d bias+gelu: %.3f ms  %.1f TFLOP/s" % (M, N, K, cg, ms, 2.0 * M * N * K / ms / 1e9), flush=True)
+        ms = _time(lambda: torch.matmul(a, b.t()))
         print("      cuBLAS reference           : %.3f ms  %.1f TFLOP/s" % (ms, 2.0 * M * N * K / ms / 1e9), flush=True)
+    # weight-gradient shapes: MN-major x MN-major, fp32 accumulate, library-chosen split-K
+    for (M, N, K) in [(3072, 768, 3992), (768, 3072, 3992), (2304, 768, 3992), (768, 768, 3992), (512, 1536, 127992)]:
+        a, b = rnd(K, M), rnd(K, N)
+        c = torch.zeros(M, N, device=dev, dtype=torch.float32)
+        for cg in (1, 2):
+            ms = _time(lambda: G.gemm(G.mat_t(a), G.mat_t(b), c, M, N, K, atomic=True, ksplit=-1, cta_group=cg))
+            print("perf wgrad M=%d N=%d K=%d cg=%d: %.3f ms  %.1f TFLOP/s" % (M, N, K, cg, ms, 2.0 * M * N * K / ms / 1e9), flush=True)
+        ms = _time(lambda: torch.matmul(a.t(), b))
+        print("      cuBLAS reference           : %.3f ms  %.1f TFLOP/s" % (ms, 2.0 * M * N * K / ms / 1e9), flush=True)
+
+
+def case_epiperf():
+    """Cost of each epilogue feature on the FFN-1 shape (graph-timed)."""
+    M, N, K = 3992, 3072, 768
+    a, b = rnd(M, K), rnd(N, K)
+    c = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+    c2 = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+    res = rnd(M, N)
+    bias = torch.randn(N, device=dev)
+    cm = torch.rand(N, device=dev)
+    variants = {
+        "plain": {}, "bias": dict(bias=bias), "gelu": dict(act=1), "colmask": dict(colmask=cm), "c2": dict(c2=c2),
+        "residual": dict(residual=res), "bias+gelu": dict(bias=bias, act=1),
+        "bias+gelu+colmask+c2": dict(bias=bias, act=1, colmask=cm, c2=c2), "fp32 out": None,
+    }
+    for name, kw in variants.items():
+        if kw is None:
+            cf = torch.empty(M, N, device=dev, dtype=torch.float32)
+            ms = _time(lambda: G.gemm(G.mat(a), G.mat(b), cf, M, N, K))
+        else:
+            ms = _time(lambda: G.gemm(G.mat(a), G.mat(b), c, M, N, K, **kw))
+        print("epiperf %-24s %.1f us  %.1f TFLOP/s" % (name, ms * 1e3, 2.0 * M * N * K / ms / 1e9), flush=True)
+
+
+def case_one():
+    """One launch of the FFN-1 GEMM with its full epilogue (target of `ncu --set full`)."""
+    M, N, K = 3992, 3072, 768
+    a, b = rnd(M, K), rnd(N, K)
+    c = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+    bias = torch.randn(N, device=dev)
+    for _ in range(3):
+        G.gemm(G.mat(a), G.mat(b), c, M, N, K, bias=bias, act=1)
+        G.gemm(G.mat(a), G.mat(b), c, M, N, K)
+    torch.cuda.synchronize()
 
 
 def main():
@@ -196,6 +249,8 @@ def main():
         "batched": case_batched,
         "conv": case_conv,
         "perf": case_perf,
+        "epiperf": case_epiperf,
+        "one": case_one,
     }
     for name, fn in cases.items():
         if flt and flt not in name:
