@@ -83,6 +83,10 @@ typedef struct {
 
 int dph_gemm_bf16(const dph_gemm_desc_t* desc, void* stream);
 
+/* Debug hook, not part of the drop-in surface: when `buf` is non-NULL every following dph_gemm_bf16 launch writes a
+ * per-CTA event timeline (64 uint64 %globaltimer stamps per CTA, see csrc/gemm_tcgen05.cu); NULL switches it off. */
+int dph_gemm_debug_timeline(void* buf);
+
 /* fp32 CUDA-core GEMM used by the fp32 parity mode (TF32 off; tcgen05 has no true-fp32 MMA):
  *   C[b][m,n] (+)= epilogue( alpha * sum_k A[b](m,k) * B[b](n,k) )
  * element (row, k) of an operand lives at ptr + b0*bs0 + b1*bs1 + row*rs + (k / kin)*kxs + (k % kin)*cs,

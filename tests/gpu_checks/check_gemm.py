@@ -223,6 +223,16 @@ def case_epiperf():
         print("epiperf %-24s %.1f us  %.1f TFLOP/s" % (name, ms * 1e3, 2.0 * M * N * K / ms / 1e9), flush=True)
 
 
+def case_plain():
+    """Plain FFN-1-shaped GEMM launches only (target of `ncu --set full`)."""
+    M, N, K = 3992, 3072, 768
+    a, b = rnd(M, K), rnd(N, K)
+    c = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+    for _ in range(6):
+        G.gemm(G.mat(a), G.mat(b), c, M, N, K)
+    torch.cuda.synchronize()
+
+
 def case_one():
     """One launch of the FFN-1 GEMM with its full epilogue (target of `ncu --set full`)."""
     M, N, K = 3992, 3072, 768
@@ -251,6 +261,7 @@ def main():
         "perf": case_perf,
         "epiperf": case_epiperf,
         "one": case_one,
+        "plain": case_plain,
     }
     for name, fn in cases.items():
         if flt and flt not in name:
