@@ -43,6 +43,12 @@ DPH_DEVICE void tma_load_2d(uint32_t smem_dst, const CUtensorMap* m, uint32_t ba
       "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
 }
+// raw MUFU.EX2 (no range fix-ups): arguments here are <= ~0, underflow flushes to 0
+DPH_DEVICE float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 DPH_DEVICE void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // byte offset of 16-byte chunk `c` (0..7) of row `r` inside a [rows][64 bf16] 128B-swizzled K-major tile
@@ -162,7 +168,7 @@ __global__ void __launch_bounds__(128, 2)
         if (j < T) mx = fmaxf(mx, x);
       }
     }
-    const float alpha = exp2f(m2 - mx);  // m2 = -inf on the first tile -> 0
+    const float alpha = fast_exp2(m2 - mx);  // m2 = -inf on the first tile -> 0
     m2 = mx;
     l *= alpha;
 #pragma unroll
@@ -184,7 +190,7 @@ __global__ void __launch_bounds__(128, 2)
           float x = __uint_as_float(r[jj + u]) * sc2;
           if (p.emb) x += gate_i * tb[min(max(j - i + T - 1, 0), 2 * T - 2)] * kLog2e;
           if (j >= len) x += -10000.0f * kLog2e;
-          float pe = (j < T) ? exp2f(x - m2) : 0.f;
+          float pe = (j < T) ? fast_exp2(x - m2) : 0.f;
           lsum += pe;
           if (p.drop_p > 0.f) pe *= dropout_scale(p.seed, drop_row + (unsigned long long)j, thresh, inv_keep);
           pv[u] = pe;
@@ -304,50 +310,68 @@ __global__ void __launch_bounds__(256)
   }
 }
 
-// dq32 (M, inner) fp32 accumulator -> bf16 Q slot of dqkv, and clear the accumulator for the next layer
-__global__ void attn_dq_convert_kernel(float* __restrict__ dq32, bf16* __restrict__ dqkv, long long M, int inner) {
-  const long long n4 = M * inner / 4;
-  for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < n4; v += (long long)gridDim.x * blockDim.x) {
-    float4 f = reinterpret_cast<float4*>(dq32)[v];
-    reinterpret_cast<float4*>(dq32)[v] = make_float4(0.f, 0.f, 0.f, 0.f);
-    const long long e = v * 4;
-    const long long row = e / inner;
-    const int col = (int)(e - row * inner);
-    uint2 u;
-    u.x = pack_bf16x2(f.x, f.y);
-    u.y = pack_bf16x2(f.z, f.w);
-    *reinterpret_cast<uint2*>(dqkv + row * (3LL * inner) + 2 * inner + col) = u;
+// dq32 (M, inner) fp32 accumulator -> bf16 Q slot of dqkv, and clear the accumulator for the next layer.
+// One thread per 8 consecutive columns (32-byte load, 32-byte zero store, 16-byte bf16 store); blockIdx.y walks rows.
+__global__ void __launch_bounds__(256)
+    attn_dq_convert_kernel(float* __restrict__ dq32, bf16* __restrict__ dqkv, long long M, int inner) {
+  const int c8 = blockIdx.x * blockDim.x + threadIdx.x;  // group of 8 columns
+  if (c8 * 8 >= inner) return;
+  const uint32_t zero[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+  for (long long row = blockIdx.y; row < M; row += gridDim.y) {
+    float* src = dq32 + row * inner + c8 * 8;
+    uint32_t v[8];
+    asm volatile("ld.global.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+                 : "l"(src)
+                 : "memory");
+    stg_256(src, zero);
+    uint4 u;
+    u.x = pack_bf16x2(__uint_as_float(v[0]), __uint_as_float(v[1]));
+    u.y = pack_bf16x2(__uint_as_float(v[2]), __uint_as_float(v[3]));
+    u.z = pack_bf16x2(__uint_as_float(v[4]), __uint_as_float(v[5]));
+    u.w = pack_bf16x2(__uint_as_float(v[6]), __uint_as_float(v[7]));
+    *reinterpret_cast<uint4*>(dqkv + row * (3LL * inner) + 2 * inner + c8 * 8) = u;
   }
 }
 
 // ------------------------------------------------------------------------------------------------------------
 // backward, step 2: one CTA per (key tile, head, utterance); loops over the query tiles
 // ------------------------------------------------------------------------------------------------------------
+constexpr int BWD_THREADS = 256;                         // 8 warps: two per TMEM lane quadrant, each half the columns
 constexpr int BWD_SK = 0;                                // K    [128 j][64]            16 KB
 constexpr int BWD_SV = BWD_SK + ATT_BK * ATT_D * 2;      // V    [128 j][64]            16 KB
-constexpr int BWD_SQ = BWD_SV + ATT_BK * ATT_D * 2;      // Q    [128 i][64]            16 KB
-constexpr int BWD_SDO = BWD_SQ + ATT_BQ * ATT_D * 2;     // dO   [128 i][64]            16 KB
-constexpr int BWD_SP = BWD_SDO + ATT_BQ * ATT_D * 2;     // Pd   2 x [128 i][64 j]      32 KB
+constexpr int BWD_SQ = BWD_SV + ATT_BK * ATT_D * 2;      // Q    2 x [128 i][64]        32 KB (double buffered)
+constexpr int BWD_SDO = BWD_SQ + 2 * ATT_BQ * ATT_D * 2; // dO   2 x [128 i][64]        32 KB
+constexpr int BWD_SP = BWD_SDO + 2 * ATT_BQ * ATT_D * 2; // Pd   2 x [128 i][64 j]      32 KB
 constexpr int BWD_SDS = BWD_SP + ATT_BQ * ATT_BK * 2;    // dS   2 x [128 i][64 j]      32 KB
 constexpr int BWD_TB = BWD_SDS + ATT_BQ * ATT_BK * 2;    // bias table (2T-1 floats)     8 KB
 constexpr int BWD_HIST = BWD_TB + 2048 * 4;              // embedding-gradient histogram 4 KB
 constexpr int BWD_BAR = BWD_HIST + 1024 * 4;
 constexpr int BWD_SMEM = BWD_BAR + 64 + 1024;
 
-__global__ void __launch_bounds__(128, 1)
+// Pipeline per query tile qt (tensor core work is issued by thread 0, everything else by all 8 warps):
+//   S = Q K^T, dP = dO V^T (TMEM)  ->  P, dS (registers -> bf16 tiles in smem)  ->  dV += P^T dO, dK += dS^T Q,
+//   dQ = dS K (TMEM)  ->  dQ accumulated into the fp32 buffer with 16-byte vector reductions.
+// S / dP of tile qt+1 are issued right behind the gradient MMAs of tile qt (Q / dO are double buffered), so the
+// tensor core works on them while the warps drain dQ.
+__global__ void __launch_bounds__(BWD_THREADS, 1)
     attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
-                    const AttnParams p, const float* __restrict__ lse, const float* __restrict__ delta,
-                    float* __restrict__ dq32, bf16* __restrict__ dqkv, float* __restrict__ dgate,
-                    float* __restrict__ demb, int num_buckets) {
+                    const __grid_constant__ AttnParams p, const float* __restrict__ lse,
+                    const float* __restrict__ delta, float* __restrict__ dq32, bf16* __restrict__ dqkv,
+                    float* __restrict__ dgate, float* __restrict__ demb, int num_buckets) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* gbase = smem_raw + (sbase - smem_u32(smem_raw));
   const uint32_t sK = sbase + BWD_SK, sV = sbase + BWD_SV, sQ = sbase + BWD_SQ, sDO = sbase + BWD_SDO,
                  sP = sbase + BWD_SP, sDS = sbase + BWD_SDS;
+  constexpr uint32_t QBUF = ATT_BQ * ATT_D * 2;  // bytes of one Q / dO buffer
   float* tb = reinterpret_cast<float*>(gbase + BWD_TB);
   float* hist = reinterpret_cast<float*>(gbase + BWD_HIST);
-  const uint32_t bar_kv = sbase + BWD_BAR, bar_qdo = bar_kv + 8, bar_mma = bar_kv + 16, tmem_slot = bar_kv + 24;
-  const int tid = threadIdx.x, warp = tid >> 5;
+  const uint32_t bar_kv = sbase + BWD_BAR, bar_qdo = bar_kv + 8 /* [2] */, bar_s = bar_kv + 24, bar_g = bar_kv + 32,
+                 tmem_slot = bar_kv + 40;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int quad = warp & 3, half = warp >> 2;
+  const int rit = quad * 32 + lane;  // row of this thread inside a 128-row tile
   const int kt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int T = p.T;
   const int k0 = kt * ATT_BK;
@@ -356,7 +380,9 @@ __global__ void __launch_bounds__(128, 1)
   if (tid == 0) {
     mbar_init(bar_kv, 1);
     mbar_init(bar_qdo, 1);
-    mbar_init(bar_mma, 1);
+    mbar_init(bar_qdo + 8, 1);
+    mbar_init(bar_s, 1);
+    mbar_init(bar_g, 1);
     mbar_fence_init();
     tma_prefetch_desc(&tmQKV);
     tma_prefetch_desc(&tmDO);
@@ -369,9 +395,10 @@ __global__ void __launch_bounds__(128, 1)
   int htot = h;
   if (p.emb) {
     htot = p.head_index ? p.head_index[h] : h;
-    for (int r = tid; r < 2 * T - 1; r += 128) tb[r] = __ldg(p.emb + (long long)p.rel_table[r] * p.Htot + htot);
+    for (int r = tid; r < 2 * T - 1; r += BWD_THREADS)
+      tb[r] = __ldg(p.emb + (long long)p.rel_table[r] * p.Htot + htot);
     if (demb)
-      for (int r = tid; r < num_buckets; r += 128) hist[r] = 0.f;
+      for (int r = tid; r < num_buckets; r += BWD_THREADS) hist[r] = 0.f;
   }
   tc_fence_before();
   __syncthreads();
@@ -380,43 +407,52 @@ __global__ void __launch_bounds__(128, 1)
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
   const uint32_t tS = tmem_base, tP = tmem_base + 128, tdV = tmem_base + 256, tdK = tmem_base + 320,
                  tdQ = tmem_base + 384;
-  const uint32_t lane_off = ((uint32_t)(warp * 32)) << 16;
+  const uint32_t lane_off = ((uint32_t)(quad * 32)) << 16;
+  constexpr uint32_t idesc_s = make_idesc_bf16(ATT_BQ, ATT_BK, false, false);   // S, dP : K-major x K-major
+  constexpr uint32_t idesc_kv = make_idesc_bf16(ATT_BK, ATT_D, true, true);     // dV, dK: A^T (MN-major) x MN-major
+  constexpr uint32_t idesc_q = make_idesc_bf16(ATT_BQ, ATT_D, false, true);     // dQ    : K-major x MN-major
+
+  auto load_qdo = [&](int qt) {  // thread 0 only
+    const uint32_t buf = (uint32_t)(qt & 1);
+    mbar_expect_tx(bar_qdo + 8 * buf, 2 * ATT_BQ * ATT_D * 2);
+    tma_load_2d(sQ + buf * QBUF, &tmQKV, bar_qdo + 8 * buf, 2 * p.inner + h * ATT_D, b * T + qt * ATT_BQ);
+    tma_load_2d(sDO + buf * QBUF, &tmDO, bar_qdo + 8 * buf, h * ATT_D, b * T + qt * ATT_BQ);
+  };
+  auto issue_scores = [&](int qt) {  // thread 0 only: S and dP of query tile qt
+    const uint32_t buf = (uint32_t)(qt & 1);
+    mbar_wait(bar_qdo + 8 * buf, (uint32_t)((qt >> 1) & 1));
+    tc_fence_after();
+#pragma unroll
+    for (int k = 0; k < ATT_D / 16; ++k)
+      umma_f16_ss(tS, make_smem_desc(sQ + buf * QBUF + k * 32, 0, 1024, 2), make_smem_desc(sK + k * 32, 0, 1024, 2),
+                  idesc_s, k > 0 ? 1u : 0u);
+#pragma unroll
+    for (int k = 0; k < ATT_D / 16; ++k)
+      umma_f16_ss(tP, make_smem_desc(sDO + buf * QBUF + k * 32, 0, 1024, 2), make_smem_desc(sV + k * 32, 0, 1024, 2),
+                  idesc_s, k > 0 ? 1u : 0u);
+    umma_commit(bar_s);
+  };
 
   if (tid == 0) {
     mbar_expect_tx(bar_kv, 2 * ATT_BK * ATT_D * 2);
     tma_load_2d(sK, &tmQKV, bar_kv, h * ATT_D, b * T + k0);
     tma_load_2d(sV, &tmQKV, bar_kv, p.inner + h * ATT_D, b * T + k0);
-    mbar_expect_tx(bar_qdo, 2 * ATT_BQ * ATT_D * 2);
-    tma_load_2d(sQ, &tmQKV, bar_qdo, 2 * p.inner + h * ATT_D, b * T);
-    tma_load_2d(sDO, &tmDO, bar_qdo, h * ATT_D, b * T);
+    load_qdo(0);
+    if (nq > 1) load_qdo(1);
+    mbar_wait(bar_kv, 0);
+    issue_scores(0);
   }
   const int len = p.lengths ? (int)p.lengths[b] : T;
   const uint32_t thresh = (uint32_t)(p.drop_p * 4294967296.0);
   const float inv_keep = p.drop_p > 0.f ? 1.f / (1.f - p.drop_p) : 1.f;
   const float sc2 = p.scale * kLog2e;
   const float hm = p.head_mask ? __ldg(p.head_mask + h) : 1.f;
-  uint32_t mma_phase = 0;
-  constexpr uint32_t idesc_s = make_idesc_bf16(ATT_BQ, ATT_BK, false, false);   // S, dP : K-major x K-major
-  constexpr uint32_t idesc_kv = make_idesc_bf16(ATT_BK, ATT_D, true, true);     // dV, dK: A^T (MN-major) x MN-major
-  constexpr uint32_t idesc_q = make_idesc_bf16(ATT_BQ, ATT_D, false, true);     // dQ    : K-major x MN-major
 
   for (int qt = 0; qt < nq; ++qt) {
+    const uint32_t buf = (uint32_t)(qt & 1);
+    const uint32_t ph = (uint32_t)(qt & 1);
     const int q0 = qt * ATT_BQ;
-    const int i = q0 + tid;
-    if (tid == 0) {
-      if (qt == 0) mbar_wait(bar_kv, 0);
-      mbar_wait(bar_qdo, (uint32_t)(qt & 1));
-      tc_fence_after();
-#pragma unroll
-      for (int k = 0; k < ATT_D / 16; ++k)
-        umma_f16_ss(tS, make_smem_desc(sQ + k * 32, 0, 1024, 2), make_smem_desc(sK + k * 32, 0, 1024, 2), idesc_s,
-                    k > 0 ? 1u : 0u);
-#pragma unroll
-      for (int k = 0; k < ATT_D / 16; ++k)
-        umma_f16_ss(tP, make_smem_desc(sDO + k * 32, 0, 1024, 2), make_smem_desc(sV + k * 32, 0, 1024, 2), idesc_s,
-                    k > 0 ? 1u : 0u);
-      umma_commit(bar_mma);
-    }
+    const int i = q0 + rit;
     float L2 = 0.f, dl = 0.f, gate_i = 1.f;
     const bool row_ok = i < T;
     if (row_ok) {
@@ -426,12 +462,12 @@ __global__ void __launch_bounds__(128, 1)
       if (p.emb && p.gate) gate_i = p.gate[((long long)b * p.Htot + htot) * T + i];
     }
     const unsigned long long drop_row = ((unsigned long long)(b * p.H + h) * T + (unsigned long long)i) * T;
-    mbar_wait(bar_mma, mma_phase);
-    mma_phase ^= 1u;
+    mbar_wait(bar_s, ph);
     tc_fence_after();
     float dg = 0.f;
 #pragma unroll 1
-    for (int c = 0; c < ATT_BK / 32; ++c) {
+    for (int cc = 0; cc < 2; ++cc) {
+      const int c = half * 2 + cc;  // 32-key chunk of this warp
       uint32_t rs[32], rp[32];
       tmem_ld_32x32(tS + lane_off + c * 32, rs);
       tmem_ld_32x32(tP + lane_off + c * 32, rp);
@@ -451,7 +487,7 @@ __global__ void __launch_bounds__(128, 1)
           }
           if (j >= len) x += -10000.0f * kLog2e;
           const bool ok = row_ok && (j < T);
-          const float pe = ok ? exp2f(x - L2) : 0.f;
+          const float pe = ok ? fast_exp2(x - L2) : 0.f;
           float ds_scale = 1.f;
           if (p.drop_p > 0.f) ds_scale = dropout_scale(p.seed, drop_row + (unsigned long long)j, thresh, inv_keep);
           const float dp = __uint_as_float(rp[jj + u]) * hm * ds_scale;  // d loss / d p_ij
@@ -469,7 +505,7 @@ __global__ void __launch_bounds__(128, 1)
       const uint32_t off = (uint32_t)(c >> 1) * (ATT_BQ * 128);
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
-        const uint32_t so = off + sw128(tid, (c & 1) * 4 + q);
+        const uint32_t so = off + sw128(rit, (c & 1) * 4 + q);
         asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sP + so), "r"(pk[4 * q]), "r"(pk[4 * q + 1]),
                      "r"(pk[4 * q + 2]), "r"(pk[4 * q + 3])
                      : "memory");
@@ -481,7 +517,7 @@ __global__ void __launch_bounds__(128, 1)
     if (dgate && p.emb && p.gate && row_ok) atomicAdd(dgate + ((long long)b * p.Htot + htot) * T + i, dg);
     fence_async_smem();
     tc_fence_before();
-    __syncthreads();
+    __syncthreads();  // P / dS complete, S / dP consumed, dQ of the previous tile drained
     if (tid == 0) {
       tc_fence_after();
 #pragma unroll
@@ -489,46 +525,41 @@ __global__ void __launch_bounds__(128, 1)
         const uint32_t acc = (qt > 0 || k > 0) ? 1u : 0u;
         // dV[j, e] += sum_i Pd[i, j] dO[i, e]
         umma_f16_ss(tdV, make_smem_desc(sP + k * 2048, ATT_BQ * 128, 1024, 2),
-                    make_smem_desc(sDO + k * 2048, ATT_BQ * 128, 1024, 2), idesc_kv, acc);
+                    make_smem_desc(sDO + buf * QBUF + k * 2048, ATT_BQ * 128, 1024, 2), idesc_kv, acc);
         // dK[j, e] += sum_i dS[i, j] Q[i, e]
         umma_f16_ss(tdK, make_smem_desc(sDS + k * 2048, ATT_BQ * 128, 1024, 2),
-                    make_smem_desc(sQ + k * 2048, ATT_BQ * 128, 1024, 2), idesc_kv, acc);
+                    make_smem_desc(sQ + buf * QBUF + k * 2048, ATT_BQ * 128, 1024, 2), idesc_kv, acc);
       }
 #pragma unroll
       for (int k = 0; k < ATT_BK / 16; ++k)  // dQ[i, e] = sum_j dS[i, j] K[j, e]
         umma_f16_ss(tdQ, make_smem_desc(sDS + (k >> 2) * (ATT_BQ * 128) + (k & 3) * 32, 0, 1024, 2),
                     make_smem_desc(sK + k * 2048, ATT_BK * 128, 1024, 2), idesc_q, k > 0 ? 1u : 0u);
-      umma_commit(bar_mma);
+      umma_commit(bar_g);
+      if (qt + 1 < nq) issue_scores(qt + 1);  // runs on the tensor core while the warps drain dQ below
     }
-    mbar_wait(bar_mma, mma_phase);
-    mma_phase ^= 1u;
+    mbar_wait(bar_g, ph);
     tc_fence_after();
-    if (tid == 0 && qt + 1 < nq) {
-      mbar_expect_tx(bar_qdo, 2 * ATT_BQ * ATT_D * 2);
-      tma_load_2d(sQ, &tmQKV, bar_qdo, 2 * p.inner + h * ATT_D, b * T + q0 + ATT_BQ);
-      tma_load_2d(sDO, &tmDO, bar_qdo, h * ATT_D, b * T + q0 + ATT_BQ);
-    }
-#pragma unroll
-    for (int c = 0; c < ATT_D / 32; ++c) {
+    if (tid == 0 && qt + 2 < nq) load_qdo(qt + 2);  // this tile's Q / dO buffer is free again
+    {
       uint32_t r[32];
-      tmem_ld_32x32(tdQ + lane_off + c * 32, r);
+      tmem_ld_32x32(tdQ + lane_off + half * 32, r);
       tmem_ld_wait();
       if (row_ok) {
-        float* dst = dq32 + ((long long)(b * T + i)) * p.inner + h * ATT_D + c * 32;
+        float* dst = dq32 + ((long long)(b * T + i)) * p.inner + h * ATT_D + half * 32;
 #pragma unroll
-        for (int jj = 0; jj < 32; ++jj) atomicAdd(dst + jj, __uint_as_float(r[jj]) * p.scale);
+        for (int jj = 0; jj < 32; jj += 4)
+          red_add_v4(dst + jj, __uint_as_float(r[jj]) * p.scale, __uint_as_float(r[jj + 1]) * p.scale,
+                     __uint_as_float(r[jj + 2]) * p.scale, __uint_as_float(r[jj + 3]) * p.scale);
       }
     }
-    tc_fence_before();
-    __syncthreads();
+    tc_fence_before();  // orders this thread's TMEM reads before the next tile's __syncthreads / MMAs
   }
-  // ---- epilogue: dV (x head mask) and dK (x scale) of this key tile
-  const int j = k0 + tid;
-#pragma unroll
-  for (int which = 0; which < 2; ++which) {
-    const uint32_t ta = which == 0 ? tdV : tdK;
-    const float mul = which == 0 ? hm : p.scale;
-    bf16* dst = dqkv + ((long long)(b * T + j)) * (3LL * p.inner) + (which == 0 ? p.inner : 0) + h * ATT_D;
+  // ---- epilogue: dV (x head mask, warps 0-3) and dK (x scale, warps 4-7) of this key tile
+  {
+    const int j = k0 + rit;
+    const uint32_t ta = half == 0 ? tdV : tdK;
+    const float mul = half == 0 ? hm : p.scale;
+    bf16* dst = dqkv + ((long long)(b * T + j)) * (3LL * p.inner) + (half == 0 ? p.inner : 0) + h * ATT_D;
 #pragma unroll
     for (int c = 0; c < ATT_D / 32; ++c) {
       uint32_t r[32];
@@ -549,7 +580,7 @@ __global__ void __launch_bounds__(128, 1)
   }
   if (demb && p.emb) {
     __syncthreads();
-    for (int r = tid; r < num_buckets; r += 128) {
+    for (int r = tid; r < num_buckets; r += BWD_THREADS) {
       const float v = hist[r];
       if (v != 0.f) atomicAdd(demb + (long long)r * p.Htot + htot, v);
     }
@@ -663,10 +694,13 @@ extern "C" int dph_attn_bwd(const void* qkv, const void* dctx, const void* o_un,
                                                                          dmask_h, B, H, T, inner);
   AttnParams p = attn_params(B, H, T, scale, lengths, rel_table, emb, gate, head_index, Htot, drop_p, seed, head_mask);
   dim3 grid((T + ATT_BK - 1) / ATT_BK, H, B);
-  attn_bwd_kernel<<<grid, 128, BWD_SMEM, s>>>(tmq, tmd, p, lse, delta, dq32, (bf16*)dqkv, dgate, demb, num_buckets);
-  long long n4 = M * inner / 4;
-  int cg = (int)((n4 + 255) / 256 < 148 * 8 ? (n4 + 255) / 256 : 148 * 8);
-  attn_dq_convert_kernel<<<cg, 256, 0, s>>>(dq32, (bf16*)dqkv, M, inner);
+  attn_bwd_kernel<<<grid, BWD_THREADS, BWD_SMEM, s>>>(tmq, tmd, p, lse, delta, dq32, (bf16*)dqkv, dgate, demb, num_buckets);
+  {
+    const int gx = (inner / 8 + 255) / 256;
+    long long gy = M < 148LL * 16 ? M : 148LL * 16;
+    attn_dq_convert_kernel<<<dim3(gx, (unsigned)gy), inner / 8 < 256 ? ((inner / 8 + 31) / 32) * 32 : 256, 0, s>>>(
+        dq32, (bf16*)dqkv, M, inner);
+  }
   dph_count_launch(3);
   return dph_check_last("attn_bwd");
 }

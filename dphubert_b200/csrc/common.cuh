@@ -88,12 +88,19 @@ DPH_DEVICE float block_sum(float v, float* red) {
 // backward pass can regenerate the identical keep mask.
 // `dph_rng_epoch` lives in device memory and is advanced by a one-thread kernel (dph_rng_advance) once per
 // training step, so a step captured in a CUDA graph (kernel arguments frozen) still draws fresh masks every replay.
+// 32-bit arithmetic only (64-bit multiplies cost ~4 instructions each on the integer pipe): the seed, the epoch and
+// the high half of the index fold into a key, the low half goes through the murmur3 finaliser.
 DPH_DEVICE uint32_t hash_u32(uint64_t seed, uint64_t idx) {
-  uint64_t z = seed + dph_rng_epoch * 0xD1B54A32D192ED03ull + idx * 0x9E3779B97F4A7C15ull + 0x632BE59BD9B4E019ull;
-  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
-  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
-  z = z ^ (z >> 31);
-  return (uint32_t)(z >> 32);
+  const uint64_t ep = dph_rng_epoch;
+  const uint32_t key = (uint32_t)seed ^ ((uint32_t)(seed >> 32) * 0x85EBCA6Bu) ^ ((uint32_t)ep * 0xC2B2AE35u) ^
+                       ((uint32_t)(ep >> 32) * 0x27D4EB2Fu) ^ ((uint32_t)(idx >> 32) * 0x165667B1u);
+  uint32_t x = (uint32_t)idx * 0x9E3779B1u + key;
+  x ^= x >> 16;
+  x *= 0x85EBCA6Bu;
+  x ^= x >> 13;
+  x *= 0xC2B2AE35u;
+  x ^= x >> 16;
+  return x;
 }
 // keep-probability test: returns scale (1/(1-p)) or 0.
 DPH_DEVICE float dropout_scale(uint64_t seed, uint64_t idx, uint32_t thresh, float inv_keep) {
