@@ -16,8 +16,9 @@ void set_error(const char* fmt, ...);
 // Thread block = 32 column groups (VEC columns each) x 8 row lanes; a block owns a strip of 32*VEC columns and a
 // contiguous chunk of rows.  Column partial sums are reduced across the 8 row lanes in shared memory and leave the
 // block as ONE line-wide RED per column (same-address float atomics serialise in L2: keep them few and coalesced).
-template <typename T, int VEC>
-__global__ void __launch_bounds__(256)
+// ZP = false: no pre-activation involved (plain dropout / gate scaling and the bias column sums), the cheap variant.
+template <typename T, int VEC, bool ZP>
+__global__ void __launch_bounds__(256, 3)
     epilogue_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ z, const float* __restrict__ colmask,
                         const float* __restrict__ scalar, T* __restrict__ dout, float* __restrict__ dmask,
                         float* __restrict__ dbias, float* __restrict__ dscalar, int rows, int C, int rows_per_blk,
@@ -41,39 +42,53 @@ __global__ void __launch_bounds__(256)
   float a_scalar = 0.f;
   const uint32_t thresh = (uint32_t)(drop_p * 4294967296.0);
   const float inv_keep = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
-  const bool need_z = (z != nullptr);
+  constexpr int RB = ZP ? 2 : 4;  // rows in flight per thread (independent loads issued back to back)
   if (active) {
-#pragma unroll 2
-    for (int r = r0 + ty; r < r1; r += 8) {
-      float d[VEC], zz[VEC];
-      const long long ioff = (long long)r * in_ld + c0;
-      if constexpr (VEC > 1) {
-        load_vec(dy + ioff, d);
-        if (need_z) load_vec(z + (long long)r * z_ld + c0, zz);
-      } else {
-        d[0] = to_f(dy[ioff]);
-        if (need_z) zz[0] = to_f(z[(long long)r * z_ld + c0]);
+    for (int rb = r0 + ty; rb < r1; rb += 8 * RB) {
+      float d[RB][VEC], zz[RB][VEC];
+#pragma unroll
+      for (int q = 0; q < RB; ++q) {
+        const int r = rb + 8 * q;
+        if (r < r1) {
+          const long long ioff = (long long)r * in_ld + c0;
+          if constexpr (VEC > 1) {
+            load_vec(dy + ioff, d[q]);
+            if constexpr (ZP) load_vec(z + (long long)r * z_ld + c0, zz[q]);
+          } else {
+            d[q][0] = to_f(dy[ioff]);
+            if constexpr (ZP) zz[q][0] = to_f(z[(long long)r * z_ld + c0]);
+          }
+        }
       }
 #pragma unroll
-      for (int j = 0; j < VEC; ++j) {
-        float ds = d[j];
-        if (drop_p > 0.f) ds *= dropout_scale(seed, (unsigned long long)r * C + c0 + j, thresh, inv_keep);
-        float az = need_z ? (act == 1 ? gelu_erf(zz[j]) : zz[j]) : 0.f;
-        a_scalar += ds * az * cm[j];
-        float dm = ds * sc;
-        a_mask[j] += dm * az;
-        float dv = dm * cm[j];
-        if (act == 1) dv *= gelu_erf_grad(zz[j]);
-        a_bias[j] += dv;
-        d[j] = dv;
-      }
-      if (dout) {
-        const int b = r / rows_per_batch, t = r - b * rows_per_batch;
-        const long long ooff = (long long)b * out_bs + (long long)(t + out_row_off) * C + c0;
-        if constexpr (VEC > 1) {
-          store_vec(dout + ooff, d);
-        } else {
-          dout[ooff] = from_f<T>(d[0]);
+      for (int q = 0; q < RB; ++q) {
+        const int r = rb + 8 * q;
+        if (r < r1) {
+#pragma unroll
+          for (int j = 0; j < VEC; ++j) {
+            float ds = d[q][j];
+            if (drop_p > 0.f) ds *= dropout_scale(seed, (unsigned long long)r * C + c0 + j, thresh, inv_keep);
+            const float dm = ds * sc;
+            float dv = dm * cm[j];
+            if constexpr (ZP) {
+              float az = zz[q][j], gz = 1.f;
+              if (act == 1) gelu_and_grad_fast(zz[q][j], az, gz);
+              a_scalar += ds * az * cm[j];
+              a_mask[j] += dm * az;
+              dv *= gz;
+            }
+            a_bias[j] += dv;
+            d[q][j] = dv;
+          }
+          if (dout) {
+            const int b = r / rows_per_batch, t = r - b * rows_per_batch;
+            const long long ooff = (long long)b * out_bs + (long long)(t + out_row_off) * C + c0;
+            if constexpr (VEC > 1) {
+              store_vec(dout + ooff, d[q]);
+            } else {
+              dout[ooff] = from_f<T>(d[q][0]);
+            }
+          }
         }
       }
     }
@@ -271,8 +286,10 @@ extern "C" int dph_epilogue_bwd(const void* dy, const void* z, const float* colm
   const int VECW = vec_ok ? vecw : 1;
   const int cols_per_blk = 32 * VECW;
   const int gx = (C + cols_per_blk - 1) / cols_per_blk;
-  int gy = (148 * 3 + gx - 1) / gx;          // ~3 CTAs of 256 threads per SM
-  const int max_gy = (rows + 15) / 16;       // at least 16 rows per CTA
+  const bool zp = (z != nullptr);
+  int gy = (148 * 3) / gx;                       // three resident CTAs of 256 threads per SM, one wave
+  (void)zp;
+  const int max_gy = (rows + 31) / 32;           // at least 32 rows (one 4-deep load batch per row lane) per CTA
   if (gy > max_gy) gy = max_gy;
   if (gy < 1) gy = 1;
   if (gy > 65535) gy = 65535;
@@ -280,9 +297,18 @@ extern "C" int dph_epilogue_bwd(const void* dy, const void* z, const float* colm
   gy = (rows + rows_per_blk - 1) / rows_per_blk;
   dim3 grid(gx, gy);
 #define EB_LAUNCH(T, V)                                                                                             \
-  epilogue_bwd_kernel<T, V><<<grid, 256, 0, s>>>((const T*)dy, (const T*)z, colmask, scalar, (T*)dout, dmask, dbias, \
-                                                 dscalar, rows, C, rows_per_blk, act, drop_p, seed, rows_per_batch,  \
-                                                 out_bs, out_row_off, in_ld, z_ld)
+  do {                                                                                                              \
+    if (zp)                                                                                                         \
+      epilogue_bwd_kernel<T, V, true><<<grid, 256, 0, s>>>((const T*)dy, (const T*)z, colmask, scalar, (T*)dout,    \
+                                                           dmask, dbias, dscalar, rows, C, rows_per_blk, act,      \
+                                                           drop_p, seed, rows_per_batch, out_bs, out_row_off,      \
+                                                           in_ld, z_ld);                                            \
+    else                                                                                                            \
+      epilogue_bwd_kernel<T, V, false><<<grid, 256, 0, s>>>((const T*)dy, (const T*)z, colmask, scalar, (T*)dout,   \
+                                                            dmask, dbias, dscalar, rows, C, rows_per_blk, act,     \
+                                                            drop_p, seed, rows_per_batch, out_bs, out_row_off,     \
+                                                            in_ld, z_ld);                                           \
+  } while (0)
   if (dtype == DPH_DTYPE_BF16) {
     if (vec_ok) EB_LAUNCH(bf16, 8);
     else EB_LAUNCH(bf16, 1);
