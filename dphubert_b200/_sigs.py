@@ -36,7 +36,7 @@ SIGS = {
     # conv0.cu
     "dph_conv0_stats": [vp, i64, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f32, vp],
     "dph_conv0_fwd": [vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp],
-    "dph_conv0_bwd": [vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32,
+    "dph_conv0_bwd": [vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32,
                       i32, i32, vp],
     "dph_wave_norm": [vp, i64, vp, i64, vp, i32, i32, f32, vp],
     # softmax.cu

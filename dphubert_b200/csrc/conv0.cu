@@ -89,37 +89,35 @@ __global__ void conv0_stats_kernel(const double* __restrict__ R, const float* __
 // ------------------------------------------------------------------------------------------------------------
 // forward apply
 // ------------------------------------------------------------------------------------------------------------
-template <typename T, bool FAST_GELU>
-DPH_DEVICE float gelu_sel(float x) {
-  return gelu_erf(x);
-}
+// Two adjacent channels per thread, every frame of the tile in turn: a warp writes 64 consecutive channels (128 B of
+// bf16) per frame, the 2 x k weights stay in registers, the waveform window is broadcast from shared memory.
+constexpr int C0A_TT = 256;  // frames per CTA
 
 template <typename T>
-__global__ void __launch_bounds__(C0_THREADS)
+__global__ void __launch_bounds__(C0_THREADS, 3)
     conv0_apply_kernel(const float* __restrict__ wave, long long wave_bs, const float* __restrict__ w,
                        const float* __restrict__ bias, const float* __restrict__ gamma, const float* __restrict__ beta,
                        const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ mask,
-                       T* __restrict__ y, int C, int k, int stride, int T1, int norm, int act, int vec_ok) {
-  __shared__ float sx[C0_TT * 8 + C0_MAXK + 8];
+                       T* __restrict__ y, int C, int k, int stride, int T1, int norm, int act, int pair_vec) {
+  __shared__ float sx[C0A_TT * 8 + C0_MAXK + 8];
   const int b = blockIdx.y;
-  const int t0 = blockIdx.x * C0_TT;
-  const int nt = min(C0_TT, T1 - t0);
+  const int t0 = blockIdx.x * C0A_TT;
+  const int nt = min(C0A_TT, T1 - t0);
   const float* x = wave + (long long)b * wave_bs + (long long)t0 * stride;
   const int nsamp = (nt - 1) * stride + k;
   for (int i = threadIdx.x; i < nsamp; i += blockDim.x) sx[i] = x[i];
   __syncthreads();
-  const int cg = threadIdx.x & 63, fl = threadIdx.x >> 6;
-  for (int cbase = 0; cbase < C; cbase += 512) {
-    const int c0 = cbase + cg * 8;
+  for (int cbase = 0; cbase < C; cbase += 2 * C0_THREADS) {
+    const int c0 = cbase + 2 * threadIdx.x;
     if (c0 >= C) continue;
-    float wr[8][C0_MAXK], scale[8], shift[8], mk[8];
+    float wr[2][C0_MAXK], scale[2], shift[2], mk[2];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
+    for (int j = 0; j < 2; ++j) {
       const int c = c0 + j;
       const bool ok = c < C;
 #pragma unroll
       for (int q = 0; q < C0_MAXK; ++q) wr[j][q] = (ok && q < k) ? __ldg(w + c * k + q) : 0.f;
-      float bb = (ok && bias) ? __ldg(bias + c) : 0.f;
+      const float bb = (ok && bias) ? __ldg(bias + c) : 0.f;
       if (norm && ok) {
         const float rs = rstd[b * C + c], mu = mean[b * C + c], g = __ldg(gamma + c);
         scale[j] = rs * g;
@@ -130,154 +128,71 @@ __global__ void __launch_bounds__(C0_THREADS)
       }
       mk[j] = (ok && mask) ? __ldg(mask + c) : 1.f;
     }
-    for (int tt = fl; tt < nt; tt += 4) {
+    const bool two = c0 + 1 < C;
+    T* dst = y + ((long long)b * T1 + t0) * C + c0;
+#pragma unroll 4
+    for (int tt = 0; tt < nt; ++tt, dst += C) {
       float xs[C0_MAXK];
 #pragma unroll
       for (int q = 0; q < C0_MAXK; ++q) xs[q] = (q < k) ? sx[tt * stride + q] : 0.f;
-      float o[8];
+      float o[2];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
+      for (int j = 0; j < 2; ++j) {
         float z = 0.f;
 #pragma unroll
         for (int q = 0; q < C0_MAXK; ++q) z = fmaf(wr[j][q], xs[q], z);
         float u = fmaf(z, scale[j], shift[j]);
-        if (act) u = gelu_erf(u);
+        if (act) u = gelu_erf_fast(u);
         o[j] = u * mk[j];
       }
-      T* dst = y + ((long long)b * T1 + t0 + tt) * C + c0;
-      if (vec_ok) {
-        if constexpr (sizeof(T) == 2) {
-          store_vec(reinterpret_cast<bf16*>(dst), o);
+      if constexpr (sizeof(T) == 2) {
+        if (pair_vec && two) {
+          *reinterpret_cast<uint32_t*>(dst) = pack_bf16x2(o[0], o[1]);
         } else {
-          float lo[4] = {o[0], o[1], o[2], o[3]}, hi[4] = {o[4], o[5], o[6], o[7]};
-          store_vec(reinterpret_cast<float*>(dst), lo);
-          store_vec(reinterpret_cast<float*>(dst) + 4, hi);
+          dst[0] = from_f<T>(o[0]);
+          if (two) dst[1] = from_f<T>(o[1]);
         }
       } else {
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if (c0 + j < C) dst[j] = from_f<T>(o[j]);
+        dst[0] = from_f<T>(o[0]);
+        if (two) dst[1] = from_f<T>(o[1]);
       }
     }
   }
 }
 
 // ------------------------------------------------------------------------------------------------------------
-// backward pass 1: per (b, c) sums  A = sum_t du,  Bq = sum_t du * yn,  and dmask partial  sum dy * act(u)
-//   u = yn * gamma + beta,  du = dy * mask * act'(u)
+// Single-pass backward (used whenever the waveform moments of the forward pass are available).
+//   du = dy * mask * act'(u),  yn = (w.x + bias - mean) * rstd,  u = yn * gamma + beta
+// GroupNorm's backward  dz = rstd * gamma * (du - A/T - yn * Bq/T)  needs the full-utterance sums A = sum du and
+// Bq = sum du * yn before the weight gradient  dW[c,q] = sum_t dz * x[s t + q]  can be formed -- but dW is linear in
+// them:  dW = rstd * gamma * (S1 - (A/T) Sx - (Bq/T) S3)  with  S1[c,q] = sum_t du x_q  (accumulated here, in the
+// same pass as A and Bq),  Sx[q] = sum_t x_q  and  S3[c,q] = sum_t yn x_q = rstd * (sum_p w_p R[p,q] + (bias - mean)
+// Sx[q]),  both of which follow from the 65 fp64 waveform moments R of the forward pass.  dy is read once.
+// scratch layout: per (b, c) 16 floats  [A, Bq, S1[0..9], unused x4].
 // ------------------------------------------------------------------------------------------------------------
-template <typename T>
-__global__ void __launch_bounds__(C0_THREADS)
-    conv0_bwd_reduce_kernel(const float* __restrict__ wave, long long wave_bs, const float* __restrict__ w,
-                            const float* __restrict__ bias, const float* __restrict__ gamma,
-                            const float* __restrict__ beta, const float* __restrict__ mean,
-                            const float* __restrict__ rstd, const float* __restrict__ mask, const T* __restrict__ dy,
-                            float* __restrict__ sumA, float* __restrict__ sumB, float* __restrict__ dmask, int C, int k,
-                            int stride, int T1, int norm, int act, int vec_ok) {
-  __shared__ float sx[C0_TT * 8 + C0_MAXK + 8];
-  const int b = blockIdx.y;
-  const int t0 = blockIdx.x * C0_TT;
-  const int nt = min(C0_TT, T1 - t0);
-  const float* x = wave + (long long)b * wave_bs + (long long)t0 * stride;
-  const int nsamp = (nt - 1) * stride + k;
-  for (int i = threadIdx.x; i < nsamp; i += blockDim.x) sx[i] = x[i];
-  __syncthreads();
-  const int cg = threadIdx.x & 63, fl = threadIdx.x >> 6;
-  for (int cbase = 0; cbase < C; cbase += 512) {
-    const int c0 = cbase + cg * 8;
-    if (c0 >= C) continue;
-    float wr[8][C0_MAXK], nsc[8], nsh[8], gm[8], bt[8], mk[8];
-    float aA[8], aB[8], aM[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int c = c0 + j;
-      const bool ok = c < C;
-#pragma unroll
-      for (int q = 0; q < C0_MAXK; ++q) wr[j][q] = (ok && q < k) ? __ldg(w + c * k + q) : 0.f;
-      float bb = (ok && bias) ? __ldg(bias + c) : 0.f;
-      if (norm && ok) {
-        const float rs = rstd[b * C + c], mu = mean[b * C + c];
-        nsc[j] = rs;
-        nsh[j] = (bb - mu) * rs;
-        gm[j] = __ldg(gamma + c);
-        bt[j] = __ldg(beta + c);
-      } else {
-        nsc[j] = 1.f;
-        nsh[j] = bb;
-        gm[j] = 1.f;
-        bt[j] = 0.f;
-      }
-      mk[j] = (ok && mask) ? __ldg(mask + c) : 1.f;
-      aA[j] = aB[j] = aM[j] = 0.f;
-    }
-    for (int tt = fl; tt < nt; tt += 4) {
-      float xs[C0_MAXK];
-#pragma unroll
-      for (int q = 0; q < C0_MAXK; ++q) xs[q] = (q < k) ? sx[tt * stride + q] : 0.f;
-      float d[8];
-      const T* src = dy + ((long long)b * T1 + t0 + tt) * C + c0;
-      if (vec_ok) {
-        if constexpr (sizeof(T) == 2) {
-          load_vec(reinterpret_cast<const bf16*>(src), d);
-        } else {
-          load_vec_f32(reinterpret_cast<const float*>(src), d);
-        }
-      } else {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) d[j] = (c0 + j < C) ? to_f(src[j]) : 0.f;
-      }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        float z = 0.f;
-#pragma unroll
-        for (int q = 0; q < C0_MAXK; ++q) z = fmaf(wr[j][q], xs[q], z);
-        const float yn = fmaf(z, nsc[j], nsh[j]);
-        const float u = fmaf(yn, gm[j], bt[j]);
-        const float au = act ? gelu_erf(u) : u;
-        aM[j] += d[j] * au;
-        const float du = d[j] * mk[j] * (act ? gelu_erf_grad(u) : 1.f);
-        aA[j] += du;
-        aB[j] += du * yn;
-      }
-    }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int c = c0 + j;
-      if (c < C) {
-        atomicAdd(sumA + b * C + c, aA[j]);
-        atomicAdd(sumB + b * C + c, aB[j]);
-        if (dmask) atomicAdd(dmask + c, aM[j]);
-      }
-    }
-  }
-}
+constexpr int C0F_TT = 256;  // frames per CTA
 
-// ------------------------------------------------------------------------------------------------------------
-// backward pass 2: dz = rstd * gamma * (du - A/T1 - yn * Bq/T1);  dW[c,q] += sum_t dz * x[s t + q];  dbias += sum dz
-// ------------------------------------------------------------------------------------------------------------
 template <typename T>
-__global__ void __launch_bounds__(C0_THREADS)
-    conv0_bwd_wgrad_kernel(const float* __restrict__ wave, long long wave_bs, const float* __restrict__ w,
+__global__ void __launch_bounds__(C0_THREADS, 3)
+    conv0_bwd_fused_kernel(const float* __restrict__ wave, long long wave_bs, const float* __restrict__ w,
                            const float* __restrict__ bias, const float* __restrict__ gamma,
                            const float* __restrict__ beta, const float* __restrict__ mean,
                            const float* __restrict__ rstd, const float* __restrict__ mask, const T* __restrict__ dy,
-                           const float* __restrict__ sumA, const float* __restrict__ sumB, float* __restrict__ dW,
-                           float* __restrict__ dbias, int C, int k, int stride, int T1, int norm, int act, int vec_ok) {
-  __shared__ float sx[C0_TT * 8 + C0_MAXK + 8];
+                           float* __restrict__ scratch, float* __restrict__ dmask, int C, int k, int stride, int T1,
+                           int norm, int act, int pair_vec) {
+  __shared__ float sx[C0F_TT * 8 + C0_MAXK + 8];
   const int b = blockIdx.y;
-  const int t0 = blockIdx.x * C0_TT;
-  const int nt = min(C0_TT, T1 - t0);
+  const int t0 = blockIdx.x * C0F_TT;
+  const int nt = min(C0F_TT, T1 - t0);
   const float* x = wave + (long long)b * wave_bs + (long long)t0 * stride;
   const int nsamp = (nt - 1) * stride + k;
   for (int i = threadIdx.x; i < nsamp; i += blockDim.x) sx[i] = x[i];
   __syncthreads();
-  const float invT = 1.f / (float)T1;
-  // 2 adjacent channels per thread: a warp reads 64 consecutive channels (128 B of bf16) per frame, and the
-  // 2 x k weight-gradient accumulators stay in registers across all frames of the tile.
+  // 2 adjacent channels per thread: a warp reads 64 consecutive channels (128 B of bf16) per frame
   for (int cbase = 0; cbase < C; cbase += 2 * C0_THREADS) {
     const int c0 = cbase + 2 * threadIdx.x;
     if (c0 >= C) continue;
-    float wr[2][C0_MAXK], acc[2][C0_MAXK], nsc[2], nsh[2], gm[2], bt[2], mA[2], mB[2], rs[2], mk[2], accb[2];
+    float wr[2][C0_MAXK], s1[2][C0_MAXK], nsc[2], nsh[2], gm[2], bt[2], mk[2], aA[2], aB[2], aM[2];
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
       const int c = c0 + j;
@@ -285,42 +200,40 @@ __global__ void __launch_bounds__(C0_THREADS)
 #pragma unroll
       for (int q = 0; q < C0_MAXK; ++q) {
         wr[j][q] = (ok && q < k) ? __ldg(w + c * k + q) : 0.f;
-        acc[j][q] = 0.f;
+        s1[j][q] = 0.f;
       }
       const float bb = (ok && bias) ? __ldg(bias + c) : 0.f;
-      nsc[j] = 1.f; nsh[j] = bb; gm[j] = 1.f; bt[j] = 0.f; mA[j] = 0.f; mB[j] = 0.f; rs[j] = 1.f;
+      nsc[j] = 1.f; nsh[j] = bb; gm[j] = 1.f; bt[j] = 0.f;
       if (norm && ok) {
-        rs[j] = rstd[b * C + c];
-        const float mu = mean[b * C + c];
-        nsc[j] = rs[j];
-        nsh[j] = (bb - mu) * rs[j];
+        const float rs = rstd[b * C + c], mu = mean[b * C + c];
+        nsc[j] = rs;
+        nsh[j] = (bb - mu) * rs;
         gm[j] = __ldg(gamma + c);
         bt[j] = __ldg(beta + c);
-        mA[j] = sumA[b * C + c] * invT;
-        mB[j] = sumB[b * C + c] * invT;
       }
       mk[j] = (ok && mask) ? __ldg(mask + c) : 1.f;
-      accb[j] = 0.f;
+      aA[j] = aB[j] = aM[j] = 0.f;
     }
-    const bool pair_ok = vec_ok && (c0 + 1 < C);
-    for (int tt = 0; tt < nt; ++tt) {
+    const bool two = c0 + 1 < C;
+    const T* src = dy + ((long long)b * T1 + t0) * C + c0;
+#pragma unroll 2
+    for (int tt = 0; tt < nt; ++tt, src += C) {
       float xs[C0_MAXK];
 #pragma unroll
       for (int q = 0; q < C0_MAXK; ++q) xs[q] = (q < k) ? sx[tt * stride + q] : 0.f;
-      const T* src = dy + ((long long)b * T1 + t0 + tt) * C + c0;
       float d[2];
       if constexpr (sizeof(T) == 2) {
-        if (pair_ok) {
-          float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(src));
+        if (pair_vec && two) {
+          const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(src));
           d[0] = f.x;
           d[1] = f.y;
         } else {
           d[0] = to_f(src[0]);
-          d[1] = (c0 + 1 < C) ? to_f(src[1]) : 0.f;
+          d[1] = two ? to_f(src[1]) : 0.f;
         }
       } else {
         d[0] = to_f(src[0]);
-        d[1] = (c0 + 1 < C) ? to_f(src[1]) : 0.f;
+        d[1] = two ? to_f(src[1]) : 0.f;
       }
 #pragma unroll
       for (int j = 0; j < 2; ++j) {
@@ -329,36 +242,79 @@ __global__ void __launch_bounds__(C0_THREADS)
         for (int q = 0; q < C0_MAXK; ++q) z = fmaf(wr[j][q], xs[q], z);
         const float yn = fmaf(z, nsc[j], nsh[j]);
         const float u = fmaf(yn, gm[j], bt[j]);
-        const float du = d[j] * mk[j] * (act ? gelu_erf_grad(u) : 1.f);
-        const float dz = norm ? rs[j] * gm[j] * (du - mA[j] - yn * mB[j]) : du;
-        accb[j] += dz;
+        float au = u, gu = 1.f;
+        if (act) gelu_and_grad_fast(u, au, gu);
+        aM[j] = fmaf(d[j], au, aM[j]);
+        const float du = d[j] * mk[j] * gu;
+        aA[j] += du;
+        aB[j] = fmaf(du, yn, aB[j]);
 #pragma unroll
-        for (int q = 0; q < C0_MAXK; ++q) acc[j][q] = fmaf(dz, xs[q], acc[j][q]);
+        for (int q = 0; q < C0_MAXK; ++q) s1[j][q] = fmaf(du, xs[q], s1[j][q]);
       }
     }
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
       const int c = c0 + j;
       if (c < C) {
-        for (int q = 0; q < k; ++q) atomicAdd(dW + c * k + q, acc[j][q]);
-        if (dbias) atomicAdd(dbias + c, accb[j]);
+        float* o = scratch + ((long long)b * C + c) * 16;
+        red_add_v4(o, aA[j], aB[j], s1[j][0], s1[j][1]);
+        red_add_v4(o + 4, s1[j][2], s1[j][3], s1[j][4], s1[j][5]);
+        red_add_v4(o + 8, s1[j][6], s1[j][7], s1[j][8], s1[j][9]);
+        if (dmask) atomicAdd(dmask + c, aM[j]);
       }
     }
   }
 }
 
-// dgamma[c] += sum_b Bq[b,c];  dbeta[c] += sum_b A[b,c]
-__global__ void conv0_bwd_affine_kernel(const float* __restrict__ sumA, const float* __restrict__ sumB,
-                                        float* __restrict__ dgamma, float* __restrict__ dbeta, int B, int C) {
+// One thread per channel: fold the per-utterance sums into dW, dbias, dgamma, dbeta (fp64 arithmetic: the three terms
+// of dW cancel to leading order).
+__global__ void conv0_bwd_finalize_kernel(const float* __restrict__ scratch, const double* __restrict__ R,
+                                          const float* __restrict__ w, const float* __restrict__ bias,
+                                          const float* __restrict__ gamma, const float* __restrict__ mean,
+                                          const float* __restrict__ rstd, float* __restrict__ dW,
+                                          float* __restrict__ dbias, float* __restrict__ dgamma,
+                                          float* __restrict__ dbeta, int B, int C, int k, int T1, int norm) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
-  float a = 0.f, q = 0.f;
+  double dw[C0_MAXK];
+  for (int q = 0; q < C0_MAXK; ++q) dw[q] = 0.0;
+  double db = 0.0, dg = 0.0, dbt = 0.0;
+  const double invT = 1.0 / (double)T1;
   for (int b = 0; b < B; ++b) {
-    a += sumA[b * C + c];
-    q += sumB[b * C + c];
+    const float* s = scratch + ((long long)b * C + c) * 16;
+    const double A = s[0], Bq = s[1];
+    if (!norm) {
+      for (int q = 0; q < k; ++q) dw[q] += (double)s[2 + q];
+      db += A;
+      continue;
+    }
+    const double* r = R + (long long)b * C0_NR;
+    const double rs = rstd[b * C + c], g = gamma[c];
+    const double shift = (bias ? (double)bias[c] : 0.0) - (double)mean[b * C + c];
+    // second moments as a full symmetric matrix lookup: R2(p, q), p <= q stored row by row after the 10 first moments
+    auto r2 = [&](int p_, int q_) {
+      const int lo = p_ < q_ ? p_ : q_, hi = p_ < q_ ? q_ : p_;
+      // offset of row lo in the packed upper triangle of a C0_MAXK x C0_MAXK matrix
+      const int off = lo * C0_MAXK - lo * (lo - 1) / 2;
+      return r[C0_MAXK + off + (hi - lo)];
+    };
+    double syn = 0.0;  // sum_t yn (zero up to rounding)
+    for (int p_ = 0; p_ < k; ++p_) syn += (double)w[c * k + p_] * r[p_];
+    syn = rs * (syn + shift * (double)T1);
+    for (int q = 0; q < k; ++q) {
+      double wr2 = 0.0;
+      for (int p_ = 0; p_ < k; ++p_) wr2 += (double)w[c * k + p_] * r2(p_, q);
+      const double s3 = rs * (wr2 + shift * r[q]);
+      dw[q] += rs * g * ((double)s[2 + q] - A * invT * r[q] - Bq * invT * s3);
+    }
+    db += rs * g * (A - A - Bq * invT * syn);
+    dg += Bq;
+    dbt += A;
   }
-  if (dgamma) atomicAdd(dgamma + c, q);
-  if (dbeta) atomicAdd(dbeta + c, a);
+  for (int q = 0; q < k; ++q) atomicAdd(dW + c * k + q, (float)dw[q]);
+  if (dbias) atomicAdd(dbias + c, (float)db);
+  if (norm && dgamma) atomicAdd(dgamma + c, (float)dg);
+  if (norm && dbeta) atomicAdd(dbeta + c, (float)dbt);
 }
 
 
@@ -437,57 +393,46 @@ extern "C" int dph_conv0_fwd(const float* wave, int64_t wave_bs, const float* w,
   int rc = conv0_check(C, k, stride, T1);
   if (rc) return rc;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  dim3 grid((T1 + C0_TT - 1) / C0_TT, B);
-  const int vec_ok = (C % 8 == 0) && ((reinterpret_cast<uintptr_t>(y) & 15) == 0);
+  dim3 grid((T1 + C0A_TT - 1) / C0A_TT, B);
+  const int pair_vec = (C % 2 == 0) && ((reinterpret_cast<uintptr_t>(y) & 3) == 0);
   if (dtype == DPH_DTYPE_BF16)
     conv0_apply_kernel<bf16><<<grid, C0_THREADS, 0, s>>>(wave, wave_bs, w, bias, gamma, beta, mean, rstd, mask,
-                                                         (bf16*)y, C, k, stride, T1, norm, act, vec_ok);
+                                                         (bf16*)y, C, k, stride, T1, norm, act, pair_vec);
   else
     conv0_apply_kernel<float><<<grid, C0_THREADS, 0, s>>>(wave, wave_bs, w, bias, gamma, beta, mean, rstd, mask,
-                                                          (float*)y, C, k, stride, T1, norm, act, vec_ok);
+                                                          (float*)y, C, k, stride, T1, norm, act, pair_vec);
   dph_count_launch();
   return dph_check_last("conv0_fwd");
 }
 
-// scratch: 2 * B * C floats (sumA, sumB), zeroed here.
+// scratch: 16 * B * C floats (per (b, c): A, Bq, S1[10], pad), zeroed here. `moments` = the (B, 65) fp64 waveform
+// moments dph_conv0_stats produced for the forward pass (required when norm != 0).
 extern "C" int dph_conv0_bwd(const float* wave, int64_t wave_bs, const float* w, const float* bias, const float* gamma,
-                             const float* beta, const float* mean, const float* rstd, const float* mask, const void* dy,
-                             float* scratch, float* dW, float* dbias, float* dgamma, float* dbeta, float* dmask, int B,
-                             int C, int k, int stride, int T1, int norm, int act, int dtype, void* stream) {
+                             const float* beta, const float* mean, const float* rstd, const double* moments,
+                             const float* mask, const void* dy, float* scratch, float* dW, float* dbias, float* dgamma,
+                             float* dbeta, float* dmask, int B, int C, int k, int stride, int T1, int norm, int act,
+                             int dtype, void* stream) {
   int rc = conv0_check(C, k, stride, T1);
   if (rc) return rc;
+  if (norm && !moments) {
+    set_error("conv0_bwd: the GroupNorm backward needs the waveform moments of the forward pass");
+    return DPH_ERR_ARG;
+  }
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  dim3 grid((T1 + C0_TT - 1) / C0_TT, B);
-  const int vec_ok = (C % 8 == 0) && ((reinterpret_cast<uintptr_t>(dy) & 15) == 0);
-  float* sumA = scratch;
-  float* sumB = scratch + (size_t)B * C;
-  int launches = 0;
-  if (norm || dmask) {
-    cudaMemsetAsync(scratch, 0, sizeof(float) * 2 * B * C, s);
-    if (dtype == DPH_DTYPE_BF16)
-      conv0_bwd_reduce_kernel<bf16><<<grid, C0_THREADS, 0, s>>>(wave, wave_bs, w, bias, gamma, beta, mean, rstd, mask,
-                                                                (const bf16*)dy, sumA, sumB, dmask, C, k, stride, T1,
-                                                                norm, act, vec_ok);
-    else
-      conv0_bwd_reduce_kernel<float><<<grid, C0_THREADS, 0, s>>>(wave, wave_bs, w, bias, gamma, beta, mean, rstd, mask,
-                                                                 (const float*)dy, sumA, sumB, dmask, C, k, stride, T1,
-                                                                 norm, act, vec_ok);
-    ++launches;
-  }
+  dim3 grid((T1 + C0F_TT - 1) / C0F_TT, B);
+  const int pair_vec = (C % 2 == 0) && ((reinterpret_cast<uintptr_t>(dy) & 3) == 0);
+  cudaMemsetAsync(scratch, 0, sizeof(float) * 16 * (size_t)B * C, s);
   if (dtype == DPH_DTYPE_BF16)
-    conv0_bwd_wgrad_kernel<bf16><<<grid, C0_THREADS, 0, s>>>(wave, wave_bs, w, bias, gamma, beta, mean, rstd, mask,
-                                                             (const bf16*)dy, sumA, sumB, dW, dbias, C, k, stride, T1,
-                                                             norm, act, vec_ok);
+    conv0_bwd_fused_kernel<bf16><<<grid, C0_THREADS, 0, s>>>(wave, wave_bs, w, bias, gamma, beta, mean, rstd, mask,
+                                                             (const bf16*)dy, scratch, dmask, C, k, stride, T1, norm,
+                                                             act, pair_vec);
   else
-    conv0_bwd_wgrad_kernel<float><<<grid, C0_THREADS, 0, s>>>(wave, wave_bs, w, bias, gamma, beta, mean, rstd, mask,
-                                                              (const float*)dy, sumA, sumB, dW, dbias, C, k, stride, T1,
-                                                              norm, act, vec_ok);
-  ++launches;
-  if (norm && (dgamma || dbeta)) {
-    conv0_bwd_affine_kernel<<<(C + 127) / 128, 128, 0, s>>>(sumA, sumB, dgamma, dbeta, B, C);
-    ++launches;
-  }
-  dph_count_launch(launches);
+    conv0_bwd_fused_kernel<float><<<grid, C0_THREADS, 0, s>>>(wave, wave_bs, w, bias, gamma, beta, mean, rstd, mask,
+                                                              (const float*)dy, scratch, dmask, C, k, stride, T1, norm,
+                                                              act, pair_vec);
+  conv0_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, s>>>(scratch, moments, w, bias, gamma, mean, rstd, dW, dbias,
+                                                            dgamma, dbeta, B, C, k, T1, norm);
+  dph_count_launch(2);
   return dph_check_last("conv0_bwd");
 }
 

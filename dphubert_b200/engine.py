@@ -551,7 +551,7 @@ def conv_stack_fwd(plan: Plan, wave, masks, save: bool, A=None):
                 ops.conv0_stats(wave, w, bias, moments, mean, rstd, B, Cout, k, s, Tout, ln.eps)
                 ops.conv0_fwd(wave, w, bias, plan.view(ln.weight), plan.view(ln.bias), mean, rstd, colmask, y, B, Cout,
                               k, s, Tout, 1, 1)
-                rec.update(mean=mean, rstd=rstd, mode="gn")
+                rec.update(mean=mean, rstd=rstd, moments=moments, mode="gn")
             elif ln is not None:
                 z = A("conv%d_z" % i, (B, Tout, Cout), dt)
                 ops.conv0_fwd(wave, w, bias, None, None, None, None, None, z, B, Cout, k, s, Tout, 0, 0)
@@ -672,20 +672,20 @@ def conv_stack_bwd(plan: Plan, st, dfeat, dmasks, A):
         wreq = conv.weight.requires_grad
         if i == 0:
             w = plan.view(conv.weight)
-            scratch = A("conv0_scratch", (2 * B * Cout,), torch.float32)
+            scratch = A("conv0_scratch", (16 * B * Cout,), torch.float32)
             if rec["mode"] == "gn":
-                ops.conv0_bwd(wave, w, bias, plan.view(ln.weight), plan.view(ln.bias), rec["mean"], rec["rstd"], colmask,
-                              dy, scratch, plan.gview(conv.weight), gbias, plan.gview(ln.weight), plan.gview(ln.bias),
+                ops.conv0_bwd(wave, w, bias, plan.view(ln.weight), plan.view(ln.bias), rec["mean"], rec["rstd"],
+                              rec["moments"], colmask, dy, scratch, plan.gview(conv.weight), gbias, plan.gview(ln.weight), plan.gview(ln.bias),
                               dm_out, B, Cout, k, s, Tout, 1, 1)
             elif rec["mode"] == "ln":
                 dz = A("conv0_dz", (B, Tout, Cout), dt)
                 ops.layernorm_bwd(dy, rec["z"], plan.view(ln.weight), plan.view(ln.bias), rec["mean"], rec["rstd"], dz,
                                   plan.gview(ln.weight), plan.gview(ln.bias), B * Tout, Cout, colmask=colmask,
                                   dmask=dm_out, act=1)
-                ops.conv0_bwd(wave, w, bias, None, None, None, None, None, dz, scratch, plan.gview(conv.weight), gbias,
+                ops.conv0_bwd(wave, w, bias, None, None, None, None, None, None, dz, scratch, plan.gview(conv.weight), gbias,
                               None, None, None, B, Cout, k, s, Tout, 0, 0)
             else:
-                ops.conv0_bwd(wave, w, bias, None, None, None, None, colmask, dy, scratch, plan.gview(conv.weight),
+                ops.conv0_bwd(wave, w, bias, None, None, None, None, None, colmask, dy, scratch, plan.gview(conv.weight),
                               gbias, None, None, dm_out, B, Cout, k, s, Tout, 0, 1)
         else:
             # dz in a per-utterance zero-padded row layout so the dgrad GEMM can read rows t'-j out of range

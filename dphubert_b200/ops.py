@@ -111,11 +111,13 @@ def conv0_fwd(wave, w, bias, gamma, beta, mean, rstd, mask, y, B, C, k, stride, 
           "dph_conv0_fwd")
 
 
-def conv0_bwd(wave, w, bias, gamma, beta, mean, rstd, mask, dy, scratch, dW, dbias, dgamma, dbeta, dmask, B, C, k, stride,
-              T1, norm, act):
+def conv0_bwd(wave, w, bias, gamma, beta, mean, rstd, moments, mask, dy, scratch, dW, dbias, dgamma, dbeta, dmask, B, C, k,
+              stride, T1, norm, act):
+    """`moments`: the (B*65,) fp64 buffer conv0_stats filled in the forward pass (GroupNorm mode); `scratch`: 16*B*C."""
     check(_L().dph_conv0_bwd(ptr(wave), wave.stride(0), ptr(w), ptr(bias), ptr(gamma), ptr(beta), ptr(mean), ptr(rstd),
-                             ptr(mask), ptr(dy), ptr(scratch), ptr(dW), ptr(dbias), ptr(dgamma), ptr(dbeta), ptr(dmask),
-                             B, C, k, stride, T1, norm, act, dtype_code(dy), stream_ptr()), "dph_conv0_bwd")
+                             ptr(moments), ptr(mask), ptr(dy), ptr(scratch), ptr(dW), ptr(dbias), ptr(dgamma),
+                             ptr(dbeta), ptr(dmask), B, C, k, stride, T1, norm, act, dtype_code(dy), stream_ptr()),
+          "dph_conv0_bwd")
 
 
 def wave_norm(wave, out, lengths, B, T0, eps=1e-5):

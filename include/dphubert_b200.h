@@ -141,10 +141,13 @@ int dph_conv0_stats(const float* wave, int64_t wave_bs, const float* w, const fl
 int dph_conv0_fwd(const float* wave, int64_t wave_bs, const float* w, const float* bias, const float* gamma,
                   const float* beta, const float* mean, const float* rstd, const float* mask, void* y, int B, int C, int k,
                   int stride, int T1, int norm, int act, int dtype, void* stream);
+/* backward in ONE pass over dy: per-(b, c) sums A, Bq, S1[q] = sum_t du x[s t + q] are accumulated together and the
+ * GroupNorm-corrected weight gradient is assembled from them and the forward pass's waveform moments. */
 int dph_conv0_bwd(const float* wave, int64_t wave_bs, const float* w, const float* bias, const float* gamma,
-                  const float* beta, const float* mean, const float* rstd, const float* mask, const void* dy,
-                  float* scratch /* 2*B*C */, float* dW, float* dbias, float* dgamma, float* dbeta, float* dmask, int B,
-                  int C, int k, int stride, int T1, int norm, int act, int dtype, void* stream);
+                  const float* beta, const float* mean, const float* rstd, const double* moments /* B*65, norm only */,
+                  const float* mask, const void* dy, float* scratch /* 16*B*C */, float* dW, float* dbias,
+                  float* dgamma, float* dbeta, float* dmask, int B, int C, int k, int stride, int T1, int norm, int act,
+                  int dtype, void* stream);
 int dph_wave_norm(const float* in, int64_t in_bs, float* out, int64_t out_bs, const int64_t* lengths, int B, int T0,
                   float eps, void* stream);
 

@@ -293,8 +293,8 @@ def conv0_fwd(wave, w, bias, gamma, beta, mean, rstd, mask, y, B, C, k, stride, 
     y.view(B, T1, C).copy_(z.transpose(1, 2))
 
 
-def conv0_bwd(wave, w, bias, gamma, beta, mean, rstd, mask, dy, scratch, dW, dbias, dgamma, dbeta, dmask, B, C, k, stride,
-              T1, norm, act):
+def conv0_bwd(wave, w, bias, gamma, beta, mean, rstd, moments, mask, dy, scratch, dW, dbias, dgamma, dbeta, dmask, B, C, k,
+              stride, T1, norm, act):
     z = _conv0_z(wave, w, bias, B, C, k, stride, T1)  # (B, C, T)
     d = _flat(dy)[: B * T1 * C].view(B, T1, C).float().transpose(1, 2)
     if norm:
