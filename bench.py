@@ -123,14 +123,18 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
 
 
-def run_reference(args, rank):
-    """The reference algorithm on the host cores: the CPU oracle (functional restatement of the reference's PyTorch
-    code, pinned against it by tests/golden) — the reference itself is Python and does not travel to the GPU box.
-    Each step = one full forward + backward of the same training step on a bounded sample of the workload."""
+def workload_string(name, workload, world):
+    return "%s teacher -> %s student, %s step (teacher fwd + student fwd/bwd + heads + loss%s + clip + AdamW%s)" % (
+        name, "HardConcrete-masked" if workload != "distill" else "un-masked", workload,
+        " + L0 Lagrangian" if workload != "distill" else "", " + NCCL grad all-reduce" if world > 1 else "")
+
+
+def oracle_step(args):
+    """The same training step through the CPU oracle (functional restatement of the reference's PyTorch code, pinned
+    against it by tests/golden): forward + backward + clip_grad_norm_(10) + AdamW over the reference's three parameter
+    groups, on a bounded sample of the workload. Returns (one_step_fn, audio_seconds_per_step, threads, description)."""
     import dphubert_oracle as O
 
-    if rank != 0:
-        return
     threads = os.cpu_count() or 1
     torch.set_num_threads(threads)
     teacher, student, projs, layers, cfg, scfg, name = build_models(args.workload, None, None)
@@ -139,10 +143,20 @@ def run_reference(args, rank):
     t_sd = {k: v.detach() for k, v in teacher.state_dict().items()}
     s_sd = {k: v.detach().clone().requires_grad_(v.is_floating_point() and "dummy" not in k)
             for k, v in student.state_dict().items()}
-    heads = [(p.weight.detach().clone().requires_grad_(True), p.bias.detach().clone().requires_grad_(True)) for p in projs]
+    uniq = {}
+    for p in projs:
+        uniq.setdefault(id(p), (p.weight.detach().clone().requires_grad_(True), p.bias.detach().clone().requires_grad_(True)))
+    heads = [uniq[id(p)] for p in projs]
     lam = [torch.tensor(0.0, requires_grad=True), torch.tensor(0.0, requires_grad=True)] if args.workload != "distill" else None
     n0 = sum(p.numel() for p in teacher.parameters())
     g = torch.Generator().manual_seed(2022)
+    main = [v for k, v in s_sd.items() if v.requires_grad and "log_alpha" not in k] + [t for wb in uniq.values() for t in wb]
+    groups = [{"params": main, "lr": 2e-4, "weight_decay": 0.0}]
+    if lam is not None:
+        groups.append({"params": [v for k, v in s_sd.items() if v.requires_grad and "log_alpha" in k], "lr": 0.02})
+        groups.append({"params": lam, "lr": -0.02})  # lightning.py:200-238: gradient ascent on the multipliers
+    opt = torch.optim.AdamW(groups, weight_decay=0.0)
+    every = [p for grp in groups for p in grp["params"]]
 
     def one():
         wave = 0.1 * torch.randn(B, T0, generator=g)
@@ -150,23 +164,34 @@ def run_reference(args, rank):
         noise = {k: torch.empty(s_sd[k + ".log_alpha"].shape).uniform_(1e-6, 1 - 1e-6, generator=g) for k in O.gate_keys(s_sd)}
         loss, _ = O.distill_step_loss(t_sd, cfg, s_sd, scfg, heads, layers, wave, lengths, noise, lam, 0.75, n0,
                                       (0.0, 1.0, 1.0), "raw")
+        opt.zero_grad(set_to_none=True)
         loss.backward()
-        for v in s_sd.values():
-            v.grad = None
+        torch.nn.utils.clip_grad_norm_(every, 10.0)
+        opt.step()
         return float(loss.detach())
 
+    desc = "%d x %.0f s utterances per step (the reference's CPU algorithm: oracle port, fp32, torch %d threads)" % (B, secs, threads)
+    return one, B * secs, threads, desc, name
+
+
+def run_reference(args, rank):
+    """`--impl reference`: the reference's algorithm for the path on the host cores. The reference is pure Python and
+    does not travel to the GPU box, so this is the oracle port (cpu_baseline.kind = "port")."""
+    if rank != 0:
+        return
+    one, audio, threads, desc, name = oracle_step(args)
     for _ in range(args.warmup):
         one()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         one()
     dt = (time.perf_counter() - t0) / args.steps
-    val = B * secs / dt
-    sample = "%d x %.0f s utterances per step, fp32, forward+backward (no optimizer), %d steps" % (B, secs, args.steps)
+    val = audio / dt
+    sample = "%s, %d timed steps" % (desc, args.steps)
     line = {"impl": "reference", "metric": "prune-step audio-sec/sec", "value": val, "unit": "audio-s/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "%s teacher -> student, %s step" % (name, args.workload), "sample": sample},
+            "config": {"workload": workload_string(name, args.workload, 1), "sample": sample},
             "cpu_baseline": {"value": val, "unit": "audio-s/s", "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
@@ -174,32 +199,15 @@ def run_reference(args, rank):
 
 def cpu_baseline(args):
     """Bounded CPU sample of the same step through the oracle (reported baseline, not the target)."""
-    import dphubert_oracle as O
-
-    threads = os.cpu_count() or 1
-    torch.set_num_threads(threads)
-    teacher, student, projs, layers, cfg, scfg, name = build_models(args.workload, None, None)
-    B, secs = 2, 4.0
-    T0 = int(secs * SR)
-    t_sd = {k: v.detach() for k, v in teacher.state_dict().items()}
-    s_sd = {k: v.detach().clone().requires_grad_(v.is_floating_point() and "dummy" not in k)
-            for k, v in student.state_dict().items()}
-    heads = [(p.weight.detach().clone().requires_grad_(True), p.bias.detach().clone().requires_grad_(True)) for p in projs]
-    lam = [torch.tensor(0.0, requires_grad=True), torch.tensor(0.0, requires_grad=True)] if args.workload != "distill" else None
-    n0 = sum(p.numel() for p in teacher.parameters())
-    g = torch.Generator().manual_seed(2022)
+    one, audio, threads, desc, _ = oracle_step(args)
     times = []
-    for i in range(3):
-        wave = 0.1 * torch.randn(B, T0, generator=g)
-        noise = {k: torch.empty(s_sd[k + ".log_alpha"].shape).uniform_(1e-6, 1 - 1e-6, generator=g) for k in O.gate_keys(s_sd)}
+    for _ in range(4):
         t0 = time.perf_counter()
-        loss, _ = O.distill_step_loss(t_sd, cfg, s_sd, scfg, heads, layers, wave, torch.full((B,), T0), noise, lam, 0.75, n0,
-                                      (0.0, 1.0, 1.0), "raw")
-        loss.backward()
+        one()
         times.append(time.perf_counter() - t0)
     dt = min(times[1:])
-    return {"value": B * secs / dt, "unit": "audio-s/s", "cores": threads, "kind": "port",
-            "sample": "oracle forward+backward of the same step on %d x %.0f s, fp32, best of 2 after 1 warm-up" % (B, secs)}
+    return {"value": audio / dt, "unit": "audio-s/s", "cores": threads, "kind": "port",
+            "sample": desc + ", best of 3 after 1 warm-up"}
 
 
 def run_ours(args, rank, world, local_rank):
@@ -295,10 +303,7 @@ def run_ours(args, rank, world, local_rank):
         "metric": "prune-step audio-sec/sec", "value": audio / (ms_dev / 1e3), "unit": "audio-s/s", "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
-        "config": {"workload": "%s teacher -> %s student, %s step (teacher fwd + student fwd/bwd + heads + loss%s + "
-                               "clip + AdamW%s)" % (name, "HardConcrete-masked" if args.workload != "distill" else "un-masked",
-                                                    args.workload, " + L0 Lagrangian" if args.workload != "distill" else "",
-                                                    " + NCCL grad all-reduce" if world > 1 else ""),
+        "config": {"workload": workload_string(name, args.workload, world),
                    "batch_per_gpu": B, "seconds_per_utt": secs, "global_batch": B * world, "parallelism": "dp%d" % world,
                    "cuda_graph": not args.no_graph,
                    "l2_policy": "inputs larger than L2: one step touches > 10 GB of activations / weights / optimizer state"},
@@ -315,8 +320,14 @@ def run_ours(args, rank, world, local_rank):
     if rank == 0:
         print(json.dumps(line), flush=True)
     if dist is not None:
+        # tearing the NCCL communicator down while a captured graph still references its kernels can block:
+        # release the graph first, and leave without the (optional) communicator destruction
         dist.barrier()
-        dist.destroy_process_group()
+        torch.cuda.synchronize()
+        step._graph = None
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def gemm_table(step, wave, lengths, G, path):
@@ -369,8 +380,10 @@ def roofline(step, wave, lengths, G, dev):
     """Dominant kernel = the tcgen05 GEMM (every Linear / conv / attention product): re-issue exactly the GEMM launches
     of one step back to back and time them with CUDA events -> algorithmic TFLOP/s against the measured bf16 peak."""
     G.TRACE = []
+    hook, step.splan.grad_hook = step.splan.grad_hook, None  # rank-local pass: no collectives
     step._push_scalars()
     step._body(wave, lengths)
+    step.splan.grad_hook = hook
     trace, G.TRACE = G.TRACE, None
     step.zero_grad()
     torch.cuda.synchronize()
@@ -402,6 +415,10 @@ def roofline(step, wave, lengths, G, dev):
 
 def main():
     args = parse()
+    if os.environ.get("DPH_BENCH_FAULT"):  # debugging aid: dump every thread's Python stack if the run stalls
+        import faulthandler
+
+        faulthandler.dump_traceback_later(float(os.environ["DPH_BENCH_FAULT"]), exit=True)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -115,6 +115,22 @@ class Plan:
                 p.data = view
         self.params = ordered
         self.bind_grads()
+        # called by encoder_bwd after each transformer layer's backward with the layer index (see layer_lin_range)
+        self.grad_hook = None
+        self.layer_lin_range = []
+        for layer in tr.layers:
+            ws = []
+            if layer.attention is not None:
+                a_ = layer.attention
+                ws += [a_.k_proj.weight, a_.v_proj.weight, a_.q_proj.weight, a_.out_proj.weight]
+            if layer.feed_forward is not None:
+                ws += [layer.feed_forward.intermediate_dense.weight, layer.feed_forward.output_dense.weight]
+            if ws:
+                lo = min(self.offsets[id(w)] for w in ws)
+                hi = max(self.offsets[id(w)] + _align(w.numel()) for w in ws)
+                self.layer_lin_range.append((lo, hi))
+            else:
+                self.layer_lin_range.append(None)
 
         self.dtype = None
         self.lin16 = None
@@ -1208,6 +1224,8 @@ def encoder_bwd(plan: Plan, st, dh, dmasks, A):
             dxl = _ffn_bwd(plan, rec["ff"], ds, ds, dmasks, A, tag) if "ff" in rec else ds
             dx1 = _ln_bwd(plan, rec["ln1"], dxl, None, A, tag + "ln1_")
             g = _attention_bwd(plan, rec["att"], dx1, dx1, B, T, dmasks, A, tag, wl) if "att" in rec else dx1
+        if plan.grad_hook is not None:
+            plan.grad_hook(li)  # every weight gradient of transformer layer li has been issued (data-parallel overlap)
     assert idx == 0
     d_h0_head = dh[0]
     if g is not None:

@@ -108,6 +108,8 @@ class NativeDistillStep:
 
         self.tplan = get_plan(teacher)
         self.splan = get_plan(student)
+        self._pending, self._covered = [], []
+        self.splan.grad_hook = self._layer_grads_ready if self.world > 1 else None
         dev = self.splan.device
         self.device = dev
         if teacher.compute_dtype != student.compute_dtype:
@@ -319,15 +321,47 @@ class NativeDistillStep:
         # derived GEMM operands that are not plain casts (tap-major conv weights, weight-normalised pos conv)
         self.splan.rebuild_derived(self.dt, cast_lin=False)
 
+    # ------------------------------------------------------------------------------------------------ data parallel
+    # DDP's gradient mean (distill.py:41 strategy="ddp"): the Linear-weight gradients of transformer layer l (one
+    # contiguous 28 MB slice of the gradient arena for HuBERT Base) are all-reduced as soon as the backward pass has
+    # left that layer, on NCCL's own stream, while the earlier layers' backward keeps the SMs busy; everything else
+    # (conv stack, biases, norms, log_alpha, heads, lambdas) follows after the backward. Works inside CUDA graph capture.
+    def _reduce_async(self, t):
+        import torch.distributed as dist
+
+        if t.numel() == 0:
+            return
+        if t.is_cuda:
+            w = dist.all_reduce(t, op=dist.ReduceOp.AVG, group=self.pg, async_op=True)
+            self._pending.append((w, None))
+        else:  # gloo (CPU tests): no AVG
+            w = dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
+            self._pending.append((w, t))
+
+    def _layer_grads_ready(self, li):
+        rng = self.splan.layer_lin_range[li]
+        if rng is None:
+            return
+        lo, hi = rng
+        self._reduce_async(self.splan.garena[lo:hi])
+        self._covered.append((lo, hi))
+
     def _allreduce(self):
         if self.world <= 1:
             return
-        import torch.distributed as dist
-
-        for _, g in self.arenas():
-            dist.all_reduce(g, op=dist.ReduceOp.AVG if g.is_cuda else dist.ReduceOp.SUM, group=self.pg)
-            if not g.is_cuda:
-                g.mul_(1.0 / self.world)
+        g = self.splan.garena
+        pos = 0
+        for lo, hi in sorted(self._covered):
+            self._reduce_async(g[pos:lo])
+            pos = max(pos, hi)
+        self._reduce_async(g[pos:])
+        for _, ga in self.arenas()[1:]:
+            self._reduce_async(ga)
+        for w, t in self._pending:
+            w.wait()
+            if t is not None:
+                t.mul_(1.0 / self.world)
+        self._pending, self._covered = [], []
 
     # ------------------------------------------------------------------------------------------------ public
     def zero_grad(self):

@@ -208,6 +208,29 @@ int dph_wavlm_gate_bwd(const void* x, const float* Wg, const float* cst, const f
                        int dtype, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
+ * Fused multi-head self-attention for head_dim = 64, T <= 1024, bf16 (tcgen05 + TMEM + TMA; csrc/attention.cu).
+ * Replaces wav2vec2/components.py:406-426 (SelfAttention.forward: q k^T, padding mask, softmax, dropout, p v, head
+ * mask) and :629-647 (WavLM gated relative-position bias) together with their autograd backward, without ever
+ * materialising a (B, H, T, T) tensor.
+ *   qkv   : (B*T, 3*H*64) bf16, the fused projection output laid out [k | v | q] per row
+ *   ctx   : (B*T, H*64) bf16 context (head-masked); ctx_un: the same before the head mask (saved for backward; may
+ *           be NULL when nothing is saved);  lse: (B, H, T) fp32 log-sum-exp of the scaled scores (may be NULL)
+ *   lengths (B) or NULL: keys >= length get the reference's additive -10000 mask
+ *   rel_table (2T-1) / emb (num_buckets, Htot) / gate (B, Htot, T) / head_index (H): WavLM bias, all NULL for HuBERT
+ *   backward: dctx (B*T, H*64) bf16 -> dqkv (B*T, 3*H*64) bf16; delta (B, H, T) fp32 scratch; dq32 (B*T, H*64) fp32
+ *           accumulator that must be zero on entry and is left zeroed; dmask_h (H) fp32 head-mask gradient (+=);
+ *           dgate (B, Htot, T) / demb (num_buckets, Htot) fp32 WavLM gradients (+=) or NULL.
+ * ---------------------------------------------------------------------------------------------------------- */
+int dph_attn_fwd(const void* qkv, void* ctx, void* ctx_un, float* lse, int B, int H, int T, float scale,
+                 const int64_t* lengths, const int* rel_table, const float* emb, const float* gate,
+                 const int* head_index, int Htot, float drop_p, uint64_t seed, const float* head_mask, void* stream);
+int dph_attn_bwd(const void* qkv, const void* dctx, const void* o_un, const float* lse, float* delta, float* dq32,
+                 void* dqkv, float* dmask_h, int B, int H, int T, float scale, const int64_t* lengths,
+                 const int* rel_table, const float* emb, const float* gate, const int* head_index, int Htot,
+                 float drop_p, uint64_t seed, const float* head_mask, float* dgate, float* demb, int num_buckets,
+                 void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
  * HardConcrete gates, expected model size, Lagrangian.
  * Replaces wav2vec2/hardconcrete.py:76-99, the get_num_params tree (components.py:122-134, 187-196, 276-277, 438-449,
  * 750-761, 859-865, 929-934, 1005-1009; model.py:109-113) and lightning.py:267-271 (+ autograd).
