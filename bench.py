@@ -408,8 +408,14 @@ def roofline(step, wave, lengths, G, dev):
     except Exception:  # noqa: BLE001
         pass
     ach = flops / (ms / 1e3) / 1e12
+    traffic = None  # DRAM bytes per launch of this kernel, from the committed `ncu --set full` capture
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_gemm_dram_traffic.json")) as f:
+            traffic = float(json.load(f)["dram_bytes_per_launch"])
+    except Exception:  # noqa: BLE001
+        pass
     return {"bound": "tensor", "kernel": "gemm_bf16_kernel (tcgen05)", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
-            "frac": ach / peak, "traffic": None, "launches_per_step": len(trace), "ms_per_step_in_kernel": ms,
+            "frac": ach / peak, "traffic": traffic, "launches_per_step": len(trace), "ms_per_step_in_kernel": ms,
             "avg_launch_us": ms * 1e3 / max(len(trace), 1), "algorithmic_flops_per_step": flops, "peak_source": src}
 
 

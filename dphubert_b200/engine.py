@@ -115,6 +115,9 @@ class Plan:
                 p.data = view
         self.params = ordered
         self.bind_grads()
+        # optional second CUDA stream for the weight-gradient GEMMs of the transformer: they are off the critical
+        # path of the backward pass (nothing downstream reads them) and fill the tail of the dgrad kernels
+        self.side_stream = None
         # called by encoder_bwd after each transformer layer's backward with the layer index (see layer_lin_range)
         self.grad_hook = None
         self.layer_lin_range = []
@@ -1018,11 +1021,41 @@ def _ksplit(Mo, No, K):
     return -1
 
 
+class _on_side:
+    """Run the enclosed launches on the plan's side stream (after everything issued so far on the current stream).
+    Inputs must stay untouched until the streams are joined again: every buffer a weight-gradient GEMM reads is a
+    per-layer static buffer that is written once per step."""
+
+    def __init__(self, plan):
+        self.side = plan.side_stream
+        self.ctx = None
+
+    def __enter__(self):
+        if self.side is not None:
+            self.side.wait_stream(torch.cuda.current_stream())
+            self.ctx = torch.cuda.stream(self.side)
+            self.ctx.__enter__()
+        return self
+
+    def __exit__(self, *exc):
+        if self.ctx is not None:
+            self.ctx.__exit__(*exc)
+        return False
+
+
+def join_side(plan):
+    """current stream waits for the side stream (end of the backward pass)"""
+    if plan.side_stream is not None:
+        torch.cuda.current_stream().wait_stream(plan.side_stream)
+
+
 def _wgrad(plan, dy2d, x2d, param, Mo, No, Krows):
     """grad(param)[o, i] += sum_m dy[m, o] * x[m, i]   (fp32, atomically accumulated into the gradient arena)"""
     if not param.requires_grad:
         return
-    G.gemm(G.mat_t(dy2d), G.mat_t(x2d), plan.gview(param), Mo, No, Krows, atomic=True, ksplit=_ksplit(Mo, No, Krows))
+    with _on_side(plan):
+        G.gemm(G.mat_t(dy2d), G.mat_t(x2d), plan.gview(param), Mo, No, Krows, atomic=True,
+               ksplit=_ksplit(Mo, No, Krows))
 
 
 def _gslot(plan, dmasks, hc):
@@ -1148,7 +1181,8 @@ def _attention_bwd(plan, rec, dout, dresid, B, T, dmasks, A, tag, wl):
     if kvq_w[0].requires_grad:
         o0 = plan.offsets[id(kvq_w[0])]
         gw = plan.garena[o0:o0 + 3 * inner * D].view(3 * inner, D)
-        G.gemm(G.mat_t(dqkv), G.mat_t(xin), gw, 3 * inner, D, M, atomic=True, ksplit=_ksplit(3 * inner, D, M))
+        with _on_side(plan):
+            G.gemm(G.mat_t(dqkv), G.mat_t(xin), gw, 3 * inner, D, M, atomic=True, ksplit=_ksplit(3 * inner, D, M))
     dx = A(tag + "att_dx", (M, D), dt)
     G.gemm(G.mat(dqkv), G.mat_t(plan.wcat(kvq_w, dt)), dx, M, D, 3 * inner, residual=dresid)
     if dgate is not None:
@@ -1330,6 +1364,7 @@ def backward_core(plan: Plan, st, dh, dmasks, A):
     dfeat = encoder_bwd(plan, enc, dh, dmasks, A)
     if dfeat is not None:
         conv_stack_bwd(plan, st["conv"], dfeat, dmasks, A)
+    join_side(plan)
 
 
 class _ModelFn(torch.autograd.Function):

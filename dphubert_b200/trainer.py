@@ -110,6 +110,8 @@ class NativeDistillStep:
         self.splan = get_plan(student)
         self._pending, self._covered = [], []
         self.splan.grad_hook = self._layer_grads_ready if self.world > 1 else None
+        self.two_streams = True   # teacher forward / weight-gradient GEMMs on side streams (CUDA only)
+        self.tstream = None
         dev = self.splan.device
         self.device = dev
         if teacher.compute_dtype != student.compute_dtype:
@@ -201,11 +203,24 @@ class NativeDistillStep:
         dt = self.dt
         splan, tplan = self.splan, self.tplan
         ops.rng_advance()
-        # ---- teacher (eval, no grad)
-        t_h, _, _ = engine.forward_core(tplan, wave, lengths, {}, self.At, False, save=False)
+        # ---- teacher (eval, no grad) on its own stream, concurrently with the student forward: the two passes share
+        # nothing but the input waveform, and each one's kernel tails / small kernels fill the other's bubbles
+        if wave.is_cuda and self.two_streams:
+            if self.tstream is None:
+                self.tstream = torch.cuda.Stream()
+                splan.side_stream = torch.cuda.Stream()
+            main = torch.cuda.current_stream()
+            self.tstream.wait_stream(main)
+            with torch.cuda.stream(self.tstream):
+                t_h, _, _ = engine.forward_core(tplan, wave, lengths, {}, self.At, False, save=False)
+        else:
+            main = None
+            t_h, _, _ = engine.forward_core(tplan, wave, lengths, {}, self.At, False, save=False)
         # ---- student
         masks, u = self._sample_masks()
         s_h, _, st = engine.forward_core(splan, wave, lengths, masks, self.As, self.student.training, save=True)
+        if main is not None:
+            main.wait_stream(self.tstream)
         B, T, D = s_h[0].shape
         M = B * T
         nL = len(self.layers)
@@ -254,8 +269,9 @@ class NativeDistillStep:
             else:
                 ops.epilogue_bwd(dpred, M, Dt, dbias=gb)
             src = s_h[src_i].view(M, D)
-            G.gemm(G.mat_t(dpred), G.mat_t(src), self.heads.gview(lin.weight), Dt, D, M, atomic=True,
-                   ksplit=engine._ksplit(Dt, D, M))
+            with engine._on_side(splan):
+                G.gemm(G.mat_t(dpred), G.mat_t(src), self.heads.gview(lin.weight), Dt, D, M, atomic=True,
+                       ksplit=engine._ksplit(Dt, D, M))
             Wt = G.mat_t(self.heads.W(lin.weight, dt))
             if dh[src_i] is None:
                 dh[src_i] = A("dhid%d" % src_i, (M, D), dt)
@@ -343,7 +359,13 @@ class NativeDistillStep:
         if rng is None:
             return
         lo, hi = rng
-        self._reduce_async(self.splan.garena[lo:hi])
+        side = self.splan.side_stream
+        if side is not None:
+            # the slice holds Linear-weight gradients only, all produced on the side stream: NCCL orders itself after it
+            with torch.cuda.stream(side):
+                self._reduce_async(self.splan.garena[lo:hi])
+        else:
+            self._reduce_async(self.splan.garena[lo:hi])
         self._covered.append((lo, hi))
 
     def _allreduce(self):
