@@ -28,8 +28,10 @@ namespace dph {
 
 constexpr int BM = 128;
 constexpr int BK = 64;
-constexpr int kEpiWarps = 8;
-constexpr int kGemmThreads = 64 + 32 * kEpiWarps;
+// Eight epilogue warps: measured best. Sixteen (one per 64-column slice of a 256-wide tile) cap the kernel at 96
+// registers per thread and lose more to spills and barrier traffic than the extra latency hiding returns.
+constexpr int epi_warps(int) { return 8; }
+constexpr int gemm_threads(int bn) { return 64 + 32 * epi_warps(bn); }
 
 enum EpiFeature : int {
   F_BIAS = 1,      // + bias[n]
@@ -93,8 +95,53 @@ DPH_DEVICE void stamp(unsigned long long* tl, int slot) {
 
 // Ragged / unaligned chunks (edge tiles, odd leading dimensions): reads its 32 accumulator columns from TMEM itself
 // and walks them one by one with every feature checked at run time.  Warp-collective (all lanes must call it).
-__device__ void epilogue_chunk_generic(const GemmParams& p, int b0, int b1, int row, bool row_ok, int col0,
-                                       uint32_t taddr);
+// Out of line, one copy per translation unit: its dynamically indexed array must not pull the fast path's registers
+// onto the stack, and being in the kernel's own module keeps it inside the kernel's register budget.
+static __device__ __noinline__ void epilogue_chunk_generic(const GemmParams& p, int b0, int b1, int row, bool row_ok, int col0,
+                                                    uint32_t taddr) {
+  uint32_t r[32];
+  tmem_ld_32x32(taddr, r);
+  tmem_ld_wait();
+  const int nvalid = min(32, p.N - col0);
+  if (!row_ok || nvalid <= 0) return;
+  float acc[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) acc[j] = __uint_as_float(r[j]);  // lives in local memory: indexed dynamically below
+  const long long coff = (long long)b0 * p.c_sb0 + (long long)b1 * p.c_sb1 + (long long)row * p.ldc + col0;
+  const long long roff = (long long)b0 * p.r_sb0 + (long long)b1 * p.r_sb1 + (long long)row * p.ldr + col0;
+  const uint32_t thresh = (uint32_t)(p.drop_p * 4294967296.0);
+  const float inv_keep = 1.0f / (1.0f - p.drop_p);
+  const unsigned long long dbase =
+      (((unsigned long long)b1 * p.nb0 + b0) * (unsigned long long)p.M + row) * (unsigned long long)p.N + col0;
+  const float smask = p.scalar_mask != nullptr ? __ldg(p.scalar_mask + b0 * p.scalar_sb0) : 1.0f;
+#pragma unroll 1
+  for (int j = 0; j < nvalid; ++j) {
+    float v = acc[j] * p.alpha;
+    if (p.bias != nullptr) v += __ldg(p.bias + b0 * p.vec_sb0 + col0 + j);
+    if (p.C2 != nullptr) {
+      if (p.c_dtype == 0) reinterpret_cast<bf16*>(p.C2)[coff + j] = __float2bfloat16_rn(v);
+      else reinterpret_cast<float*>(p.C2)[coff + j] = v;
+    }
+    if (p.act == 1) v = gelu_erf_fast(v);
+    if (p.colmask != nullptr) v *= __ldg(p.colmask + b0 * p.vec_sb0 + col0 + j);
+    v *= smask;
+    if (p.drop_p > 0.0f) v *= dropout_scale(p.seed, dbase + j, thresh, inv_keep);
+    if (p.residual != nullptr) {
+      v += p.r_dtype == 0 ? __bfloat162float(reinterpret_cast<const bf16*>(p.residual)[roff + j])
+                          : reinterpret_cast<const float*>(p.residual)[roff + j];
+    }
+    if (p.c_dtype == 0) {
+      bf16* o = reinterpret_cast<bf16*>(p.C) + coff + j;
+      if (p.c_mode == 2) v += __bfloat162float(*o);
+      *o = __float2bfloat16_rn(v);
+    } else {
+      float* o = reinterpret_cast<float*>(p.C) + coff + j;
+      if (p.c_mode == 1) atomicAdd(o, v);
+      else *o = (p.c_mode == 2 ? *o : 0.0f) + v;
+    }
+  }
+}
+
 
 // 32 consecutive outputs of one row as full 32-byte sectors (256-bit stores)
 DPH_DEVICE void store_bf16x32(bf16* o, const float (&v)[32]) {
@@ -268,7 +315,7 @@ DPH_DEVICE void epilogue_chunk(const GemmParams& p, const TileCoord& tc, int row
 }
 
 template <int BN, bool A_MN, bool B_MN, int CG, int F>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+__global__ void __launch_bounds__(gemm_threads(BN), 1)
     gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                      const __grid_constant__ GemmParams p) {
   using Cfg = GemmCfg<BN, CG>;
@@ -307,7 +354,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
       }
       for (int a = 0; a < 2; ++a) {
         mbar_init(tfull_bar(a), 1);
-        mbar_init(tempty_bar(a), kEpiWarps * CG);  // leader's barrier collects the epilogue warps of both CTAs
+        mbar_init(tempty_bar(a), epi_warps(BN) * CG);  // leader's barrier collects the epilogue warps of both CTAs
       }
       mbar_fence_init();
     }
@@ -509,7 +556,7 @@ static int launch_inst(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)grid);
-  cfg.blockDim = dim3(kGemmThreads);
+  cfg.blockDim = dim3(gemm_threads(BN));
   cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];

@@ -6,51 +6,6 @@ namespace dph {
 
 __device__ unsigned long long* g_gemm_timeline = nullptr;
 
-__device__ __noinline__ void epilogue_chunk_generic(const GemmParams& p, int b0, int b1, int row, bool row_ok, int col0,
-                                                    uint32_t taddr) {
-  uint32_t r[32];
-  tmem_ld_32x32(taddr, r);
-  tmem_ld_wait();
-  const int nvalid = min(32, p.N - col0);
-  if (!row_ok || nvalid <= 0) return;
-  float acc[32];
-#pragma unroll
-  for (int j = 0; j < 32; ++j) acc[j] = __uint_as_float(r[j]);  // lives in local memory: indexed dynamically below
-  const long long coff = (long long)b0 * p.c_sb0 + (long long)b1 * p.c_sb1 + (long long)row * p.ldc + col0;
-  const long long roff = (long long)b0 * p.r_sb0 + (long long)b1 * p.r_sb1 + (long long)row * p.ldr + col0;
-  const uint32_t thresh = (uint32_t)(p.drop_p * 4294967296.0);
-  const float inv_keep = 1.0f / (1.0f - p.drop_p);
-  const unsigned long long dbase =
-      (((unsigned long long)b1 * p.nb0 + b0) * (unsigned long long)p.M + row) * (unsigned long long)p.N + col0;
-  const float smask = p.scalar_mask != nullptr ? __ldg(p.scalar_mask + b0 * p.scalar_sb0) : 1.0f;
-#pragma unroll 1
-  for (int j = 0; j < nvalid; ++j) {
-    float v = acc[j] * p.alpha;
-    if (p.bias != nullptr) v += __ldg(p.bias + b0 * p.vec_sb0 + col0 + j);
-    if (p.C2 != nullptr) {
-      if (p.c_dtype == 0) reinterpret_cast<bf16*>(p.C2)[coff + j] = __float2bfloat16_rn(v);
-      else reinterpret_cast<float*>(p.C2)[coff + j] = v;
-    }
-    if (p.act == 1) v = gelu_erf_fast(v);
-    if (p.colmask != nullptr) v *= __ldg(p.colmask + b0 * p.vec_sb0 + col0 + j);
-    v *= smask;
-    if (p.drop_p > 0.0f) v *= dropout_scale(p.seed, dbase + j, thresh, inv_keep);
-    if (p.residual != nullptr) {
-      v += p.r_dtype == 0 ? __bfloat162float(reinterpret_cast<const bf16*>(p.residual)[roff + j])
-                          : reinterpret_cast<const float*>(p.residual)[roff + j];
-    }
-    if (p.c_dtype == 0) {
-      bf16* o = reinterpret_cast<bf16*>(p.C) + coff + j;
-      if (p.c_mode == 2) v += __bfloat162float(*o);
-      *o = __float2bfloat16_rn(v);
-    } else {
-      float* o = reinterpret_cast<float*>(p.C) + coff + j;
-      if (p.c_mode == 1) atomicAdd(o, v);
-      else *o = (p.c_mode == 2 ? *o : 0.0f) + v;
-    }
-  }
-}
-
 }  // namespace dph
 
 // =================================================================================================
