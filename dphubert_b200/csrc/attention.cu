@@ -345,7 +345,8 @@ constexpr int BWD_SDO = BWD_SQ + 2 * ATT_BQ * ATT_D * 2; // dO   2 x [128 i][64]
 constexpr int BWD_SP = BWD_SDO + 2 * ATT_BQ * ATT_D * 2; // Pd   2 x [128 i][64 j]      32 KB
 constexpr int BWD_SDS = BWD_SP + ATT_BQ * ATT_BK * 2;    // dS   2 x [128 i][64 j]      32 KB
 constexpr int BWD_TB = BWD_SDS + ATT_BQ * ATT_BK * 2;    // bias table (2T-1 floats)     8 KB
-constexpr int BWD_HIST = BWD_TB + 2048 * 4;              // embedding-gradient histogram 4 KB
+constexpr int BWD_DIAG = BWD_TB + 2048 * 4;              // embedding gradient per diagonal j - i (2T-1 floats) 8 KB
+constexpr int BWD_HIST = BWD_DIAG + 2048 * 4;            // ... folded into buckets at the end    4 KB
 constexpr int BWD_BAR = BWD_HIST + 1024 * 4;
 constexpr int BWD_SMEM = BWD_BAR + 64 + 1024;
 
@@ -366,6 +367,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
                  sP = sbase + BWD_SP, sDS = sbase + BWD_SDS;
   constexpr uint32_t QBUF = ATT_BQ * ATT_D * 2;  // bytes of one Q / dO buffer
   float* tb = reinterpret_cast<float*>(gbase + BWD_TB);
+  float* sdiag = reinterpret_cast<float*>(gbase + BWD_DIAG);
   float* hist = reinterpret_cast<float*>(gbase + BWD_HIST);
   const uint32_t bar_kv = sbase + BWD_BAR, bar_qdo = bar_kv + 8 /* [2] */, bar_s = bar_kv + 24, bar_g = bar_kv + 32,
                  tmem_slot = bar_kv + 40;
@@ -397,8 +399,10 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
     htot = p.head_index ? p.head_index[h] : h;
     for (int r = tid; r < 2 * T - 1; r += BWD_THREADS)
       tb[r] = __ldg(p.emb + (long long)p.rel_table[r] * p.Htot + htot);
-    if (demb)
+    if (demb) {
       for (int r = tid; r < num_buckets; r += BWD_THREADS) hist[r] = 0.f;
+      for (int r = tid; r < 2 * T - 1; r += BWD_THREADS) sdiag[r] = 0.f;
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -496,7 +500,9 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
           dv[u] = ds;
           if (p.emb && ok) {
             dg += ds * tbv;
-            if (demb) atomicAdd(&hist[p.rel_table[j - i + T - 1]], ds * gate_i);
+            // per-diagonal sums: the lanes of a warp hold 32 consecutive rows i at the same key j, i.e. 32
+            // consecutive diagonals -> conflict-free shared-memory atomics (buckets would collide heavily)
+            if (demb) atomicAdd(&sdiag[j - i + T - 1], ds * gate_i);
           }
         }
         pk[jj >> 1] = pack_bf16x2(pv[0], pv[1]);
@@ -579,6 +585,11 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
     }
   }
   if (demb && p.emb) {
+    __syncthreads();
+    for (int r = tid; r < 2 * T - 1; r += BWD_THREADS) {
+      const float v = sdiag[r];
+      if (v != 0.f) atomicAdd(&hist[p.rel_table[r]], v);
+    }
     __syncthreads();
     for (int r = tid; r < num_buckets; r += BWD_THREADS) {
       const float v = hist[r];

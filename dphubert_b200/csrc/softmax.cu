@@ -195,21 +195,40 @@ __global__ void wavlm_gate_fwd_kernel(const T* __restrict__ x, const float* __re
 }
 
 // backward of the gate: accumulates dWg (8,Dh), dbg (8), dconst (Htot) and ADDS the input gradient into dx.
+// One warp per (b, t, h) row, lane l owns head-dim elements l, l+32, ...: the pre-sigmoid gradient takes only two
+// distinct values per row (outputs 0-3 share dpa, 4-7 share dpb), so dWg needs two register accumulators per owned
+// element and the input gradient two precomputed column sums of Wg; partial sums meet in shared memory once per warp.
 template <typename T>
 __global__ void __launch_bounds__(256)
     wavlm_gate_bwd_kernel(const T* __restrict__ x, const float* __restrict__ Wg, const float* __restrict__ cst,
                           const float* __restrict__ ga_in, const float* __restrict__ gb_in,
                           const float* __restrict__ dgate, T* __restrict__ dx, float* __restrict__ dWg,
                           float* __restrict__ dbg, float* __restrict__ dcst, int B, int Tn, int Htot, int Dh) {
-  extern __shared__ float sh[];  // [8*Dh + 8 + Htot]
-  float* s_dW = sh;
-  float* s_db = sh + 8 * Dh;
-  float* s_dc = s_db + 8;
-  for (int q = threadIdx.x; q < 8 * Dh + 8 + Htot; q += blockDim.x) sh[q] = 0.f;
+  constexpr int NPL = 4;          // head-dim elements per lane (Dh <= 128)
+  extern __shared__ float sh[];   // [2*Dh + 2 + Htot]
+  float* s_A = sh;
+  float* s_B = sh + Dh;
+  float* s_db = sh + 2 * Dh;
+  float* s_dc = s_db + 2;
+  for (int q = threadIdx.x; q < 2 * Dh + 2 + Htot; q += blockDim.x) sh[q] = 0.f;
   __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float wA[NPL], wB[NPL], accA[NPL], accB[NPL];
+#pragma unroll
+  for (int q = 0; q < NPL; ++q) {
+    const int d = lane + 32 * q;
+    wA[q] = wB[q] = accA[q] = accB[q] = 0.f;
+    if (d < Dh) {
+#pragma unroll
+      for (int o8 = 0; o8 < 4; ++o8) {
+        wA[q] += __ldg(Wg + o8 * Dh + d);
+        wB[q] += __ldg(Wg + (o8 + 4) * Dh + d);
+      }
+    }
+  }
+  float dbA = 0.f, dbB = 0.f;
   const long long total = (long long)B * Tn * Htot;
-  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-       idx += (long long)gridDim.x * blockDim.x) {
+  for (long long idx = (long long)blockIdx.x * 8 + warp; idx < total; idx += (long long)gridDim.x * 8) {
     const int h = (int)(idx % Htot);
     const long long bt = idx / Htot;
     const int t = (int)(bt % Tn), b = (int)(bt / Tn);
@@ -217,26 +236,37 @@ __global__ void __launch_bounds__(256)
     const float dg = dgate[o], ga = ga_in[o], gb = gb_in[o], c = cst[h];
     // gate = ga * (gb * c - 1) + 2
     const float dga = dg * (gb * c - 1.f), dgb = dg * ga * c;
-    atomicAdd(&s_dc[h], dg * ga * gb);
     const float dpa = dga * ga * (1.f - ga), dpb = dgb * gb * (1.f - gb);  // wrt the pre-sigmoid sums
+    if (lane == 0) atomicAdd(&s_dc[h], dg * ga * gb);
+    dbA += dpa;
+    dbB += dpb;
     const long long xo = bt * ((long long)Htot * Dh) + (long long)h * Dh;
 #pragma unroll
-    for (int o8 = 0; o8 < 8; ++o8) atomicAdd(&s_db[o8], o8 < 4 ? dpa : dpb);
-    for (int d = 0; d < Dh; ++d) {
-      const float xd = to_f(x[xo + d]);
-      float gx = 0.f;
-#pragma unroll
-      for (int o8 = 0; o8 < 8; ++o8) {
-        const float dp = o8 < 4 ? dpa : dpb;
-        atomicAdd(&s_dW[o8 * Dh + d], dp * xd);
-        gx = fmaf(dp, __ldg(Wg + o8 * Dh + d), gx);
+    for (int q = 0; q < NPL; ++q) {
+      const int d = lane + 32 * q;
+      if (d < Dh) {
+        const float xd = to_f(x[xo + d]);
+        accA[q] = fmaf(dpa, xd, accA[q]);
+        accB[q] = fmaf(dpb, xd, accB[q]);
+        if (dx) dx[xo + d] = from_f<T>(to_f(dx[xo + d]) + dpa * wA[q] + dpb * wB[q]);
       }
-      if (dx) dx[xo + d] = from_f<T>(to_f(dx[xo + d]) + gx);
     }
   }
+#pragma unroll
+  for (int q = 0; q < NPL; ++q) {
+    const int d = lane + 32 * q;
+    if (d < Dh) {
+      atomicAdd(&s_A[d], accA[q]);
+      atomicAdd(&s_B[d], accB[q]);
+    }
+  }
+  if (lane == 0) {
+    atomicAdd(&s_db[0], dbA);
+    atomicAdd(&s_db[1], dbB);
+  }
   __syncthreads();
-  for (int q = threadIdx.x; q < 8 * Dh; q += blockDim.x) atomicAdd(dWg + q, s_dW[q]);
-  for (int q = threadIdx.x; q < 8; q += blockDim.x) atomicAdd(dbg + q, s_db[q]);
+  for (int q = threadIdx.x; q < 8 * Dh; q += blockDim.x) atomicAdd(dWg + q, (q / Dh) < 4 ? s_A[q % Dh] : s_B[q % Dh]);
+  for (int q = threadIdx.x; q < 8; q += blockDim.x) atomicAdd(dbg + q, q < 4 ? s_db[0] : s_db[1]);
   for (int q = threadIdx.x; q < Htot; q += blockDim.x) atomicAdd(dcst + q, s_dc[q]);
 }
 
@@ -305,8 +335,13 @@ extern "C" int dph_wavlm_gate_fwd(const void* x, const float* Wg, const float* b
 extern "C" int dph_wavlm_gate_bwd(const void* x, const float* Wg, const float* cst, const float* ga, const float* gb,
                                   const float* dgate, void* dx, float* dWg, float* dbg, float* dcst, int B, int T,
                                   int Htot, int Dh, int dtype, void* stream) {
-  const size_t smem = sizeof(float) * (8 * Dh + 8 + Htot);
-  const int grid = 148;
+  if (Dh <= 0 || Dh > 128) {
+    set_error("wavlm_gate_bwd: head dim %d not supported (<= 128)", Dh);
+    return DPH_ERR_UNSUPPORTED;
+  }
+  const size_t smem = sizeof(float) * (2 * Dh + 2 + Htot);
+  const long long rows = (long long)B * T * Htot;
+  const int grid = (int)(rows / 8 < 148 * 4 ? (rows + 7) / 8 : 148 * 4);
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   if (dtype == DPH_DTYPE_BF16)
     wavlm_gate_bwd_kernel<bf16><<<grid, 256, smem, s>>>((const bf16*)x, Wg, cst, ga, gb, dgate, (bf16*)dx, dWg, dbg, dcst,
