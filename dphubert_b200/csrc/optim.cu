@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(256)
     adamw_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, long long n,
                  const float* __restrict__ lr_dev, float beta1, float beta2, float eps, float wd,
                  const int* __restrict__ step_dev, const double* __restrict__ gnorm_sq, float max_norm,
-                 bf16* __restrict__ p_bf16, int zero_grad) {
+                 bf16* __restrict__ p_bf16, int zero_grad, int vec_ok) {
   const float lr = lr_dev[0];
   const int step = step_dev[0];
   float clip = 1.f;
@@ -56,13 +56,40 @@ __global__ void __launch_bounds__(256)
   const float step_size = lr / bc1;
   const float inv_sqrt_bc2 = rsqrtf(bc2);
   const float decay = 1.f - lr * wd;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-    const float gr = g[i] * clip;
-    float pi = p[i] * decay;
-    const float mi = beta1 * m[i] + (1.f - beta1) * gr;
-    const float vi = beta2 * v[i] + (1.f - beta2) * gr * gr;
+  auto upd = [&](float& pi, float gi, float& mi, float& vi) {
+    const float gr = gi * clip;
+    pi *= decay;
+    mi = beta1 * mi + (1.f - beta1) * gr;
+    vi = beta2 * vi + (1.f - beta2) * gr * gr;
     const float denom = sqrtf(vi) * inv_sqrt_bc2 + eps;
     pi -= step_size * mi / denom;
+  };
+  // 16-byte main loop (all four arrays 16-byte aligned: checked by the launcher), scalar tail
+  const long long n4 = vec_ok ? n / 4 : 0;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    float4 p4 = reinterpret_cast<float4*>(p)[i];
+    const float4 g4 = reinterpret_cast<const float4*>(g)[i];
+    float4 m4 = reinterpret_cast<float4*>(m)[i];
+    float4 v4 = reinterpret_cast<float4*>(v)[i];
+    upd(p4.x, g4.x, m4.x, v4.x);
+    upd(p4.y, g4.y, m4.y, v4.y);
+    upd(p4.z, g4.z, m4.z, v4.z);
+    upd(p4.w, g4.w, m4.w, v4.w);
+    reinterpret_cast<float4*>(p)[i] = p4;
+    reinterpret_cast<float4*>(m)[i] = m4;
+    reinterpret_cast<float4*>(v)[i] = v4;
+    if (WRITE_BF16) {
+      uint2 u;
+      u.x = pack_bf16x2(p4.x, p4.y);
+      u.y = pack_bf16x2(p4.z, p4.w);
+      reinterpret_cast<uint2*>(p_bf16)[i] = u;
+    }
+    if (zero_grad) reinterpret_cast<float4*>(g)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  for (long long i = n4 * 4 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x) {
+    float pi = p[i], mi = m[i], vi = v[i];
+    upd(pi, g[i], mi, vi);
     p[i] = pi;
     m[i] = mi;
     v[i] = vi;
@@ -107,15 +134,18 @@ extern "C" int dph_adamw(float* p, float* g, float* m, float* v, int64_t n, cons
     set_error("adamw: bad arguments");
     return DPH_ERR_ARG;
   }
-  long long blocks = (n + 255) / 256;
-  if (blocks > 148 * 16) blocks = 148 * 16;
+  auto al = [](const void* q, uintptr_t a) { return (reinterpret_cast<uintptr_t>(q) & (a - 1)) == 0; };
+  const int vec_ok = al(p, 16) && al(g, 16) && al(m, 16) && al(v, 16) && (!p_bf16 || al(p_bf16, 8));
+  long long blocks = ((vec_ok ? n / 4 : n) + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks < 1) blocks = 1;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   if (p_bf16)
     adamw_kernel<true><<<(unsigned)blocks, 256, 0, s>>>(p, g, m, v, n, lr_dev, beta1, beta2, eps, weight_decay, step_dev,
-                                                        gnorm_sq, max_norm, (bf16*)p_bf16, zero_grad);
+                                                        gnorm_sq, max_norm, (bf16*)p_bf16, zero_grad, vec_ok);
   else
     adamw_kernel<false><<<(unsigned)blocks, 256, 0, s>>>(p, g, m, v, n, lr_dev, beta1, beta2, eps, weight_decay, step_dev,
-                                                         gnorm_sq, max_norm, nullptr, zero_grad);
+                                                         gnorm_sq, max_norm, nullptr, zero_grad, vec_ok);
   dph_count_launch();
   return dph_check_last("adamw");
 }
