@@ -33,7 +33,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="prune", choices=["prune", "distill", "wavlm", "large"])
+    ap.add_argument("--workload", default="prune", choices=["prune", "distill", "wavlm", "large", "final"])
     ap.add_argument("--batch", type=int, default=8)
     ap.add_argument("--seconds", type=float, default=0.0, help="audio seconds per utterance (default 10; large: 15)")
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
@@ -57,7 +57,7 @@ def model_configs(workload):
     else:
         cfg, layers, name = hubert_base_config(), [0, 4, 8, 12], "HuBERT Base 12L/768d"
     scfg = dict(cfg)
-    if workload != "distill":
+    if workload not in ("distill", "final"):
         scfg.update(extractor_prune_conv_channels=True, encoder_prune_attention_heads=True,
                     encoder_prune_feed_forward_intermediate=True)  # run.sh:32 pruning_units=conv,head,interm
     return cfg, scfg, layers, name
@@ -74,8 +74,11 @@ def build_models(workload, device, dtype):
     for p in teacher.parameters():
         p.requires_grad = False
     teacher.eval()
-    student = wav2vec2_model(**scfg)
-    student.load_state_dict(teacher.state_dict(), strict=False)
+    if workload == "final":
+        student, scfg = pruned_student(cfg, teacher)
+    else:
+        student = wav2vec2_model(**scfg)
+        student.load_state_dict(teacher.state_dict(), strict=False)
     student.train()
     D = cfg["encoder_embed_dim"]
     first, shared = torch.nn.Linear(D, D), torch.nn.Linear(D, D)
@@ -92,6 +95,31 @@ def build_models(workload, device, dtype):
         teacher.set_compute_dtype(dtype)
         student.set_compute_dtype(dtype)
     return teacher, student, projs, layers, cfg, scfg, name
+
+
+def pruned_student(cfg, teacher):
+    """Second stage (final_distill.py:61-65): a masked student with seeded gate parameters is pruned with `prune()` and
+    re-built from the resulting ragged config exactly as prune.py:33-74 does (about a quarter of the parameters left)."""
+    from dphubert_b200.wav2vec2.model import wav2vec2_model
+
+    mcfg = dict(cfg)
+    mcfg.update(extractor_prune_conv_channels=True, encoder_prune_attention_heads=True,
+                encoder_prune_feed_forward_intermediate=True)
+    masked = wav2vec2_model(**mcfg)
+    masked.load_state_dict(teacher.state_dict(), strict=False)
+    gen = torch.Generator().manual_seed(75)
+    with torch.no_grad():
+        for n, p in masked.named_parameters():
+            if n.endswith("log_alpha"):
+                conv = "conv_layers" in n
+                p.copy_(torch.randn(p.shape, generator=gen) * 3.0 + (1.0 if conv else -5.0))
+    conv_config, use_att, use_ff, num_heads, remaining, ff_dims = masked.prune()
+    pcfg = dict(cfg)
+    pcfg.update(extractor_conv_layer_config=conv_config, encoder_use_attention=use_att, encoder_use_feed_forward=use_ff,
+                encoder_num_heads=num_heads, encoder_ff_interm_features=ff_dims)
+    student = wav2vec2_model(**pcfg)
+    student.load_state_dict(masked.state_dict(), strict=True)
+    return student, pcfg
 
 
 class ClockSampler(threading.Thread):
@@ -124,9 +152,10 @@ class ClockSampler(threading.Thread):
 
 
 def workload_string(name, workload, world):
+    masked = workload not in ("distill", "final")
+    kind = "HardConcrete-masked" if masked else ("pruned (ragged, prune())" if workload == "final" else "un-masked")
     return "%s teacher -> %s student, %s step (teacher fwd + student fwd/bwd + heads + loss%s + clip + AdamW%s)" % (
-        name, "HardConcrete-masked" if workload != "distill" else "un-masked", workload,
-        " + L0 Lagrangian" if workload != "distill" else "", " + NCCL grad all-reduce" if world > 1 else "")
+        name, kind, workload, " + L0 Lagrangian" if masked else "", " + NCCL grad all-reduce" if world > 1 else "")
 
 
 def oracle_step(args):
@@ -147,7 +176,7 @@ def oracle_step(args):
     for p in projs:
         uniq.setdefault(id(p), (p.weight.detach().clone().requires_grad_(True), p.bias.detach().clone().requires_grad_(True)))
     heads = [uniq[id(p)] for p in projs]
-    lam = [torch.tensor(0.0, requires_grad=True), torch.tensor(0.0, requires_grad=True)] if args.workload != "distill" else None
+    lam = [torch.tensor(0.0, requires_grad=True), torch.tensor(0.0, requires_grad=True)] if args.workload not in ("distill", "final") else None
     n0 = sum(p.numel() for p in teacher.parameters())
     g = torch.Generator().manual_seed(2022)
     main = [v for k, v in s_sd.items() if v.requires_grad and "log_alpha" not in k] + [t for wb in uniq.values() for t in wb]
@@ -229,7 +258,7 @@ def run_ours(args, rank, world, local_rank):
     B, T0 = args.batch, int(secs * SR)
     teacher, student, projs, layers, cfg, scfg, name = build_models(args.workload, dev, dtype)
     step = NativeDistillStep(teacher, student, layers, projs, "layer2layer", 0.0, 1.0, 1.0, "raw",
-                             use_reg=args.workload != "distill", learning_rate=2e-4, reg_learning_rate=0.02,
+                             use_reg=args.workload not in ("distill", "final"), learning_rate=2e-4, reg_learning_rate=0.02,
                              warmup_updates=15000, max_updates=50000, target_sparsity=0.75, sparsity_warmup_updates=5000,
                              clip_norm=10.0)
     step.global_step = 5000  # full target sparsity

@@ -18,8 +18,8 @@ SIGS = {
     "dph_gemm_bf16": [vp, vp],
     "dph_gemm_f32": [vp, vp],
     # norm.cu
-    "dph_layernorm_fwd": [vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, f32, i32, f32, u64, i32, vp],
-    "dph_layernorm_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, f32, u64, i32, i64, i32, i32,
+    "dph_layernorm_fwd": [vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, f32, i32, f32, u64, i32, vp],
+    "dph_layernorm_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, u64, i32, i64, i32, i32,
                           vp],
     # elementwise.cu
     "dph_epilogue_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, f32, u64, i32, i64, i32, i64, i64, i32, vp],

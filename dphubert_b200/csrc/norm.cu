@@ -20,8 +20,10 @@ template <typename T, int NPL>
 __global__ void __launch_bounds__(256)
     layernorm_fwd_kernel(const T* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
                          T* __restrict__ y, T* __restrict__ y_pre, float* __restrict__ mean_out,
-                         float* __restrict__ rstd_out, const float* __restrict__ colmask, int rows, int D, float eps,
-                         int act, float drop_p, unsigned long long seed) {
+                         float* __restrict__ rstd_out, const float* __restrict__ colmask, int rows, int D, int Dv,
+                         float eps, int act, float drop_p, unsigned long long seed) {
+  // Dv <= D: only the first Dv columns of a row take part (zero-padded channel layout of ragged pruned models);
+  // the padding columns are written as zeros.
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (warp >= rows) return;
@@ -31,20 +33,20 @@ __global__ void __launch_bounds__(256)
 #pragma unroll
   for (int k = 0; k < NPL; ++k) {
     const int i = lane + 32 * k;
-    v[k] = (i < D) ? to_f(xr[i]) : 0.f;
+    v[k] = (i < Dv) ? to_f(xr[i]) : 0.f;
     s += v[k];
   }
   s = warp_sum(s);
-  const float mean = s / D;
+  const float mean = s / Dv;
   float q = 0.f;
 #pragma unroll
   for (int k = 0; k < NPL; ++k) {
     const int i = lane + 32 * k;
-    float d = (i < D) ? v[k] - mean : 0.f;
+    float d = (i < Dv) ? v[k] - mean : 0.f;
     q += d * d;
   }
   q = warp_sum(q);
-  const float rstd = rsqrtf(q / D + eps);
+  const float rstd = rsqrtf(q / Dv + eps);
   if (lane == 0) {
     if (mean_out) mean_out[warp] = mean;
     if (rstd_out) rstd_out[warp] = rstd;
@@ -56,6 +58,11 @@ __global__ void __launch_bounds__(256)
   for (int k = 0; k < NPL; ++k) {
     const int i = lane + 32 * k;
     if (i >= D) break;
+    if (i >= Dv) {
+      if (y_pre) y_pre[(long long)warp * D + i] = from_f<T>(0.f);
+      yr[i] = from_f<T>(0.f);
+      continue;
+    }
     float o = (v[k] - mean) * rstd * __ldg(w + i) + __ldg(b + i);
     if (y_pre) y_pre[(long long)warp * D + i] = from_f<T>(o);
     if (act == 1) o = gelu_erf(o);
@@ -73,7 +80,7 @@ __global__ void __launch_bounds__(256)
                          const float* __restrict__ w, const float* __restrict__ b, const float* __restrict__ mean_in,
                          const float* __restrict__ rstd_in, T* __restrict__ dx, float* __restrict__ dw,
                          float* __restrict__ db, const float* __restrict__ colmask, float* __restrict__ dmask, int rows,
-                         int D, int act, float drop_p, unsigned long long seed, int rows_per_warp,
+                         int D, int Dv, int act, float drop_p, unsigned long long seed, int rows_per_warp,
                          int rows_per_batch, long long out_bs, int out_row_off) {
   extern __shared__ float sh[];  // [3][D] : dw, db, dmask partials
   float* s_dw = sh;
@@ -102,7 +109,7 @@ __global__ void __launch_bounds__(256)
       const int i = lane + 32 * k;
       g[k] = 0.f;
       xh[k] = 0.f;
-      if (i >= D) continue;
+      if (i >= Dv) continue;
       float d = to_f(dy[off + i]);
       if (dy2) d += to_f(dy2[off + i]);
       float xhat = (to_f(x[off + i]) - mean) * rstd;
@@ -126,20 +133,20 @@ __global__ void __launch_bounds__(256)
       s1 += gg;
       s2 += gg * xhat;
     }
-    s1 = warp_sum(s1) / D;
-    s2 = warp_sum(s2) / D;
+    s1 = warp_sum(s1) / Dv;
+    s2 = warp_sum(s2) / Dv;
     const int ob = row / rows_per_batch;
     const long long ooff = (long long)ob * out_bs + (long long)(row - ob * rows_per_batch + out_row_off) * D;
 #pragma unroll
     for (int k = 0; k < NPL; ++k) {
       const int i = lane + 32 * k;
-      if (i < D) dx[ooff + i] = from_f<T>(rstd * (g[k] - s1 - xh[k] * s2));
+      if (i < D) dx[ooff + i] = from_f<T>(i < Dv ? rstd * (g[k] - s1 - xh[k] * s2) : 0.f);
     }
   }
 #pragma unroll
   for (int k = 0; k < NPL; ++k) {
     const int i = lane + 32 * k;
-    if (i >= D) break;
+    if (i >= Dv) break;
     atomicAdd(&s_dw[i], a_dw[k]);
     atomicAdd(&s_db[i], a_db[k]);
     if (dmask) atomicAdd(&s_dm[i], a_dm[k]);
@@ -295,9 +302,10 @@ __global__ void __launch_bounds__(LNB_WARPS * 32, 1)
 using namespace dph;
 
 extern "C" int dph_layernorm_fwd(const void* x, const float* w, const float* b, void* y, void* y_pre, float* mean,
-                                 float* rstd, const float* colmask, int rows, int D, float eps, int act, float drop_p,
-                                 uint64_t seed, int dtype, void* stream) {
-  if (!x || !w || !b || !y || rows <= 0 || D <= 0 || D > 32 * LN_MAX_PER_LANE) {
+                                 float* rstd, const float* colmask, int rows, int D, int d_valid, float eps, int act,
+                                 float drop_p, uint64_t seed, int dtype, void* stream) {
+  if (d_valid <= 0) d_valid = D;
+  if (!x || !w || !b || !y || rows <= 0 || D <= 0 || D > 32 * LN_MAX_PER_LANE || d_valid > D) {
     set_error("layernorm_fwd: bad arguments (D=%d)", D);
     return DPH_ERR_ARG;
   }
@@ -309,7 +317,7 @@ extern "C" int dph_layernorm_fwd(const void* x, const float* w, const float* b, 
     const bool al = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(w) |
                       reinterpret_cast<uintptr_t>(b)) & 15) == 0;
     const int q = D / (32 * vec);
-    if (al && !y_pre && !colmask && act == 0 && D % (32 * vec) == 0 && q >= 1 && q <= 4) {
+    if (al && !y_pre && !colmask && act == 0 && d_valid == D && D % (32 * vec) == 0 && q >= 1 && q <= 4) {
       int g = (rows + warps_per_blk - 1) / warps_per_blk;
       if (g > 148 * 8) g = 148 * 8;
 #define LN_FV(T, Q)                                                                                                  \
@@ -329,10 +337,12 @@ extern "C" int dph_layernorm_fwd(const void* x, const float* w, const float* b, 
   do {                                                                                                           \
     if (dtype == DPH_DTYPE_BF16)                                                                                 \
       layernorm_fwd_kernel<bf16, NPL><<<grid, 256, 0, s>>>((const bf16*)x, w, b, (bf16*)y, (bf16*)y_pre, mean,   \
-                                                           rstd, colmask, rows, D, eps, act, drop_p, seed);      \
+                                                           rstd, colmask, rows, D, d_valid, eps, act, drop_p,    \
+                                                           seed);                                                \
     else                                                                                                         \
       layernorm_fwd_kernel<float, NPL><<<grid, 256, 0, s>>>((const float*)x, w, b, (float*)y, (float*)y_pre,     \
-                                                            mean, rstd, colmask, rows, D, eps, act, drop_p, seed); \
+                                                            mean, rstd, colmask, rows, D, d_valid, eps, act,       \
+                                                            drop_p, seed);                                       \
   } while (0)
   if (D <= 512) LN_FWD(16);
   else if (D <= 768) LN_FWD(24);
@@ -345,15 +355,17 @@ extern "C" int dph_layernorm_fwd(const void* x, const float* w, const float* b, 
 
 extern "C" int dph_layernorm_bwd(const void* dy, const void* dy2, const void* x, const float* w, const float* b,
                                  const float* mean, const float* rstd, void* dx, float* dw, float* db,
-                                 const float* colmask, float* dmask, int rows, int D, int act, float drop_p,
-                                 uint64_t seed, int rows_per_batch, int64_t out_bs, int out_row_off, int dtype,
-                                 void* stream) {
+                                 const float* colmask, float* dmask, int rows, int D, int d_valid, int act,
+                                 float drop_p, uint64_t seed, int rows_per_batch, int64_t out_bs, int out_row_off,
+                                 int dtype, void* stream) {
+  if (d_valid <= 0) d_valid = D;
   if (rows_per_batch <= 0) {
     rows_per_batch = rows;
     out_bs = 0;
     out_row_off = 0;
   }
-  if (!dy || !x || !w || !b || !mean || !rstd || !dx || rows <= 0 || D <= 0 || D > 32 * LN_MAX_PER_LANE) {
+  if (!dy || !x || !w || !b || !mean || !rstd || !dx || rows <= 0 || D <= 0 || D > 32 * LN_MAX_PER_LANE ||
+      d_valid > D) {
     set_error("layernorm_bwd: bad arguments (D=%d)", D);
     return DPH_ERR_ARG;
   }
@@ -365,7 +377,8 @@ extern "C" int dph_layernorm_bwd(const void* dy, const void* dy2, const void* x,
                       reinterpret_cast<uintptr_t>(dy2) | reinterpret_cast<uintptr_t>(w)) & 15) == 0;
     const int q = D / (32 * vec);
     const bool fp32_ok = dtype == DPH_DTYPE_BF16 || q <= 4;
-    if (al && !colmask && !dmask && act == 0 && rows_per_batch == rows && out_row_off == 0 && D % (32 * vec) == 0 &&
+    if (al && !colmask && !dmask && act == 0 && d_valid == D && rows_per_batch == rows && out_row_off == 0 &&
+        D % (32 * vec) == 0 &&
         q >= 1 && q <= (dtype == DPH_DTYPE_BF16 ? 4 : 8) && fp32_ok) {
       int g = (rows + LNB_WARPS - 1) / LNB_WARPS;
       if (g > 148) g = 148;
@@ -403,14 +416,15 @@ extern "C" int dph_layernorm_bwd(const void* dy, const void* dy2, const void* x,
     if (dtype == DPH_DTYPE_BF16)                                                                                 \
       layernorm_bwd_kernel<bf16, NPL><<<grid, 256, smem, s>>>((const bf16*)dy, (const bf16*)dy2, (const bf16*)x, \
                                                               w, b, mean, rstd, (bf16*)dx, dw, db, colmask,      \
-                                                              dmask, rows, D, act, drop_p, seed, rows_per_warp, \
+                                                              dmask, rows, D, d_valid, act, drop_p, seed,       \
+                                                              rows_per_warp,                                     \
                                                               rows_per_batch, out_bs, out_row_off);              \
     else                                                                                                         \
       layernorm_bwd_kernel<float, NPL><<<grid, 256, smem, s>>>((const float*)dy, (const float*)dy2,              \
                                                                (const float*)x, w, b, mean, rstd, (float*)dx,    \
-                                                               dw, db, colmask, dmask, rows, D, act, drop_p,     \
-                                                               seed, rows_per_warp, rows_per_batch, out_bs,      \
-                                                               out_row_off);                                     \
+                                                               dw, db, colmask, dmask, rows, D, d_valid, act,   \
+                                                               drop_p, seed, rows_per_warp, rows_per_batch,      \
+                                                               out_bs, out_row_off);                             \
   } while (0)
   if (D <= 512) LN_BWD(16);
   else if (D <= 768) LN_BWD(24);

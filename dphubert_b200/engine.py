@@ -135,6 +135,7 @@ class Plan:
             else:
                 self.layer_lin_range.append(None)
 
+        self.alias_params = []   # parameters of a real model that are views of this (padded shadow) model's
         self.dtype = None
         self.lin16 = None
         self.conv_w = {}     # layer index -> (wf, wd) in compute dtype (bf16 mode only)
@@ -198,7 +199,7 @@ class Plan:
 
     # ------------------------------------------------------------------ derived weights
     def _vkey(self):
-        return sum(p._version for p in self.params)
+        return sum(p._version for p in self.params) + sum(p._version for p in self.alias_params)
 
     def mark_dirty(self):
         self.dirty = True
@@ -302,9 +303,10 @@ def _dgrad_tap_perm(k, stride):
 
 
 _PLANS = {}
+_SHADOWS = {}   # id(model) -> padding.Shadow: ragged pruned models run on a zero-padded structural copy in bf16 mode
 
 
-def get_plan(model) -> Plan:
+def _plan_of(model) -> Plan:
     plan = _PLANS.get(id(model))
     if plan is not None and plan.model is model and plan.still_bound() and len(plan.params) == sum(
             1 for _ in model.parameters()):
@@ -314,8 +316,33 @@ def get_plan(model) -> Plan:
     return plan
 
 
+def get_plan(model) -> Plan:
+    from . import padding
+
+    sh = _SHADOWS.get(id(model))
+    if sh is not None and (sh.true is not model or not sh.aliased()):
+        _SHADOWS.pop(id(model))
+        _PLANS.pop(id(sh.model), None)
+        sh = None
+    if sh is None and model.compute_dtype == torch.bfloat16 and padding.is_ragged(model):
+        _require_cuda(next(model.parameters()), "the model")
+        sh = padding.Shadow(model)
+        plan = _plan_of(sh.model)
+        sh.alias()
+        plan.alias_params = [p for p, _ in sh.pairs]
+        _PLANS.pop(id(model), None)
+        _SHADOWS[id(model)] = sh
+    if sh is not None:
+        sh.sync()
+        return _plan_of(sh.model)
+    return _plan_of(model)
+
+
 def invalidate(model):
     _PLANS.pop(id(model), None)
+    sh = _SHADOWS.pop(id(model), None)
+    if sh is not None:
+        _PLANS.pop(id(sh.model), None)
 
 
 # ----------------------------------------------------------------------------------------------------------------
@@ -490,6 +517,11 @@ def fused_num_params(model):
 # ----------------------------------------------------------------------------------------------------------------
 # Convolutional feature extractor (components.py:94-120, 158-185)
 # ----------------------------------------------------------------------------------------------------------------
+def _valid(ln):
+    """Number of real columns of a LayerNorm whose width was zero-padded (see padding.py); 0 = all."""
+    return int(getattr(ln, "valid_features", 0))
+
+
 def _frames(n, k, s):
     return (n - k) // s + 1 if n >= k else 0
 
@@ -577,7 +609,7 @@ def conv_stack_fwd(plan: Plan, wave, masks, save: bool, A=None):
                 mean = A("conv%d_mean" % i, (B * Tout,), torch.float32)
                 rstd = A("conv%d_rstd" % i, (B * Tout,), torch.float32)
                 ops.layernorm_fwd(z, plan.view(ln.weight), plan.view(ln.bias), y, B * Tout, Cout, ln.eps, mean, rstd,
-                                  colmask=colmask, act=1)
+                                  colmask=colmask, act=1, d_valid=_valid(ln))
                 rec.update(z=z, mean=mean, rstd=rstd, mode="ln")
             else:
                 ops.conv0_fwd(wave, w, bias, None, None, None, None, colmask, y, B, Cout, k, s, Tout, 0, 1)
@@ -598,7 +630,7 @@ def conv_stack_fwd(plan: Plan, wave, masks, save: bool, A=None):
                 mean = A("conv%d_mean" % i, (B * Tout,), torch.float32)
                 rstd = A("conv%d_rstd" % i, (B * Tout,), torch.float32)
                 ops.layernorm_fwd(z, plan.view(ln.weight), plan.view(ln.bias), y, B * Tout, Cout, ln.eps, mean, rstd,
-                                  colmask=colmask, act=1)
+                                  colmask=colmask, act=1, d_valid=_valid(ln))
                 rec.update(z=z, mean=mean, rstd=rstd, mode="ln")
         rec["y"] = y
         st["layers"].append(rec)
@@ -700,7 +732,7 @@ def conv_stack_bwd(plan: Plan, st, dfeat, dmasks, A):
                 dz = A("conv0_dz", (B, Tout, Cout), dt)
                 ops.layernorm_bwd(dy, rec["z"], plan.view(ln.weight), plan.view(ln.bias), rec["mean"], rec["rstd"], dz,
                                   plan.gview(ln.weight), plan.gview(ln.bias), B * Tout, Cout, colmask=colmask,
-                                  dmask=dm_out, act=1)
+                                  dmask=dm_out, act=1, d_valid=_valid(ln))
                 ops.conv0_bwd(wave, w, bias, None, None, None, None, None, None, dz, scratch, plan.gview(conv.weight), gbias,
                               None, None, None, B, Cout, k, s, Tout, 0, 0)
             else:
@@ -715,7 +747,8 @@ def conv_stack_bwd(plan: Plan, st, dfeat, dmasks, A):
             if rec["mode"] == "ln":
                 ops.layernorm_bwd(dy, rec["z"], plan.view(ln.weight), plan.view(ln.bias), rec["mean"], rec["rstd"], dzp,
                                   plan.gview(ln.weight), plan.gview(ln.bias), B * Tout, Cout, colmask=colmask,
-                                  dmask=dm_out, act=1, rows_per_batch=Tout, out_bs=rows_pb * Cout, out_row_off=padr)
+                                  dmask=dm_out, act=1, rows_per_batch=Tout, out_bs=rows_pb * Cout, out_row_off=padr,
+                                  d_valid=_valid(ln))
                 if gbias is not None:
                     # bias gradient = column sum of dz
                     for b in range(B):
@@ -887,7 +920,7 @@ def _ln_fwd(plan, ln, x, rows, D, A, tag, drop_p=0.0):
     rstd = A(tag + "rstd", (rows,), torch.float32)
     seed = _seed(drop_p)
     ops.layernorm_fwd(x, plan.view(ln.weight), plan.view(ln.bias), y, rows, D, ln.eps, mean, rstd, drop_p=drop_p,
-                      seed=seed)
+                      seed=seed, d_valid=_valid(ln))
     return y, {"ln": ln, "x": x, "mean": mean, "rstd": rstd, "drop_p": drop_p, "seed": seed}
 
 
@@ -1076,7 +1109,7 @@ def _ln_bwd(plan, rec, dy, dy2, A, tag):
     rows, D = x.shape[0], x.shape[1]
     dx = A(tag + "dx", (rows, D), x.dtype)
     ops.layernorm_bwd(dy, x, plan.view(ln.weight), plan.view(ln.bias), rec["mean"], rec["rstd"], dx, _gb(plan, ln.weight),
-                      _gb(plan, ln.bias), rows, D, dy2=dy2, drop_p=rec["drop_p"], seed=rec["seed"])
+                      _gb(plan, ln.bias), rows, D, dy2=dy2, drop_p=rec["drop_p"], seed=rec["seed"], d_valid=_valid(ln))
     return dx
 
 
@@ -1448,6 +1481,7 @@ def model_forward(model, waveforms, lengths=None):
     if model.aux is not None:
         B, T, D = x.shape
         plan = get_plan(model)
+        model = plan.model  # the padded shadow of a ragged pruned model, else the model itself
         out = torch.empty(B * T, model.aux.out_features, dtype=x.dtype, device=x.device)
         xd = x.detach().contiguous().view(B * T, D)
         G.gemm(G.mat(xd), G.mat(plan.W(model.aux.weight, x.dtype)), out, B * T, model.aux.out_features, D,

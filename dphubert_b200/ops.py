@@ -67,17 +67,18 @@ def group_mask_bwd(dy, z, mask, dout, dmask, rows, C, group):
 # ----------------------------------------------------------------------------------------------------------------
 # norms / elementwise
 # ----------------------------------------------------------------------------------------------------------------
-def layernorm_fwd(x, w, b, y, rows, D, eps, mean=None, rstd=None, y_pre=None, colmask=None, act=0, drop_p=0.0, seed=0):
+def layernorm_fwd(x, w, b, y, rows, D, eps, mean=None, rstd=None, y_pre=None, colmask=None, act=0, drop_p=0.0, seed=0,
+                  d_valid=0):
     check(_L().dph_layernorm_fwd(ptr(x), ptr(w), ptr(b), ptr(y), ptr(y_pre), ptr(mean), ptr(rstd), ptr(colmask), rows, D,
-                                 eps, act, drop_p, seed, dtype_code(x), stream_ptr()), "dph_layernorm_fwd")
+                                 d_valid, eps, act, drop_p, seed, dtype_code(x), stream_ptr()), "dph_layernorm_fwd")
     return y
 
 
 def layernorm_bwd(dy, x, w, b, mean, rstd, dx, dw, db, rows, D, dy2=None, colmask=None, dmask=None, act=0, drop_p=0.0,
-                  seed=0, rows_per_batch=0, out_bs=0, out_row_off=0):
+                  seed=0, rows_per_batch=0, out_bs=0, out_row_off=0, d_valid=0):
     check(_L().dph_layernorm_bwd(ptr(dy), ptr(dy2), ptr(x), ptr(w), ptr(b), ptr(mean), ptr(rstd), ptr(dx), ptr(dw),
-                                 ptr(db), ptr(colmask), ptr(dmask), rows, D, act, drop_p, seed, rows_per_batch, out_bs,
-                                 out_row_off, dtype_code(x), stream_ptr()), "dph_layernorm_bwd")
+                                 ptr(db), ptr(colmask), ptr(dmask), rows, D, d_valid, act, drop_p, seed, rows_per_batch,
+                                 out_bs, out_row_off, dtype_code(x), stream_ptr()), "dph_layernorm_bwd")
     return dx
 
 

@@ -155,14 +155,16 @@ int dph_wave_norm(const float* in, int64_t in_bs, float* out, int64_t out_bs, co
  * Row LayerNorm (+ optional GELU, column mask, dropout) forward / backward.
  * Replaces nn.LayerNorm at components.py:54-61 (channel LN of the Large extractor), :271, :808-811, :839, :850-856,
  * :879, :888-889, :905-906 and the dropout at :891.
+ * Rows have D columns of which the first d_valid (0 = all) are normalised; the rest is zero padding of a ragged
+ * (pruned, prune.py:33-59) channel count and is written back as zeros.
  * ---------------------------------------------------------------------------------------------------------- */
 int dph_layernorm_fwd(const void* x, const float* w, const float* b, void* y, void* y_pre, float* mean, float* rstd,
-                      const float* colmask, int rows, int D, float eps, int act, float drop_p, uint64_t seed, int dtype,
-                      void* stream);
+                      const float* colmask, int rows, int D, int d_valid, float eps, int act, float drop_p, uint64_t seed,
+                      int dtype, void* stream);
 int dph_layernorm_bwd(const void* dy, const void* dy2, const void* x, const float* w, const float* b, const float* mean,
                       const float* rstd, void* dx, float* dw, float* db, const float* colmask, float* dmask, int rows, int D,
-                      int act, float drop_p, uint64_t seed, int rows_per_batch, int64_t out_bs, int out_row_off, int dtype,
-                      void* stream);
+                      int d_valid, int act, float drop_p, uint64_t seed, int rows_per_batch, int64_t out_bs, int out_row_off,
+                      int dtype, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * Elementwise / column-reduction helpers around the GEMMs.

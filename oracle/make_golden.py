@@ -149,16 +149,25 @@ def case_forward(wav2vec2_model, kind, seed):
     return out
 
 
-def case_step(wav2vec2_model, rl, kind, seed, units=("conv", "head", "interm"), use_reg=True, mode="layer2layer"):
+def case_step(wav2vec2_model, rl, kind, seed, units=("conv", "head", "interm"), use_reg=True, mode="layer2layer",
+              pruned_from=None):
+    """One `_step` of the reference. `pruned_from` = a prune_*.pt fixture: the student is that ragged pruned model
+    (final_distill.py:61-65), no gates, use_reg False."""
     cfg = small_cfg(kind)
     torch.manual_seed(seed)
     teacher = wav2vec2_model(**cfg).eval()
     randomize(teacher, seed + 1)
     for p in teacher.parameters():
         p.requires_grad = False
-    scfg = student_cfg(cfg, units if use_reg else ())
-    student = wav2vec2_model(**scfg)
-    student.load_state_dict(teacher.state_dict(), strict=False)
+    if pruned_from is not None:
+        assert not use_reg
+        scfg = copy.deepcopy(pruned_from["pruned_cfg"])
+        student = wav2vec2_model(**scfg)
+        student.load_state_dict(pruned_from["pruned_sd"], strict=True)
+    else:
+        scfg = student_cfg(cfg, units if use_reg else ())
+        student = wav2vec2_model(**scfg)
+        student.load_state_dict(teacher.state_dict(), strict=False)
     g = torch.Generator().manual_seed(seed + 2)
     with torch.no_grad():
         for n, p in student.named_parameters():
@@ -333,9 +342,19 @@ def case_prune(wav2vec2_model, kind, seed, units=("conv", "head", "interm", "att
     return out
 
 
+def final_distill_cases(wav2vec2_model, rl):
+    """Second training stage: the pruned (ragged) students of the prune_* fixtures distilled from a full teacher."""
+    for kind, seed in (("base", 300), ("wavlm", 320)):
+        pruned = torch.load(os.path.join(OUT, "prune_%s.pt" % kind), weights_only=False)
+        torch.save(case_step(wav2vec2_model, rl, kind, seed, use_reg=False, pruned_from=pruned),
+                   os.path.join(OUT, "step_final_%s.pt" % kind))
+
+
 def main():
     wav2vec2_model, rl = import_reference()
     os.makedirs(OUT, exist_ok=True)
+    if "--final-only" in sys.argv:  # adds the final-distill fixtures without rewriting the others
+        return final_distill_cases(wav2vec2_model, rl)
     for kind, seed in (("base", 0), ("large", 10), ("wavlm", 20)):
         torch.save(case_forward(wav2vec2_model, kind, seed), os.path.join(OUT, "forward_%s.pt" % kind))
     for kind, seed in (("base", 100), ("large", 110), ("wavlm", 120)):
@@ -345,6 +364,7 @@ def main():
                          mode="predlayer"), os.path.join(OUT, "step_base_allunits_predlayer.pt"))
     for kind, seed in (("base", 200), ("wavlm", 220)):
         torch.save(case_prune(wav2vec2_model, kind, seed), os.path.join(OUT, "prune_%s.pt" % kind))
+    final_distill_cases(wav2vec2_model, rl)
     # known-answer anchors of the full-size models: parameter counts
     from wav2vec2.model import wav2vec2_model as ref_build
     sys.path.insert(0, ROOT)

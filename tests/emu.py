@@ -161,13 +161,16 @@ def wave_norm(wave, out, lengths, B, T0, eps=1e-5):
 
 
 # ------------------------------------------------------------------------------------------------ norms / epilogue
-def layernorm_fwd(x, w, b, y, rows, D, eps, mean=None, rstd=None, y_pre=None, colmask=None, act=0, drop_p=0.0, seed=0):
+def layernorm_fwd(x, w, b, y, rows, D, eps, mean=None, rstd=None, y_pre=None, colmask=None, act=0, drop_p=0.0, seed=0,
+                  d_valid=0):
     assert drop_p == 0.0
-    xf = x.reshape(rows, D).float()
-    mu = xf.mean(1, keepdim=True)
-    var = ((xf - mu) ** 2).mean(1, keepdim=True)
+    Dv = d_valid or D
+    valid = (torch.arange(D) < Dv).float()
+    xf = x.reshape(rows, D).float() * valid
+    mu = xf.sum(1, keepdim=True) / Dv
+    var = (((xf - mu) * valid) ** 2).sum(1, keepdim=True) / Dv
     rs = torch.rsqrt(var + eps)
-    o = (xf - mu) * rs * w + b
+    o = ((xf - mu) * rs * w + b) * valid
     if mean is not None:
         mean.copy_(mu.view(-1))
     if rstd is not None:
@@ -196,12 +199,14 @@ def _scatter_rows(dst, src, rows, C, rows_per_batch, out_bs, out_row_off):
 
 
 def layernorm_bwd(dy, x, w, b, mean, rstd, dx, dw, db, rows, D, dy2=None, colmask=None, dmask=None, act=0, drop_p=0.0,
-                  seed=0, rows_per_batch=0, out_bs=0, out_row_off=0):
+                  seed=0, rows_per_batch=0, out_bs=0, out_row_off=0, d_valid=0):
     assert drop_p == 0.0
-    d = _flat(dy)[: rows * D].view(rows, D).float()
+    Dv = d_valid or D
+    valid = (torch.arange(D) < Dv).float()
+    d = _flat(dy)[: rows * D].view(rows, D).float() * valid
     if dy2 is not None:
-        d = d + _flat(dy2)[: rows * D].view(rows, D).float()
-    xh = (_flat(x)[: rows * D].view(rows, D).float() - mean.view(-1, 1)) * rstd.view(-1, 1)
+        d = d + _flat(dy2)[: rows * D].view(rows, D).float() * valid
+    xh = (_flat(x)[: rows * D].view(rows, D).float() - mean.view(-1, 1)) * rstd.view(-1, 1) * valid
     if act == 1 or colmask is not None:
         u = xh * w + b
         m = colmask if colmask is not None else 1.0
@@ -217,10 +222,10 @@ def layernorm_bwd(dy, x, w, b, mean, rstd, dx, dw, db, rows, D, dy2=None, colmas
         dw += (d * xh).sum(0)
     if db is not None:
         db += d.sum(0)
-    g = d * w
-    s1 = g.mean(1, keepdim=True)
-    s2 = (g * xh).mean(1, keepdim=True)
-    res = rstd.view(-1, 1) * (g - s1 - xh * s2)
+    g = d * w * valid
+    s1 = g.sum(1, keepdim=True) / Dv
+    s2 = (g * xh).sum(1, keepdim=True) / Dv
+    res = rstd.view(-1, 1) * (g - s1 - xh * s2) * valid
     _scatter_rows(dx, res, rows, D, rows_per_batch, out_bs, out_row_off)
     return dx
 
@@ -697,3 +702,4 @@ def install(monkeypatch):
     monkeypatch.setattr(engine, "_require_cuda", lambda t, what: None)
     monkeypatch.setattr(engine, "_is_native", lambda t: True)
     monkeypatch.setattr(engine, "_PLANS", {})
+    monkeypatch.setattr(engine, "_SHADOWS", {})

@@ -102,6 +102,25 @@ def test_layernorm_fwd_bwd(dt, D):
 
 
 @pytest.mark.parametrize("dt", [F32, BF16])
+@pytest.mark.parametrize("D,Dv", [(448, 397), (512, 500), (64, 50)])
+def test_layernorm_zero_padded_width(dt, D, Dv):
+    """d_valid < D: only the real columns of a zero-padded row are normalised; padding comes back as exact zeros."""
+    rows = 257
+    x, w, b = rnd(rows, D, dtype=dt), rnd(D) * 0.2 + 1, rnd(D) * 0.1
+    for t in (x, w, b):
+        t[..., Dv:] = 0
+    for act in (0, 1):
+        y, mean, rstd = rnd(rows, D, dtype=dt), zer(rows), zer(rows)
+        both("layernorm_fwd", (x, w, b, y, rows, D, 1e-5), dict(mean=mean, rstd=rstd, act=act, d_valid=Dv))
+        assert float(y[:, Dv:].abs().max()) == 0.0
+        dy = rnd(rows, D, dtype=dt)
+        dx, dw, db = rnd(rows, D, dtype=dt), zer(D), zer(D)
+        both("layernorm_bwd", (dy, x, w, b, mean, rstd, dx, dw, db, rows, D), dict(act=act, d_valid=Dv),
+             tol=3e-2 if dt == BF16 else 2e-4)
+        assert float(dx[:, Dv:].abs().max()) == 0.0 and float(dw[Dv:].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("dt", [F32, BF16])
 @pytest.mark.parametrize("C", [768, 3072, 100])
 def test_epilogue_bwd(dt, C):
     rows = 517

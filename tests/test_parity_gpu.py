@@ -117,6 +117,49 @@ def test_prune_is_bit_exact(kind):
         assert rel_err(a, b) < 1e-4
 
 
+@pytest.mark.parametrize("kind", ["base", "wavlm"])
+def test_pruned_model_on_tensor_cores(kind):
+    """Ragged pruned model in bf16: runs on the tcgen05 path through its zero-padded shadow (padding.py); the real
+    model keeps the reference's shapes and values."""
+    g = load_golden("prune_" + kind)
+    pm = build_model(g["pruned_cfg"], g["pruned_sd"], DEV, torch.bfloat16)
+    with torch.no_grad():
+        h, _ = pm.extract_features(g["wave"].to(DEV), None)
+    for a, b in zip(h, g["hiddens_pruned"]):
+        assert a.shape == b.shape and rel_err(a, b) < 2e-2
+    sd = pm.state_dict()
+    for k, v in g["pruned_sd"].items():
+        assert torch.equal(sd[k].cpu(), v), k
+
+
+@pytest.mark.parametrize("kind", ["base", "wavlm"])
+@pytest.mark.parametrize("dtype,tol,gtol", CASES)
+def test_final_distill_step_matches_reference(kind, dtype, tol, gtol):
+    """final_distill.py:61-65 — distillation into the ragged pruned student."""
+    g = load_golden("step_final_" + kind)
+    step, teacher, student, projs, lam = build_step(g, DEV, dtype)
+    terms = run_body(step, g, DEV)
+    ref = float(g["loss"])
+    assert abs(terms["loss"] - ref) < tol * abs(ref), (terms, ref)
+    errs = grad_errors(g, student, projs, lam, floor=1e-5 if dtype == torch.float32 else 1e-3)
+    bad = {k: v for k, v in errs.items() if not v < gtol}
+    assert errs and not bad, bad
+    # a full step (clip + AdamW + derived-weight refresh), captured and replayed, leaves the padding at zero
+    step.capture(g["wave"].to(DEV), g["lengths"].to(DEV))
+    step.replay()
+    torch.cuda.synchronize()
+    if dtype == torch.bfloat16:
+        from dphubert_b200 import engine
+
+        sh = engine._SHADOWS[id(student)]
+        for p, q in sh.pairs:
+            if q.shape != p.shape:
+                mask = torch.ones_like(q, dtype=torch.bool)
+                mask[tuple(slice(0, n) for n in p.shape)] = False
+                assert float(q.detach()[mask].abs().max()) == 0.0
+    assert all(torch.isfinite(p).all() for p in student.parameters())
+
+
 def test_no_cpu_fallback():
     from dphubert_b200 import _lib
 
