@@ -113,10 +113,9 @@ def pruned_student(cfg, teacher):
             if n.endswith("log_alpha"):
                 conv = "conv_layers" in n
                 p.copy_(torch.randn(p.shape, generator=gen) * 3.0 + (1.0 if conv else -5.0))
-    conv_config, use_att, use_ff, num_heads, remaining, ff_dims = masked.prune()
-    pcfg = dict(cfg)
-    pcfg.update(extractor_conv_layer_config=conv_config, encoder_use_attention=use_att, encoder_use_feed_forward=use_ff,
-                encoder_num_heads=num_heads, encoder_ff_interm_features=ff_dims)
+    from dphubert_b200.checkpoint import pruned_config
+
+    pcfg = pruned_config(mcfg, masked.prune())
     student = wav2vec2_model(**pcfg)
     student.load_state_dict(masked.state_dict(), strict=True)
     return student, pcfg

@@ -39,6 +39,8 @@ SIGS = {
     "dph_conv0_bwd": [vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32,
                       i32, i32, vp],
     "dph_wave_norm": [vp, i64, vp, i64, vp, i32, i32, f32, vp],
+    # collate.cu
+    "dph_collate_crop": [vp, i32, vp, vp, vp, vp, i32, i32, vp],
     # softmax.cu
     "dph_softmax_fwd": [vp, i64, vp, vp, i64, vp, i32, i32, i32, f32, u64, vp, vp, vp, vp, i32, i32, vp],
     "dph_softmax_bwd": [vp, vp, i64, vp, i64, i32, i32, i32, f32, u64, vp, vp, vp, vp, i32, vp, vp, i32, i32, vp],

@@ -127,6 +127,14 @@ def wave_norm(wave, out, lengths, B, T0, eps=1e-5):
     return out
 
 
+def collate_crop(pool, start, length, out, lengths_out, B, T):
+    """out[b, :] = pool[start[b] : start[b] + length[b]] zero-padded to T (audio_dataset.py:285-363 on the device)"""
+    code = {torch.float32: 1, torch.int16: 2}[pool.dtype]
+    check(_L().dph_collate_crop(ptr(pool), code, ptr(start), ptr(length), ptr(out), ptr(lengths_out), B, T, stream_ptr()),
+          "dph_collate_crop")
+    return out
+
+
 # ----------------------------------------------------------------------------------------------------------------
 # attention probabilities
 # ----------------------------------------------------------------------------------------------------------------

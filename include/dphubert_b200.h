@@ -20,6 +20,7 @@ extern "C" {
 
 #define DPH_DTYPE_BF16 0
 #define DPH_DTYPE_F32 1
+#define DPH_DTYPE_I16 2 /* 16-bit PCM, dph_collate_crop's sample pool only */
 
 /* ------------------------------------------------------------------------------------------------------------
  * Library introspection
@@ -281,6 +282,16 @@ int dph_adamw(float* p, float* g, float* m, float* v, int64_t n, const float* lr
               float weight_decay, const int* step_dev, const double* gnorm_sq, float max_norm, void* p_bf16, int zero_grad,
               void* stream);
 int dph_scale(float* x, int64_t n, float a, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Batch assembly (memory-bound gather): out[b, t] = pool[start[b] + t] for t < len[b], zero beyond; lengths_out[b] =
+ * min(len[b], T).  `pool` = all pre-decoded utterances back to back (fp32 or int16 PCM / 32768) in HBM or mapped
+ * pinned host memory.  Replaces the CPU crop / pad collate at dataset/audio_dataset.py:285-363 (`_crop_audio`,
+ * `CollateFnAudio.__call__`) and the per-batch host-to-device copy; offsets are drawn by the host with the reference's
+ * RNG calls (audio_dataset.py:309).
+ * ---------------------------------------------------------------------------------------------------------- */
+int dph_collate_crop(const void* pool, int pool_dtype, const int64_t* start, const int* len, float* out,
+                     int64_t* lengths_out, int B, int T, void* stream);
 
 #ifdef __cplusplus
 }

@@ -350,7 +350,54 @@ def final_distill_cases(wav2vec2_model, rl):
                    os.path.join(OUT, "step_final_%s.pt" % kind))
 
 
+def sampler_cases():
+    """Batch lists / collated batches of the reference's dataset/audio_dataset.py for seeded inputs."""
+    sys.path.insert(0, REF)
+    from dataset.audio_dataset import BucketizeBatchSampler, CollateFnAudio, DistributedBatchSampler
+
+    g = torch.Generator().manual_seed(41)
+    lengths = torch.randint(20000, 260000, (700,), generator=g).tolist()
+    out = {"lengths": lengths, "cases": []}
+    for kw, seed in ((dict(num_buckets=50, min_len=32000, max_len=250000, max_token_count=16000 * 40, shuffle=True), 5),
+                     (dict(num_buckets=1000, min_len=32000, max_len=250000, max_token_count=16000 * 160, shuffle=True), 6),
+                     (dict(num_buckets=10, batch_size=7, shuffle=False, drop_last=True), 7),
+                     (dict(num_buckets=13, batch_size=16, shuffle=True, drop_last=False), 8)):
+        torch.manual_seed(seed)
+        bs = BucketizeBatchSampler(lengths, **kw)
+        case = {"kw": kw, "seed": seed, "iter_list": [list(b) for b in bs.iter_list], "len": bs.__len__(), "dist": []}
+        for dkw in (dict(num_replicas=4, shuffle=True, seed=3, drop_last=False),
+                    dict(num_replicas=3, shuffle=True, seed=1, drop_last=True),
+                    dict(num_replicas=2, shuffle=False, drop_last=False)):
+            subsets = []
+            for rank in range(dkw["num_replicas"]):
+                torch.manual_seed(seed)
+                fresh = BucketizeBatchSampler(lengths, **kw)  # shuffle=False extends the sampler's list in place
+                ds = DistributedBatchSampler(fresh, rank=rank, **dkw)
+                subsets.append([list(b) for b in ds])
+            case["dist"].append({"kw": dkw, "subsets": subsets})
+        out["cases"].append(case)
+    # collate: small utterances so the fixture stays small
+    wl = torch.randint(700, 3000, (48,), generator=g).tolist()
+    waves = [0.1 * torch.randn(1, n, generator=g) for n in wl]
+    torch.manual_seed(9)
+    bs = BucketizeBatchSampler(wl, num_buckets=6, max_token_count=12000, shuffle=True)
+    batches = [list(b) for b in bs.iter_list]
+    coll = []
+    for pad, rand_crop, seed in ((False, True, 21), (False, False, 22), (True, True, 23)):
+        torch.manual_seed(seed)
+        fn = CollateFnAudio(pad=pad, rand_crop=rand_crop)
+        res = [fn([(waves[i], wl[i]) for i in b]) for b in batches]
+        coll.append({"pad": pad, "rand_crop": rand_crop, "seed": seed, "waveforms": [r[0].clone() for r in res],
+                     "lengths": [r[1].clone() for r in res]})
+    out["collate"] = {"wave_lengths": wl, "waves": [w.clone() for w in waves], "batches": batches, "runs": coll}
+    torch.save(out, os.path.join(OUT, "samplers.pt"))
+    print("samplers: %d sampler cases, %d collate batches" % (len(out["cases"]), len(batches)))
+
+
 def main():
+    if "--samplers-only" in sys.argv:
+        os.makedirs(OUT, exist_ok=True)
+        return sampler_cases()
     wav2vec2_model, rl = import_reference()
     os.makedirs(OUT, exist_ok=True)
     if "--final-only" in sys.argv:  # adds the final-distill fixtures without rewriting the others
@@ -365,6 +412,7 @@ def main():
     for kind, seed in (("base", 200), ("wavlm", 220)):
         torch.save(case_prune(wav2vec2_model, kind, seed), os.path.join(OUT, "prune_%s.pt" % kind))
     final_distill_cases(wav2vec2_model, rl)
+    sampler_cases()
     # known-answer anchors of the full-size models: parameter counts
     from wav2vec2.model import wav2vec2_model as ref_build
     sys.path.insert(0, ROOT)

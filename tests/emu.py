@@ -676,6 +676,17 @@ def l0_norms_bwd(la_base, dla_base, seg_off, seg_len, nseg, bias, dnorm, upstrea
         dla[o:o + n] += g * sg * (1 - sg)
 
 
+def collate_crop(pool, start, length, out, lengths_out, B, T):
+    out.zero_()
+    for b in range(B):
+        n = min(int(length[b]), T)
+        src = pool[int(start[b]): int(start[b]) + n]
+        out[b, :n] = src.float() / 32768.0 if pool.dtype == torch.int16 else src
+        if lengths_out is not None:
+            lengths_out[b] = n
+    return out
+
+
 def rng_set(value):
     pass
 
@@ -689,7 +700,7 @@ _NAMES = ["memset", "memset2d", "zeros", "cast", "vec_mul", "transpose", "axpy",
           "conv0_bwd", "softmax_fwd", "softmax_bwd", "attn_fwd", "attn_bwd", "wavlm_gate_fwd", "wavlm_gate_bwd", "distill_loss_fwd",
           "distill_loss_bwd", "conv_weight_prep", "conv_wgrad_unpermute", "posconv_weight_prep", "posconv_weight_bwd",
           "sumsq", "counter_inc", "adamw", "scale_", "hardconcrete_fwd", "hardconcrete_bwd", "l0_norms", "num_params",
-          "lagrangian", "l0_norms_bwd", "rng_set", "rng_advance"]
+          "lagrangian", "l0_norms_bwd", "rng_set", "rng_advance", "collate_crop"]
 
 
 def install(monkeypatch):

@@ -58,3 +58,35 @@ def test_cpu_tensors_are_refused():
     m = M.wav2vec2_model(**g["cfg"])
     with pytest.raises(_lib.DphError):
         m.extract_features(g["wave"], None)
+
+
+@pytest.mark.parametrize("kind", ["base", "wavlm"])
+def test_prune_checkpoint_flow_matches_reference(kind, tmp_path):
+    """prune.py:11-74 / save_final_ckpt.py:25-49 as functions: same pruned config, same tensors, and the result
+    loads back strictly."""
+    from dphubert_b200 import checkpoint as C
+
+    g = load_golden("prune_" + kind)
+    base_cfg = {k: v for k, v in g["student_cfg"].items()}
+    for flag in C._GATE_FLAGS:  # the original (teacher) config has no gates; prune_state re-derives them from the keys
+        base_cfg[flag] = False
+    lsd = {"student_model." + k: v for k, v in g["state_dict"].items()}
+    lsd.update({"distill_linear_projs.0.weight": torch.eye(3), "lambda1": torch.tensor(0.0)})
+    out = C.prune_state(lsd, base_cfg)
+    ref_cfg = g["pruned_cfg"]
+    assert set(out["config"]) == set(ref_cfg)
+    for k, v in ref_cfg.items():
+        got = out["config"][k]
+        if k == "extractor_conv_layer_config":
+            assert [tuple(c) for c in got] == [tuple(c) for c in v]
+        else:
+            assert got == v, k
+    assert sorted(out["state_dict"]) == sorted(g["pruned_sd"])
+    for k, v in g["pruned_sd"].items():
+        assert torch.equal(out["state_dict"][k], v), k
+    assert list(out["distill_linear_projs"]) == ["0.weight"]
+    path = tmp_path / "pruned.pth"
+    torch.save(out, path)
+    m = C.load_pruned_model(path)
+    fin = C.final_checkpoint({"student_model." + k: v for k, v in m.state_dict().items()}, out["config"])
+    assert sorted(fin["state_dict"]) == sorted(g["pruned_sd"])
