@@ -21,7 +21,7 @@ FLAGS = [
     "-Xcompiler", "-fPIC",
     "--expt-relaxed-constexpr",
     "-I", os.path.join(ROOT, "include"),
-]
+] + os.environ.get("DPH_NVCC_EXTRA", "").split()  # e.g. -DDPH_PDL_EARLY for experiments
 
 
 def _sources():

@@ -93,6 +93,7 @@ __global__ void __launch_bounds__(128, 2)
     tmem_alloc(tmem_slot, 256);
     tmem_relinquish();
   }
+  pdl_wait();  // PDL: barrier init / TMEM allocation above overlap the previous kernel's tail
   int htot = h;
   float gate_i = 1.f;
   const int i = q0 + tid;  // query row of this thread
@@ -241,6 +242,7 @@ __global__ void __launch_bounds__(128, 2)
     __syncthreads();  // S / O_tile / P may now be overwritten
   }
 
+  pdl_trigger();  // only the context store is left: the next kernel's prologue may start on this SM
   if (i < T) {
     const float inv_l = 1.f / l;
     const float hm = p.head_mask ? __ldg(p.head_mask + h) : 1.f;
@@ -286,6 +288,8 @@ __global__ void __launch_bounds__(256)
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const long long M = (long long)B * T;
   float blk = 0.f;
+  pdl_wait();
+  pdl_trigger();
   for (int rr = 0; rr < 8; ++rr) {
     const long long row = ((long long)blockIdx.x * 8 + w) * 8 + rr;
     if (row >= M) break;
@@ -315,6 +319,8 @@ __global__ void __launch_bounds__(256)
 __global__ void __launch_bounds__(256)
     attn_dq_convert_kernel(float* __restrict__ dq32, bf16* __restrict__ dqkv, long long M, int inner) {
   const int c8 = blockIdx.x * blockDim.x + threadIdx.x;  // group of 8 columns
+  pdl_wait();
+  pdl_trigger();
   if (c8 * 8 >= inner) return;
   const uint32_t zero[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
   for (long long row = blockIdx.y; row < M; row += gridDim.y) {
@@ -394,6 +400,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
     tmem_alloc(tmem_slot, 512);
     tmem_relinquish();
   }
+  pdl_wait();
   int htot = h;
   if (p.emb) {
     htot = p.head_index ? p.head_index[h] : h;
@@ -561,6 +568,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
     tc_fence_before();  // orders this thread's TMEM reads before the next tile's __syncthreads / MMAs
   }
   // ---- epilogue: dV (x head mask, warps 0-3) and dK (x scale, warps 4-7) of this key tile
+  pdl_trigger();
   {
     const int j = k0 + rit;
     const uint32_t ta = half == 0 ? tdV : tdK;
@@ -667,7 +675,8 @@ extern "C" int dph_attn_fwd(const void* qkv, void* ctx, void* ctx_un, float* lse
   }
   AttnParams p = attn_params(B, H, T, scale, lengths, rel_table, emb, gate, head_index, Htot, drop_p, seed, head_mask);
   dim3 grid((T + ATT_BQ - 1) / ATT_BQ, H, B);
-  attn_fwd_kernel<<<grid, 128, FWD_SMEM, reinterpret_cast<cudaStream_t>(stream)>>>(tm, p, (bf16*)ctx, (bf16*)ctx_un, lse);
+  launch_pdl(attn_fwd_kernel, grid, dim3(128), FWD_SMEM, reinterpret_cast<cudaStream_t>(stream), tm, p, (bf16*)ctx,
+             (bf16*)ctx_un, lse);
   dph_count_launch();
   return dph_check_last("attn_fwd");
 }
@@ -701,16 +710,17 @@ extern "C" int dph_attn_bwd(const void* qkv, const void* dctx, const void* o_un,
     attr = true;
   }
   const long long M = (long long)B * T;
-  attn_bwd_prep_kernel<<<dim3((unsigned)((M + 63) / 64), H), 256, 0, s>>>((const bf16*)dctx, (const bf16*)o_un, delta,
-                                                                         dmask_h, B, H, T, inner);
+  launch_pdl(attn_bwd_prep_kernel, dim3((unsigned)((M + 63) / 64), H), dim3(256), 0, s, (const bf16*)dctx,
+             (const bf16*)o_un, delta, dmask_h, B, H, T, inner);
   AttnParams p = attn_params(B, H, T, scale, lengths, rel_table, emb, gate, head_index, Htot, drop_p, seed, head_mask);
   dim3 grid((T + ATT_BK - 1) / ATT_BK, H, B);
-  attn_bwd_kernel<<<grid, BWD_THREADS, BWD_SMEM, s>>>(tmq, tmd, p, lse, delta, dq32, (bf16*)dqkv, dgate, demb, num_buckets);
+  launch_pdl(attn_bwd_kernel, grid, dim3(BWD_THREADS), BWD_SMEM, s, tmq, tmd, p, lse, delta, dq32, (bf16*)dqkv, dgate,
+             demb, num_buckets);
   {
     const int gx = (inner / 8 + 255) / 256;
     long long gy = M < 148LL * 16 ? M : 148LL * 16;
-    attn_dq_convert_kernel<<<dim3(gx, (unsigned)gy), inner / 8 < 256 ? ((inner / 8 + 31) / 32) * 32 : 256, 0, s>>>(
-        dq32, (bf16*)dqkv, M, inner);
+    launch_pdl(attn_dq_convert_kernel, dim3(gx, (unsigned)gy),
+               dim3(inner / 8 < 256 ? ((inner / 8 + 31) / 32) * 32 : 256), 0, s, dq32, (bf16*)dqkv, M, inner);
   }
   dph_count_launch(3);
   return dph_check_last("attn_bwd");

@@ -23,7 +23,37 @@ int dph_check_last(const char* what);
 
 extern __device__ unsigned long long dph_rng_epoch;
 
+// Programmatic dependent launch (PDL): 1 unless the environment says DPH_PDL=0 (read once).
+bool dph_pdl_enabled();
+
 namespace dph {
+
+// ---------------------------------------------------------------------------------------------
+// Programmatic dependent launch.  A kernel launched through launch_pdl() may become resident while its stream
+// predecessor is still running (as soon as every CTA of the predecessor has executed pdl_trigger() or exited); it
+// must execute pdl_wait() before it touches global memory that any earlier kernel reads or writes.  pdl_wait()
+// returns when the predecessor grid has completed and its writes are visible, so chains stay transitively ordered.
+// Kernels that use tensor memory trigger only after their own allocation succeeded (a dependent spinning in
+// pdl_wait() while holding TMEM can then never starve the grid it waits for).
+// ---------------------------------------------------------------------------------------------
+DPH_DEVICE void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+DPH_DEVICE void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = dph_pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 
 constexpr int kNumSMsDefault = 148;
 

@@ -32,6 +32,8 @@ __global__ void __launch_bounds__(256, 3)
   const int r1 = min(rows, r0 + rows_per_blk);
   const bool active = c0 < C;
   float cm[VEC], a_mask[VEC], a_bias[VEC];
+  pdl_wait();
+  pdl_trigger();
 #pragma unroll
   for (int j = 0; j < VEC; ++j) {
     cm[j] = (active && colmask && c0 + j < C) ? __ldg(colmask + c0 + j) : 1.f;
@@ -299,15 +301,14 @@ extern "C" int dph_epilogue_bwd(const void* dy, const void* z, const float* colm
 #define EB_LAUNCH(T, V)                                                                                             \
   do {                                                                                                              \
     if (zp)                                                                                                         \
-      epilogue_bwd_kernel<T, V, true><<<grid, 256, 0, s>>>((const T*)dy, (const T*)z, colmask, scalar, (T*)dout,    \
-                                                           dmask, dbias, dscalar, rows, C, rows_per_blk, act,      \
-                                                           drop_p, seed, rows_per_batch, out_bs, out_row_off,      \
-                                                           in_ld, z_ld);                                            \
+      launch_pdl(epilogue_bwd_kernel<T, V, true>, grid, dim3(256), 0, s, (const T*)dy, (const T*)z, colmask, scalar, \
+                 (T*)dout, dmask, dbias, dscalar, rows, C, rows_per_blk, act, drop_p, (unsigned long long)seed,      \
+                 rows_per_batch, (long long)out_bs, out_row_off, (long long)in_ld, (long long)z_ld);                 \
     else                                                                                                            \
-      epilogue_bwd_kernel<T, V, false><<<grid, 256, 0, s>>>((const T*)dy, (const T*)z, colmask, scalar, (T*)dout,   \
-                                                            dmask, dbias, dscalar, rows, C, rows_per_blk, act,     \
-                                                            drop_p, seed, rows_per_batch, out_bs, out_row_off,     \
-                                                            in_ld, z_ld);                                           \
+      launch_pdl(epilogue_bwd_kernel<T, V, false>, grid, dim3(256), 0, s, (const T*)dy, (const T*)z, colmask,       \
+                 scalar, (T*)dout, dmask, dbias, dscalar, rows, C, rows_per_blk, act, drop_p,                       \
+                 (unsigned long long)seed, rows_per_batch, (long long)out_bs, out_row_off, (long long)in_ld,        \
+                 (long long)z_ld);                                                                                  \
   } while (0)
   if (dtype == DPH_DTYPE_BF16) {
     if (vec_ok) EB_LAUNCH(bf16, 8);

@@ -367,6 +367,11 @@ __global__ void __launch_bounds__(gemm_threads(BN), 1)
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+  // everything above touched only shared / tensor memory: it may overlap the tail of the previous kernel (PDL)
+  pdl_wait();
+#ifdef DPH_PDL_EARLY
+  pdl_trigger();
+#endif
   if (threadIdx.x == 0) stamp(tl, 1);
 
   if (warp == 0) {
@@ -418,6 +423,8 @@ __global__ void __launch_bounds__(gemm_threads(BN), 1)
       }
       stamp(tl, 3);
     }
+    // all operand loads of this CTA are in flight: the next kernel may start its prologue on SMs that drain
+    pdl_trigger();
   } else if (warp == 1) {
     // ======================= MMA issuer (leader CTA only) =======================
     if (rank == 0) {
@@ -559,13 +566,22 @@ static int launch_inst(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
   cfg.blockDim = dim3(gemm_threads(BN));
   cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = CG;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (CG > 1) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = CG;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  if (dph_pdl_enabled()) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = (CG > 1) ? 1 : 0;
+  cfg.numAttrs = na;
   cudaError_t e = cudaLaunchKernelEx(&cfg, kfn, ta, tb, p);
   if (e != cudaSuccess) {
     set_error("gemm_bf16_kernel launch: %s", cudaGetErrorString(e));

@@ -175,6 +175,8 @@ __global__ void __launch_bounds__(256)
   const int warps_per_blk = blockDim.x >> 5;
   const uint32_t thresh = (uint32_t)(drop_p * 4294967296.0);
   const float inv_keep = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+  pdl_wait();
+  pdl_trigger();
   for (int row = blockIdx.x * warps_per_blk + (threadIdx.x >> 5); row < rows; row += gridDim.x * warps_per_blk) {
     const T* xr = x + (long long)row * D;
     float v[Q][VEC];
@@ -230,6 +232,8 @@ __global__ void __launch_bounds__(LNB_WARPS * 32, 1)
   const uint32_t thresh = (uint32_t)(drop_p * 4294967296.0);
   const float inv_keep = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
   float a_dw[Q][VEC], a_db[Q][VEC], wv[Q][VEC];
+  pdl_wait();
+  pdl_trigger();
 #pragma unroll
   for (int q = 0; q < Q; ++q) {
     load_vec_f32(w + (lane + 32 * q) * VEC, wv[q]);
@@ -321,7 +325,8 @@ extern "C" int dph_layernorm_fwd(const void* x, const float* w, const float* b, 
       int g = (rows + warps_per_blk - 1) / warps_per_blk;
       if (g > 148 * 8) g = 148 * 8;
 #define LN_FV(T, Q)                                                                                                  \
-  layernorm_fwd_vec_kernel<T, Q><<<g, 256, 0, s>>>((const T*)x, w, b, (T*)y, mean, rstd, rows, D, eps, drop_p, seed)
+  launch_pdl(layernorm_fwd_vec_kernel<T, Q>, dim3(g), dim3(256), 0, s, (const T*)x, w, b, (T*)y, mean, rstd, rows, D,  \
+             eps, drop_p, (unsigned long long)seed)
       if (dtype == DPH_DTYPE_BF16) {
         if (q == 1) LN_FV(bf16, 1); else if (q == 2) LN_FV(bf16, 2); else if (q == 3) LN_FV(bf16, 3); else LN_FV(bf16, 4);
       } else {
@@ -390,8 +395,8 @@ extern "C" int dph_layernorm_bwd(const void* dy, const void* dy2, const void* x,
       cudaFuncSetAttribute(layernorm_bwd_vec_kernel<T, Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);   \
       attr = true;                                                                                                    \
     }                                                                                                                 \
-    layernorm_bwd_vec_kernel<T, Q><<<g, LNB_WARPS * 32, smem, s>>>((const T*)dy, (const T*)dy2, (const T*)x, w, mean, \
-                                                                   rstd, (T*)dx, dw, db, rows, D, drop_p, seed);      \
+    launch_pdl(layernorm_bwd_vec_kernel<T, Q>, dim3(g), dim3(LNB_WARPS * 32), smem, s, (const T*)dy, (const T*)dy2,   \
+               (const T*)x, w, mean, rstd, (T*)dx, dw, db, rows, D, drop_p, (unsigned long long)seed);               \
   } while (0)
       if (dtype == DPH_DTYPE_BF16) {
         if (q == 1) LN_BV(bf16, 1); else if (q == 2) LN_BV(bf16, 2); else if (q == 3) LN_BV(bf16, 3); else LN_BV(bf16, 4);

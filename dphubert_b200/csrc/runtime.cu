@@ -2,6 +2,7 @@
 #include <atomic>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -13,6 +14,14 @@ __global__ void rng_epoch_kernel(unsigned long long value, int advance) {
 
 static std::atomic<long long> g_launches{0};
 static thread_local char g_err[512] = "";
+
+bool dph_pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("DPH_PDL");
+    return !(e != nullptr && e[0] == '0');
+  }();
+  return on;
+}
 
 void dph_count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
