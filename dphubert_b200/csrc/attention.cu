@@ -11,6 +11,8 @@
 // Layout: q/k/v are read straight out of the fused projection buffer qkv[(b T + t)][k | v | q] (row stride 3 * H * 64)
 // by TMA; the context is written as ctx[(b T + t)][h * 64 + e].
 #include "common.cuh"
+#include <type_traits>
+
 #include "../../include/dphubert_b200.h"
 
 namespace dph {
@@ -63,6 +65,7 @@ constexpr int FWD_TB = FWD_SP + ATT_BQ * ATT_BK * 2;     // bias table, up to 2*
 constexpr int FWD_BAR = FWD_TB + 2048 * 4;               // mbarriers + tmem slot
 constexpr int FWD_SMEM = FWD_BAR + 64 + 1024;            // + alignment slack
 
+template <bool BIAS, bool DROP>
 __global__ void __launch_bounds__(128, 2)
     attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p, bf16* __restrict__ ctx,
                     bf16* __restrict__ ctx_un, float* __restrict__ lse) {
@@ -97,7 +100,7 @@ __global__ void __launch_bounds__(128, 2)
   int htot = h;
   float gate_i = 1.f;
   const int i = q0 + tid;  // query row of this thread
-  if (p.emb) {
+  if constexpr (BIAS) {
     htot = p.head_index ? p.head_index[h] : h;
     for (int r = tid; r < 2 * T - 1; r += 128) tb[r] = __ldg(p.emb + (long long)p.rel_table[r] * p.Htot + htot);
     if (p.gate && i < T) gate_i = p.gate[((long long)b * p.Htot + htot) * T + i];
@@ -121,7 +124,9 @@ __global__ void __launch_bounds__(128, 2)
   const int len = p.lengths ? (int)p.lengths[b] : T;
   const uint32_t thresh = (uint32_t)(p.drop_p * 4294967296.0);
   const float inv_keep = p.drop_p > 0.f ? 1.f / (1.f - p.drop_p) : 1.f;
-  const unsigned long long drop_row = ((unsigned long long)(b * p.H + h) * T + (unsigned long long)i) * T;
+  // dropout element index: rows padded to an even stride so that keys (2q, 2q+1) share one hash (dropout_scale2)
+  const unsigned long long drop_row =
+      ((unsigned long long)(b * p.H + h) * T + (unsigned long long)i) * (unsigned long long)((T + 1) & ~1);
   const float sc2 = p.scale * kLog2e;
 
   float m2 = -INFINITY, l = 0.f;  // running max (log2 domain) and sum
@@ -153,27 +158,47 @@ __global__ void __launch_bounds__(128, 2)
       tma_load_2d(sK, &tmQKV, bar_k, h * ATT_D, b * T + k0 + ATT_BK);
     }
 
+    // Interior tiles without a position bias take the lean path: the row maximum is taken on the raw scores
+    // (the scale is positive) and each probability costs one FFMA + one MUFU.EX2.  CTA-uniform branch.
+    const bool edge = BIAS || (k0 + ATT_BK > T) || (k0 + ATT_BK > len);
+    // general logit (log2 domain) of key j for this thread's query
+    auto logit = [&](uint32_t raw, int j) {
+      float x = __uint_as_float(raw) * sc2;
+      if constexpr (BIAS) x += gate_i * tb[min(max(j - i + T - 1, 0), 2 * T - 2)] * kLog2e;
+      if (j >= len) x += -10000.0f * kLog2e;
+      return x;
+    };
     // ---- pass A: row maximum of this tile (log2 domain)
     float mx = m2;
+    if (!edge) {
+      float mr = -INFINITY;
 #pragma unroll 1
-    for (int c = 0; c < ATT_BK / 32; ++c) {
-      uint32_t r[32];
-      tmem_ld_32x32(tS + lane_off + c * 32, r);
-      tmem_ld_wait();
+      for (int c = 0; c < ATT_BK / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(tS + lane_off + c * 32, r);
+        tmem_ld_wait();
 #pragma unroll
-      for (int jj = 0; jj < 32; ++jj) {
-        const int j = k0 + c * 32 + jj;
-        float x = __uint_as_float(r[jj]) * sc2;
-        if (p.emb) x += gate_i * tb[min(max(j - i + T - 1, 0), 2 * T - 2)] * kLog2e;
-        if (j >= len) x += -10000.0f * kLog2e;
-        if (j < T) mx = fmaxf(mx, x);
+        for (int jj = 0; jj < 32; ++jj) mr = fmaxf(mr, __uint_as_float(r[jj]));
+      }
+      mx = fmaxf(mx, mr * sc2);
+    } else {
+#pragma unroll 1
+      for (int c = 0; c < ATT_BK / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(tS + lane_off + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int jj = 0; jj < 32; ++jj) {
+          const int j = k0 + c * 32 + jj;
+          const float x = logit(r[jj], j);
+          if (j < T) mx = fmaxf(mx, x);
+        }
       }
     }
-    const float alpha = fast_exp2(m2 - mx);  // m2 = -inf on the first tile -> 0
+    const float alpha = fast_exp2(m2 - mx);  // m2 = -inf on the first tile -> 0; applied to O when the tile is added
     m2 = mx;
     l *= alpha;
-#pragma unroll
-    for (int e = 0; e < ATT_D; ++e) o[e] *= alpha;
+    const float nm2 = -m2;
     // ---- pass B: probabilities -> bf16 P tile in shared memory (K-major, 128B swizzle, two 64-key blocks)
     float lsum = 0.f;
 #pragma unroll 1
@@ -184,19 +209,23 @@ __global__ void __launch_bounds__(128, 2)
       uint32_t pk[16];
 #pragma unroll
       for (int jj = 0; jj < 32; jj += 2) {
-        float pv[2];
-#pragma unroll
-        for (int u = 0; u < 2; ++u) {
-          const int j = k0 + c * 32 + jj + u;
-          float x = __uint_as_float(r[jj + u]) * sc2;
-          if (p.emb) x += gate_i * tb[min(max(j - i + T - 1, 0), 2 * T - 2)] * kLog2e;
-          if (j >= len) x += -10000.0f * kLog2e;
-          float pe = (j < T) ? fast_exp2(x - m2) : 0.f;
-          lsum += pe;
-          if (p.drop_p > 0.f) pe *= dropout_scale(p.seed, drop_row + (unsigned long long)j, thresh, inv_keep);
-          pv[u] = pe;
+        const int j = k0 + c * 32 + jj;
+        float p0, p1;
+        if (!edge) {
+          p0 = fast_exp2(fmaf(__uint_as_float(r[jj]), sc2, nm2));
+          p1 = fast_exp2(fmaf(__uint_as_float(r[jj + 1]), sc2, nm2));
+        } else {
+          p0 = (j < T) ? fast_exp2(logit(r[jj], j) + nm2) : 0.f;
+          p1 = (j + 1 < T) ? fast_exp2(logit(r[jj + 1], j + 1) + nm2) : 0.f;
         }
-        pk[jj >> 1] = pack_bf16x2(pv[0], pv[1]);
+        lsum += p0 + p1;
+        if constexpr (DROP) {
+          float s0, s1;
+          dropout_scale2(p.seed, drop_row + (unsigned long long)j, thresh, inv_keep, s0, s1);
+          p0 *= s0;
+          p1 *= s1;
+        }
+        pk[jj >> 1] = pack_bf16x2(p0, p1);
       }
       // 32 keys = 4 chunks of 16 bytes; key block (c / 2), chunk index within the 64-key block ((c & 1) * 4 + q)
       const uint32_t blk = sP + (uint32_t)(c >> 1) * (ATT_BQ * 128);
@@ -236,7 +265,7 @@ __global__ void __launch_bounds__(128, 2)
       tmem_ld_32x32(tO + lane_off + c * 32, r);
       tmem_ld_wait();
 #pragma unroll
-      for (int jj = 0; jj < 32; ++jj) o[c * 32 + jj] += __uint_as_float(r[jj]);
+      for (int jj = 0; jj < 32; ++jj) o[c * 32 + jj] = fmaf(o[c * 32 + jj], alpha, __uint_as_float(r[jj]));
     }
     tc_fence_before();
     __syncthreads();  // S / O_tile / P may now be overwritten
@@ -361,6 +390,7 @@ constexpr int BWD_SMEM = BWD_BAR + 64 + 1024;
 //   dQ = dS K (TMEM)  ->  dQ accumulated into the fp32 buffer with 16-byte vector reductions.
 // S / dP of tile qt+1 are issued right behind the gradient MMAs of tile qt (Q / dO are double buffered), so the
 // tensor core works on them while the warps drain dQ.
+template <bool BIAS, bool DROP>
 __global__ void __launch_bounds__(BWD_THREADS, 1)
     attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
                     const __grid_constant__ AttnParams p, const float* __restrict__ lse,
@@ -402,7 +432,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
   }
   pdl_wait();
   int htot = h;
-  if (p.emb) {
+  if constexpr (BIAS) {
     htot = p.head_index ? p.head_index[h] : h;
     for (int r = tid; r < 2 * T - 1; r += BWD_THREADS)
       tb[r] = __ldg(p.emb + (long long)p.rel_table[r] * p.Htot + htot);
@@ -470,14 +500,21 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
       const long long ro = ((long long)(b * p.H + h)) * T + i;
       L2 = lse[ro] * kLog2e;
       dl = delta[ro] * hm;
-      if (p.emb && p.gate) gate_i = p.gate[((long long)b * p.Htot + htot) * T + i];
+      if constexpr (BIAS) {
+        if (p.gate) gate_i = p.gate[((long long)b * p.Htot + htot) * T + i];
+      }
     }
-    const unsigned long long drop_row = ((unsigned long long)(b * p.H + h) * T + (unsigned long long)i) * T;
+    const unsigned long long drop_row =
+        ((unsigned long long)(b * p.H + h) * T + (unsigned long long)i) * (unsigned long long)((T + 1) & ~1);
     mbar_wait(bar_s, ph);
     tc_fence_after();
     float dg = 0.f;
-#pragma unroll 1
-    for (int cc = 0; cc < 2; ++cc) {
+    // Interior tile pairs (all 128 queries and keys valid, no padding mask) without a position bias take the lean
+    // path: 5 instructions per score (FFMA, EX2, FFMA, FMUL, half a pack pair).  CTA-uniform choice.
+    const bool edge = BIAS || (q0 + ATT_BQ > T) || (k0 + ATT_BK > T) || (k0 + ATT_BK > len);
+    const float nL2 = -L2, ndl = -dl;
+    auto do_chunk = [&](auto edge_tag, int cc) {
+      constexpr bool EDGE = decltype(edge_tag)::value;
       const int c = half * 2 + cc;  // 32-key chunk of this warp
       uint32_t rs[32], rp[32];
       tmem_ld_32x32(tS + lane_off + c * 32, rs);
@@ -487,29 +524,41 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
 #pragma unroll
       for (int jj = 0; jj < 32; jj += 2) {
         float pv[2], dv[2];
+        float dsc[2] = {1.f, 1.f};  // dropout scales of this key pair (one hash, same mask as the forward)
+        if constexpr (DROP)
+          dropout_scale2(p.seed, drop_row + (unsigned long long)(k0 + c * 32 + jj), thresh, inv_keep, dsc[0], dsc[1]);
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
           const int j = k0 + c * 32 + jj + u;
-          float x = __uint_as_float(rs[jj + u]) * sc2;
-          float tbv = 0.f;
-          if (p.emb) {
-            tbv = tb[min(max(j - i + T - 1, 0), 2 * T - 2)];
-            x += gate_i * tbv * kLog2e;
+          float pe;
+          [[maybe_unused]] float tbv = 0.f;
+          [[maybe_unused]] bool ok = true;
+          if constexpr (!EDGE) {
+            pe = fast_exp2(fmaf(__uint_as_float(rs[jj + u]), sc2, nL2));
+          } else {
+            float x = fmaf(__uint_as_float(rs[jj + u]), sc2, nL2);
+            if constexpr (BIAS) {
+              tbv = tb[min(max(j - i + T - 1, 0), 2 * T - 2)];
+              x += gate_i * tbv * kLog2e;
+            }
+            if (j >= len) x += -10000.0f * kLog2e;
+            ok = row_ok && (j < T);
+            pe = ok ? fast_exp2(x) : 0.f;
           }
-          if (j >= len) x += -10000.0f * kLog2e;
-          const bool ok = row_ok && (j < T);
-          const float pe = ok ? fast_exp2(x - L2) : 0.f;
-          float ds_scale = 1.f;
-          if (p.drop_p > 0.f) ds_scale = dropout_scale(p.seed, drop_row + (unsigned long long)j, thresh, inv_keep);
-          const float dp = __uint_as_float(rp[jj + u]) * hm * ds_scale;  // d loss / d p_ij
-          const float ds = pe * (dp - dl);
-          pv[u] = pe * ds_scale;
+          // d loss / d p_ij = dP * head mask (* dropout scale); dS = P (dP - delta)
+          float t;
+          if constexpr (DROP) t = fmaf(__uint_as_float(rp[jj + u]) * hm, dsc[u], ndl);
+          else t = fmaf(__uint_as_float(rp[jj + u]), hm, ndl);
+          const float ds = pe * t;
+          pv[u] = DROP ? pe * dsc[u] : pe;
           dv[u] = ds;
-          if (p.emb && ok) {
-            dg += ds * tbv;
-            // per-diagonal sums: the lanes of a warp hold 32 consecutive rows i at the same key j, i.e. 32
-            // consecutive diagonals -> conflict-free shared-memory atomics (buckets would collide heavily)
-            if (demb) atomicAdd(&sdiag[j - i + T - 1], ds * gate_i);
+          if constexpr (BIAS) {
+            if (ok) {
+              dg += ds * tbv;
+              // per-diagonal sums: the lanes of a warp hold 32 consecutive rows i at the same key j, i.e. 32
+              // consecutive diagonals -> conflict-free shared-memory atomics (buckets would collide heavily)
+              if (demb) atomicAdd(&sdiag[j - i + T - 1], ds * gate_i);
+            }
           }
         }
         pk[jj >> 1] = pack_bf16x2(pv[0], pv[1]);
@@ -526,8 +575,15 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
                      "r"(dk[4 * q + 2]), "r"(dk[4 * q + 3])
                      : "memory");
       }
+    };
+    if (edge) {
+#pragma unroll 1
+      for (int cc = 0; cc < 2; ++cc) do_chunk(std::true_type{}, cc);
+    } else {
+#pragma unroll 1
+      for (int cc = 0; cc < 2; ++cc) do_chunk(std::false_type{}, cc);
     }
-    if (dgate && p.emb && p.gate && row_ok) atomicAdd(dgate + ((long long)b * p.Htot + htot) * T + i, dg);
+    if (BIAS && dgate && p.gate && row_ok) atomicAdd(dgate + ((long long)b * p.Htot + htot) * T + i, dg);
     fence_async_smem();
     tc_fence_before();
     __syncthreads();  // P / dS complete, S / dP consumed, dQ of the previous tile drained
@@ -666,7 +722,10 @@ extern "C" int dph_attn_fwd(const void* qkv, void* ctx, void* ctx_un, float* lse
   if (rc) return rc;
   static bool attr = false;
   if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
+    cudaError_t e = cudaFuncSetAttribute(attn_fwd_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(attn_fwd_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(attn_fwd_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(attn_fwd_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
     if (e != cudaSuccess) {
       set_error("attn_fwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
       return DPH_ERR_CUDA;
@@ -675,8 +734,16 @@ extern "C" int dph_attn_fwd(const void* qkv, void* ctx, void* ctx_un, float* lse
   }
   AttnParams p = attn_params(B, H, T, scale, lengths, rel_table, emb, gate, head_index, Htot, drop_p, seed, head_mask);
   dim3 grid((T + ATT_BQ - 1) / ATT_BQ, H, B);
-  launch_pdl(attn_fwd_kernel, grid, dim3(128), FWD_SMEM, reinterpret_cast<cudaStream_t>(stream), tm, p, (bf16*)ctx,
-             (bf16*)ctx_un, lse);
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const bool bias = emb != nullptr, drop = drop_p > 0.f;
+#define ATT_FWD(BI, DR) \
+  launch_pdl(attn_fwd_kernel<BI, DR>, grid, dim3(128), FWD_SMEM, s, tm, p, (bf16*)ctx, (bf16*)ctx_un, lse)
+  if (bias) {
+    if (drop) ATT_FWD(true, true); else ATT_FWD(true, false);
+  } else {
+    if (drop) ATT_FWD(false, true); else ATT_FWD(false, false);
+  }
+#undef ATT_FWD
   dph_count_launch();
   return dph_check_last("attn_fwd");
 }
@@ -702,7 +769,10 @@ extern "C" int dph_attn_bwd(const void* qkv, const void* dctx, const void* o_un,
   if (rc) return rc;
   static bool attr = false;
   if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
+    cudaError_t e = cudaFuncSetAttribute(attn_bwd_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(attn_bwd_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(attn_bwd_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(attn_bwd_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
     if (e != cudaSuccess) {
       set_error("attn_bwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
       return DPH_ERR_CUDA;
@@ -714,8 +784,16 @@ extern "C" int dph_attn_bwd(const void* qkv, const void* dctx, const void* o_un,
              (const bf16*)o_un, delta, dmask_h, B, H, T, inner);
   AttnParams p = attn_params(B, H, T, scale, lengths, rel_table, emb, gate, head_index, Htot, drop_p, seed, head_mask);
   dim3 grid((T + ATT_BK - 1) / ATT_BK, H, B);
-  launch_pdl(attn_bwd_kernel, grid, dim3(BWD_THREADS), BWD_SMEM, s, tmq, tmd, p, lse, delta, dq32, (bf16*)dqkv, dgate,
-             demb, num_buckets);
+  const bool bias = emb != nullptr, drop = drop_p > 0.f;
+#define ATT_BWD(BI, DR)                                                                                             \
+  launch_pdl(attn_bwd_kernel<BI, DR>, grid, dim3(BWD_THREADS), BWD_SMEM, s, tmq, tmd, p, lse, delta, dq32,          \
+             (bf16*)dqkv, dgate, demb, num_buckets)
+  if (bias) {
+    if (drop) ATT_BWD(true, true); else ATT_BWD(true, false);
+  } else {
+    if (drop) ATT_BWD(false, true); else ATT_BWD(false, false);
+  }
+#undef ATT_BWD
   {
     const int gx = (inner / 8 + 255) / 256;
     long long gy = M < 148LL * 16 ? M : 148LL * 16;

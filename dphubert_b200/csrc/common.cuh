@@ -148,9 +148,21 @@ DPH_DEVICE uint32_t hash_u32(uint64_t seed, uint64_t idx) {
   x ^= x >> 16;
   return x;
 }
-// keep-probability test: returns scale (1/(1-p)) or 0.
+// keep-probability test: returns scale (1/(1-p)) or 0.  One 32-bit hash decides TWO neighbouring elements (index
+// pair 2q, 2q+1: low / high 16 bits against the top 16 bits of the threshold, i.e. p quantised to 1/65536), so
+// vectorised callers whose base index is even pay for half a hash per element (dropout_scale2).
 DPH_DEVICE float dropout_scale(uint64_t seed, uint64_t idx, uint32_t thresh, float inv_keep) {
-  return (hash_u32(seed, idx) >= thresh) ? inv_keep : 0.0f;
+  const uint32_t h = hash_u32(seed, idx >> 1);
+  const uint32_t bits = (idx & 1ull) ? (h >> 16) : (h & 0xFFFFu);
+  return (bits >= (thresh >> 16)) ? inv_keep : 0.0f;
+}
+// idx_even must be even: scales of elements idx_even and idx_even + 1.
+DPH_DEVICE void dropout_scale2(uint64_t seed, uint64_t idx_even, uint32_t thresh, float inv_keep, float& s0,
+                               float& s1) {
+  const uint32_t h = hash_u32(seed, idx_even >> 1);
+  const uint32_t t16 = thresh >> 16;
+  s0 = ((h & 0xFFFFu) >= t16) ? inv_keep : 0.0f;
+  s1 = ((h >> 16) >= t16) ? inv_keep : 0.0f;
 }
 
 template <typename T> DPH_DEVICE float to_f(T v);
