@@ -124,6 +124,7 @@ __global__ void __launch_bounds__(128, 2)
   const int len = p.lengths ? (int)p.lengths[b] : T;
   const uint32_t thresh = (uint32_t)(p.drop_p * 4294967296.0);
   const float inv_keep = p.drop_p > 0.f ? 1.f / (1.f - p.drop_p) : 1.f;
+  const uint32_t dkey = DROP ? dropout_key(p.seed) : 0u;  // (after pdl_wait: the epoch is written earlier in the step)
   // dropout element index: rows padded to an even stride so that keys (2q, 2q+1) share one hash (dropout_scale2)
   const unsigned long long drop_row =
       ((unsigned long long)(b * p.H + h) * T + (unsigned long long)i) * (unsigned long long)((T + 1) & ~1);
@@ -201,8 +202,8 @@ __global__ void __launch_bounds__(128, 2)
     const float nm2 = -m2;
     // ---- pass B: probabilities -> bf16 P tile in shared memory (K-major, 128B swizzle, two 64-key blocks)
     float lsum = 0.f;
-#pragma unroll 1
-    for (int c = 0; c < ATT_BK / 32; ++c) {
+    auto pass_b = [&](auto edge_tag, int c) {
+      constexpr bool EDGE = decltype(edge_tag)::value;
       uint32_t r[32];
       tmem_ld_32x32(tS + lane_off + c * 32, r);
       tmem_ld_wait();
@@ -211,7 +212,7 @@ __global__ void __launch_bounds__(128, 2)
       for (int jj = 0; jj < 32; jj += 2) {
         const int j = k0 + c * 32 + jj;
         float p0, p1;
-        if (!edge) {
+        if constexpr (!EDGE) {
           p0 = fast_exp2(fmaf(__uint_as_float(r[jj]), sc2, nm2));
           p1 = fast_exp2(fmaf(__uint_as_float(r[jj + 1]), sc2, nm2));
         } else {
@@ -221,7 +222,7 @@ __global__ void __launch_bounds__(128, 2)
         lsum += p0 + p1;
         if constexpr (DROP) {
           float s0, s1;
-          dropout_scale2(p.seed, drop_row + (unsigned long long)j, thresh, inv_keep, s0, s1);
+          dropout_scale2_keyed(dkey, drop_row + (unsigned long long)j, thresh, inv_keep, s0, s1);
           p0 *= s0;
           p1 *= s1;
         }
@@ -236,6 +237,13 @@ __global__ void __launch_bounds__(128, 2)
                      "r"(pk[4 * q + 2]), "r"(pk[4 * q + 3])
                      : "memory");
       }
+    };
+    if (edge) {
+#pragma unroll 1
+      for (int c = 0; c < ATT_BK / 32; ++c) pass_b(std::true_type{}, c);
+    } else {
+#pragma unroll 1
+      for (int c = 0; c < ATT_BK / 32; ++c) pass_b(std::false_type{}, c);
     }
     l += lsum;
     fence_async_smem();
@@ -486,6 +494,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
   const int len = p.lengths ? (int)p.lengths[b] : T;
   const uint32_t thresh = (uint32_t)(p.drop_p * 4294967296.0);
   const float inv_keep = p.drop_p > 0.f ? 1.f / (1.f - p.drop_p) : 1.f;
+  const uint32_t dkey = DROP ? dropout_key(p.seed) : 0u;  // (after pdl_wait: the epoch is written earlier in the step)
   const float sc2 = p.scale * kLog2e;
   const float hm = p.head_mask ? __ldg(p.head_mask + h) : 1.f;
 
@@ -526,7 +535,8 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
         float pv[2], dv[2];
         float dsc[2] = {1.f, 1.f};  // dropout scales of this key pair (one hash, same mask as the forward)
         if constexpr (DROP)
-          dropout_scale2(p.seed, drop_row + (unsigned long long)(k0 + c * 32 + jj), thresh, inv_keep, dsc[0], dsc[1]);
+          dropout_scale2_keyed(dkey, drop_row + (unsigned long long)(k0 + c * 32 + jj), thresh, inv_keep, dsc[0],
+                               dsc[1]);
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
           const int j = k0 + c * 32 + jj + u;

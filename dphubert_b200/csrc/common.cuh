@@ -136,10 +136,14 @@ DPH_DEVICE float block_sum(float v, float* red) {
 // training step, so a step captured in a CUDA graph (kernel arguments frozen) still draws fresh masks every replay.
 // 32-bit arithmetic only (64-bit multiplies cost ~4 instructions each on the integer pipe): the seed, the epoch and
 // the high half of the index fold into a key, the low half goes through the murmur3 finaliser.
-DPH_DEVICE uint32_t hash_u32(uint64_t seed, uint64_t idx) {
+// The (seed, epoch) part of the key: hoist it out of inner loops (it costs a global load and four multiplies).
+DPH_DEVICE uint32_t dropout_key(uint64_t seed) {
   const uint64_t ep = dph_rng_epoch;
-  const uint32_t key = (uint32_t)seed ^ ((uint32_t)(seed >> 32) * 0x85EBCA6Bu) ^ ((uint32_t)ep * 0xC2B2AE35u) ^
-                       ((uint32_t)(ep >> 32) * 0x27D4EB2Fu) ^ ((uint32_t)(idx >> 32) * 0x165667B1u);
+  return (uint32_t)seed ^ ((uint32_t)(seed >> 32) * 0x85EBCA6Bu) ^ ((uint32_t)ep * 0xC2B2AE35u) ^
+         ((uint32_t)(ep >> 32) * 0x27D4EB2Fu);
+}
+DPH_DEVICE uint32_t hash_u32_keyed(uint32_t key, uint64_t idx) {
+  key ^= (uint32_t)(idx >> 32) * 0x165667B1u;
   uint32_t x = (uint32_t)idx * 0x9E3779B1u + key;
   x ^= x >> 16;
   x *= 0x85EBCA6Bu;
@@ -148,6 +152,7 @@ DPH_DEVICE uint32_t hash_u32(uint64_t seed, uint64_t idx) {
   x ^= x >> 16;
   return x;
 }
+DPH_DEVICE uint32_t hash_u32(uint64_t seed, uint64_t idx) { return hash_u32_keyed(dropout_key(seed), idx); }
 // keep-probability test: returns scale (1/(1-p)) or 0.  One 32-bit hash decides TWO neighbouring elements (index
 // pair 2q, 2q+1: low / high 16 bits against the top 16 bits of the threshold, i.e. p quantised to 1/65536), so
 // vectorised callers whose base index is even pay for half a hash per element (dropout_scale2).
@@ -157,12 +162,40 @@ DPH_DEVICE float dropout_scale(uint64_t seed, uint64_t idx, uint32_t thresh, flo
   return (bits >= (thresh >> 16)) ? inv_keep : 0.0f;
 }
 // idx_even must be even: scales of elements idx_even and idx_even + 1.
-DPH_DEVICE void dropout_scale2(uint64_t seed, uint64_t idx_even, uint32_t thresh, float inv_keep, float& s0,
-                               float& s1) {
-  const uint32_t h = hash_u32(seed, idx_even >> 1);
+DPH_DEVICE void dropout_scale2_keyed(uint32_t key, uint64_t idx_even, uint32_t thresh, float inv_keep, float& s0,
+                                     float& s1) {
+  const uint32_t h = hash_u32_keyed(key, idx_even >> 1);
   const uint32_t t16 = thresh >> 16;
   s0 = ((h & 0xFFFFu) >= t16) ? inv_keep : 0.0f;
   s1 = ((h >> 16) >= t16) ? inv_keep : 0.0f;
+}
+DPH_DEVICE void dropout_scale2(uint64_t seed, uint64_t idx_even, uint32_t thresh, float inv_keep, float& s0,
+                               float& s1) {
+  dropout_scale2_keyed(dropout_key(seed), idx_even, thresh, inv_keep, s0, s1);
+}
+
+// v[0..N) *= dropout scale of the N consecutive elements starting at idx.  Aligned pairs share one hash when idx is
+// even (the usual case: even row strides); otherwise one hash per element.  Same decisions as dropout_scale().
+template <int N>
+DPH_DEVICE void dropout_apply_vec(uint64_t seed, uint64_t idx, uint32_t thresh, float inv_keep, float (&v)[N]) {
+  const uint32_t key = dropout_key(seed);
+  const uint32_t t16 = thresh >> 16;
+  if ((N % 2) == 0 && (idx & 1ull) == 0ull) {
+#pragma unroll
+    for (int j = 0; j + 1 < N; j += 2) {
+      const uint32_t h = hash_u32_keyed(key, (idx + j) >> 1);
+      v[j] *= ((h & 0xFFFFu) >= t16) ? inv_keep : 0.0f;
+      v[j + 1] *= ((h >> 16) >= t16) ? inv_keep : 0.0f;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < N; ++j) {
+      const uint64_t e = idx + j;
+      const uint32_t h = hash_u32_keyed(key, e >> 1);
+      const uint32_t bits = (e & 1ull) ? (h >> 16) : (h & 0xFFFFu);
+      v[j] *= (bits >= t16) ? inv_keep : 0.0f;
+    }
+  }
 }
 
 template <typename T> DPH_DEVICE float to_f(T v);

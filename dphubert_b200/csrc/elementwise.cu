@@ -66,10 +66,10 @@ __global__ void __launch_bounds__(256, 3)
       for (int q = 0; q < RB; ++q) {
         const int r = rb + 8 * q;
         if (r < r1) {
+          if (drop_p > 0.f) dropout_apply_vec<VEC>(seed, (unsigned long long)r * C + c0, thresh, inv_keep, d[q]);
 #pragma unroll
           for (int j = 0; j < VEC; ++j) {
-            float ds = d[q][j];
-            if (drop_p > 0.f) ds *= dropout_scale(seed, (unsigned long long)r * C + c0 + j, thresh, inv_keep);
+            const float ds = d[q][j];
             const float dm = ds * sc;
             float dv = dm * cm[j];
             if constexpr (ZP) {

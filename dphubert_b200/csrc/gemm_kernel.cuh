@@ -253,8 +253,7 @@ DPH_DEVICE void epilogue_chunk(const GemmParams& p, const TileCoord& tc, int row
       const unsigned long long base =
           (((unsigned long long)tc.b1 * p.nb0 + tc.b0) * (unsigned long long)p.M + row) * (unsigned long long)p.N +
           col0;
-#pragma unroll
-      for (int j = 0; j < 32; ++j) v[j] *= dropout_scale(p.seed, base + j, thresh, inv_keep);
+      dropout_apply_vec<32>(p.seed, base, thresh, inv_keep, v);
     }
   }
   if constexpr ((F & F_RES) != 0) {

@@ -209,10 +209,8 @@ __global__ void __launch_bounds__(256)
       load_vec_f32(w + c0, wv);
       load_vec_f32(b + c0, bv);
 #pragma unroll
-      for (int j = 0; j < VEC; ++j) {
-        o[j] = (v[q][j] - mean) * rstd * wv[j] + bv[j];
-        if (drop_p > 0.f) o[j] *= dropout_scale(seed, (unsigned long long)row * D + c0 + j, thresh, inv_keep);
-      }
+      for (int j = 0; j < VEC; ++j) o[j] = (v[q][j] - mean) * rstd * wv[j] + bv[j];
+      if (drop_p > 0.f) dropout_apply_vec<VEC>(seed, (unsigned long long)row * D + c0, thresh, inv_keep, o);
       store_vec(yr + c0, o);
     }
   }
@@ -256,10 +254,10 @@ __global__ void __launch_bounds__(LNB_WARPS * 32, 1)
 #pragma unroll
         for (int j = 0; j < VEC; ++j) g[q][j] += t[j];
       }
+      if (drop_p > 0.f) dropout_apply_vec<VEC>(seed, (unsigned long long)off + c0, thresh, inv_keep, g[q]);
 #pragma unroll
       for (int j = 0; j < VEC; ++j) {
-        float d = g[q][j];
-        if (drop_p > 0.f) d *= dropout_scale(seed, (unsigned long long)off + c0 + j, thresh, inv_keep);
+        const float d = g[q][j];
         const float xhat = (xh[q][j] - mean) * rstd;
         a_dw[q][j] += d * xhat;
         a_db[q][j] += d;
