@@ -343,6 +343,8 @@ def run_ours(args, rank, world, local_rank):
     }
     if rank == 0 and not args.no_roofline and dtype == torch.bfloat16:
         line["roofline"] = roofline(step, wave, lengths, G, dev)
+        if world == 1:
+            line["roofline_hbm"] = hbm_kernels(B, secs, dev)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args)
     if rank == 0:
@@ -402,6 +404,114 @@ def gemm_table(step, wave, lengths, G, path):
             f.write("%8.3f %5d %9.1f %8.1f   %s\n" % (ms, n, ms * 1e3 / n, fl / ms / 1e9, " ".join(str(k) for k in key)))
         f.write("# total %.3f ms, %d launches, %.1f TFLOP/s\n" % (sum(r[0] for r in rows), len(trace),
                                                                 sum(r[2] for r in rows) / sum(r[0] for r in rows) / 1e9))
+
+
+def hbm_kernels(B, seconds, dev):
+    """The memory-bound kernels of the step, each timed alone at the step's sizes (CUDA events around single launches,
+    L2 flushed by a 512 MB memset before every timed launch, median of 5): algorithmic bytes / time against the measured
+    HBM copy bandwidth.  Algorithmic bytes per unit are SURVEY.md 8(d)'s figures (stated per entry)."""
+    from dphubert_b200 import ops
+
+    BF, F32 = torch.bfloat16, torch.float32
+    peak, src = 6550.0, "fallback"
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peak, src = float(json.load(f)["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs"
+    except Exception:  # noqa: BLE001
+        pass
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+    T0 = int(seconds * SR)
+    T1 = (T0 - 10) // 5 + 1
+    T = T1
+    for k in (3, 3, 3, 3, 2, 2):
+        T = (T - k) // 2 + 1
+    rows, D, C = B * T, 768, 512
+    g = torch.Generator(device=dev).manual_seed(1)
+
+    def rn(*shape, dtype=BF, scale=1.0):
+        return (torch.randn(*shape, device=dev, generator=g) * scale).to(dtype)
+
+    def timeit(fn):
+        for _ in range(2):
+            fn()
+        ts = []
+        for _ in range(5):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1) * 1e3)
+        return sorted(ts)[len(ts) // 2]
+
+    out = []
+
+    def add(name, nbytes, fn, what):
+        us = timeit(fn)
+        gbs = nbytes / us / 1e3
+        out.append({"kernel": name, "us": round(us, 2), "algorithmic_bytes": int(nbytes), "achieved_gbs": round(gbs, 1),
+                    "frac": round(gbs / peak, 3), "bytes_model": what})
+
+    # conv-0 block (components.py:94-120, layer 0): conv k=10 s=5 + GroupNorm + GELU + channel mask
+    wave = rn(B, T0, dtype=F32, scale=0.1)
+    w0, gam, bet = rn(C, 10, dtype=F32, scale=0.3), rn(C, dtype=F32), rn(C, dtype=F32)
+    mask = torch.rand(C, device=dev, generator=g)
+    moments = torch.zeros(B * 65, dtype=torch.float64, device=dev)
+    mean, rstd = torch.zeros(B * C, device=dev), torch.zeros(B * C, device=dev)
+    y = torch.empty(B, T1, C, dtype=BF, device=dev)
+    ops.conv0_stats(wave, w0, None, moments, mean, rstd, B, C, 10, 5, T1, 1e-5)
+    add("conv0_fwd (conv+GroupNorm+GELU+mask)", B * (4 * T0 + 2 * C * T1),
+        lambda: ops.conv0_fwd(wave, w0, None, gam, bet, mean, rstd, mask, y, B, C, 10, 5, T1, 1, 1),
+        "read 4*T0 + write 2*512*T1 per utterance")
+    dy = rn(B, T1, C)
+    scratch = torch.zeros(16 * B * C, device=dev)
+    dW, dgam, dbet, dmask = torch.zeros(C, 10, device=dev), torch.zeros(C, device=dev), torch.zeros(C, device=dev), \
+        torch.zeros(C, device=dev)
+    add("conv0_bwd (recompute, dy read once)", B * (4 * T0 + 2 * C * T1),
+        lambda: ops.conv0_bwd(wave, w0, None, gam, bet, mean, rstd, moments, mask, dy, scratch, dW, None, dgam, dbet, dmask,
+                              B, C, 10, 5, T1, 1, 1),
+        "read 4*T0 + read 2*512*T1 per utterance")
+    del y, dy
+    # LayerNorm(768) over the (B*T, 768) encoder activation
+    x, yy = rn(rows, D), torch.empty(rows, D, dtype=BF, device=dev)
+    lw, lb = rn(D, dtype=F32), rn(D, dtype=F32)
+    mu, rs = torch.zeros(rows, device=dev), torch.zeros(rows, device=dev)
+    add("layernorm_fwd", 2 * 2 * rows * D, lambda: ops.layernorm_fwd(x, lw, lb, yy, rows, D, 1e-5, mean=mu, rstd=rs),
+        "read + write 2*rows*768")
+    dx, dlw, dlb = torch.empty(rows, D, dtype=BF, device=dev), torch.zeros(D, device=dev), torch.zeros(D, device=dev)
+    add("layernorm_bwd", 3 * 2 * rows * D, lambda: ops.layernorm_bwd(yy, x, lw, lb, mu, rs, dx, dlw, dlb, rows, D),
+        "read dy, x + write dx, 2*rows*768 each")
+    # FFN hidden backward: GELU' * mask (+ bias / mask gradient column sums) over (B*T, 3072)
+    F = 3072
+    dyh, z, dout = rn(rows, F), rn(rows, F), torch.empty(rows, F, dtype=BF, device=dev)
+    cm, dm, db = torch.rand(F, device=dev, generator=g), torch.zeros(F, device=dev), torch.zeros(F, device=dev)
+    add("epilogue_bwd (GELU' * mask, dbias, dmask)", 3 * 2 * rows * F,
+        lambda: ops.epilogue_bwd(dyh, rows, F, z=z, colmask=cm, dout=dout, dmask=dm, dbias=db, act=1),
+        "read dy, z + write dz, 2*rows*3072 each")
+    # DistillLoss over 4 layers x (B*T, 768)
+    lr_rows = 4 * rows
+    a, b2 = rn(lr_rows, D), rn(lr_rows, D)
+    rowstat, acc, lo = torch.zeros(lr_rows, 4, device=dev), torch.zeros(8, device=dev), torch.zeros(4, device=dev)
+    add("distill_loss_fwd (L1 + cosine)", 2 * 2 * lr_rows * D,
+        lambda: ops.distill_loss_fwd(a, b2, rowstat, acc, lo, lr_rows, D, 0.0, 1.0, 1.0, 0, True, True, lr_rows),
+        "read pred + target, 2*4*rows*768 each")
+    da, up = torch.empty(lr_rows, D, dtype=BF, device=dev), torch.ones(1, device=dev)
+    add("distill_loss_bwd", 3 * 2 * lr_rows * D,
+        lambda: ops.distill_loss_bwd(a, b2, rowstat, up, da, lr_rows, lr_rows, D, 0.0, 1.0, 1.0, 0),
+        "read pred + target + write grad")
+    # clip + AdamW + bf16 mirror + gradient zeroing over the 85 M Linear weights
+    n = 84_934_656
+    pp, gg, m1, m2 = (torch.zeros(n, device=dev) for _ in range(4))
+    pb = torch.empty(n, dtype=BF, device=dev)
+    lr_d, st_d, gn = torch.full((1,), 1e-4, device=dev), torch.ones(1, device=dev), torch.ones(1, device=dev)
+    add("adamw (clip + update + bf16 mirror + zero grad)", 30 * n,
+        lambda: ops.adamw(pp, gg, m1, m2, lr_d, 0.9, 0.98, 1e-6, 0.0, st_d, gn, 10.0, pb, True),
+        "16 B read + 14 B write per parameter")
+    so = torch.zeros(1, device=dev)
+    add("sumsq (gradient norm)", 4 * n, lambda: ops.sumsq(gg, so), "4 B read per parameter")
+    return {"peak_gbs": peak, "peak_source": src, "l2_policy": "512 MB memset before each timed launch",
+            "kernels": out}
 
 
 def roofline(step, wave, lengths, G, dev):
