@@ -364,6 +364,12 @@ __global__ void __launch_bounds__(1024)
 
 using namespace dph;
 
+namespace dph {
+int conv0_fwd_tc(const float* wave, long long wave_bs, const float* w, const float* bias, const float* gamma,
+                 const float* beta, const float* mean, const float* rstd, const float* mask, bf16* y, int B, int C, int k,
+                 int stride, int T1, int norm, int act, cudaStream_t s);
+}
+
 static int conv0_check(int C, int k, int stride, int T1) {
   if (C <= 0 || k <= 0 || k > C0_MAXK || stride <= 0 || stride > 8 || T1 <= 0) {
     set_error("conv0: unsupported shape C=%d k=%d stride=%d T1=%d (k <= 10, stride <= 8)", C, k, stride, T1);
@@ -395,6 +401,14 @@ extern "C" int dph_conv0_fwd(const float* wave, int64_t wave_bs, const float* w,
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   dim3 grid((T1 + C0A_TT - 1) / C0A_TT, B);
   const int pair_vec = (C % 2 == 0) && ((reinterpret_cast<uintptr_t>(y) & 3) == 0);
+  if (dtype == DPH_DTYPE_BF16) {
+    // tensor-core path (conv0_tc.cu) for the usual shapes; anything outside its envelope takes the CUDA-core kernel
+    rc = conv0_fwd_tc(wave, wave_bs, w, bias, gamma, beta, mean, rstd, mask, (bf16*)y, B, C, k, stride, T1, norm, act, s);
+    if (rc != DPH_ERR_UNSUPPORTED) {
+      if (rc == DPH_OK) dph_count_launch();
+      return rc ? rc : dph_check_last("conv0_fwd_tc");
+    }
+  }
   if (dtype == DPH_DTYPE_BF16)
     conv0_apply_kernel<bf16><<<grid, C0_THREADS, 0, s>>>(wave, wave_bs, w, bias, gamma, beta, mean, rstd, mask,
                                                          (bf16*)y, C, k, stride, T1, norm, act, pair_vec);
