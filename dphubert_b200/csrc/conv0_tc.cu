@@ -20,20 +20,24 @@
 namespace dph {
 void set_error(const char* fmt, ...);
 
+int make_tmap_nd_bf16(CUtensorMap* out, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                      const uint32_t* box, int swizzle);
+
 namespace c0tc {
 constexpr int TT = 128;                 // frames per tile (= TMEM lanes)
 constexpr int NB = 256;                 // channels per MMA / accumulator
 constexpr int MAXC = 512;
 constexpr int MAXK = 10;
-constexpr int MAXS = 8;                 // stride limit (window staging buffer)
-constexpr int EPI_WARPS = 8;
-constexpr int THREADS = 32 * (1 + EPI_WARPS);
-constexpr int WIN = (TT - 1) * MAXS + MAXK + 6;              // staged waveform samples per tile
+constexpr int EPI_WARPS = 16;                   // four per TMEM lane quadrant, 64 accumulator columns each
+constexpr int EPI_COLS = NB / (EPI_WARPS / 4);  // columns per epilogue warp
+constexpr int EPI_CHUNKS = EPI_COLS / 32;
+constexpr int PROD_WARPS = 4;           // one window row per producer thread
+constexpr int THREADS = 32 * (PROD_WARPS + EPI_WARPS);
 constexpr int S_B = 0;                                       // weights  [512][64] bf16, 128B swizzle   64 KB
 constexpr int S_A = S_B + MAXC * 128;                        // windows  2 x [128][64] bf16             32 KB
 constexpr int S_TAB = S_A + 2 * TT * 128;                    // per-channel {sc, sh, sc m, sh m} pairs  8 KB
-constexpr int S_WIN = S_TAB + MAXC * 16;                     // fp32 waveform window
-constexpr int S_BAR = S_WIN + ((WIN * 4 + 15) / 16) * 16;    // barriers
+constexpr int S_OUT = S_TAB + MAXC * 16;                     // output staging, 4 KB per epilogue warp          64 KB
+constexpr int S_BAR = S_OUT + EPI_WARPS * 4096;              // barriers
 constexpr int SMEM = S_BAR + 128 + 1024;
 
 DPH_DEVICE uint32_t sw128(int r, int c) { return (uint32_t)(r * 128 + ((c ^ (r & 7)) << 4)); }
@@ -83,13 +87,13 @@ struct Params {
 };
 
 template <bool ACT>
-__global__ void __launch_bounds__(THREADS, 1) conv0_fwd_tc_kernel(const __grid_constant__ Params p) {
+__global__ void __launch_bounds__(THREADS, 1)
+    conv0_fwd_tc_kernel(const __grid_constant__ Params p, const __grid_constant__ CUtensorMap tmY) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* gbase = smem_raw + (sbase - smem_u32(smem_raw));
   const uint32_t sB = sbase + S_B, sA = sbase + S_A;
   float* tab = reinterpret_cast<float*>(gbase + S_TAB);
-  float* win = reinterpret_cast<float*>(gbase + S_WIN);
   const uint32_t bar0 = sbase + S_BAR;
   auto a_free = [&](int i) { return bar0 + 8u * i; };        // [2] MMAs that read A buffer i have completed
   auto t_full = [&](int i) { return bar0 + 16u + 8u * i; };  // [2] accumulator i is complete
@@ -148,82 +152,80 @@ __global__ void __launch_bounds__(THREADS, 1) conv0_fwd_tc_kernel(const __grid_c
   const long long total = (long long)p.B * p.ntile * p.nblk;
   const long long u0 = total * blockIdx.x / gridDim.x, u1 = total * (blockIdx.x + 1) / gridDim.x;
 
-  if (warp == 0) {
-    // ======================= window builder + MMA issuer =======================
-    int acc = 0, abuf = -1, nA = 0;
+  if (warp < PROD_WARPS) {
+    // ======================= window builders (128 threads, one frame each) + MMA issuer (thread 0) ===============
+    int acc = 0, nA = 0;
     uint32_t acc_ph = 0;
-    long long cur_tile = -1;
-    for (long long u = u0; u < u1; ++u) {
-      const int blk = (int)(u % p.nblk);
-      const long long bt = u / p.nblk;
-      if (bt != cur_tile) {
-        cur_tile = bt;
-        abuf = nA & 1;
-        const int b = (int)(bt / p.ntile), t0 = (int)(bt % p.ntile) * TT;
-        // wait until the MMAs that read this buffer two tiles ago are done
-        if (nA >= 2) mbar_wait(a_free(abuf), (uint32_t)(((nA >> 1) - 1) & 1));
-        ++nA;
-        const float* x = p.wave + (long long)b * p.wave_bs + (long long)t0 * p.stride;
+    const long long bt0 = u0 / p.nblk, bt1 = (u1 + p.nblk - 1) / p.nblk;
+    for (long long bt = bt0; bt < bt1 && u0 < u1; ++bt, ++nA) {
+      const int abuf = nA & 1;
+      const int b = (int)(bt / p.ntile), t0 = (int)(bt % p.ntile) * TT;
+      // wait until the MMAs that read this buffer two tiles ago are done
+      if (nA >= 2) mbar_wait(a_free(abuf), (uint32_t)(((nA >> 1) - 1) & 1));
+      {
+        const int r = tid;  // frame of this thread inside the tile
         const int nt = min(TT, p.T1 - t0);
-        const int nsamp = (nt - 1) * p.stride + p.k;
-        for (int i = lane; i < nsamp; i += 32) win[i] = x[i];
-        __syncwarp();
-#pragma unroll 1
-        for (int rr = 0; rr < TT / 32; ++rr) {
-          const int r = rr * 32 + lane;
-          unsigned short row[32];
+        unsigned short row[32];
 #pragma unroll
-          for (int q = 0; q < 32; ++q) row[q] = 0;
-          if (r < nt) {
+        for (int q = 0; q < 32; ++q) row[q] = 0;
+        if (r < nt) {
+          const float* x = p.wave + (long long)b * p.wave_bs + (long long)(t0 + r) * p.stride;
+          float xv[MAXK];
 #pragma unroll
-            for (int q = 0; q < MAXK; ++q) {
-              const float v = q < p.k ? win[r * p.stride + q] : 0.f;
-              unsigned short hi, lo;
-              split_bf16(v, hi, lo);
-              row[q] = hi;
-              row[MAXK + q] = lo;
-              row[2 * MAXK + q] = hi;
-            }
-          }
+          for (int q = 0; q < MAXK; ++q) xv[q] = q < p.k ? __ldg(x + q) : 0.f;
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            uint4 v4;
-            v4.x = row[8 * j] | ((uint32_t)row[8 * j + 1] << 16);
-            v4.y = row[8 * j + 2] | ((uint32_t)row[8 * j + 3] << 16);
-            v4.z = row[8 * j + 4] | ((uint32_t)row[8 * j + 5] << 16);
-            v4.w = row[8 * j + 6] | ((uint32_t)row[8 * j + 7] << 16);
-            *reinterpret_cast<uint4*>(gbase + S_A + abuf * (TT * 128) + sw128(r, j)) = v4;
+          for (int q = 0; q < MAXK; ++q) {
+            unsigned short hi, lo;
+            split_bf16(xv[q], hi, lo);
+            row[q] = hi;
+            row[MAXK + q] = lo;
+            row[2 * MAXK + q] = hi;
           }
         }
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        __syncwarp();
-      }
-      // accumulator must have been drained by the epilogue
-      mbar_wait(t_empty(acc), acc_ph ^ 1u);
-      tc_fence_after();
-      if (lane == 0) {
-        const int nb = min(NB, p.C - blk * NB);
-        const uint32_t idesc = make_idesc_bf16(TT, nb, false, false);
-        const uint32_t a_addr = sA + (uint32_t)abuf * (TT * 128), b_addr = sB + (uint32_t)blk * (NB * 128);
 #pragma unroll
-        for (int kk = 0; kk < 2; ++kk)
-          umma_f16_ss(tmem_base + (uint32_t)(acc * NB), make_smem_desc(a_addr + kk * 32, 0, 1024, 2),
-                      make_smem_desc(b_addr + kk * 32, 0, 1024, 2), idesc, kk > 0 ? 1u : 0u);
-        umma_commit(t_full(acc));
-        const bool last_use = (blk == p.nblk - 1) || (u + 1 == u1);
-        if (last_use) umma_commit(a_free(abuf));
+        for (int j = 0; j < 4; ++j) {
+          uint4 v4;
+          v4.x = row[8 * j] | ((uint32_t)row[8 * j + 1] << 16);
+          v4.y = row[8 * j + 2] | ((uint32_t)row[8 * j + 3] << 16);
+          v4.z = row[8 * j + 4] | ((uint32_t)row[8 * j + 5] << 16);
+          v4.w = row[8 * j + 6] | ((uint32_t)row[8 * j + 7] << 16);
+          *reinterpret_cast<uint4*>(gbase + S_A + abuf * (TT * 128) + sw128(r, j)) = v4;
+        }
       }
-      __syncwarp();
-      acc ^= 1;
-      if (acc == 0) acc_ph ^= 1u;
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      asm volatile("bar.sync 2, %0;" ::"n"(PROD_WARPS * 32));
+      if (warp == 0) {
+        const long long ua = bt * p.nblk > u0 ? bt * p.nblk : u0;
+        const long long ub = (bt + 1) * p.nblk < u1 ? (bt + 1) * p.nblk : u1;
+        for (long long u = ua; u < ub; ++u) {
+          const int blk = (int)(u % p.nblk);
+          mbar_wait(t_empty(acc), acc_ph ^ 1u);  // accumulator drained by the epilogue
+          tc_fence_after();
+          if (lane == 0) {
+            const int nb = min(NB, p.C - blk * NB);
+            const uint32_t idesc = make_idesc_bf16(TT, nb, false, false);
+            const uint32_t a_addr = sA + (uint32_t)abuf * (TT * 128), b_addr = sB + (uint32_t)blk * (NB * 128);
+#pragma unroll
+            for (int kk = 0; kk < 2; ++kk)
+              umma_f16_ss(tmem_base + (uint32_t)(acc * NB), make_smem_desc(a_addr + kk * 32, 0, 1024, 2),
+                          make_smem_desc(b_addr + kk * 32, 0, 1024, 2), idesc, kk > 0 ? 1u : 0u);
+            umma_commit(t_full(acc));
+            if (u + 1 == ub) umma_commit(a_free(abuf));
+          }
+          __syncwarp();
+          acc ^= 1;
+          if (acc == 0) acc_ph ^= 1u;
+        }
+      }
     }
     pdl_trigger();
   } else {
     // ======================= epilogue warps =======================
-    const int ew = warp - 1;
+    const int ew = warp - PROD_WARPS;
     const int quad = warp & 3;           // TMEM lane quadrant this warp may read
-    const int chalf = ew >> 2;           // which 128 of the accumulator's 256 columns
-    const int etid = tid - 32;
+    const int chalf = ew >> 2;           // which EPI_COLS-wide slice of the accumulator's 256 columns
+    const int etid = tid - PROD_WARPS * 32;
+    const uint32_t stage = sbase + S_OUT + (uint32_t)ew * 4096u;
     int acc = 0, cur_b = -1;
     uint32_t acc_ph = 0;
     constexpr float GA = 0.7977176713187712f, GB = 0.03679851046109153f, GC = -0.00031586434495541917f;
@@ -260,23 +262,28 @@ __global__ void __launch_bounds__(THREADS, 1) conv0_fwd_tc_kernel(const __grid_c
       }
       mbar_wait(t_full(acc), acc_ph);
       tc_fence_after();
-      const int t = t0 + quad * 32 + lane;
       const int nb = min(NB, p.C - blk * NB);
-      const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * NB + chalf * (NB / 2));
+      const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * NB + chalf * EPI_COLS);
+      const bool active = chalf * EPI_COLS < nb;  // C is a multiple of 64: a warp's 64 columns are all in or all out
+      if (active) {
+        // the TMA store of the previous unit must have finished reading this warp's staging tile
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        __syncwarp();
+      }
 #pragma unroll 1
-      for (int ch = 0; ch < 4; ++ch) {
-        const int cl = chalf * (NB / 2) + ch * 32;  // column inside the accumulator (warp-uniform)
+      for (int ch = 0; ch < EPI_CHUNKS; ++ch) {
+        const int cl = chalf * EPI_COLS + ch * 32;  // column inside the accumulator (warp-uniform)
         uint32_t r[32];
-        if (cl < nb) {
+        if (active) {
           tmem_ld_32x32(taddr + ch * 32, r);
           tmem_ld_wait();
         }
-        if (ch == 3) {  // all TMEM reads of this accumulator are done: hand it back
+        if (ch == EPI_CHUNKS - 1) {  // all TMEM reads of this accumulator are done: hand it back
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(t_empty(acc));
         }
-        if (cl >= nb) continue;
+        if (!active) continue;
         const int c0 = blk * NB + cl;
         const float4* tp = reinterpret_cast<const float4*>(tab + (c0 >> 1) * 8);
         uint32_t o[16];
@@ -303,17 +310,32 @@ __global__ void __launch_bounds__(THREADS, 1) conv0_fwd_tc_kernel(const __grid_c
           }
           o[j] = pack_bf16x2(y0, y1);
         }
-        if (t < p.T1) {
-          bf16* dst = p.y + ((long long)b * p.T1 + t) * p.C + c0;
-          const uint32_t lo8[8] = {o[0], o[1], o[2], o[3], o[4], o[5], o[6], o[7]};
-          const uint32_t hi8[8] = {o[8], o[9], o[10], o[11], o[12], o[13], o[14], o[15]};
-          stg_256(dst, lo8);
-          stg_256(dst + 16, hi8);
+        // stage this thread's 64 bytes (frame = lane, channels ch * 32 ..) in the warp's 128B-swizzled 32 x 64 tile
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const uint32_t addr = stage + sw128(lane, ch * 4 + q);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(o[4 * q]), "r"(o[4 * q + 1]),
+                       "r"(o[4 * q + 2]), "r"(o[4 * q + 3])
+                       : "memory");
+        }
+      }
+      if (active) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) {
+          // one coalesced bulk store of the warp's 32 frames x 64 channels; frames >= T1 are clipped by the map
+          asm volatile(
+              "cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(
+                  reinterpret_cast<uint64_t>(&tmY)),
+              "r"(blk * NB + chalf * EPI_COLS), "r"(t0 + quad * 32), "r"(b), "r"(stage)
+              : "memory");
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         }
       }
       acc ^= 1;
       if (acc == 0) acc_ph ^= 1u;
     }
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
   tc_fence_before();
   __syncthreads();
@@ -330,7 +352,7 @@ int conv0_fwd_tc(const float* wave, long long wave_bs, const float* w, const flo
                  const float* beta, const float* mean, const float* rstd, const float* mask, bf16* y, int B, int C, int k,
                  int stride, int T1, int norm, int act, cudaStream_t s) {
   using namespace c0tc;
-  if (C % 64 != 0 || C > MAXC || k > MAXK || stride > MAXS || (reinterpret_cast<uintptr_t>(y) & 31) != 0)
+  if (C % 64 != 0 || C > MAXC || k > MAXK || (reinterpret_cast<uintptr_t>(y) & 31) != 0)
     return DPH_ERR_UNSUPPORTED;
   static bool attr = false;
   if (!attr) {
@@ -352,9 +374,17 @@ int conv0_fwd_tc(const float* wave, long long wave_bs, const float* w, const flo
   int dev = 0, sms = kNumSMsDefault;
   if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int grid = (int)(total < sms ? total : sms);
+  CUtensorMap tm;
+  {
+    const uint64_t dims[3] = {(uint64_t)C, (uint64_t)T1, (uint64_t)B};
+    const uint64_t strides[2] = {(uint64_t)C * 2, (uint64_t)T1 * C * 2};
+    const uint32_t box[3] = {64, 32, 1};
+    const int rc = make_tmap_nd_bf16(&tm, y, 3, dims, strides, box, 3);
+    if (rc) return rc;
+  }
   cudaError_t e;
-  if (act) e = launch_pdl(conv0_fwd_tc_kernel<true>, dim3(grid), dim3(THREADS), SMEM, s, p);
-  else e = launch_pdl(conv0_fwd_tc_kernel<false>, dim3(grid), dim3(THREADS), SMEM, s, p);
+  if (act) e = launch_pdl(conv0_fwd_tc_kernel<true>, dim3(grid), dim3(THREADS), SMEM, s, p, tm);
+  else e = launch_pdl(conv0_fwd_tc_kernel<false>, dim3(grid), dim3(THREADS), SMEM, s, p, tm);
   if (e != cudaSuccess) {
     set_error("conv0_fwd_tc launch: %s", cudaGetErrorString(e));
     return DPH_ERR_CUDA;

@@ -98,6 +98,35 @@ int make_tmap_2d(CUtensorMap* out, const void* ptr, uint64_t cols, uint64_t rows
   return DPH_OK;
 }
 
+// General bf16 tensor map (rank <= 5; strides in bytes for dims 1..rank-1; swizzle: 0 none, 1 32B, 2 64B, 3 128B).
+int make_tmap_nd_bf16(CUtensorMap* out, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                      const uint32_t* box, int swizzle) {
+  PFN_encodeTiled enc = get_encode_fn();
+  if (!enc) {
+    set_error("cuTensorMapEncodeTiled unavailable");
+    return DPH_ERR_CUDA;
+  }
+  cuuint64_t d[5], st[4];
+  cuuint32_t bx[5], es[5];
+  for (int i = 0; i < rank; ++i) {
+    d[i] = dims[i];
+    bx[i] = box[i];
+    es[i] = 1;
+    if (i > 0) st[i - 1] = strides_bytes[i - 1];
+  }
+  const CUtensorMapSwizzle sw = swizzle == 3 ? CU_TENSOR_MAP_SWIZZLE_128B
+                                : swizzle == 2 ? CU_TENSOR_MAP_SWIZZLE_64B
+                                : swizzle == 1 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_NONE;
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(ptr), d, st, bx, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled(rank %d) failed: %d", rank, (int)r);
+    return DPH_ERR_CUDA;
+  }
+  return DPH_OK;
+}
+
 static int num_sms() {
   static int n = 0;
   if (n == 0) {
