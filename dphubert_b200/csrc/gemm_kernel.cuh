@@ -375,7 +375,9 @@ __global__ void __launch_bounds__(gemm_threads(BN), 1)
 
   if (warp == 0) {
     // ======================= TMA producer (both CTAs of a pair) =======================
-    if (lane == 0) {
+    // elect.sync instead of `lane == 0`: ptxas then knows that one lane is active and keeps coordinates / descriptors
+    // in uniform registers without per-operand waterfall loops
+    if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       for (int t = unit; t < total_tiles; t += nunits) {
@@ -445,7 +447,7 @@ __global__ void __launch_bounds__(gemm_threads(BN), 1)
           tc_fence_after();
           if (lane == 0 && kb == kb_begin) stamp(tl, 8 + 2 * ti);
           if (lane == 0 && kb == kb_end - 1) stamp(tl, 9 + 2 * ti);
-          if (lane == 0) {
+          if (elect_one()) {
             const uint32_t sA = smem_base + stage * Cfg::STAGE_BYTES;
             const uint32_t sB = sA + Cfg::A_BYTES;
 #pragma unroll

@@ -949,10 +949,13 @@ def _posconv_fwd(plan, pc, h0, B, T, A, tag):
     zpc = A(tag + "pos_z", (B * T, D), dt)
     xpre = A(tag + "pos_out", (B * T, D), dt)
     # output frame t reads staging rows (front + b (T+pad) + t) - K/2 + tap
-    a = View(xp, T, K * Cgp, Wd, kin=Cgp, kxs=Wd, sb0=Cgp, sb1=(T + pad) * Wd, offset=(front - K // 2) * Wd)
-    bv = View(wp, Cg, K * Cgp, K * Cgp, kin=Cgp, kxs=Cgp, sb0=Cg * K * Cgp)
-    G.gemm(a, bv, xpre, T, Cg, K * Cgp, nb0=Gn, nb1=B, ldc=D, c_sb0=Cg, c_sb1=T * D, bias=plan.view(pc.conv.bias),
-           vec_sb0=Cg, act=1, residual=h0, ldr=D, r_sb0=Cg, r_sb1=T * D, c2=zpc)
+    if ops.posconv_tc_ok(dt, Cg, Cgp, K):
+        ops.posconv_tc(xp, wp, plan.view(pc.conv.bias), h0, xpre, zpc, B, T, D, Gn, Cg, Cgp, K, T + pad, front - K // 2, 1)
+    else:
+        a = View(xp, T, K * Cgp, Wd, kin=Cgp, kxs=Wd, sb0=Cgp, sb1=(T + pad) * Wd, offset=(front - K // 2) * Wd)
+        bv = View(wp, Cg, K * Cgp, K * Cgp, kin=Cgp, kxs=Cgp, sb0=Cg * K * Cgp)
+        G.gemm(a, bv, xpre, T, Cg, K * Cgp, nb0=Gn, nb1=B, ldc=D, c_sb0=Cg, c_sb1=T * D, bias=plan.view(pc.conv.bias),
+               vec_sb0=Cg, act=1, residual=h0, ldr=D, r_sb0=Cg, r_sb1=T * D, c2=zpc)
     return xpre, {"pc": pc, "xp": xp, "zpc": zpc, "front": front, "pad": pad, "rows": rows}
 
 
@@ -1317,10 +1320,13 @@ def encoder_bwd(plan: Plan, st, dh, dmasks, A):
         norm, _, wdp, _ = plan.pos_w
         dh0 = A("dh0", (M, D), dt)
         off = front - (K - 1 - K // 2)
-        a = View(dzp, T, K * Cgp, Wd, kin=Cgp, kxs=Wd, sb0=Cgp, sb1=(T + pad) * Wd, offset=off * Wd)
-        bv = View(wdp, Cg, K * Cgp, K * Cgp, kin=Cgp, kxs=Cgp, sb0=Cg * K * Cgp)
-        G.gemm(a, bv, dh0, T, Cg, K * Cgp, nb0=Gn, nb1=B, ldc=D, c_sb0=Cg, c_sb1=T * D, residual=dxpre, ldr=D, r_sb0=Cg,
-               r_sb1=T * D)
+        if ops.posconv_tc_ok(dt, Cg, Cgp, K):
+            ops.posconv_tc(dzp, wdp, None, dxpre, dh0, None, B, T, pc.embed_dim, Gn, Cg, Cgp, K, T + pad, off, 0)
+        else:
+            a = View(dzp, T, K * Cgp, Wd, kin=Cgp, kxs=Wd, sb0=Cgp, sb1=(T + pad) * Wd, offset=off * Wd)
+            bv = View(wdp, Cg, K * Cgp, K * Cgp, kin=Cgp, kxs=Cgp, sb0=Cg * K * Cgp)
+            G.gemm(a, bv, dh0, T, Cg, K * Cgp, nb0=Gn, nb1=B, ldc=D, c_sb0=Cg, c_sb1=T * D, residual=dxpre, ldr=D,
+                   r_sb0=Cg, r_sb1=T * D)
         if pc.conv.weight_v.requires_grad:
             Kext = B * (T + pad)
             dwp = A("pos_dwp", (Gn, Cgp, K, Cgp), torch.float32)

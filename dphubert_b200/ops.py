@@ -101,6 +101,16 @@ def posconv_pad(x, xp, B, T, G, Cg, Cgp, front, pad):
 # ----------------------------------------------------------------------------------------------------------------
 # conv0
 # ----------------------------------------------------------------------------------------------------------------
+def posconv_tc(xp, wp, bias, residual, out, c2, B, T, D, G, Cg, Cgp, K, rows_b, row0, act):
+    """Tap-stationary tensor-core positional conv (bf16): out = [residual +] act(conv(xp, wp) + bias)."""
+    check(_L().dph_posconv_tc(ptr(xp), xp.shape[0], ptr(wp), ptr(bias), ptr(residual), ptr(out), ptr(c2), B, T, D, G, Cg,
+                              Cgp, K, rows_b, row0, act, stream_ptr()), "dph_posconv_tc")
+
+
+def posconv_tc_ok(dt, Cg, Cgp, K):
+    return dt == torch.bfloat16 and Cgp == 64 and Cg % 16 == 0 and 16 <= Cg <= 64 and K % 8 == 0 and 64 <= K <= 128
+
+
 def conv0_stats(wave, w, bias, moments, mean, rstd, B, C, k, stride, T1, eps):
     check(_L().dph_conv0_stats(ptr(wave), wave.stride(0), ptr(w), ptr(bias), ptr(moments), ptr(mean), ptr(rstd), B, C, k,
                                stride, T1, eps, stream_ptr()), "dph_conv0_stats")

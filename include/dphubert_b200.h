@@ -186,6 +186,14 @@ int dph_posconv_pad(const void* x, void* xp, int B, int T, int G, int Cg, int Cg
                     void* stream);
 int dph_posconv_unpad(const void* xp, void* x, int B, int T, int G, int Cg, int Cgp, int front, int pad, int accumulate,
                       int dtype, void* stream);
+/* Grouped positional convolution as a tap-stationary tensor-core implicit GEMM (bf16; components.py:319-333 +
+ * :885-892): out = [residual +] act(conv(xp, wp) + bias), optional pre-activation copy c2.  xp = the staging copy of
+ * dph_posconv_pad (rows_total x G*64), wp = (G*Cg, K*64) tap-major weights of dph_posconv_weight_prep (forward) or
+ * its tap-flipped transposed copy (input gradient).  rows_b = staging rows per utterance, row0 = staging row that
+ * (b = 0, t = 0, tap = 0) reads.  Cgp must be 64, Cg a multiple of 16 (<= 64), K a multiple of 8 in [64, 128]. */
+int dph_posconv_tc(const void* xp, long long rows_total, const void* wp, const float* bias, const void* residual,
+                   void* out, void* c2, int B, int T, int D, int G, int Cg, int Cgp, int K, int rows_b, int row0,
+                   int act, void* stream);
 int dph_axpy(void* dst, const void* src, int64_t n, int dtype, void* stream);
 int dph_cast(const void* in, int in_dtype, void* out, int out_dtype, int64_t n, void* stream);
 int dph_vec_mul(const float* a, const float* b, float* out, float alpha, float beta, int n, void* stream);

@@ -273,6 +273,23 @@ def posconv_pad(x, xp, B, T, G_, Cg, Cgp, front, pad):
         blk[:, :, :Cg] = xv[b]
 
 
+def posconv_tc(xp, wp, bias, residual, out, c2, B, T, D, G_, Cg, Cgp, K, rows_b, row0, act):
+    xf = _flat(xp).view(-1, G_, Cgp).float()
+    w = wp.reshape(G_, Cg, K, Cgp).float()
+    ov = out.view(B, T, D)
+    for b in range(B):
+        idx = torch.arange(T)[:, None] + torch.arange(K)[None, :] + (row0 + b * rows_b)
+        z = torch.einsum("tkgc,gnkc->tgn", xf[idx], w).reshape(T, D)
+        if bias is not None:
+            z = z + bias.float()
+        if c2 is not None:
+            c2.view(B, T, D)[b] = z.to(c2.dtype)
+        y = torch.nn.functional.gelu(z) if act == 1 else z
+        if residual is not None:
+            y = y + residual.view(B, T, D)[b].float()
+        ov[b] = y.to(out.dtype)
+
+
 # ------------------------------------------------------------------------------------------------ conv layer 0
 def _conv0_z(wave, w, bias, B, C, k, stride, T1):
     z = torch.nn.functional.conv1d(wave[:, None, :].float(), w.view(C, 1, k), bias, stride=stride)  # (B, C, T)
@@ -696,7 +713,7 @@ def rng_advance():
 
 
 _NAMES = ["memset", "memset2d", "zeros", "cast", "vec_mul", "transpose", "axpy", "group_mask_bwd", "wave_norm",
-          "layernorm_fwd", "layernorm_bwd", "epilogue_bwd", "pad_rows_zero", "posconv_pad", "conv0_stats", "conv0_fwd",
+          "layernorm_fwd", "layernorm_bwd", "epilogue_bwd", "pad_rows_zero", "posconv_pad", "posconv_tc", "conv0_stats", "conv0_fwd",
           "conv0_bwd", "softmax_fwd", "softmax_bwd", "attn_fwd", "attn_bwd", "wavlm_gate_fwd", "wavlm_gate_bwd", "distill_loss_fwd",
           "distill_loss_bwd", "conv_weight_prep", "conv_wgrad_unpermute", "posconv_weight_prep", "posconv_weight_bwd",
           "sumsq", "counter_inc", "adamw", "scale_", "hardconcrete_fwd", "hardconcrete_bwd", "l0_norms", "num_params",

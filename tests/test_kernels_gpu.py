@@ -355,3 +355,25 @@ def test_fused_attention_dropout_matches_unfused_mask():
     ref = (Pd[..., :T] @ v).permute(0, 2, 1, 3).reshape(Bn * T, inner)
     err = (ctx.float() - ref).abs().max().item() / ref.abs().max().item()
     assert err < 2e-2, err
+
+
+@pytest.mark.parametrize("Bn,T,Gn,Cg,K,mode", [(2, 499, 16, 48, 128, "fwd"), (2, 499, 16, 48, 128, "dgrad"),
+                                                (1, 130, 4, 64, 128, "fwd"), (3, 257, 2, 16, 64, "dgrad")])
+def test_posconv_tc(Bn, T, Gn, Cg, K, mode):
+    """tap-stationary tensor-core positional conv against the gather + einsum restatement (engine geometry: rows
+    front + b (T + pad) + t, pad = K, front = K / 2)"""
+    Cgp, D = 64, Gn * Cg
+    pad, front = K, K // 2
+    rows = front + Bn * (T + pad) + K
+    x = rnd(Bn * T, D, dtype=BF16)
+    xp = zer(rows, Gn * Cgp, dtype=BF16)
+    ops.posconv_pad(x, xp, Bn, T, Gn, Cg, Cgp, front, pad)
+    wp = zer(Gn, Cg, K, Cgp, dtype=BF16)
+    wp[..., :Cg] = rnd(Gn, Cg, K, Cg, dtype=BF16, scale=0.05)
+    res = rnd(Bn * T, D, dtype=BF16)
+    out = zer(Bn * T, D, dtype=BF16)
+    if mode == "fwd":
+        both("posconv_tc", (xp, wp, rnd(D), res, out, zer(Bn * T, D, dtype=BF16), Bn, T, D, Gn, Cg, Cgp, K, T + pad,
+                            front - K // 2, 1))
+    else:
+        both("posconv_tc", (xp, wp, None, res, out, None, Bn, T, D, Gn, Cg, Cgp, K, T + pad, front - (K - 1 - K // 2), 0))
