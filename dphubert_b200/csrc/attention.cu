@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(128, 2)
   const uint32_t tS = tmem_base, tO = tmem_base + 128;
   const uint32_t lane_off = ((uint32_t)(warp * 32)) << 16;
 
-  if (tid == 0) {
+  if (warp == 0 && elect_one()) {
     mbar_expect_tx(bar_q, ATT_BQ * ATT_D * 2);
     tma_load_2d(sQ, &tmQKV, bar_q, 2 * p.inner + h * ATT_D, row_q);
     mbar_expect_tx(bar_k, ATT_BK * ATT_D * 2);
@@ -140,7 +140,7 @@ __global__ void __launch_bounds__(128, 2)
 
   for (int t = 0; t < ntiles; ++t) {
     const int k0 = t * ATT_BK;
-    if (tid == 0) {
+    if (warp == 0 && elect_one()) {
       if (t == 0) mbar_wait(bar_q, 0);
       mbar_wait(bar_k, (uint32_t)(t & 1));
       tc_fence_after();
@@ -154,7 +154,7 @@ __global__ void __launch_bounds__(128, 2)
     mbar_wait(bar_mma, mma_phase);
     mma_phase ^= 1u;
     tc_fence_after();
-    if (tid == 0 && t + 1 < ntiles) {  // K tile is free again: fetch the next one while the softmax runs
+    if (warp == 0 && elect_one() && t + 1 < ntiles) {  // K tile is free again: fetch the next one while the softmax runs
       mbar_expect_tx(bar_k, ATT_BK * ATT_D * 2);
       tma_load_2d(sK, &tmQKV, bar_k, h * ATT_D, b * T + k0 + ATT_BK);
     }
@@ -250,7 +250,7 @@ __global__ void __launch_bounds__(128, 2)
     tc_fence_before();
     __syncthreads();
     // ---- O_tile = P V
-    if (tid == 0) {
+    if (warp == 0 && elect_one()) {
       mbar_wait(bar_v, (uint32_t)(t & 1));
       tc_fence_after();
       const uint32_t vb = sV;
@@ -263,7 +263,7 @@ __global__ void __launch_bounds__(128, 2)
     mbar_wait(bar_mma, mma_phase);
     mma_phase ^= 1u;
     tc_fence_after();
-    if (tid == 0 && t + 1 < ntiles) {
+    if (warp == 0 && elect_one() && t + 1 < ntiles) {
       mbar_expect_tx(bar_v, ATT_BK * ATT_D * 2);
       tma_load_2d(sV, &tmQKV, bar_v, p.inner + h * ATT_D, b * T + k0 + ATT_BK);
     }
@@ -482,7 +482,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
     umma_commit(bar_s);
   };
 
-  if (tid == 0) {
+  if (warp == 0 && elect_one()) {
     mbar_expect_tx(bar_kv, 2 * ATT_BK * ATT_D * 2);
     tma_load_2d(sK, &tmQKV, bar_kv, h * ATT_D, b * T + k0);
     tma_load_2d(sV, &tmQKV, bar_kv, p.inner + h * ATT_D, b * T + k0);
@@ -597,7 +597,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
     fence_async_smem();
     tc_fence_before();
     __syncthreads();  // P / dS complete, S / dP consumed, dQ of the previous tile drained
-    if (tid == 0) {
+    if (warp == 0 && elect_one()) {
       tc_fence_after();
 #pragma unroll
       for (int k = 0; k < ATT_BQ / 16; ++k) {  // reduction over the 128 queries of this tile
@@ -618,7 +618,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
     }
     mbar_wait(bar_g, ph);
     tc_fence_after();
-    if (tid == 0 && qt + 2 < nq) load_qdo(qt + 2);  // this tile's Q / dO buffer is free again
+    if (warp == 0 && elect_one() && qt + 2 < nq) load_qdo(qt + 2);  // this tile's Q / dO buffer is free again
     {
       uint32_t r[32];
       tmem_ld_32x32(tdQ + lane_off + half * 32, r);

@@ -201,7 +201,7 @@ __global__ void __launch_bounds__(THREADS, 1)
           const int blk = (int)(u % p.nblk);
           mbar_wait(t_empty(acc), acc_ph ^ 1u);  // accumulator drained by the epilogue
           tc_fence_after();
-          if (lane == 0) {
+          if (elect_one()) {
             const int nb = min(NB, p.C - blk * NB);
             const uint32_t idesc = make_idesc_bf16(TT, nb, false, false);
             const uint32_t a_addr = sA + (uint32_t)abuf * (TT * 128), b_addr = sB + (uint32_t)blk * (NB * 128);
