@@ -106,6 +106,68 @@ DPH_DEVICE void gelu_and_grad_fast(float x, float& g, float& dg) {
 }
 DPH_DEVICE float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
 
+// ---- packed fp32x2 arithmetic (Blackwell FFMA2 / FMUL2 / FADD2: two fp32 lanes per issue slot) -----------------
+typedef unsigned long long f32x2;
+DPH_DEVICE f32x2 pk2(float a, float b) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+DPH_DEVICE f32x2 bc2(float a) { return pk2(a, a); }
+DPH_DEVICE void upk2(f32x2 r, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(r)); }
+DPH_DEVICE f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+DPH_DEVICE f32x2 mul2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+DPH_DEVICE f32x2 add2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+DPH_DEVICE float tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// GELU(u) = u Phi(u) with Phi(u) ~ 0.5 + 0.5 tanh(u (a + b u^2 + c u^4)), u^2 clamped at 64 (|Phi error| < 2e-5 before
+// MUFU.TANH's own 2^-11: below bf16 resolution).  Used on the bf16 activation path only; fp32 keeps the erf forms.
+constexpr float kGeluTA = 0.7977176713187712f, kGeluTB = 0.03679851046109153f, kGeluTC = -0.00031586434495541917f;
+// two lanes at once: g = GELU(u), dg = GELU'(u) = Phi + u Phi',  Phi' = 0.5 (1 - tanh^2)(a + 3 b u^2 + 5 c u^4)
+DPH_DEVICE void gelu_and_grad_tanh2(f32x2 u, f32x2& g, f32x2& dg) {
+  float s0, s1;
+  upk2(mul2(u, u), s0, s1);
+  const f32x2 s = pk2(fminf(s0, 64.f), fminf(s1, 64.f));
+  f32x2 q = fma2(s, bc2(kGeluTC), bc2(kGeluTB));
+  q = fma2(q, s, bc2(kGeluTA));
+  float a0, a1;
+  upk2(mul2(q, u), a0, a1);
+  const f32x2 th = pk2(tanh_approx(a0), tanh_approx(a1));
+  const f32x2 h = fma2(th, bc2(0.5f), bc2(0.5f));
+  g = mul2(u, h);
+  f32x2 qp = fma2(s, bc2(5.f * kGeluTC), bc2(3.f * kGeluTB));
+  qp = fma2(qp, s, bc2(kGeluTA));
+  const f32x2 t2 = fma2(mul2(th, th), bc2(-1.f), bc2(1.f));  // 1 - tanh^2
+  const f32x2 w = mul2(mul2(t2, qp), u);
+  dg = fma2(w, bc2(0.5f), h);
+}
+DPH_DEVICE f32x2 gelu_tanh2(f32x2 u) {
+  float s0, s1;
+  upk2(mul2(u, u), s0, s1);
+  const f32x2 s = pk2(fminf(s0, 64.f), fminf(s1, 64.f));
+  f32x2 q = fma2(s, bc2(kGeluTC), bc2(kGeluTB));
+  q = fma2(q, s, bc2(kGeluTA));
+  float a0, a1;
+  upk2(mul2(q, u), a0, a1);
+  const f32x2 th = pk2(tanh_approx(a0), tanh_approx(a1));
+  return mul2(u, fma2(th, bc2(0.5f), bc2(0.5f)));
+}
+
 DPH_DEVICE float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

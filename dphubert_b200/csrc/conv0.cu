@@ -173,7 +173,7 @@ __global__ void __launch_bounds__(C0_THREADS, 3)
 constexpr int C0F_TT = 256;  // frames per CTA
 
 template <typename T>
-__global__ void __launch_bounds__(C0_THREADS, 3)
+__global__ void __launch_bounds__(C0_THREADS, 2)
     conv0_bwd_fused_kernel(const float* __restrict__ wave, long long wave_bs, const float* __restrict__ w,
                            const float* __restrict__ bias, const float* __restrict__ gamma,
                            const float* __restrict__ beta, const float* __restrict__ mean,
@@ -216,8 +216,51 @@ __global__ void __launch_bounds__(C0_THREADS, 3)
     }
     const bool two = c0 + 1 < C;
     const T* src = dy + ((long long)b * T1 + t0) * C + c0;
+    bool done = false;
+    if constexpr (sizeof(T) == 2) {
+      if (pair_vec && two) {
+        // bf16 path: the channel pair of this thread runs on packed fp32x2 arithmetic (FFMA2: half the issue slots
+        // for the taps and the weight-gradient sums) with the tanh-form GELU / GELU' of the tensor-core forward
+        f32x2 wr2[C0_MAXK], s12[C0_MAXK];
+#pragma unroll
+        for (int q = 0; q < C0_MAXK; ++q) {
+          wr2[q] = pk2(wr[0][q], wr[1][q]);
+          s12[q] = pk2(0.f, 0.f);
+        }
+        const f32x2 nsc2 = pk2(nsc[0], nsc[1]), nsh2 = pk2(nsh[0], nsh[1]), gm2 = pk2(gm[0], gm[1]),
+                    bt2 = pk2(bt[0], bt[1]), mk2 = pk2(mk[0], mk[1]);
+        f32x2 aA2 = pk2(0.f, 0.f), aB2 = aA2, aM2 = aA2;
 #pragma unroll 2
-    for (int tt = 0; tt < nt; ++tt, src += C) {
+        for (int tt = 0; tt < nt; ++tt, src += C) {
+          float xs[C0_MAXK];
+#pragma unroll
+          for (int q = 0; q < C0_MAXK; ++q) xs[q] = (q < k) ? sx[tt * stride + q] : 0.f;
+          const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(src));
+          const f32x2 d2 = pk2(f.x, f.y);
+          f32x2 z2 = pk2(0.f, 0.f);
+#pragma unroll
+          for (int q = 0; q < C0_MAXK; ++q) z2 = fma2(wr2[q], bc2(xs[q]), z2);
+          const f32x2 yn2 = fma2(z2, nsc2, nsh2);
+          const f32x2 u2 = fma2(yn2, gm2, bt2);
+          f32x2 au2 = u2, gu2 = pk2(1.f, 1.f);
+          if (act) gelu_and_grad_tanh2(u2, au2, gu2);
+          aM2 = fma2(d2, au2, aM2);
+          const f32x2 du2 = mul2(mul2(d2, mk2), gu2);
+          aA2 = add2(aA2, du2);
+          aB2 = fma2(du2, yn2, aB2);
+#pragma unroll
+          for (int q = 0; q < C0_MAXK; ++q) s12[q] = fma2(du2, bc2(xs[q]), s12[q]);
+        }
+        upk2(aA2, aA[0], aA[1]);
+        upk2(aB2, aB[0], aB[1]);
+        upk2(aM2, aM[0], aM[1]);
+#pragma unroll
+        for (int q = 0; q < C0_MAXK; ++q) upk2(s12[q], s1[0][q], s1[1][q]);
+        done = true;
+      }
+    }
+#pragma unroll 2
+    for (int tt = 0; tt < (done ? 0 : nt); ++tt, src += C) {
       float xs[C0_MAXK];
 #pragma unroll
       for (int q = 0; q < C0_MAXK; ++q) xs[q] = (q < k) ? sx[tt * stride + q] : 0.f;

@@ -42,27 +42,6 @@ constexpr int SMEM = S_BAR + 128 + 1024;
 
 DPH_DEVICE uint32_t sw128(int r, int c) { return (uint32_t)(r * 128 + ((c ^ (r & 7)) << 4)); }
 
-DPH_DEVICE unsigned long long pk2(float a, float b) {
-  unsigned long long r;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
-  return r;
-}
-DPH_DEVICE void upk2(unsigned long long r, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(r)); }
-DPH_DEVICE unsigned long long fma2(unsigned long long a, unsigned long long b, unsigned long long c) {
-  unsigned long long r;
-  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
-  return r;
-}
-DPH_DEVICE unsigned long long mul2(unsigned long long a, unsigned long long b) {
-  unsigned long long r;
-  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-  return r;
-}
-DPH_DEVICE float tanh_approx(float x) {
-  float y;
-  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
 // hi / lo bf16 split of a float
 DPH_DEVICE void split_bf16(float v, unsigned short& hi, unsigned short& lo) {
   const bf16 h = __float2bfloat16_rn(v);
