@@ -220,8 +220,15 @@ DPH_DEVICE void epilogue_chunk(const GemmParams& p, const TileCoord& tc, int row
   }
   if constexpr ((F & F_GELU) != 0) {
     if (p.act == 1) {
+      if (p.c_dtype == 0) {
+        // bf16 output: tanh-form GELU on packed fp32x2 lanes (one MUFU and ~4.5 issue slots per element, error below
+        // bf16 resolution); an fp32 output keeps the erf form
 #pragma unroll
-      for (int j = 0; j < 32; ++j) v[j] = gelu_erf_fast(v[j]);
+        for (int j = 0; j < 32; j += 2) upk2(gelu_tanh2(pk2(v[j], v[j + 1])), v[j], v[j + 1]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = gelu_erf_fast(v[j]);
+      }
     }
   }
   if constexpr ((F & F_COLMASK) != 0) {
