@@ -23,41 +23,48 @@ constexpr int C0_NR = C0_MAXK + C0_MAXK * (C0_MAXK + 1) / 2;  // 65 moments
 // ------------------------------------------------------------------------------------------------------------
 // waveform moments  (B, 65) fp64
 // ------------------------------------------------------------------------------------------------------------
+// One thread per moment: the block stages MOM_TT frames of the waveform in shared memory, thread (m, grp) walks the
+// frames grp, grp + 3, ... for its moment m (the first k: sums, the rest: products x_j x_l, j <= l) in fp64, the three
+// frame groups are folded in shared memory and the block issues one fp64 atomic per moment.
+constexpr int MOM_TT = 1024;
 __global__ void __launch_bounds__(256)
     conv0_moments_kernel(const float* __restrict__ wave, long long wave_bs, int T1, int k, int stride,
                          double* __restrict__ R) {
+  extern __shared__ float mx[];  // (MOM_TT - 1) * stride + k samples
+  __shared__ double part[3][C0_NR];
   const int b = blockIdx.y;
-  const float* x = wave + (long long)b * wave_bs;
-  double acc[C0_NR];
-#pragma unroll
-  for (int i = 0; i < C0_NR; ++i) acc[i] = 0.0;
-  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < T1; t += gridDim.x * blockDim.x) {
-    float xs[C0_MAXK];
-#pragma unroll
-    for (int j = 0; j < C0_MAXK; ++j) xs[j] = (j < k) ? x[(long long)t * stride + j] : 0.f;
-    int idx = C0_MAXK;
-#pragma unroll
-    for (int j = 0; j < C0_MAXK; ++j) {
-      acc[j] += (double)xs[j];
-#pragma unroll
-      for (int l = j; l < C0_MAXK; ++l) acc[idx++] += (double)xs[j] * (double)xs[l];
+  const int t0 = blockIdx.x * MOM_TT;
+  const int nt = min(MOM_TT, T1 - t0);
+  const float* x = wave + (long long)b * wave_bs + (long long)t0 * stride;
+  const int nsamp = (nt - 1) * stride + k;
+  for (int i = threadIdx.x; i < nsamp; i += blockDim.x) mx[i] = x[i];
+  __syncthreads();
+  const int m = threadIdx.x % C0_NR, grp = threadIdx.x / C0_NR;
+  if (grp < 3) {
+    // moment index -> (j, l): m < MAXK is the plain sum of tap j = m; the products follow row by row (j <= l)
+    int j = m, l = -1;
+    if (m >= C0_MAXK) {
+      int r = m - C0_MAXK;
+      j = 0;
+      while (r >= C0_MAXK - j) {
+        r -= C0_MAXK - j;
+        ++j;
+      }
+      l = j + r;
     }
-  }
-  __shared__ double sh[8];
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  for (int i = 0; i < C0_NR; ++i) {
-    double v = acc[i];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (lane == 0) sh[w] = v;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      double tot = 0.0;
-      for (int q = 0; q < (int)(blockDim.x >> 5); ++q) tot += sh[q];
-      atomicAdd(R + (long long)b * C0_NR + i, tot);
+    double acc = 0.0;
+    if (j < k && l < k) {
+      if (l < 0) {
+        for (int t = grp; t < nt; t += 3) acc += (double)mx[t * stride + j];
+      } else {
+        for (int t = grp; t < nt; t += 3) acc += (double)mx[t * stride + j] * (double)mx[t * stride + l];
+      }
     }
-    __syncthreads();
+    part[grp][m] = acc;
   }
+  __syncthreads();
+  if (threadIdx.x < C0_NR)
+    atomicAdd(R + (long long)b * C0_NR + threadIdx.x, part[0][threadIdx.x] + part[1][threadIdx.x] + part[2][threadIdx.x]);
 }
 
 // mean / rstd per (b, c) from the moments
@@ -309,21 +316,23 @@ __global__ void __launch_bounds__(C0_THREADS, 2)
   }
 }
 
-// One thread per channel: fold the per-utterance sums into dW, dbias, dgamma, dbeta (fp64 arithmetic: the three terms
-// of dW cancel to leading order).
+// One thread per (utterance, channel): fold the per-utterance sums into dW, dbias, dgamma, dbeta (fp64 arithmetic: the
+// three terms of dW cancel to leading order).
 __global__ void conv0_bwd_finalize_kernel(const float* __restrict__ scratch, const double* __restrict__ R,
                                           const float* __restrict__ w, const float* __restrict__ bias,
                                           const float* __restrict__ gamma, const float* __restrict__ mean,
                                           const float* __restrict__ rstd, float* __restrict__ dW,
                                           float* __restrict__ dbias, float* __restrict__ dgamma,
                                           float* __restrict__ dbeta, int B, int C, int k, int T1, int norm) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
+  // one thread per (utterance, channel): the per-utterance terms are independent and meet in the final atomics
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * C) return;
+  const int c = i % C, b0 = i / C;
   double dw[C0_MAXK];
   for (int q = 0; q < C0_MAXK; ++q) dw[q] = 0.0;
   double db = 0.0, dg = 0.0, dbt = 0.0;
   const double invT = 1.0 / (double)T1;
-  for (int b = 0; b < B; ++b) {
+  for (int b = b0; b < b0 + 1; ++b) {
     const float* s = scratch + ((long long)b * C + c) * 16;
     const double A = s[0], Bq = s[1];
     if (!norm) {
@@ -428,9 +437,13 @@ extern "C" int dph_conv0_stats(const float* wave, int64_t wave_bs, const float* 
   if (rc) return rc;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   cudaMemsetAsync(moments, 0, sizeof(double) * B * C0_NR, s);
-  int gx = (T1 + 256 * 4 - 1) / (256 * 4);
-  if (gx > 64) gx = 64;
-  conv0_moments_kernel<<<dim3(gx, B), 256, 0, s>>>(wave, wave_bs, T1, k, stride, moments);
+  const int gx = (T1 + MOM_TT - 1) / MOM_TT;
+  const size_t mom_smem = sizeof(float) * ((size_t)(MOM_TT - 1) * stride + k);
+  if (mom_smem > 48 * 1024) {
+    set_error("conv0_stats: stride %d too large for the moment kernel's staging buffer", stride);
+    return DPH_ERR_UNSUPPORTED;
+  }
+  conv0_moments_kernel<<<dim3(gx, B), 256, mom_smem, s>>>(wave, wave_bs, T1, k, stride, moments);
   conv0_stats_kernel<<<(B * C + 127) / 128, 128, 0, s>>>(moments, w, bias, mean, rstd, B, C, k, T1, eps);
   dph_count_launch(2);
   return dph_check_last("conv0_stats");
@@ -487,7 +500,7 @@ extern "C" int dph_conv0_bwd(const float* wave, int64_t wave_bs, const float* w,
     conv0_bwd_fused_kernel<float><<<grid, C0_THREADS, 0, s>>>(wave, wave_bs, w, bias, gamma, beta, mean, rstd, mask,
                                                               (const float*)dy, scratch, dmask, C, k, stride, T1, norm,
                                                               act, pair_vec);
-  conv0_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, s>>>(scratch, moments, w, bias, gamma, mean, rstd, dW, dbias,
+  conv0_bwd_finalize_kernel<<<(B * C + 127) / 128, 128, 0, s>>>(scratch, moments, w, bias, gamma, mean, rstd, dW, dbias,
                                                             dgamma, dbeta, B, C, k, T1, norm);
   dph_count_launch(2);
   return dph_check_last("conv0_bwd");
