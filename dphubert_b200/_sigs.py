@@ -27,6 +27,7 @@ SIGS = {
     "dph_posconv_pad": [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp],
     "dph_posconv_unpad": [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp],
     "dph_posconv_tc": [vp, i64, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp],
+    "dph_conv_out_lengths": [vp, vp, i32, i32, vp, vp, vp],
     "dph_cast": [vp, i32, vp, i32, i64, vp],
     "dph_vec_mul": [vp, vp, vp, f32, f32, i32, vp],
     "dph_transpose": [vp, i32, vp, i32, i32, i32, i32, vp],

@@ -469,3 +469,50 @@ extern "C" int dph_group_mask_bwd(const void* dy, const void* z, const float* ma
   dph_count_launch();
   return dph_check_last("group_mask_bwd");
 }
+
+
+// Frame counts after the conv stack (ConvLayerBlock.forward, components.py:116-119: floor((L - k) / s) + 1, clamped
+// at 0, layer after layer) for all utterances in one launch.
+namespace dph {
+struct ConvGeom {
+  int n;
+  int k[16];
+  int s[16];
+};
+__global__ void conv_out_lengths_kernel(const long long* __restrict__ in, long long* __restrict__ out, int B,
+                                        ConvGeom g) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  long long L = in[b];
+  for (int i = 0; i < g.n; ++i) {
+    const long long num = L - g.k[i];
+    long long q = num / g.s[i];
+    if ((num % g.s[i] != 0) && ((num < 0) != (g.s[i] < 0))) --q;  // floor division
+    L = q + 1;
+    if (L < 0) L = 0;
+  }
+  out[b] = L;
+}
+}  // namespace dph
+
+extern "C" int dph_conv_out_lengths(const int64_t* lengths, int64_t* out, int B, int nlayers, const int* ksizes,
+                                    const int* strides, void* stream) {
+  if (!lengths || !out || B <= 0 || nlayers < 0 || nlayers > 16 || (nlayers > 0 && (!ksizes || !strides))) {
+    set_error("conv_out_lengths: bad arguments");
+    return DPH_ERR_ARG;
+  }
+  dph::ConvGeom g;
+  g.n = nlayers;
+  for (int i = 0; i < 16; ++i) {
+    g.k[i] = i < nlayers ? ksizes[i] : 1;
+    g.s[i] = i < nlayers ? strides[i] : 1;
+    if (g.s[i] <= 0) {
+      set_error("conv_out_lengths: stride must be positive");
+      return DPH_ERR_ARG;
+    }
+  }
+  dph::conv_out_lengths_kernel<<<(B + 127) / 128, 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const long long*>(lengths), reinterpret_cast<long long*>(out), B, g);
+  dph_count_launch();
+  return dph_check_last("conv_out_lengths");
+}

@@ -1360,10 +1360,10 @@ def _out_lengths(model, lengths):
     """Integer frame arithmetic of ConvLayerBlock.forward (components.py:116-119)."""
     if lengths is None:
         return None
-    for blk in model.feature_extractor.conv_layers:
-        lengths = torch.div(lengths - blk.kernel_size, blk.stride, rounding_mode="floor") + 1
-        lengths = torch.clamp(lengths, min=0)
-    return lengths
+    blks = list(model.feature_extractor.conv_layers)
+    lengths = lengths.contiguous()
+    return ops.conv_out_lengths(lengths, torch.empty_like(lengths), [int(b.kernel_size) for b in blks],
+                                [int(b.stride) for b in blks])
 
 
 def forward_core(plan: Plan, wave, lengths, masks, A, train, save=True, num_layers=None, final_norm=False,

@@ -93,6 +93,17 @@ def pad_rows_zero(x, lengths, B, T, D):
     check(_L().dph_pad_rows_zero(ptr(x), ptr(lengths), B, T, D, dtype_code(x), stream_ptr()), "dph_pad_rows_zero")
 
 
+def conv_out_lengths(lengths, out, ksizes, strides):
+    """Frame counts after the conv stack for all utterances in one launch (components.py:116-119)."""
+    import ctypes
+    n = len(ksizes)
+    ks = (ctypes.c_int * max(n, 1))(*ksizes)
+    ss = (ctypes.c_int * max(n, 1))(*strides)
+    check(_L().dph_conv_out_lengths(ptr(lengths), ptr(out), lengths.numel(), n, ks, ss, stream_ptr()),
+          "dph_conv_out_lengths")
+    return out
+
+
 def posconv_pad(x, xp, B, T, G, Cg, Cgp, front, pad):
     check(_L().dph_posconv_pad(ptr(x), ptr(xp), B, T, G, Cg, Cgp, front, pad, dtype_code(x), stream_ptr()),
           "dph_posconv_pad")

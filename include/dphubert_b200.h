@@ -194,6 +194,10 @@ int dph_posconv_unpad(const void* xp, void* x, int B, int T, int G, int Cg, int 
 int dph_posconv_tc(const void* xp, long long rows_total, const void* wp, const float* bias, const void* residual,
                    void* out, void* c2, int B, int T, int D, int G, int Cg, int Cgp, int K, int rows_b, int row0,
                    int act, void* stream);
+/* Frame counts after the conv stack: L <- max(floor((L - k_i) / s_i) + 1, 0) for i < nlayers (components.py:116-119);
+ * ksizes / strides are HOST arrays of nlayers (<= 16) ints. */
+int dph_conv_out_lengths(const int64_t* lengths, int64_t* out, int B, int nlayers, const int* ksizes, const int* strides,
+                         void* stream);
 int dph_axpy(void* dst, const void* src, int64_t n, int dtype, void* stream);
 int dph_cast(const void* in, int in_dtype, void* out, int out_dtype, int64_t n, void* stream);
 int dph_vec_mul(const float* a, const float* b, float* out, float alpha, float beta, int n, void* stream);

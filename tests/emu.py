@@ -262,6 +262,14 @@ def pad_rows_zero(x, lengths, B, T, D):
         xv[b, n:] = 0
 
 
+def conv_out_lengths(lengths, out, ksizes, strides):
+    L = lengths.clone()
+    for k, s in zip(ksizes, strides):
+        L = torch.clamp(torch.div(L - k, s, rounding_mode="floor") + 1, min=0)
+    out.copy_(L)
+    return out
+
+
 def posconv_pad(x, xp, B, T, G_, Cg, Cgp, front, pad):
     xv = x.reshape(B, T, G_, Cg)
     Wd = G_ * Cgp
@@ -713,7 +721,7 @@ def rng_advance():
 
 
 _NAMES = ["memset", "memset2d", "zeros", "cast", "vec_mul", "transpose", "axpy", "group_mask_bwd", "wave_norm",
-          "layernorm_fwd", "layernorm_bwd", "epilogue_bwd", "pad_rows_zero", "posconv_pad", "posconv_tc", "conv0_stats", "conv0_fwd",
+          "layernorm_fwd", "layernorm_bwd", "epilogue_bwd", "pad_rows_zero", "conv_out_lengths", "posconv_pad", "posconv_tc", "conv0_stats", "conv0_fwd",
           "conv0_bwd", "softmax_fwd", "softmax_bwd", "attn_fwd", "attn_bwd", "wavlm_gate_fwd", "wavlm_gate_bwd", "distill_loss_fwd",
           "distill_loss_bwd", "conv_weight_prep", "conv_wgrad_unpermute", "posconv_weight_prep", "posconv_weight_bwd",
           "sumsq", "counter_inc", "adamw", "scale_", "hardconcrete_fwd", "hardconcrete_bwd", "l0_norms", "num_params",
