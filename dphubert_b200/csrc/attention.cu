@@ -317,36 +317,66 @@ __global__ void __launch_bounds__(128, 2)
 // ------------------------------------------------------------------------------------------------------------
 // backward, step 1: delta'[b,h,i] = sum_e dctx[b,i,h,e] * O_un[b,i,h,e]  (and the head-mask gradient = its sum)
 // ------------------------------------------------------------------------------------------------------------
+// One warp per row, 16-byte loads: lane l of pass q holds columns (q * 32 + l) * 8 .. + 8, i.e. head (q * 32 + l) / 8;
+// the eight lanes of a head fold with three shuffles.  blockIdx.x walks rows (8 warps x ROWS_PER_WARP each).
+constexpr int PREP_RPW = 4;
 __global__ void __launch_bounds__(256)
     attn_bwd_prep_kernel(const bf16* __restrict__ dctx, const bf16* __restrict__ o_un, float* __restrict__ delta,
                          float* __restrict__ dmask_h, int B, int H, int T, int inner) {
-  __shared__ float red[8];
-  const int h = blockIdx.y;
+  __shared__ float red[8][32];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const long long M = (long long)B * T;
-  float blk = 0.f;
+  const int nchunk = inner >> 3;            // 16-byte chunks per row (8 per head)
+  const int npass = (nchunk + 31) >> 5;
   pdl_wait();
   pdl_trigger();
-  for (int rr = 0; rr < 8; ++rr) {
-    const long long row = ((long long)blockIdx.x * 8 + w) * 8 + rr;
-    if (row >= M) break;
-    const long long off = row * inner + h * ATT_D + lane * 2;
-    const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(dctx + off));
-    const float2 c = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(o_un + off));
-    float d = warp_sum(a.x * c.x + a.y * c.y);
-    if (lane == 0) {
+  for (int q0 = 0; q0 < npass; q0 += 4) {   // up to 4 passes (= 16 heads) per sweep over the rows
+    float hsum[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int rr = 0; rr < PREP_RPW; ++rr) {
+      const long long row = ((long long)blockIdx.x * 8 + w) * PREP_RPW + rr;
+      if (row >= M) break;
       const int b = (int)(row / T), i = (int)(row - (long long)b * T);
-      delta[((long long)(b * H + h)) * T + i] = d;
-      blk += d;
+#pragma unroll
+      for (int qq = 0; qq < 4; ++qq) {
+        const int chunk = (q0 + qq) * 32 + lane;
+        float d = 0.f;
+        if (chunk < nchunk) {
+          const uint4 a = *reinterpret_cast<const uint4*>(dctx + row * inner + chunk * 8);
+          const uint4 c = *reinterpret_cast<const uint4*>(o_un + row * inner + chunk * 8);
+          const uint32_t av[4] = {a.x, a.y, a.z, a.w}, cv[4] = {c.x, c.y, c.z, c.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float2 fa = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&av[e]));
+            const float2 fc = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&cv[e]));
+            d = fmaf(fa.x, fc.x, d);
+            d = fmaf(fa.y, fc.y, d);
+          }
+        }
+        d += __shfl_xor_sync(0xffffffffu, d, 1);
+        d += __shfl_xor_sync(0xffffffffu, d, 2);
+        d += __shfl_xor_sync(0xffffffffu, d, 4);
+        if ((lane & 7) == 0 && chunk < nchunk) {
+          const int h = chunk >> 3;
+          delta[((long long)(b * H + h)) * T + i] = d;
+          hsum[qq] += d;
+        }
+      }
     }
-  }
-  if (dmask_h) {
-    if (lane == 0) red[w] = blk;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      float t = 0.f;
-      for (int q = 0; q < 8; ++q) t += red[q];
-      atomicAdd(dmask_h + h, t);
+    if (dmask_h) {
+#pragma unroll
+      for (int qq = 0; qq < 4; ++qq) {
+        red[w][lane] = hsum[qq];
+        __syncthreads();
+        if (w == 0 && (lane & 7) == 0) {
+          const int chunk = (q0 + qq) * 32 + lane;
+          if (chunk < nchunk) {
+            float t = 0.f;
+            for (int k = 0; k < 8; ++k) t += red[k][lane];
+            atomicAdd(dmask_h + (chunk >> 3), t);
+          }
+        }
+        __syncthreads();
+      }
     }
   }
 }
@@ -355,12 +385,15 @@ __global__ void __launch_bounds__(256)
 // One thread per 8 consecutive columns (32-byte load, 32-byte zero store, 16-byte bf16 store); blockIdx.y walks rows.
 __global__ void __launch_bounds__(256)
     attn_dq_convert_kernel(float* __restrict__ dq32, bf16* __restrict__ dqkv, long long M, int inner) {
-  const int c8 = blockIdx.x * blockDim.x + threadIdx.x;  // group of 8 columns
   pdl_wait();
   pdl_trigger();
-  if (c8 * 8 >= inner) return;
+  const int per_row = inner >> 3;  // groups of 8 columns per row
+  const long long total = M * per_row;
   const uint32_t zero[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
-  for (long long row = blockIdx.y; row < M; row += gridDim.y) {
+  for (long long it = (long long)blockIdx.x * blockDim.x + threadIdx.x; it < total;
+       it += (long long)gridDim.x * blockDim.x) {
+    const long long row = it / per_row;
+    const int c8 = (int)(it - row * per_row);
     float* src = dq32 + row * inner + c8 * 8;
     uint32_t v[8];
     asm volatile("ld.global.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
@@ -790,8 +823,8 @@ extern "C" int dph_attn_bwd(const void* qkv, const void* dctx, const void* o_un,
     attr = true;
   }
   const long long M = (long long)B * T;
-  launch_pdl(attn_bwd_prep_kernel, dim3((unsigned)((M + 63) / 64), H), dim3(256), 0, s, (const bf16*)dctx,
-             (const bf16*)o_un, delta, dmask_h, B, H, T, inner);
+  launch_pdl(attn_bwd_prep_kernel, dim3((unsigned)((M + 8 * PREP_RPW - 1) / (8 * PREP_RPW))), dim3(256), 0, s,
+             (const bf16*)dctx, (const bf16*)o_un, delta, dmask_h, B, H, T, inner);
   AttnParams p = attn_params(B, H, T, scale, lengths, rel_table, emb, gate, head_index, Htot, drop_p, seed, head_mask);
   dim3 grid((T + ATT_BK - 1) / ATT_BK, H, B);
   const bool bias = emb != nullptr, drop = drop_p > 0.f;
@@ -805,10 +838,10 @@ extern "C" int dph_attn_bwd(const void* qkv, const void* dctx, const void* o_un,
   }
 #undef ATT_BWD
   {
-    const int gx = (inner / 8 + 255) / 256;
-    long long gy = M < 148LL * 16 ? M : 148LL * 16;
-    launch_pdl(attn_dq_convert_kernel, dim3(gx, (unsigned)gy),
-               dim3(inner / 8 < 256 ? ((inner / 8 + 31) / 32) * 32 : 256), 0, s, dq32, (bf16*)dqkv, M, inner);
+    const long long items = M * (inner / 8);
+    long long nb = (items + 255) / 256;
+    if (nb > 148LL * 16) nb = 148LL * 16;
+    launch_pdl(attn_dq_convert_kernel, dim3((unsigned)nb), dim3(256), 0, s, dq32, (bf16*)dqkv, M, inner);
   }
   dph_count_launch(3);
   return dph_check_last("attn_bwd");
