@@ -11,6 +11,7 @@
 // Layout: q/k/v are read straight out of the fused projection buffer qkv[(b T + t)][k | v | q] (row stride 3 * H * 64)
 // by TMA; the context is written as ctx[(b T + t)][h * 64 + e].
 #include "common.cuh"
+#include <stdlib.h>
 #include <type_traits>
 
 #include "../../include/dphubert_b200.h"
@@ -322,7 +323,7 @@ __global__ void __launch_bounds__(128, 2)
 constexpr int PREP_RPW = 4;
 __global__ void __launch_bounds__(256)
     attn_bwd_prep_kernel(const bf16* __restrict__ dctx, const bf16* __restrict__ o_un, float* __restrict__ delta,
-                         float* __restrict__ dmask_h, int B, int H, int T, int inner) {
+                         float* __restrict__ dmask_h, int B, int H, int T, int inner, bf16* __restrict__ dq_zero) {
   __shared__ float red[8][32];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const long long M = (long long)B * T;
@@ -341,6 +342,8 @@ __global__ void __launch_bounds__(256)
         const int chunk = (q0 + qq) * 32 + lane;
         float d = 0.f;
         if (chunk < nchunk) {
+          if (dq_zero)  // Q slot of dqkv: the backward kernel accumulates dQ into it with bf16x2 reductions
+            *reinterpret_cast<uint4*>(dq_zero + row * (3LL * inner) + 2 * inner + chunk * 8) = make_uint4(0u, 0u, 0u, 0u);
           const uint4 a = *reinterpret_cast<const uint4*>(dctx + row * inner + chunk * 8);
           const uint4 c = *reinterpret_cast<const uint4*>(o_un + row * inner + chunk * 8);
           const uint32_t av[4] = {a.x, a.y, a.z, a.w}, cv[4] = {c.x, c.y, c.z, c.w};
@@ -436,7 +439,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
     attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
                     const __grid_constant__ AttnParams p, const float* __restrict__ lse,
                     const float* __restrict__ delta, float* __restrict__ dq32, bf16* __restrict__ dqkv,
-                    float* __restrict__ dgate, float* __restrict__ demb, int num_buckets) {
+                    float* __restrict__ dgate, float* __restrict__ demb, int num_buckets, int dq_bf16) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* gbase = smem_raw + (sbase - smem_u32(smem_raw));
@@ -656,7 +659,21 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
       uint32_t r[32];
       tmem_ld_32x32(tdQ + lane_off + half * 32, r);
       tmem_ld_wait();
-      if (row_ok) {
+      if (row_ok && dq_bf16) {
+        // bf16x2 vector reductions straight into the (pre-zeroed) Q slot of dqkv: 8 values per 16-byte RED, a quarter
+        // of the L2 atomic-ALU work of the fp32 path (which bounds this kernel), and no conversion pass afterwards
+        bf16* dst = dqkv + ((long long)(b * T + i)) * (3LL * p.inner) + 2 * p.inner + h * ATT_D + half * 32;
+#pragma unroll
+        for (int jj = 0; jj < 32; jj += 8) {
+          const uint32_t u0 = pack_bf16x2(__uint_as_float(r[jj]) * p.scale, __uint_as_float(r[jj + 1]) * p.scale);
+          const uint32_t u1 = pack_bf16x2(__uint_as_float(r[jj + 2]) * p.scale, __uint_as_float(r[jj + 3]) * p.scale);
+          const uint32_t u2 = pack_bf16x2(__uint_as_float(r[jj + 4]) * p.scale, __uint_as_float(r[jj + 5]) * p.scale);
+          const uint32_t u3 = pack_bf16x2(__uint_as_float(r[jj + 6]) * p.scale, __uint_as_float(r[jj + 7]) * p.scale);
+          asm volatile("red.global.add.noftz.v4.bf16x2 [%0], {%1, %2, %3, %4};" ::"l"(dst + jj), "r"(u0), "r"(u1),
+                       "r"(u2), "r"(u3)
+                       : "memory");
+        }
+      } else if (row_ok) {
         float* dst = dq32 + ((long long)(b * T + i)) * p.inner + h * ATT_D + half * 32;
 #pragma unroll
         for (int jj = 0; jj < 32; jj += 4)
@@ -823,26 +840,31 @@ extern "C" int dph_attn_bwd(const void* qkv, const void* dctx, const void* o_un,
     attr = true;
   }
   const long long M = (long long)B * T;
+  static const int dq_bf16 = [] {
+    const char* e = getenv("DPH_DQ_BF16");
+    return (e != nullptr && e[0] == '0') ? 0 : 1;
+  }();
   launch_pdl(attn_bwd_prep_kernel, dim3((unsigned)((M + 8 * PREP_RPW - 1) / (8 * PREP_RPW))), dim3(256), 0, s,
-             (const bf16*)dctx, (const bf16*)o_un, delta, dmask_h, B, H, T, inner);
+             (const bf16*)dctx, (const bf16*)o_un, delta, dmask_h, B, H, T, inner,
+             dq_bf16 ? (bf16*)dqkv : (bf16*)nullptr);
   AttnParams p = attn_params(B, H, T, scale, lengths, rel_table, emb, gate, head_index, Htot, drop_p, seed, head_mask);
   dim3 grid((T + ATT_BK - 1) / ATT_BK, H, B);
   const bool bias = emb != nullptr, drop = drop_p > 0.f;
 #define ATT_BWD(BI, DR)                                                                                             \
   launch_pdl(attn_bwd_kernel<BI, DR>, grid, dim3(BWD_THREADS), BWD_SMEM, s, tmq, tmd, p, lse, delta, dq32,          \
-             (bf16*)dqkv, dgate, demb, num_buckets)
+             (bf16*)dqkv, dgate, demb, num_buckets, dq_bf16)
   if (bias) {
     if (drop) ATT_BWD(true, true); else ATT_BWD(true, false);
   } else {
     if (drop) ATT_BWD(false, true); else ATT_BWD(false, false);
   }
 #undef ATT_BWD
-  {
+  if (!dq_bf16) {
     const long long items = M * (inner / 8);
     long long nb = (items + 255) / 256;
     if (nb > 148LL * 16) nb = 148LL * 16;
     launch_pdl(attn_dq_convert_kernel, dim3((unsigned)nb), dim3(256), 0, s, dq32, (bf16*)dqkv, M, inner);
   }
-  dph_count_launch(3);
+  dph_count_launch(dq_bf16 ? 2 : 3);
   return dph_check_last("attn_bwd");
 }
