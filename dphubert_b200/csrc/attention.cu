@@ -126,9 +126,9 @@ __global__ void __launch_bounds__(128, 2)
   const uint32_t thresh = (uint32_t)(p.drop_p * 4294967296.0);
   const float inv_keep = p.drop_p > 0.f ? 1.f / (1.f - p.drop_p) : 1.f;
   const uint32_t dkey = DROP ? dropout_key(p.seed) : 0u;  // (after pdl_wait: the epoch is written earlier in the step)
-  // dropout element index: rows padded to an even stride so that keys (2q, 2q+1) share one hash (dropout_scale2)
-  const unsigned long long drop_row =
-      ((unsigned long long)(b * p.H + h) * T + (unsigned long long)i) * (unsigned long long)((T + 1) & ~1);
+  // dropout: the row (b, h, i) folds into the key once, a key pair (2q, 2q+1) then shares one 32-bit hash
+  const uint32_t drop_rkey =
+      dropout_row_key(dkey, (unsigned long long)(b * p.H + h) * T + (unsigned long long)i);
   const float sc2 = p.scale * kLog2e;
 
   float m2 = -INFINITY, l = 0.f;  // running max (log2 domain) and sum
@@ -214,8 +214,10 @@ __global__ void __launch_bounds__(128, 2)
         const int j = k0 + c * 32 + jj;
         float p0, p1;
         if constexpr (!EDGE) {
-          p0 = fast_exp2(fmaf(__uint_as_float(r[jj]), sc2, nm2));
-          p1 = fast_exp2(fmaf(__uint_as_float(r[jj + 1]), sc2, nm2));
+          float e0, e1;
+          upk2(fma2(pk2(__uint_as_float(r[jj]), __uint_as_float(r[jj + 1])), bc2(sc2), bc2(nm2)), e0, e1);
+          p0 = fast_exp2(e0);
+          p1 = fast_exp2(e1);
         } else {
           p0 = (j < T) ? fast_exp2(logit(r[jj], j) + nm2) : 0.f;
           p1 = (j + 1 < T) ? fast_exp2(logit(r[jj + 1], j + 1) + nm2) : 0.f;
@@ -223,7 +225,7 @@ __global__ void __launch_bounds__(128, 2)
         lsum += p0 + p1;
         if constexpr (DROP) {
           float s0, s1;
-          dropout_scale2_keyed(dkey, drop_row + (unsigned long long)j, thresh, inv_keep, s0, s1);
+          dropout_row_pair(drop_rkey, (uint32_t)j >> 1, thresh, inv_keep, s0, s1);
           p0 *= s0;
           p1 *= s1;
         }
@@ -549,8 +551,8 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
         if (p.gate) gate_i = p.gate[((long long)b * p.Htot + htot) * T + i];
       }
     }
-    const unsigned long long drop_row =
-        ((unsigned long long)(b * p.H + h) * T + (unsigned long long)i) * (unsigned long long)((T + 1) & ~1);
+    const uint32_t drop_rkey =
+        dropout_row_key(dkey, (unsigned long long)(b * p.H + h) * T + (unsigned long long)i);
     mbar_wait(bar_s, ph);
     tc_fence_after();
     float dg = 0.f;
@@ -571,10 +573,26 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
         float pv[2], dv[2];
         float dsc[2] = {1.f, 1.f};  // dropout scales of this key pair (one hash, same mask as the forward)
         if constexpr (DROP)
-          dropout_scale2_keyed(dkey, drop_row + (unsigned long long)(k0 + c * 32 + jj), thresh, inv_keep, dsc[0],
-                               dsc[1]);
+          dropout_row_pair(drop_rkey, (uint32_t)(k0 + c * 32 + jj) >> 1, thresh, inv_keep, dsc[0], dsc[1]);
+        if constexpr (!EDGE) {
+          // interior tile: the key pair on packed fp32x2 lanes (FFMA2 / FMUL2), two MUFU.EX2
+          float e0, e1;
+          upk2(fma2(pk2(__uint_as_float(rs[jj]), __uint_as_float(rs[jj + 1])), bc2(sc2), bc2(nL2)), e0, e1);
+          const f32x2 pe2 = pk2(fast_exp2(e0), fast_exp2(e1));
+          const f32x2 rp2 = pk2(__uint_as_float(rp[jj]), __uint_as_float(rp[jj + 1]));
+          f32x2 t2, pv2 = pe2;
+          if constexpr (DROP) {
+            const f32x2 d2 = pk2(dsc[0], dsc[1]);
+            t2 = fma2(rp2, mul2(d2, bc2(hm)), bc2(ndl));
+            pv2 = mul2(pe2, d2);
+          } else {
+            t2 = fma2(rp2, bc2(hm), bc2(ndl));
+          }
+          upk2(pv2, pv[0], pv[1]);
+          upk2(mul2(pe2, t2), dv[0], dv[1]);
+        }
 #pragma unroll
-        for (int u = 0; u < 2; ++u) {
+        for (int u = 0; u < (EDGE ? 2 : 0); ++u) {
           const int j = k0 + c * 32 + jj + u;
           float pe;
           [[maybe_unused]] float tbv = 0.f;

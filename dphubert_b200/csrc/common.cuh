@@ -236,6 +236,34 @@ DPH_DEVICE void dropout_scale2(uint64_t seed, uint64_t idx_even, uint32_t thresh
   dropout_scale2_keyed(dropout_key(seed), idx_even, thresh, inv_keep, s0, s1);
 }
 
+// Attention-probability dropout uses a 2-D index (row = (b H + h) T + i, key j): the row folds into the key once per
+// thread and a key PAIR (2 jp, 2 jp + 1) then costs one 32-bit multiply-add plus the finaliser (no 64-bit arithmetic
+// in the inner loop).  The fused attention kernels and the unfused softmax kernels share these two functions.
+DPH_DEVICE uint32_t dropout_row_key(uint32_t key, uint64_t row) {
+  return key ^ ((uint32_t)row * 0x165667B1u) ^ ((uint32_t)(row >> 32) * 0x27D4EB2Fu);
+}
+DPH_DEVICE uint32_t hash_row_pair(uint32_t row_key, uint32_t jp) {
+  uint32_t x = jp * 0x9E3779B1u + row_key;
+  x ^= x >> 16;
+  x *= 0x85EBCA6Bu;
+  x ^= x >> 13;
+  x *= 0xC2B2AE35u;
+  x ^= x >> 16;
+  return x;
+}
+// scales of keys 2 jp and 2 jp + 1 of a row
+DPH_DEVICE void dropout_row_pair(uint32_t row_key, uint32_t jp, uint32_t thresh, float inv_keep, float& s0, float& s1) {
+  const uint32_t h = hash_row_pair(row_key, jp);
+  const uint32_t t16 = thresh >> 16;
+  s0 = ((h & 0xFFFFu) >= t16) ? inv_keep : 0.0f;
+  s1 = ((h >> 16) >= t16) ? inv_keep : 0.0f;
+}
+DPH_DEVICE float dropout_row_elem(uint32_t row_key, uint32_t j, uint32_t thresh, float inv_keep) {
+  const uint32_t h = hash_row_pair(row_key, j >> 1);
+  const uint32_t bits = (j & 1u) ? (h >> 16) : (h & 0xFFFFu);
+  return (bits >= (thresh >> 16)) ? inv_keep : 0.0f;
+}
+
 // v[0..N) *= dropout scale of the N consecutive elements starting at idx.  Aligned pairs share one hash when idx is
 // even (the usual case: even row strides); otherwise one hash per element.  Same decisions as dropout_scale().
 template <int N>

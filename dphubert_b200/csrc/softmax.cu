@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(256)
     if (j < Tn) {
       const float p = v[k] * inv;
       P[row * ldp + j] = from_f<T>(p);
-      if (Pd) Pd[row * ldp + j] = from_f<T>(p * dropout_scale(seed, (unsigned long long)row * ((Tn + 1) & ~1) + j, thresh, inv_keep));
+      if (Pd) Pd[row * ldp + j] = from_f<T>(p * dropout_row_elem(dropout_row_key(dropout_key(seed), (unsigned long long)row), (uint32_t)j, thresh, inv_keep));
     } else if (j < ldp) {
       // keep the row padding (ldp >= Tn, multiple of 8) finite and zero: it is read as K-tail by the P*V GEMM
       P[row * ldp + j] = from_f<T>(0.f);
@@ -118,7 +118,7 @@ __global__ void __launch_bounds__(256)
       if (j < Tn) {
         p[k] = to_f(P[row * ldp + j]);
         float g = dPd[row * lds + j];
-        if (drop_p > 0.f) g *= dropout_scale(seed, (unsigned long long)row * ((Tn + 1) & ~1) + j, thresh, inv_keep);
+        if (drop_p > 0.f) g *= dropout_row_elem(dropout_row_key(dropout_key(seed), (unsigned long long)row), (uint32_t)j, thresh, inv_keep);
         d[k] = g;
         dot += g * p[k];
       }
