@@ -251,6 +251,9 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         import torch.distributed as dist
 
+        # NCCL prints its version banner to STDOUT under NCCL_DEBUG=VERSION: keep stdout to the one JSON line
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
     dtype = torch.bfloat16 if args.dtype == "bf16" else torch.float32
     secs = args.seconds or (15.0 if args.workload == "large" else 10.0)

@@ -76,7 +76,7 @@ __global__ void __launch_bounds__(128, 2)
   const uint32_t sQ = sbase + FWD_SQ, sK = sbase + FWD_SK, sV = sbase + FWD_SV, sP = sbase + FWD_SP;
   float* tb = reinterpret_cast<float*>(gbase + FWD_TB);
   const uint32_t bar_q = sbase + FWD_BAR, bar_k = bar_q + 8, bar_v = bar_q + 16, bar_mma = bar_q + 24,
-                 tmem_slot = bar_q + 32;
+                 tmem_slot = bar_q + 32, bar_o = bar_q + 40;
   const int tid = threadIdx.x, warp = tid >> 5;
   const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int T = p.T;
@@ -89,6 +89,7 @@ __global__ void __launch_bounds__(128, 2)
     mbar_init(bar_k, 1);
     mbar_init(bar_v, 1);
     mbar_init(bar_mma, 1);
+    mbar_init(bar_o, 1);
     mbar_fence_init();
     tma_prefetch_desc(&tmQKV);
   }
@@ -139,19 +140,23 @@ __global__ void __launch_bounds__(128, 2)
   constexpr uint32_t idesc_s = make_idesc_bf16(ATT_BQ, ATT_BK, false, false);
   constexpr uint32_t idesc_o = make_idesc_bf16(ATT_BQ, ATT_D, false, true);
 
+  // S = Q K^T of tile `tt` (issuing lane only): the scores of tile t + 1 are issued right behind P V of tile t, so the
+  // tensor core computes them while the warps fold O (bar_mma: scores ready, bar_o: P V done)
+  auto issue_scores = [&](int tt) {
+    if (tt == 0) mbar_wait(bar_q, 0);
+    mbar_wait(bar_k, (uint32_t)(tt & 1));
+    tc_fence_after();
+#pragma unroll
+    for (int k = 0; k < ATT_D / 16; ++k)
+      umma_f16_ss(tS, make_smem_desc(sQ + k * 32, 0, 1024, 2), make_smem_desc(sK + k * 32, 0, 1024, 2), idesc_s,
+                  k > 0 ? 1u : 0u);
+    umma_commit(bar_mma);
+  };
+  if (warp == 0 && elect_one()) issue_scores(0);
+  uint32_t o_phase = 0;
+
   for (int t = 0; t < ntiles; ++t) {
     const int k0 = t * ATT_BK;
-    if (warp == 0 && elect_one()) {
-      if (t == 0) mbar_wait(bar_q, 0);
-      mbar_wait(bar_k, (uint32_t)(t & 1));
-      tc_fence_after();
-      const uint32_t kb = sK;
-#pragma unroll
-      for (int k = 0; k < ATT_D / 16; ++k)
-        umma_f16_ss(tS, make_smem_desc(sQ + k * 32, 0, 1024, 2), make_smem_desc(kb + k * 32, 0, 1024, 2), idesc_s,
-                    k > 0 ? 1u : 0u);
-      umma_commit(bar_mma);
-    }
     mbar_wait(bar_mma, mma_phase);
     mma_phase ^= 1u;
     tc_fence_after();
@@ -261,10 +266,11 @@ __global__ void __launch_bounds__(128, 2)
       for (int k = 0; k < ATT_BK / 16; ++k)
         umma_f16_ss(tO, make_smem_desc(sP + (k >> 2) * (ATT_BQ * 128) + (k & 3) * 32, 0, 1024, 2),
                     make_smem_desc(vb + k * 2048, ATT_BK * 128, 1024, 2), idesc_o, k > 0 ? 1u : 0u);
-      umma_commit(bar_mma);
+      umma_commit(bar_o);
+      if (t + 1 < ntiles) issue_scores(t + 1);  // every thread is past its reads of S (the barrier above)
     }
-    mbar_wait(bar_mma, mma_phase);
-    mma_phase ^= 1u;
+    mbar_wait(bar_o, o_phase);
+    o_phase ^= 1u;
     tc_fence_after();
     if (warp == 0 && elect_one() && t + 1 < ntiles) {
       mbar_expect_tx(bar_v, ATT_BK * ATT_D * 2);
@@ -278,8 +284,9 @@ __global__ void __launch_bounds__(128, 2)
 #pragma unroll
       for (int jj = 0; jj < 32; ++jj) o[c * 32 + jj] = fmaf(o[c * 32 + jj], alpha, __uint_as_float(r[jj]));
     }
+    // no barrier here: P (shared memory) is free because P V has completed, and the next P V, which overwrites the O
+    // tile, is only issued behind the next tile's block barrier
     tc_fence_before();
-    __syncthreads();  // S / O_tile / P may now be overwritten
   }
 
   pdl_trigger();  // only the context store is left: the next kernel's prologue may start on this SM

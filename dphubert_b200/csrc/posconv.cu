@@ -110,6 +110,7 @@ __global__ void __launch_bounds__(THREADS, 1)
   } else if (warp == 1) {
     // ======================= MMA issuer =======================
     const uint32_t idesc = make_idesc_bf16(128, p.Cg, false, false);
+    const int kslices = (p.Cg + 15) / 16;
     int it = 0;
     for (int kk = 0; kk < ncopy; ++kk) {
       const int buf = kk & 1;
@@ -122,8 +123,10 @@ __global__ void __launch_bounds__(THREADS, 1)
           const uint32_t bb = sB + s * BSTAGE_BYTES;
           // eight independent accumulation chains (2 row halves x 4 K slices of the 64 input channels): MMAs that
           // accumulate into the same TMEM tile serialise on the MMA latency, and these MMAs are short (N = Cg)
+          // input channels Cg .. 63 of a group are zero padding in both operands: their K slices are skipped
 #pragma unroll
           for (int k16 = 0; k16 < CI / 16; ++k16) {
+            if (k16 >= kslices) break;
 #pragma unroll
             for (int half = 0; half < 2; ++half) {
               const uint32_t aa = sA + buf * SLAB_BYTES + (uint32_t)(half * 128 + 8 * j) * 128u;
@@ -170,7 +173,8 @@ __global__ void __launch_bounds__(THREADS, 1)
 #pragma unroll
       for (int j = 0; j < 16; ++j) v[j] = 0.f;
 #pragma unroll
-      for (int ks = 0; ks < 4; ++ks) {  // sum the four K-slice accumulators
+      for (int ks = 0; ks < 4; ++ks) {  // sum the K-slice accumulators that were used
+        if (ks >= (p.Cg + 15) / 16) break;
         uint32_t r[16];
         asm volatile(
             "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, "
