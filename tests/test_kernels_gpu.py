@@ -377,3 +377,32 @@ def test_posconv_tc(Bn, T, Gn, Cg, K, mode):
                             front - K // 2, 1))
     else:
         both("posconv_tc", (xp, wp, None, res, out, None, Bn, T, D, Gn, Cg, Cgp, K, T + pad, front - (K - 1 - K // 2), 0))
+
+
+def test_conv_out_lengths():
+    """frame arithmetic of the conv stack (components.py:116-119) incl. utterances shorter than a kernel"""
+    lengths = torch.tensor([160000, 64000, 400, 9, 0, 25, 399, 123457], device=DEV, dtype=torch.int64)
+    ks, ss = [10, 3, 3, 3, 3, 2, 2], [5, 2, 2, 2, 2, 2, 2]
+    out = ops.conv_out_lengths(lengths, torch.empty_like(lengths), ks, ss)
+    ref = emu.conv_out_lengths(lengths.cpu(), torch.empty(8, dtype=torch.int64), ks, ss)
+    assert torch.equal(out.cpu(), ref)
+    assert out[0].item() == 499 and out[1].item() == 199
+
+
+def test_attention_dropout_keep_rate():
+    """row-key / pair hash of the attention-probability dropout: keep rate ~ 1 - p, independent across rows and
+    between the two keys of a pair"""
+    Bn, H, T = 2, 4, 256
+    S = zer(Bn, H, T, T)
+    P, Pd = zer(Bn, H, T, T), zer(Bn, H, T, T)
+    ops.softmax_fwd(S, T, P, Pd, T, None, Bn, H, T, 0.1, 7)
+    keep = (Pd > 0).float()
+    rate = keep.mean().item()
+    assert abs(rate - 0.9) < 5e-3, rate
+    even, odd = keep[..., 0::2], keep[..., 1::2]
+    assert abs(even.mean().item() - odd.mean().item()) < 5e-3
+    corr = ((even - 0.9) * (odd - 0.9)).mean().item() / (0.9 * 0.1)
+    assert abs(corr) < 2e-2, corr
+    rows = keep.reshape(-1, T)
+    c2 = ((rows[0::2] - 0.9) * (rows[1::2] - 0.9)).mean().item() / (0.9 * 0.1)
+    assert abs(c2) < 2e-2, c2
