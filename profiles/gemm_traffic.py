@@ -1,9 +1,9 @@
-"""Per-launch DRAM traffic of the tcgen05 GEMM from an `ncu --set full` capture of one eager step.
+"""Per-launch DRAM traffic of the tcgen05 GEMM from an ncu pass over one eager step (the dram__bytes_* counters are
+the ones `--set full` reports; a full-set capture of all 239 launches is > 64 MiB and does not fit gpurun_out/).
 
-    ncu --profile-from-start off --set full --clock-control none -k regex:gemm_bf16_kernel \
-        -o gpurun_out/gemm_full python bench.py --profile-step
-    ncu -i gpurun_out/gemm_full.ncu-rep --page raw --csv > raw.csv
-    python profiles/gemm_traffic.py raw.csv profiles/r01_gemm_dram_traffic.json
+    ncu --profile-from-start off --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum \
+        --clock-control none -k regex:gemm_bf16_kernel --page raw --csv --log-file raw.csv python bench.py --profile-step
+    grep -v "^==" raw.csv > raw2.csv; python profiles/gemm_traffic.py raw2.csv profiles/r01_gemm_dram_traffic.json
 """
 import csv
 import json
@@ -30,7 +30,7 @@ def main(raw, out):
         t += val(r, "gpu__time_duration.sum")
         n += 1
     json.dump({"kernel": "gemm_bf16_kernel (tcgen05)",
-               "source": "ncu --set full --clock-control none, bench.py --profile-step, the %d GEMM launches of one eager "
+               "source": "ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum --clock-control none, bench.py --profile-step, the %d GEMM launches of one eager "
                          "step (cold caches: ncu flushes L2 between replays)" % n,
                "launches": n, "dram_read_bytes": rd, "dram_write_bytes": wr, "dram_bytes_per_launch": (rd + wr) / max(n, 1),
                "time_us_sum": t}, open(out, "w"), indent=1)
