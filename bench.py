@@ -411,7 +411,7 @@ def gemm_table(step, wave, lengths, G, path):
 
 def hbm_kernels(B, seconds, dev):
     """The memory-bound kernels of the step, each timed alone at the step's sizes (CUDA events around single launches,
-    L2 flushed by a 512 MB memset before every timed launch, median of 5): algorithmic bytes / time against the measured
+    L2 flushed by a 512 MB memset followed by a 256 MB read-only pass before every timed launch, median of 5): algorithmic bytes / time against the measured
     HBM copy bandwidth.  Algorithmic bytes per unit are SURVEY.md 8(d)'s figures (stated per entry)."""
     from dphubert_b200 import ops
 
@@ -423,6 +423,7 @@ def hbm_kernels(B, seconds, dev):
     except Exception:  # noqa: BLE001
         pass
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+    clean = torch.zeros(64 << 20, dtype=torch.int32, device=dev)  # 256 MB, only ever read
     T0 = int(seconds * SR)
     T1 = (T0 - 10) // 5 + 1
     T = T1
@@ -439,7 +440,8 @@ def hbm_kernels(B, seconds, dev):
             fn()
         ts = []
         for _ in range(5):
-            flush.zero_()
+            flush.zero_()   # evict the kernel's data from L2 ...
+            clean.sum()     # ... then push the memset's dirty lines out, so their write-back is not billed to the kernel
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
             fn()
@@ -448,13 +450,35 @@ def hbm_kernels(B, seconds, dev):
             ts.append(e0.elapsed_time(e1) * 1e3)
         return sorted(ts)[len(ts) // 2]
 
+    def timeit_sets(fn, K):
+        """Kernels whose working set fits L2 (and whose run time is a few event ticks): K launches back to back, each
+        on its own copy of the buffers (together > 2 x L2, so every launch reads cold data); time per launch."""
+        for i in range(K):
+            fn(i)
+        ts = []
+        for _ in range(3):
+            flush.zero_()
+            clean.sum()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for i in range(K):
+                fn(i)
+            e1.record()
+            torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1) * 1e3 / K)
+        return sorted(ts)[len(ts) // 2]
+
     out = []
 
-    def add(name, nbytes, fn, what):
-        us = timeit(fn)
+    def add(name, nbytes, fn, what, sets=1):
+        us = timeit(fn) if sets == 1 else timeit_sets(fn, sets)
         gbs = nbytes / us / 1e3
         out.append({"kernel": name, "us": round(us, 2), "algorithmic_bytes": int(nbytes), "achieved_gbs": round(gbs, 1),
-                    "frac": round(gbs / peak, 3), "bytes_model": what})
+                    "frac": round(gbs / peak, 3), "bytes_model": what,
+                    "timing": "single launch" if sets == 1 else "%d back-to-back launches on distinct buffers" % sets})
+
+    def nsets(nbytes):
+        return max(2, min(48, -(-320_000_000 // int(nbytes))))
 
     # conv-0 block (components.py:94-120, layer 0): conv k=10 s=5 + GroupNorm + GELU + channel mask
     wave = rn(B, T0, dtype=F32, scale=0.1)
@@ -477,32 +501,40 @@ def hbm_kernels(B, seconds, dev):
         "read 4*T0 + read 2*512*T1 per utterance")
     del y, dy
     # LayerNorm(768) over the (B*T, 768) encoder activation
-    x, yy = rn(rows, D), torch.empty(rows, D, dtype=BF, device=dev)
+    K = nsets(3 * 2 * rows * D)
+    x, yy = rn(K, rows, D), torch.empty(K, rows, D, dtype=BF, device=dev)
     lw, lb = rn(D, dtype=F32), rn(D, dtype=F32)
-    mu, rs = torch.zeros(rows, device=dev), torch.zeros(rows, device=dev)
-    add("layernorm_fwd", 2 * 2 * rows * D, lambda: ops.layernorm_fwd(x, lw, lb, yy, rows, D, 1e-5, mean=mu, rstd=rs),
-        "read + write 2*rows*768")
-    dx, dlw, dlb = torch.empty(rows, D, dtype=BF, device=dev), torch.zeros(D, device=dev), torch.zeros(D, device=dev)
-    add("layernorm_bwd", 3 * 2 * rows * D, lambda: ops.layernorm_bwd(yy, x, lw, lb, mu, rs, dx, dlw, dlb, rows, D),
-        "read dy, x + write dx, 2*rows*768 each")
+    mu, rs = torch.zeros(K, rows, device=dev), torch.zeros(K, rows, device=dev)
+    add("layernorm_fwd", 2 * 2 * rows * D,
+        lambda i: ops.layernorm_fwd(x[i], lw, lb, yy[i], rows, D, 1e-5, mean=mu[i], rstd=rs[i]),
+        "read + write 2*rows*768", sets=K)
+    dx, dlw, dlb = torch.empty(K, rows, D, dtype=BF, device=dev), torch.zeros(D, device=dev), torch.zeros(D, device=dev)
+    add("layernorm_bwd", 3 * 2 * rows * D,
+        lambda i: ops.layernorm_bwd(yy[i], x[i], lw, lb, mu[i], rs[i], dx[i], dlw, dlb, rows, D),
+        "read dy, x + write dx, 2*rows*768 each", sets=K)
+    del x, yy, dx
     # FFN hidden backward: GELU' * mask (+ bias / mask gradient column sums) over (B*T, 3072)
     F = 3072
-    dyh, z, dout = rn(rows, F), rn(rows, F), torch.empty(rows, F, dtype=BF, device=dev)
+    K = nsets(3 * 2 * rows * F)
+    dyh, z, dout = rn(K, rows, F), rn(K, rows, F), torch.empty(K, rows, F, dtype=BF, device=dev)
     cm, dm, db = torch.rand(F, device=dev, generator=g), torch.zeros(F, device=dev), torch.zeros(F, device=dev)
     add("epilogue_bwd (GELU' * mask, dbias, dmask)", 3 * 2 * rows * F,
-        lambda: ops.epilogue_bwd(dyh, rows, F, z=z, colmask=cm, dout=dout, dmask=dm, dbias=db, act=1),
-        "read dy, z + write dz, 2*rows*3072 each")
+        lambda i: ops.epilogue_bwd(dyh[i], rows, F, z=z[i], colmask=cm, dout=dout[i], dmask=dm, dbias=db, act=1),
+        "read dy, z + write dz, 2*rows*3072 each", sets=K)
+    del dyh, z, dout
     # DistillLoss over 4 layers x (B*T, 768)
     lr_rows = 4 * rows
-    a, b2 = rn(lr_rows, D), rn(lr_rows, D)
-    rowstat, acc, lo = torch.zeros(lr_rows, 4, device=dev), torch.zeros(8, device=dev), torch.zeros(4, device=dev)
+    K = nsets(3 * 2 * lr_rows * D)
+    a, b2 = rn(K, lr_rows, D), rn(K, lr_rows, D)
+    rowstat, acc, lo = torch.zeros(K, lr_rows, 4, device=dev), torch.zeros(8, device=dev), torch.zeros(4, device=dev)
     add("distill_loss_fwd (L1 + cosine)", 2 * 2 * lr_rows * D,
-        lambda: ops.distill_loss_fwd(a, b2, rowstat, acc, lo, lr_rows, D, 0.0, 1.0, 1.0, 0, True, True, lr_rows),
-        "read pred + target, 2*4*rows*768 each")
-    da, up = torch.empty(lr_rows, D, dtype=BF, device=dev), torch.ones(1, device=dev)
+        lambda i: ops.distill_loss_fwd(a[i], b2[i], rowstat[i], acc, lo, lr_rows, D, 0.0, 1.0, 1.0, 0, True, True, lr_rows),
+        "read pred + target, 2*4*rows*768 each", sets=K)
+    da, up = torch.empty(K, lr_rows, D, dtype=BF, device=dev), torch.ones(1, device=dev)
     add("distill_loss_bwd", 3 * 2 * lr_rows * D,
-        lambda: ops.distill_loss_bwd(a, b2, rowstat, up, da, lr_rows, lr_rows, D, 0.0, 1.0, 1.0, 0),
-        "read pred + target + write grad")
+        lambda i: ops.distill_loss_bwd(a[i], b2[i], rowstat[i], up, da[i], lr_rows, lr_rows, D, 0.0, 1.0, 1.0, 0),
+        "read pred + target + write grad", sets=K)
+    del a, b2, da
     # clip + AdamW + bf16 mirror + gradient zeroing over the 85 M Linear weights
     n = 84_934_656
     pp, gg, m1, m2 = (torch.zeros(n, device=dev) for _ in range(4))
@@ -513,7 +545,7 @@ def hbm_kernels(B, seconds, dev):
         "16 B read + 14 B write per parameter")
     so = torch.zeros(1, device=dev)
     add("sumsq (gradient norm)", 4 * n, lambda: ops.sumsq(gg, so), "4 B read per parameter")
-    return {"peak_gbs": peak, "peak_source": src, "l2_policy": "512 MB memset before each timed launch",
+    return {"peak_gbs": peak, "peak_source": src, "l2_policy": "512 MB memset, then a 256 MB read-only pass (leaves L2 clean), before each timed launch",
             "kernels": out}
 
 

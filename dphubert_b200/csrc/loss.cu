@@ -7,6 +7,7 @@
 // One warp per feature row (D <= 1280).  Forward writes per-row (dot, |a|, |b|) so the backward does not have to
 // re-reduce, and accumulates the three loss components into acc[0..2] (fp32 atomics, one per CTA).
 #include "common.cuh"
+#include "vec.cuh"
 #include "../../include/dphubert_b200.h"
 
 namespace dph {
@@ -17,7 +18,7 @@ constexpr int DL_NPL = 40;
 template <typename T>
 __global__ void __launch_bounds__(256)
     distill_loss_fwd_kernel(const T* __restrict__ a, const T* __restrict__ b, float* __restrict__ rowstat,
-                            float* __restrict__ acc, long long rows, int D, int cos_type, float eps) {
+                            float* __restrict__ acc, long long rows, int D, int cos_type, float eps, int vec) {
   __shared__ float red[3][8];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const long long row = (long long)blockIdx.x * 8 + w;
@@ -26,14 +27,32 @@ __global__ void __launch_bounds__(256)
     const T* ar = a + row * D;
     const T* br = b + row * D;
     float dot = 0.f, na = 0.f, nb = 0.f;
-    for (int i = lane; i < D; i += 32) {
-      const float x = to_f(ar[i]), y = to_f(br[i]);
-      const float d = x - y;
-      l2 += d * d;
-      l1 += fabsf(d);
-      dot += x * y;
-      na += x * x;
-      nb += y * y;
+    constexpr int VEC = VecOf<T>::N;
+    if (vec) {  // 16-byte loads (D a multiple of the vector width, 16-byte aligned rows)
+      for (int c0 = lane * VEC; c0 < D; c0 += 32 * VEC) {
+        float xa[VEC], xb[VEC];
+        load_vec(ar + c0, xa);
+        load_vec(br + c0, xb);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+          const float d = xa[j] - xb[j];
+          l2 = fmaf(d, d, l2);
+          l1 += fabsf(d);
+          dot = fmaf(xa[j], xb[j], dot);
+          na = fmaf(xa[j], xa[j], na);
+          nb = fmaf(xb[j], xb[j], nb);
+        }
+      }
+    } else {
+      for (int i = lane; i < D; i += 32) {
+        const float x = to_f(ar[i]), y = to_f(br[i]);
+        const float d = x - y;
+        l2 += d * d;
+        l1 += fabsf(d);
+        dot += x * y;
+        na += x * x;
+        nb += y * y;
+      }
     }
     l2 = warp_sum(l2);
     l1 = warp_sum(l1);
@@ -80,7 +99,7 @@ template <typename T>
 __global__ void __launch_bounds__(256)
     distill_loss_bwd_kernel(const T* __restrict__ a, const T* __restrict__ b, const float* __restrict__ rowstat,
                             const float* __restrict__ upstream, T* __restrict__ da, long long rows, int D, float w2,
-                            float w1, float wc, int cos_type, float eps, float n_elem, float n_rows) {
+                            float w1, float wc, int cos_type, float eps, float n_elem, float n_rows, int vec) {
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const long long row = (long long)blockIdx.x * 8 + w;
   if (row >= rows) return;
@@ -97,6 +116,22 @@ __global__ void __launch_bounds__(256)
   const T* ar = a + row * D;
   const T* br = b + row * D;
   T* dr = da + row * D;
+  constexpr int VEC = VecOf<T>::N;
+  if (vec) {
+    for (int c0 = lane * VEC; c0 < D; c0 += 32 * VEC) {
+      float xa[VEC], xb[VEC], o[VEC];
+      load_vec(ar + c0, xa);
+      load_vec(br + c0, xb);
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) {
+        const float d = xa[j] - xb[j];
+        const float gr = c2 * d + c1 * ((d > 0.f) ? 1.f : ((d < 0.f) ? -1.f : 0.f)) + kb * xb[j] - ka * xa[j];
+        o[j] = g * gr;
+      }
+      store_vec(dr + c0, o);
+    }
+    return;
+  }
   for (int i = lane; i < D; i += 32) {
     const float x = to_f(ar[i]), y = to_f(br[i]);
     const float d = x - y;
@@ -121,12 +156,14 @@ extern "C" int dph_distill_loss_fwd(const void* a, const void* b, float* rowstat
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   if (first) cudaMemsetAsync(acc, 0, 3 * sizeof(float), s);
   const unsigned grid = (unsigned)((rows + 7) / 8);
+  const int vw = dtype == DPH_DTYPE_BF16 ? 8 : 4;
+  const int vec = (D % vw == 0) && (((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b)) & 15) == 0);
   if (dtype == DPH_DTYPE_BF16)
     distill_loss_fwd_kernel<bf16><<<grid, 256, 0, s>>>((const bf16*)a, (const bf16*)b, rowstat, acc, rows, D, cos_type,
-                                                       1e-8f);
+                                                       1e-8f, vec);
   else
     distill_loss_fwd_kernel<float><<<grid, 256, 0, s>>>((const float*)a, (const float*)b, rowstat, acc, rows, D,
-                                                        cos_type, 1e-8f);
+                                                        cos_type, 1e-8f, vec);
   if (last)
     distill_loss_finalize_kernel<<<1, 32, 0, s>>>(acc, out, (float)total_rows * (float)D, (float)total_rows, w2, w1, wc);
   dph_count_launch(last ? 2 : 1);
@@ -143,12 +180,15 @@ extern "C" int dph_distill_loss_bwd(const void* a, const void* b, const float* r
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   const unsigned grid = (unsigned)((rows + 7) / 8);
   const float ne = (float)total_rows * (float)D, nr = (float)total_rows;
+  const int vw = dtype == DPH_DTYPE_BF16 ? 8 : 4;
+  const int vec = (D % vw == 0) && (((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) |
+                                      reinterpret_cast<uintptr_t>(da)) & 15) == 0);
   if (dtype == DPH_DTYPE_BF16)
     distill_loss_bwd_kernel<bf16><<<grid, 256, 0, s>>>((const bf16*)a, (const bf16*)b, rowstat, upstream, (bf16*)da, rows,
-                                                       D, w2, w1, wc, cos_type, 1e-8f, ne, nr);
+                                                       D, w2, w1, wc, cos_type, 1e-8f, ne, nr, vec);
   else
     distill_loss_bwd_kernel<float><<<grid, 256, 0, s>>>((const float*)a, (const float*)b, rowstat, upstream, (float*)da,
-                                                        rows, D, w2, w1, wc, cos_type, 1e-8f, ne, nr);
+                                                        rows, D, w2, w1, wc, cos_type, 1e-8f, ne, nr, vec);
   dph_count_launch();
   return dph_check_last("distill_loss_bwd");
 }
