@@ -18,7 +18,7 @@ void set_error(const char* fmt, ...);
 // block as ONE line-wide RED per column (same-address float atomics serialise in L2: keep them few and coalesced).
 // ZP = false: no pre-activation involved (plain dropout / gate scaling and the bias column sums), the cheap variant.
 template <typename T, int VEC, bool ZP>
-__global__ void __launch_bounds__(256, 3)
+__global__ void __launch_bounds__(256, 2)
     epilogue_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ z, const float* __restrict__ colmask,
                         const float* __restrict__ scalar, T* __restrict__ dout, float* __restrict__ dmask,
                         float* __restrict__ dbias, float* __restrict__ dscalar, int rows, int C, int rows_per_blk,
@@ -45,11 +45,45 @@ __global__ void __launch_bounds__(256, 3)
   const uint32_t thresh = (uint32_t)(drop_p * 4294967296.0);
   const float inv_keep = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
   constexpr int RB = ZP ? 2 : 4;  // rows in flight per thread (independent loads issued back to back)
+  // bf16 x 8 path: the raw 16-byte words of the NEXT row batch are requested before the current batch is processed,
+  // so the loads of one batch fly while the arithmetic of the previous one runs (the kernel is bound by bytes in flight)
+  constexpr bool PF = (VEC == 8) && (sizeof(T) == 2);
+  [[maybe_unused]] uint4 nd[RB], nz[RB];
+  [[maybe_unused]] auto fetch = [&](int rbx) {
+#pragma unroll
+    for (int q = 0; q < RB; ++q) {
+      const int r = rbx + 8 * q;
+      if (r < r1) {
+        nd[q] = *reinterpret_cast<const uint4*>(dy + (long long)r * in_ld + c0);
+        if constexpr (ZP) nz[q] = *reinterpret_cast<const uint4*>(z + (long long)r * z_ld + c0);
+      }
+    }
+  };
+  [[maybe_unused]] auto unpack8 = [](const uint4& u, float* v) {
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 f = __bfloat1622float2(h[e]);
+      v[2 * e] = f.x;
+      v[2 * e + 1] = f.y;
+    }
+  };
   if (active) {
+    if constexpr (PF) fetch(r0 + ty);
     for (int rb = r0 + ty; rb < r1; rb += 8 * RB) {
       float d[RB][VEC], zz[RB][VEC];
+      if constexpr (PF) {
 #pragma unroll
-      for (int q = 0; q < RB; ++q) {
+        for (int q = 0; q < RB; ++q) {
+          if (rb + 8 * q < r1) {
+            unpack8(nd[q], d[q]);
+            if constexpr (ZP) unpack8(nz[q], zz[q]);
+          }
+        }
+        if (rb + 8 * RB < r1) fetch(rb + 8 * RB);
+      }
+#pragma unroll
+      for (int q = 0; q < (PF ? 0 : RB); ++q) {
         const int r = rb + 8 * q;
         if (r < r1) {
           const long long ioff = (long long)r * in_ld + c0;
@@ -289,7 +323,7 @@ extern "C" int dph_epilogue_bwd(const void* dy, const void* z, const float* colm
   const int cols_per_blk = 32 * VECW;
   const int gx = (C + cols_per_blk - 1) / cols_per_blk;
   const bool zp = (z != nullptr);
-  int gy = (148 * 3) / gx;                       // three resident CTAs of 256 threads per SM, one wave
+  int gy = (148 * 2) / gx;                       // two resident CTAs of 256 threads per SM, one wave
   (void)zp;
   const int max_gy = (rows + 31) / 32;           // at least 32 rows (one 4-deep load batch per row lane) per CTA
   if (gy > max_gy) gy = max_gy;
