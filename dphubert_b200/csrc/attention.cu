@@ -46,6 +46,13 @@ DPH_DEVICE void tma_load_2d(uint32_t smem_dst, const CUtensorMap* m, uint32_t ba
       "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
 }
+DPH_DEVICE void tma_load_3d(uint32_t smem_dst, const CUtensorMap* m, uint32_t bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(
+          smem_dst),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
 // raw MUFU.EX2 (no range fix-ups): arguments here are <= ~0, underflow flushes to 0
 DPH_DEVICE float fast_exp2(float x) {
   float y;
@@ -509,8 +516,9 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
   auto load_qdo = [&](int qt) {  // thread 0 only
     const uint32_t buf = (uint32_t)(qt & 1);
     mbar_expect_tx(bar_qdo + 8 * buf, 2 * ATT_BQ * ATT_D * 2);
-    tma_load_2d(sQ + buf * QBUF, &tmQKV, bar_qdo + 8 * buf, 2 * p.inner + h * ATT_D, b * T + qt * ATT_BQ);
-    tma_load_2d(sDO + buf * QBUF, &tmDO, bar_qdo + 8 * buf, h * ATT_D, b * T + qt * ATT_BQ);
+    // 3-D maps (column, frame, utterance): frames >= T are zero-filled, never the next utterance's rows
+    tma_load_3d(sQ + buf * QBUF, &tmQKV, bar_qdo + 8 * buf, 2 * p.inner + h * ATT_D, qt * ATT_BQ, b);
+    tma_load_3d(sDO + buf * QBUF, &tmDO, bar_qdo + 8 * buf, h * ATT_D, qt * ATT_BQ, b);
   };
   auto issue_scores = [&](int qt) {  // thread 0 only: S and dP of query tile qt
     const uint32_t buf = (uint32_t)(qt & 1);
@@ -529,8 +537,8 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
 
   if (warp == 0 && elect_one()) {
     mbar_expect_tx(bar_kv, 2 * ATT_BK * ATT_D * 2);
-    tma_load_2d(sK, &tmQKV, bar_kv, h * ATT_D, b * T + k0);
-    tma_load_2d(sV, &tmQKV, bar_kv, p.inner + h * ATT_D, b * T + k0);
+    tma_load_3d(sK, &tmQKV, bar_kv, h * ATT_D, k0, b);
+    tma_load_3d(sV, &tmQKV, bar_kv, p.inner + h * ATT_D, k0, b);
     load_qdo(0);
     if (nq > 1) load_qdo(1);
     mbar_wait(bar_kv, 0);
@@ -565,7 +573,10 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
     float dg = 0.f;
     // Interior tile pairs (all 128 queries and keys valid, no padding mask) without a position bias take the lean
     // path: 5 instructions per score (FFMA, EX2, FFMA, FMUL, half a pack pair).  CTA-uniform choice.
-    const bool edge = BIAS || (q0 + ATT_BQ > T) || (k0 + ATT_BK > T) || (k0 + ATT_BK > len);
+    // Frames beyond T arrive as zeros (3-D tensor maps), which makes partial tiles harmless on the lean path: a
+    // zero dO row adds nothing to dV, its dP and (L2 = delta = 0) dS vanish, and a zero K / V row adds nothing to dQ
+    // while its own dK / dV rows are never stored.  Only a real padding mask (len < T) needs the general path.
+    const bool edge = BIAS || (len < T && k0 + ATT_BK > len);
     const float nL2 = -L2, ndl = -dl;
     auto do_chunk = [&](auto edge_tag, int cc) {
       constexpr bool EDGE = decltype(edge_tag)::value;
@@ -760,6 +771,8 @@ using namespace dph;
 namespace dph {
 int make_tmap_2d(CUtensorMap* out, const void* ptr, uint64_t cols, uint64_t rows, uint64_t row_stride_elems,
                  uint32_t box_cols, uint32_t box_rows);
+int make_tmap_nd_bf16(CUtensorMap* out, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                      const uint32_t* box, int swizzle);
 }
 
 static int attn_check(int B, int H, int T, int num_buckets) {
@@ -848,9 +861,16 @@ extern "C" int dph_attn_bwd(const void* qkv, const void* dctx, const void* o_un,
   const int inner = H * ATT_D;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   CUtensorMap tmq, tmd;
-  rc = make_tmap_2d(&tmq, qkv, 3ull * inner, (uint64_t)B * T, 3ull * inner, ATT_D, ATT_BK);
-  if (rc) return rc;
-  rc = make_tmap_2d(&tmd, dctx, (uint64_t)inner, (uint64_t)B * T, (uint64_t)inner, ATT_D, ATT_BQ);
+  {
+    const uint64_t qd[3] = {3ull * inner, (uint64_t)T, (uint64_t)B};
+    const uint64_t qs[2] = {3ull * inner * 2, (uint64_t)T * 3ull * inner * 2};
+    const uint32_t box[3] = {ATT_D, ATT_BK, 1};
+    rc = make_tmap_nd_bf16(&tmq, qkv, 3, qd, qs, box, 3);
+    if (rc) return rc;
+    const uint64_t dd[3] = {(uint64_t)inner, (uint64_t)T, (uint64_t)B};
+    const uint64_t ds[2] = {(uint64_t)inner * 2, (uint64_t)T * inner * 2};
+    rc = make_tmap_nd_bf16(&tmd, dctx, 3, dd, ds, box, 3);
+  }
   if (rc) return rc;
   static bool attr = false;
   if (!attr) {
