@@ -406,3 +406,32 @@ def test_attention_dropout_keep_rate():
     rows = keep.reshape(-1, T)
     c2 = ((rows[0::2] - 0.9) * (rows[1::2] - 0.9)).mean().item() / (0.9 * 0.1)
     assert abs(c2) < 2e-2, c2
+
+
+def test_conv0_full_size_tensor_core_vs_fp32():
+    """BASELINE size (8 x 10 s): the bf16 tensor-core forward (hi/lo split taps, tanh-form GELU) against the fp32
+    CUDA-core kernel (exact FMA chain, erf GELU) on the same inputs; every frame of every utterance is written"""
+    Bn, T0, k, s, C = 8, 160000, 10, 5, 512
+    T1 = (T0 - k) // s + 1
+    wave = rnd(Bn, T0) * 0.1
+    w = rnd(C, 1, k) * 0.3
+    gamma, beta, mask = rnd(C) * 0.2 + 1, rnd(C) * 0.1, torch.rand(C, device=DEV)
+    mean, rstd = zer(Bn * C), zer(Bn * C)
+    moments = torch.zeros(Bn * 65, device=DEV, dtype=torch.float64)
+    ops.conv0_stats(wave, w, None, moments, mean, rstd, Bn, C, k, s, T1, 1e-5)
+    y32 = torch.full((Bn, T1, C), float("nan"), device=DEV)
+    y16 = torch.full((Bn, T1, C), float("nan"), device=DEV, dtype=BF16)
+    ops.conv0_fwd(wave, w, None, gamma, beta, mean, rstd, mask, y32, Bn, C, k, s, T1, 1, 1)
+    ops.conv0_fwd(wave, w, None, gamma, beta, mean, rstd, mask, y16, Bn, C, k, s, T1, 1, 1)
+    torch.cuda.synchronize()
+    assert torch.isfinite(y16.float()).all()
+    err = (y16.float() - y32).abs()
+    # bf16 rounding of the output (2^-9 relative) + the tanh-form GELU (< 6e-4 absolute)
+    assert (err <= 4e-3 * y32.abs() + 1e-3).all(), err.max().item()
+    # GroupNorm property at full size: per (utterance, channel) the pre-activation has mean 0 / variance 1, so the
+    # statistics the kernel consumed are the ones of the conv output it produced
+    z = torch.nn.functional.conv1d(wave[:1, None, :], w, stride=s)[0, :8]
+    zn = (z - mean[:8, None]) * rstd[:8, None]
+    var = z.var(1, unbiased=False)
+    assert zn.mean(1).abs().max() < 1e-3
+    assert (zn.var(1, unbiased=False) - var / (var + 1e-5)).abs().max() < 2e-4  # rstd = 1 / sqrt(var + eps)
