@@ -435,3 +435,38 @@ def test_conv0_full_size_tensor_core_vs_fp32():
     var = z.var(1, unbiased=False)
     assert zn.mean(1).abs().max() < 1e-3
     assert (zn.var(1, unbiased=False) - var / (var + 1e-5)).abs().max() < 2e-4  # rstd = 1 / sqrt(var + eps)
+
+
+def test_fused_attention_full_size_vs_torch():
+    """BASELINE size (B = 8, H = 12, T = 499): fused tcgen05 attention forward / backward against plain torch fp32
+    matmul + softmax + autograd on the same bf16-rounded inputs (tolerance 3e-2 of the tensor's max: bf16 P / dS tiles,
+    bf16 dQ reductions)"""
+    Bn, H, T, scale = 8, 12, 499, 0.125
+    inner = H * 64
+    qkv = rnd(Bn * T, 3 * inner, dtype=BF16)
+    ctx, lse = zer(Bn * T, inner, dtype=BF16), zer(Bn, H, T)
+    ops.attn_fwd(qkv, ctx, None, lse, Bn, H, T, scale)
+    x = qkv.view(Bn, T, 3, H, 64).float().detach().requires_grad_(True)
+    k, v, q = x[:, :, 0].permute(0, 2, 1, 3), x[:, :, 1].permute(0, 2, 1, 3), x[:, :, 2].permute(0, 2, 1, 3)
+    S = scale * q @ k.transpose(-1, -2)
+    ref = (torch.softmax(S, -1) @ v).permute(0, 2, 1, 3).reshape(Bn * T, inner)
+    err = (ctx.float() - ref).abs().max().item() / ref.abs().max().item()
+    assert err < 2e-2, err
+    ref_lse = torch.logsumexp(S, -1)
+    assert (lse - ref_lse).abs().max().item() < 2e-2
+    dctx = rnd(Bn * T, inner, dtype=BF16)
+    ref.backward(dctx.float())
+    gref = x.grad.reshape(Bn * T, 3 * inner)  # same [k | v | q] layout as dqkv
+    delta, dq32 = zer(Bn, H, T), zer(Bn * T, inner)
+    dqkv = zer(Bn * T, 3 * inner, dtype=BF16)
+    ops.attn_bwd(qkv, dctx, ctx, lse, delta, dq32, dqkv, None, Bn, H, T, scale)
+    torch.cuda.synchronize()
+    for name, sl in (("dK", slice(0, inner)), ("dV", slice(inner, 2 * inner)), ("dQ", slice(2 * inner, 3 * inner))):
+        a, b = dqkv[:, sl].float(), gref[:, sl]
+        e = (a - b).abs().max().item() / b.abs().max().item()
+        assert e < 3e-2, (name, e)
+    # linearity in the upstream gradient (size-independent property of the backward)
+    dqkv2 = zer(Bn * T, 3 * inner, dtype=BF16)
+    ops.attn_bwd(qkv, (dctx.float() * 2).to(BF16), ctx, lse, delta, dq32, dqkv2, None, Bn, H, T, scale)
+    e = (dqkv2.float() - 2 * dqkv.float()).abs().max().item() / dqkv2.float().abs().max().item()
+    assert e < 2e-2, e
