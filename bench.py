@@ -222,7 +222,7 @@ def run_reference(args, rank):
             "config": {"workload": workload_string(name, args.workload, 1), "sample": sample},
             "cpu_baseline": {"value": val, "unit": "audio-s/s", "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 def cpu_baseline(args):
@@ -351,7 +351,7 @@ def run_ours(args, rank, world, local_rank):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args)
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        _emit(line)
     if dist is not None:
         # tearing the NCCL communicator down while a captured graph still references its kernels can block:
         # release the graph first, and leave without the (optional) communicator destruction
@@ -592,8 +592,28 @@ def roofline(step, wave, lengths, G, dev):
             "avg_launch_us": ms * 1e3 / max(len(trace), 1), "algorithmic_flops_per_step": flops, "peak_source": src}
 
 
+_REAL_STDOUT = None
+
+
+def _emit(line):
+    """The ONE JSON line goes to the process's original stdout; everything else (library banners such as NCCL's
+    version line, warnings) was redirected to stderr in main()."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    global _REAL_STDOUT
     args = parse()
+    # stdout carries exactly one line (the driver parses it): point fd 1 at stderr for the duration of the run, so that
+    # C libraries writing to stdout (NCCL prints its version there) cannot add lines, and keep the real stdout aside
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if os.environ.get("DPH_BENCH_FAULT"):  # debugging aid: dump every thread's Python stack if the run stalls
         import faulthandler
 
