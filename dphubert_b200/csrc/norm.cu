@@ -177,6 +177,14 @@ __global__ void __launch_bounds__(256)
   const float inv_keep = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
   pdl_wait();
   pdl_trigger();
+  // scale / shift of this lane's columns: row-invariant, requested before the row data so that their latency hides
+  // behind the statistics instead of following them
+  float wv[Q][VEC], bv[Q][VEC];
+#pragma unroll
+  for (int q = 0; q < Q; ++q) {
+    load_vec_f32(w + (lane + 32 * q) * VEC, wv[q]);
+    load_vec_f32(b + (lane + 32 * q) * VEC, bv[q]);
+  }
   for (int row = blockIdx.x * warps_per_blk + (threadIdx.x >> 5); row < rows; row += gridDim.x * warps_per_blk) {
     const T* xr = x + (long long)row * D;
     float v[Q][VEC];
@@ -205,11 +213,9 @@ __global__ void __launch_bounds__(256)
 #pragma unroll
     for (int q = 0; q < Q; ++q) {
       const int c0 = (lane + 32 * q) * VEC;
-      float wv[VEC], bv[VEC], o[VEC];
-      load_vec_f32(w + c0, wv);
-      load_vec_f32(b + c0, bv);
+      float o[VEC];
 #pragma unroll
-      for (int j = 0; j < VEC; ++j) o[j] = (v[q][j] - mean) * rstd * wv[j] + bv[j];
+      for (int j = 0; j < VEC; ++j) o[j] = (v[q][j] - mean) * rstd * wv[q][j] + bv[q][j];
       if (drop_p > 0.f) dropout_apply_vec<VEC>(seed, (unsigned long long)row * D + c0, thresh, inv_keep, o);
       store_vec(yr + c0, o);
     }
