@@ -657,23 +657,51 @@ class FreshAlloc:
 
 
 class StaticAlloc:
-    """`zero=True` buffers are cleared once, at creation: they are used for staging layouts whose padding is never
-    written afterwards."""
+    """Named workspace with fixed addresses.  A buffer is keyed by its NAME only: asking for the same name with a
+    different shape (the reference crops every batch to its shortest utterance, audio_dataset.py:285-363, so nearly
+    every batch has its own (B, T0)) hands out a view of the same storage, which grows only when a larger size than
+    ever before is requested — the workspace is bounded by the largest batch, not by the number of distinct shapes.
+    `zero=True` buffers hold staging layouts whose padding is never written afterwards: they are cleared at creation
+    and again whenever the requested shape (hence the position of the padding) changes."""
     static = True
+    SLACK = 1.0   # growth factor applied when a buffer has to be re-allocated
 
     def __init__(self, device, prefix=""):
         self.device = device
         self.prefix = prefix
-        self.bufs = {}
+        self.bufs = {}    # name -> flat storage tensor
+        self.shapes = {}  # name -> (shape, dtype) of the last view handed out
+        self.views = {}   # name -> last view
+        self.frozen = False  # set once a CUDA graph holds these addresses: shapes may no longer change
 
     def __call__(self, name, shape, dtype, zero=False):
-        key = (self.prefix + name, tuple(int(s) for s in shape), dtype)
-        t = self.bufs.get(key)
-        if t is None:
-            t = torch.empty(key[1], dtype=dtype, device=self.device)
-            if zero:
-                ops.memset(t)
-            self.bufs[key] = t
+        name = self.prefix + name
+        shape = tuple(int(s) for s in shape)
+        key = (shape, dtype)
+        if self.shapes.get(name) == key:
+            return self.views[name]
+        if self.frozen:
+            raise _lib.DphError(
+                "workspace buffer %r was captured into a CUDA graph as %s and is now requested as %s: a captured step "
+                "runs fixed shapes only (use run_step for variable-length batches)" % (name, self.shapes.get(name), key))
+        n = 1
+        for s in shape:
+            n *= s
+        store = self.bufs.get(name)
+        if store is None or store.dtype != dtype or store.numel() < n:
+            if store is not None:
+                if store.is_cuda and torch.cuda.is_current_stream_capturing():
+                    raise _lib.DphError("workspace buffer %r would have to grow during CUDA graph capture" % name)
+                if store.is_cuda:
+                    # kernels on side streams may still read the old storage; growth is rare (a new maximum size)
+                    torch.cuda.synchronize(self.device)
+            store = torch.empty(max(int(n * self.SLACK), n, 1), dtype=dtype, device=self.device)
+            self.bufs[name] = store
+        t = store[:n].view(shape)
+        if zero:
+            ops.memset(t)
+        self.shapes[name] = key
+        self.views[name] = t
         return t
 
     def nbytes(self):
