@@ -15,6 +15,7 @@ SIGS = {
     "dph_last_error": [],
     "dph_rng_set": [u64, vp],
     "dph_rng_advance": [vp],
+    "dph_rng_get": [vp, vp],
     "dph_gemm_bf16": [vp, vp],
     "dph_gemm_f32": [vp, vp],
     # norm.cu

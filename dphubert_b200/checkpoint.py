@@ -74,3 +74,24 @@ def final_checkpoint(lightning_state_dict, config):
     """save_final_ckpt.py:30-46: the student after the second distillation stage with the pruned config."""
     return {"state_dict": split_prefixed(lightning_state_dict, "student_model."), "config": config,
             "distill_linear_projs": split_prefixed(lightning_state_dict, "distill_linear_projs.")}
+
+
+def save_training_checkpoint(module, path=None):
+    """Resumable training checkpoint in the layout of a Lightning `.ckpt` (distill.py:141-144, 180-185): the flat
+    prefixed `state_dict`, `global_step`, and — under `native_step` — the Adam moments by parameter name, the optimizer
+    / scheduler step counter and the noise-stream state of the fused step.  Returns the dict; writes it when `path`."""
+    ckpt = {"state_dict": {k: v.detach().cpu().clone() for k, v in module.state_dict().items()},
+            "global_step": int(module.global_step), "epoch": int(getattr(module, "current_epoch", 0))}
+    module.on_save_checkpoint(ckpt)
+    if path is not None:
+        torch.save(ckpt, path)
+    return ckpt
+
+
+def load_training_checkpoint(module, ckpt):
+    """Inverse of `save_training_checkpoint` (`ckpt`: dict or path): weights first, then the optimizer state."""
+    if not isinstance(ckpt, dict):
+        ckpt = torch.load(ckpt, map_location="cpu", weights_only=False)
+    module.load_state_dict(ckpt["state_dict"], strict=True)
+    module.on_load_checkpoint(ckpt)
+    return module

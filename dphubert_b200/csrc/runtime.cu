@@ -12,6 +12,10 @@ __global__ void rng_epoch_kernel(unsigned long long value, int advance) {
   if (threadIdx.x == 0 && blockIdx.x == 0) dph_rng_epoch = advance ? dph_rng_epoch + 1ull : value;
 }
 
+__global__ void rng_epoch_read_kernel(unsigned long long* out) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) *out = dph_rng_epoch;
+}
+
 static std::atomic<long long> g_launches{0};
 static thread_local char g_err[512] = "";
 
@@ -55,6 +59,16 @@ int dph_rng_advance(void* stream) {
   rng_epoch_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(0ull, 1);
   dph_count_launch();
   return dph_check_last("rng_advance");
+}
+int dph_rng_get(void* out_dev, void* stream) {
+  if (out_dev == nullptr) {
+    dph::set_error("rng_get: null output pointer");
+    return DPH_ERR_ARG;
+  }
+  rng_epoch_read_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<unsigned long long*>(out_dev));
+  dph_count_launch();
+  return dph_check_last("rng_get");
 }
 long long dph_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 void dph_launch_count_reset(void) { g_launches.store(0, std::memory_order_relaxed); }

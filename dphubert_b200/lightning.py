@@ -3,10 +3,11 @@ schedulers) without a pytorch_lightning dependency.
 
 `DistillModule` keeps the reference's constructor keywords (lightning.py:143-164), attribute names, state-dict prefixes
 (`teacher_model.`, `student_model.`, `distill_linear_projs.N.`, `lambda1`, `lambda2`) and `_step` / `training_step` /
-`validation_step` / `configure_optimizers` entry points.  `training_step` is the fused native step
+`validation_step` / `configure_optimizers` entry points.  `training_step` returns the differentiable loss exactly like
+the reference (lightning.py:298-300) for an external optimizer loop; `native_training_step` is the fused native step
 (`dphubert_b200.trainer.NativeDistillStep`: forward, loss, backward, all-reduce, clip, AdamW and the LR schedule in one
-launch sequence / CUDA graph); `_step` computes the loss under autograd like the reference, for callers that drive
-their own optimizer.  The dataset / dataloader methods (lightning.py:306-342) are out of scope.
+launch sequence / CUDA graph) and refuses to be mixed with the former.  `train_dataloader` / `val_dataloader`
+(lightning.py:306-342) iterate the HBM-resident waveform pool of `dphubert_b200.data`.
 """
 import math
 import pathlib
@@ -78,9 +79,9 @@ class DistillLoss(nn.Module):
                                                     self.cos_type, self.cos_weight)
 
     def forward(self, input: torch.Tensor, target: torch.Tensor):
-        from . import _lib
+        from . import _lib, engine
 
-        if not input.is_cuda:
+        if not engine._is_native(input):
             raise _lib.DphError("DistillLoss runs only on CUDA tensors through the native kernels (no CPU fallback)")
         total, parts = _DistillLossFn.apply(input, target, float(self.l2_weight), float(self.l1_weight),
                                             float(self.cos_weight), 0 if self.cos_type == "raw" else 1)
@@ -243,13 +244,37 @@ class DistillModule(nn.Module):
         return self._native
 
     def training_step(self, batch, batch_idx):
-        """One full optimisation step (forward, backward, clip, AdamW, schedule) — returns the loss terms on the
-        device as in `NativeDistillStep.run_step`; `self.logged` carries host copies only when asked for."""
+        """Reference contract (lightning.py:298-300): the differentiable loss of `_step`, for an external optimizer
+        loop (`pl.Trainer`, or `configure_optimizers()` driven by hand).  Refuses to run once the fused native step
+        owns the optimisation of this module — mixing the two would apply two updates per batch."""
+        if self._native is not None and self._native.global_step > 0:
+            raise RuntimeError(
+                "DistillModule.training_step: this module is being optimised by the fused native step "
+                "(native_training_step / native_step()); an external optimizer loop on top would double-step. "
+                "Use one or the other.")
+        return self._step(batch, batch_idx, mode="train")
+
+    def native_training_step(self, batch, batch_idx=0):
+        """One full optimisation step (forward, backward, all-reduce, clip, AdamW, schedule) as a single launch
+        sequence — returns the loss terms on the device as in `NativeDistillStep.run_step`.  This replaces
+        `training_step` + Lightning's optimizer loop; it must not be called from inside one."""
         waveforms, lengths = batch
         step = self.native_step()
         out = step.run_step(waveforms, lengths)
         self.global_step = step.global_step
         return out
+
+    # ---- Lightning checkpoint hooks (trainer.fit(ckpt_path=...), distill.py:141-144): the native optimizer state
+    def on_save_checkpoint(self, checkpoint):
+        if self._native is not None:
+            checkpoint["native_step"] = self._native.state_dict()
+        checkpoint["global_step"] = self.global_step
+
+    def on_load_checkpoint(self, checkpoint):
+        self.global_step = int(checkpoint.get("global_step", self.global_step))
+        if "native_step" in checkpoint:
+            self.native_step().load_state_dict(checkpoint["native_step"])
+            self.global_step = self._native.global_step
 
     def validation_step(self, batch, batch_idx):
         with torch.no_grad():

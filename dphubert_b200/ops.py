@@ -317,6 +317,21 @@ def rng_advance():
     check(_L().dph_rng_advance(stream_ptr()), "dph_rng_advance")
 
 
+def rng_get(device):
+    """Current device-side RNG epoch as a Python int (synchronises; checkpointing only)."""
+    out = torch.zeros(1, dtype=torch.int64, device=device)
+    check(_L().dph_rng_get(ptr(out), stream_ptr()), "dph_rng_get")
+    return int(out.cpu()[0])
+
+
+def seed_state():
+    return int(_seed_counter[0])
+
+
+def set_seed_state(v):
+    _seed_counter[0] = int(v) & 0xFFFFFFFFFFFFFFFF
+
+
 def manual_seed(seed):
     _seed_counter[0] = (int(seed) * 0x9E3779B97F4A7C15 + 0x5DEECE66D) & 0xFFFFFFFFFFFFFFFF
 

@@ -49,6 +49,7 @@ class FlatParams:
                 v.copy_(p.data.to(device))
                 p.data = v
                 p.grad = self.gview(p)
+        self._vkey = None
         self.refresh()
 
     def view(self, p):
@@ -65,8 +66,18 @@ class FlatParams:
             return self.a16[o:o + p.numel()].view(p.shape)
         return self.view(p)
 
+    def version(self):
+        return sum(p._version for p in self.params)
+
     def refresh(self):
         ops.cast(self.arena, self.a16)
+        self._vkey = self.version()
+
+    def refresh_if_changed(self):
+        """Re-cast the bf16 operand copy when a parameter was modified behind our back (load_state_dict, an in-place
+        edit) — host-side check, so it has to run outside a captured graph."""
+        if self._vkey != self.version():
+            self.refresh()
 
 
 def _head_linear(proj):
@@ -139,12 +150,19 @@ class NativeDistillStep:
         self.global_step = 0
         # device-side step-varying scalars
         self.lr_dev = ops.zeros((4,), torch.float32, dev)       # [main, log_alpha, lambda, target sparsity]
-        self.lr_host = torch.zeros(4, dtype=torch.float32).pin_memory() if torch.cuda.is_available() else \
-            torch.zeros(4, dtype=torch.float32)
+        # ring of pinned staging slots, each guarded by an event: the host runs ahead of the device (replay() never
+        # synchronises), so a single slot could be overwritten before its queued H2D copy has executed
+        cuda = torch.cuda.is_available() and self.device.type == "cuda"
+        self._ring = [(torch.zeros(4, dtype=torch.float32).pin_memory() if cuda else torch.zeros(4, dtype=torch.float32),
+                       torch.cuda.Event() if cuda else None) for _ in range(16)]
+        self._ring_used = [False] * 16
+        self._ring_i = 0
         self.step_dev = torch.zeros(1, dtype=torch.int32, device=dev)
         self.gnorm = torch.zeros(1, dtype=torch.float64, device=dev)
         self.out = ops.zeros((16,), torch.float32, dev)  # [0:4] distill loss parts, [8:13] lagrangian block
         self._opt_state = None
+        # gate-noise stream: seeded from the host seed stream (ops.manual_seed / next_seed), saved in state_dict()
+        self._hc_seed = ops.next_seed()
         self._graph = None
         self._static_in = None
         self.comm_stream = None
@@ -167,11 +185,25 @@ class NativeDistillStep:
 
     def _push_scalars(self):
         sc = self._lr_scale(self.global_step + 1)
-        self.lr_host[0] = self.lr * sc
-        self.lr_host[1] = self.reg_lr * sc
-        self.lr_host[2] = -self.reg_lr * sc
-        self.lr_host[3] = self._target() if self.use_reg else 0.0
-        self.lr_dev.copy_(self.lr_host, non_blocking=True)
+        i = self._ring_i % len(self._ring)
+        self._ring_i += 1
+        host, ev = self._ring[i]
+        if ev is not None and self._ring_used[i]:
+            ev.synchronize()   # the copy queued from this slot 16 steps ago has executed
+        host[0] = self.lr * sc
+        host[1] = self.reg_lr * sc
+        host[2] = -self.reg_lr * sc
+        host[3] = self._target() if self.use_reg else 0.0
+        self.lr_dev.copy_(host, non_blocking=True)
+        if ev is not None:
+            ev.record()
+            self._ring_used[i] = True
+        # host-side staleness checks that a captured graph cannot replay: derived GEMM operands follow
+        # parameters changed by load_state_dict / in-place edits
+        self.heads.refresh_if_changed() if self.dt == torch.bfloat16 else None
+        if self._graph is not None:
+            self.splan.refresh(self.dt)
+            self.tplan.refresh(self.dt)
 
     # ------------------------------------------------------------------------------------------------ the step body
     def _sample_masks(self):
@@ -292,10 +324,6 @@ class NativeDistillStep:
                 ops.axpy(self.lam.garena[0:1], self.out[11:12], 1)
                 ops.axpy(self.lam.garena[1:2], self.out[12:13], 1)
 
-    @property
-    def _hc_seed(self):
-        return 0x1234ABCD
-
     def arenas(self):
         """[(param arena, grad arena)] of everything trainable."""
         out = [(self.splan.arena, self.splan.garena), (self.heads.arena, self.heads.garena)]
@@ -304,38 +332,161 @@ class NativeDistillStep:
         return out
 
     # ------------------------------------------------------------------------------------------------ optimizer
+    def _untouched(self):
+        """ids of student parameters the reference's optimizer never updates because their `.grad` stays None
+        (torch.optim.AdamW skips them, so they must not be weight-decayed either): frozen tensors such as
+        `feature_extractor.dummy_weight`, the Transformer-level LayerNorm of pre-norm models (unused by
+        `extract_features`, components.py:885-892), the `aux` head, and — in layer2layer mode — the transformer layers
+        above the last distilled one."""
+        st = self.student
+        tr = st.encoder.transformer
+        skip = {id(p) for p in st.parameters() if not p.requires_grad}
+        if not tr.layer_norm_first:
+            skip |= {id(p) for p in tr.layer_norm.parameters()}
+        if st.aux is not None:
+            skip |= {id(p) for p in st.aux.parameters()}
+        if self.mode == "layer2layer":
+            for li, layer in enumerate(tr.layers):
+                if li >= max(self.layers):
+                    skip |= {id(p) for p in layer.parameters()}
+        return skip
+
+    def _runs(self, lo, hi, skip):
+        """maximal [a, b) runs of the student arena range [lo, hi) made of parameters the optimizer updates"""
+        plan = self.splan
+        runs = []
+        for p in plan.params:
+            o = plan.offsets[id(p)]
+            if o < lo or o >= hi or id(p) in skip:
+                continue
+            e = o + (p.numel() + ALIGN - 1) // ALIGN * ALIGN
+            if runs and runs[-1][1] == o:
+                runs[-1][1] = e
+            else:
+                runs.append([o, e])
+        return runs
+
     def _segments(self):
-        """(param slice, grad slice, lr index, weight decay, bf16 mirror or None) per optimizer group segment."""
+        """(arena key, start, end, lr index, weight decay, has bf16 mirror) per optimizer launch.  With weight decay
+        off (run.sh default) a parameter with a zero gradient is left bit-identical by AdamW, so whole regions go in
+        one launch; with weight decay on, the regions are cut into runs of parameters the reference really updates."""
         sp = self.splan
-        segs = []
         bf = self.dt == torch.bfloat16
-        segs.append((sp.arena[:sp.lin_total], sp.garena[:sp.lin_total], 0, self.wd, sp.lin16 if bf else None))
-        if sp.la_off > sp.lin_total:
-            segs.append((sp.arena[sp.lin_total:sp.la_off], sp.garena[sp.lin_total:sp.la_off], 0, self.wd, None))
-        if sp.la_n:
-            segs.append((sp.arena[sp.la_off:], sp.garena[sp.la_off:], 1, 0.0, None))
-        segs.append((self.heads.arena, self.heads.garena, 0, self.wd, self.heads.a16 if bf else None))
+        regions = [(0, sp.lin_total, 0, self.wd, bf), (sp.lin_total, sp.la_off, 0, self.wd, False),
+                   (sp.la_off, sp.total, 1, 0.0, False)]
+        segs = []
+        skip = self._untouched() if self.wd != 0.0 else None
+        for lo, hi, li, wd, mirror in regions:
+            if hi <= lo:
+                continue
+            runs = [[lo, hi]] if (skip is None or wd == 0.0) else self._runs(lo, hi, skip)
+            for a, b in runs:
+                segs.append(("student", a, b, li, wd, mirror))
+        segs.append(("heads", 0, self.heads.total, 0, self.wd, bf))
         if self.lam is not None:
-            segs.append((self.lam.arena[:2], self.lam.garena[:2], 2, 0.0, None))
+            segs.append(("lam", 0, 2, 2, 0.0, False))
         return segs
+
+    def _arena_of(self, key):
+        if key == "student":
+            return self.splan.arena, self.splan.garena, self.splan.lin16
+        if key == "heads":
+            return self.heads.arena, self.heads.garena, self.heads.a16
+        return self.lam.arena, self.lam.garena, None
+
+    def _ensure_opt_state(self):
+        if self._opt_state is None:
+            keys = ["student", "heads"] + (["lam"] if self.lam is not None else [])
+            self._opt_state = {k: (ops.zeros(self._arena_of(k)[0].shape, torch.float32, self.device),
+                                   ops.zeros(self._arena_of(k)[0].shape, torch.float32, self.device)) for k in keys}
+            self._segs = self._segments()
+        return self._opt_state
 
     def _optimizer_step(self):
         """clip_grad_norm_(max_norm) + AdamW over the arenas (lightning.py:200-238, distill.py:48)."""
-        segs = self._segments()
-        if self._opt_state is None:
-            self._opt_state = [(ops.zeros(p.shape, torch.float32, self.device), ops.zeros(p.shape, torch.float32, self.device))
-                               for p, _, _, _, _ in segs]
+        state = self._ensure_opt_state()
+        segs = self._segs
         ops.counter_inc(self.step_dev)
         use_clip = self.clip_norm > 0
         if use_clip:
+            # the norm covers every gradient (untouched parameters have zero gradients)
             ops.memset(self.gnorm)
-            for _, g, _, _, _ in segs:
+            for _, g in self.arenas():
                 ops.sumsq(g, self.gnorm)
-        for (p, g, li, wd, p16), (m, v) in zip(segs, self._opt_state):
-            ops.adamw(p, g, m, v, self.lr_dev[li:li + 1], self.betas[0], self.betas[1], self.eps, wd, self.step_dev,
-                      self.gnorm if use_clip else None, self.clip_norm, p16, True)
+        for key, a, b, li, wd, mirror in segs:
+            p, g, p16 = self._arena_of(key)
+            m, v = state[key]
+            ops.adamw(p[a:b], g[a:b], m[a:b], v[a:b], self.lr_dev[li:li + 1], self.betas[0], self.betas[1], self.eps, wd,
+                      self.step_dev, self.gnorm if use_clip else None, self.clip_norm,
+                      p16[a:b] if (mirror and p16 is not None) else None, True)
+        if self.wd != 0.0:
+            # gradients of skipped runs were not cleared by the optimizer launches
+            for _, g in self.arenas():
+                ops.memset(g)
         # derived GEMM operands that are not plain casts (tap-major conv weights, weight-normalised pos conv)
         self.splan.rebuild_derived(self.dt, cast_lin=False)
+
+    # ------------------------------------------------------------------------------------------------ checkpoint state
+    def _named_slots(self):
+        """[(name, arena key, offset, numel)] of every parameter the optimizer owns, under the reference's
+        Lightning-level names (`student_model.`, `distill_linear_projs.N.`, `lambda1/2`)."""
+        out = []
+        for n, p in self.student.named_parameters():
+            out.append(("student_model." + n, "student", self.splan.offsets[id(p)], p.numel()))
+        seen = set()
+        for i, pr in enumerate(self.projs):
+            lin, gelu = _head_linear(pr)
+            if id(lin) in seen:
+                continue
+            seen.add(id(lin))
+            pre = "distill_linear_projs.%d.%s" % (i, "0." if gelu else "")
+            out.append((pre + "weight", "heads", self.heads.offsets[id(lin.weight)], lin.weight.numel()))
+            out.append((pre + "bias", "heads", self.heads.offsets[id(lin.bias)], lin.bias.numel()))
+        for i, l in enumerate(self.lambdas):
+            out.append(("lambda%d" % (i + 1), "lam", self.lam.offsets[id(l)], 1))
+        return out
+
+    def state_dict(self):
+        """Everything `trainer.fit(ckpt_path=...)` restores in the reference besides the weights (distill.py:141-144,
+        180-185): Adam moments per parameter (by name), the optimizer / scheduler step counters, `global_step`, and
+        the state of the noise streams (gate-noise seed, host seed counter, device RNG epoch).  Synchronises."""
+        state = self._ensure_opt_state()
+        moments = {}
+        for name, key, off, n in self._named_slots():
+            m, v = state[key]
+            moments[name] = {"exp_avg": m[off:off + n].detach().cpu().clone(),
+                             "exp_avg_sq": v[off:off + n].detach().cpu().clone()}
+        return {"global_step": int(self.global_step), "optimizer_step": int(self.step_dev.cpu()[0]),
+                "moments": moments, "hc_seed": int(self._hc_seed), "seed_counter": ops.seed_state(),
+                "rng_epoch": ops.rng_get(self.device), "format": 1}
+
+    def load_state_dict(self, sd):
+        """Inverse of `state_dict()`; weights are restored separately (module.load_state_dict).  A captured graph
+        stays valid: every buffer is updated in place."""
+        state = self._ensure_opt_state()
+        slots = {name: (key, off, n) for name, key, off, n in self._named_slots()}
+        missing = [k for k in slots if k not in sd["moments"]]
+        extra = [k for k in sd["moments"] if k not in slots]
+        if missing or extra:
+            raise KeyError("optimizer state does not match the model: missing %s unexpected %s" % (missing[:5], extra[:5]))
+        for name, (key, off, n) in slots.items():
+            m, v = state[key]
+            ent = sd["moments"][name]
+            if ent["exp_avg"].numel() != n:
+                raise ValueError("optimizer state of %s has %d elements, expected %d" % (name, ent["exp_avg"].numel(), n))
+            m[off:off + n].copy_(ent["exp_avg"].flatten().to(self.device))
+            v[off:off + n].copy_(ent["exp_avg_sq"].flatten().to(self.device))
+        self.global_step = int(sd["global_step"])
+        self.step_dev.fill_(int(sd["optimizer_step"]))
+        self._hc_seed = int(sd["hc_seed"])
+        ops.set_seed_state(sd["seed_counter"])
+        ops.rng_set(int(sd["rng_epoch"]))
+        if self._graph is not None and int(sd["hc_seed"]) != self._captured_hc_seed:
+            raise _lib.DphError("the gate-noise seed is baked into the captured graph: load the state before capture()")
+        # parameters were (re)loaded by the caller: rebuild every derived operand from them
+        self.heads.refresh()
+        self.splan.mark_dirty()
+        self.splan.refresh(self.dt)
 
     # ------------------------------------------------------------------------------------------------ data parallel
     # DDP's gradient mean (distill.py:41 strategy="ddp"): the Linear-weight gradients of transformer layer l (one
@@ -416,6 +567,9 @@ class NativeDistillStep:
             self._allreduce()
             self._optimizer_step()
         self._graph = g
+        self._captured_hc_seed = self._hc_seed
+        for a in (self.At, self.As, self.Ah):
+            a.frozen = True
         return g
 
     def replay(self):

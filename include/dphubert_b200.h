@@ -128,6 +128,8 @@ int dph_gemm_f32(const dph_gemm_f32_desc_t* desc, void* stream);
  * ---------------------------------------------------------------------------------------------------------- */
 int dph_rng_set(unsigned long long value, void* stream);
 int dph_rng_advance(void* stream);
+/* writes the current epoch to *out_dev (device uint64): checkpoint / resume of the noise stream (distill.py:141-144) */
+int dph_rng_get(void* out_dev, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * Waveform feature extractor, layer 0 (memory-bound): Conv1d(1->C, k<=10, stride) -> GroupNorm(C groups) -> GELU ->

@@ -712,12 +712,19 @@ def collate_crop(pool, start, length, out, lengths_out, B, T):
     return out
 
 
+_EPOCH = [0]
+
+
 def rng_set(value):
-    pass
+    _EPOCH[0] = int(value)
 
 
 def rng_advance():
-    pass
+    _EPOCH[0] += 1
+
+
+def rng_get(device):
+    return _EPOCH[0]
 
 
 _NAMES = ["memset", "memset2d", "zeros", "cast", "vec_mul", "transpose", "axpy", "group_mask_bwd", "wave_norm",
@@ -725,7 +732,7 @@ _NAMES = ["memset", "memset2d", "zeros", "cast", "vec_mul", "transpose", "axpy",
           "conv0_bwd", "softmax_fwd", "softmax_bwd", "attn_fwd", "attn_bwd", "wavlm_gate_fwd", "wavlm_gate_bwd", "distill_loss_fwd",
           "distill_loss_bwd", "conv_weight_prep", "conv_wgrad_unpermute", "posconv_weight_prep", "posconv_weight_bwd",
           "sumsq", "counter_inc", "adamw", "scale_", "hardconcrete_fwd", "hardconcrete_bwd", "l0_norms", "num_params",
-          "lagrangian", "l0_norms_bwd", "rng_set", "rng_advance", "collate_crop"]
+          "lagrangian", "l0_norms_bwd", "rng_set", "rng_advance", "rng_get", "collate_crop"]
 
 
 def install(monkeypatch):

