@@ -672,6 +672,7 @@ class StaticAlloc:
         self.bufs = {}    # name -> flat storage tensor
         self.shapes = {}  # name -> (shape, dtype) of the last view handed out
         self.views = {}   # name -> last view
+        self.seen = set() # every (name, shape, dtype) ever handed out
         self.frozen = False  # set once a CUDA graph holds these addresses: shapes may no longer change
 
     def __call__(self, name, shape, dtype, zero=False):
@@ -680,7 +681,7 @@ class StaticAlloc:
         key = (shape, dtype)
         if self.shapes.get(name) == key:
             return self.views[name]
-        if self.frozen:
+        if self.frozen and (name, key) not in self.seen:
             raise _lib.DphError(
                 "workspace buffer %r was captured into a CUDA graph as %s and is now requested as %s: a captured step "
                 "runs fixed shapes only (use run_step for variable-length batches)" % (name, self.shapes.get(name), key))
@@ -702,6 +703,7 @@ class StaticAlloc:
             ops.memset(t)
         self.shapes[name] = key
         self.views[name] = t
+        self.seen.add((name, key))
         return t
 
     def nbytes(self):

@@ -1,0 +1,27 @@
+#!/bin/bash
+# Runs ON THE GPU BOX (gpurun): launch list of one eager training step + `ncu --set full` captures of the step's
+# kernels, one report per kernel family.  Usage: bash profiles/ncu_capture.sh <tag> [kernel regex ...]
+# Reports land in gpurun_out/<tag>_<name>.ncu-rep; summarise them here with profiles/ncu_summary.py.
+set -u
+TAG=${1:-r02}
+shift || true
+CMD="python bench.py --profile-step"
+OUT=gpurun_out
+mkdir -p $OUT
+$CMD > $OUT/${TAG}_plain.log 2>&1 || { echo "plain run failed"; tail -20 $OUT/${TAG}_plain.log; exit 1; }
+ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv \
+    --log-file $OUT/${TAG}_ncu_launches_step.csv $CMD > $OUT/${TAG}_ncu_launches.log 2>&1
+echo "launch list rc=$?"
+if [ $# -eq 0 ]; then
+  set -- attn_fwd_kernel attn_bwd_kernel attn_bwd_prep conv0_fwd_tc conv0_bwd_fused posconv_tc_kernel \
+         epilogue_bwd_kernel layernorm_fwd layernorm_bwd adamw_kernel distill_loss_fwd distill_loss_bwd sumsq_kernel \
+         "gemm_bf16_kernel<256, 0, 0, 2, 103>" "gemm_bf16_kernel<192, 0, 0, 2, 45>" "gemm_bf16_kernel<256, 1, 1, 2, 384>" \
+         "gemm_bf16_kernel<256, 0, 1, 2, 45>" "gemm_bf16_kernel<64, 1, 1, 1, 45>"
+fi
+for k in "$@"; do
+  name=$(echo "$k" | tr -c 'A-Za-z0-9_' '_' | sed 's/__*/_/g')
+  ncu --set full --clock-control none --import-source on --profile-from-start off -k "regex:$k" -c 2 -f \
+      -o $OUT/${TAG}_${name} $CMD > $OUT/${TAG}_${name}.log 2>&1
+  echo "$k rc=$?"
+done
+ls -la $OUT | head -60

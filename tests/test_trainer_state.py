@@ -40,7 +40,7 @@ def test_workspace_is_bounded_by_the_largest_batch(emulated):
     check_workspace_bounded()
 
 
-def check_workspace_bounded():
+def check_workspace_bounded(exact=True):
     """ADVICE r1: the reference crops every batch to its shortest utterance, so nearly every batch has a new (B, T0);
     the named workspace must not keep one copy per shape."""
     g = load_golden("step_base")
@@ -70,10 +70,12 @@ def check_workspace_bounded():
     b[0]._push_scalars()
     a[0]._body(wave, ln)
     b[0]._body(wave, ln)
-    assert a[0].loss_terms() == b[0].loss_terms()
+    la, lb = a[0].loss_terms(), b[0].loss_terms()
+    assert la == lb if exact else abs(la["loss"] - lb["loss"]) < 1e-6 * abs(lb["loss"])
     for p, q in zip(a[2].parameters(), b[2].parameters()):
         if p.grad is not None:
-            assert torch.equal(p.grad, q.grad)
+            # GPU: weight gradients are accumulated with atomics, whose order is not fixed
+            assert torch.equal(p.grad, q.grad) if exact else rel_err(p.grad, q.grad, 1e-6) < 1e-4
 
 
 def test_resume_is_bit_exact(emulated):
@@ -108,8 +110,10 @@ def check_resume_bit_exact(exact=True):
     for p, q in zip(_params(a[2], a[3], a[4]), _params(c[2], c[3], c[4])):
         if exact:
             assert torch.equal(p.detach(), q.detach())
-        else:  # GPU: weight gradients are accumulated with atomics, whose order is not fixed
-            assert rel_err(p, q) < 1e-5
+        else:
+            # GPU: weight gradients are accumulated with atomics, whose order is not fixed; in its first steps Adam
+            # moves every weight by ~lr * sign(g), so a near-zero gradient flipping sign shows up at 2 * lr
+            assert rel_err(p, q) < 2e-3
     # a state from another model is refused
     bad = copy.deepcopy(opt_state)
     bad["moments"].pop("lambda1")
