@@ -342,6 +342,38 @@ def case_prune(wav2vec2_model, kind, seed, units=("conv", "head", "interm", "att
     return out
 
 
+def case_aux_layerdrop(wav2vec2_model, seed=400):
+    """Public `forward` (model.py:127-169) with the `aux` head and train-mode LayerDrop (components.py:894-907): the
+    reference draws `torch.rand(1).item()` once per layer from the global CPU generator, so seeding it pins the keep
+    pattern on both sides."""
+    cfg = small_cfg("base")
+    L = 4
+    cfg.update(encoder_num_layers=L, encoder_use_attention=[True] * L, encoder_use_feed_forward=[True] * L,
+               encoder_num_heads=[3] * L, encoder_ff_interm_features=[128] * L, aux_num_out=29,
+               encoder_layer_drop=0.5)
+    torch.manual_seed(seed)
+    model = wav2vec2_model(**cfg)
+    randomize(model, seed + 1)
+    wave = 0.1 * torch.randn(2, 8000, generator=torch.Generator().manual_seed(seed + 2))
+    lengths = torch.tensor([8000, 7000])
+    out = {"cfg": cfg, "state_dict": sd_of(model), "wave": wave, "lengths": lengths, "runs": []}
+    model.eval()
+    with torch.no_grad():
+        y, ol = model(wave, lengths)
+    out["eval_out"], out["out_lengths"] = y.clone(), ol.clone()
+    model.train()
+    for s in (1, 2, 3, 4):
+        torch.manual_seed(1000 + s)
+        with torch.no_grad():
+            y, _ = model(wave, lengths)
+        torch.manual_seed(1000 + s)
+        keep = [not (torch.rand(1).item() <= 0.5) for _ in range(L)]
+        out["runs"].append({"seed": 1000 + s, "keep": keep, "out": y.clone()})
+    assert len({tuple(r["keep"]) for r in out["runs"]}) > 1
+    print("aux/layerdrop: out %s, keep patterns %s" % (tuple(y.shape), [r["keep"] for r in out["runs"]]))
+    return out
+
+
 def final_distill_cases(wav2vec2_model, rl):
     """Second training stage: the pruned (ragged) students of the prune_* fixtures distilled from a full teacher."""
     for kind, seed in (("base", 300), ("wavlm", 320)):
@@ -400,6 +432,8 @@ def main():
         return sampler_cases()
     wav2vec2_model, rl = import_reference()
     os.makedirs(OUT, exist_ok=True)
+    if "--aux-only" in sys.argv:
+        return torch.save(case_aux_layerdrop(wav2vec2_model), os.path.join(OUT, "forward_base_aux.pt"))
     if "--final-only" in sys.argv:  # adds the final-distill fixtures without rewriting the others
         return final_distill_cases(wav2vec2_model, rl)
     for kind, seed in (("base", 0), ("large", 10), ("wavlm", 20)):
@@ -412,6 +446,7 @@ def main():
     for kind, seed in (("base", 200), ("wavlm", 220)):
         torch.save(case_prune(wav2vec2_model, kind, seed), os.path.join(OUT, "prune_%s.pt" % kind))
     final_distill_cases(wav2vec2_model, rl)
+    torch.save(case_aux_layerdrop(wav2vec2_model), os.path.join(OUT, "forward_base_aux.pt"))
     sampler_cases()
     # known-answer anchors of the full-size models: parameter counts
     from wav2vec2.model import wav2vec2_model as ref_build

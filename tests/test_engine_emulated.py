@@ -109,3 +109,32 @@ def test_adamw_matches_torch(emulated):
     step._optimizer_step()
     for p in allp:
         assert rel_err(p, clones[id(p)]) < 1e-5
+
+
+def check_aux_and_layerdrop(dev, dtype, tol):
+    """Public `forward` (model.py:127-169): `aux` head, trailing LayerNorm, train-mode LayerDrop with the reference's
+    host-side draws (components.py:894-907) — fixture forward_base_aux.pt holds the reference's outputs for four
+    seeded keep patterns."""
+    g = load_golden("forward_base_aux")
+    m = build_model(g["cfg"], g["state_dict"], dev, dtype)
+    wave, lengths = g["wave"].to(dev), g["lengths"].to(dev)
+    with torch.no_grad():
+        y, ol = m(wave, lengths)
+    assert torch.equal(ol.cpu(), g["out_lengths"]) and y.shape == g["eval_out"].shape
+    assert rel_err(y, g["eval_out"]) < tol
+    m.train()
+    for run in g["runs"]:
+        torch.manual_seed(run["seed"])
+        with torch.no_grad():
+            y, _ = m(wave, lengths)
+        assert rel_err(y, run["out"]) < tol, run["keep"]
+    # with gradients enabled the train-mode forward goes through the autograd bridge and gives the same values
+    run = g["runs"][1]
+    torch.manual_seed(run["seed"])
+    y, _ = m(wave, lengths)
+    assert rel_err(y, run["out"]) < tol
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 4e-2)])
+def test_aux_head_and_layerdrop(emulated, dtype, tol):
+    check_aux_and_layerdrop(CPU, dtype, tol)

@@ -470,3 +470,103 @@ def test_fused_attention_full_size_vs_torch():
     ops.attn_bwd(qkv, (dctx.float() * 2).to(BF16), ctx, lse, delta, dq32, dqkv2, None, Bn, H, T, scale)
     e = (dqkv2.float() - 2 * dqkv.float()).abs().max().item() / dqkv2.float().abs().max().item()
     assert e < 2e-2, e
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Dropout sites outside attention (all active in the benchmarked step; every parity fixture runs with p = 0):
+# the forward kernel and the backward kernel regenerate the mask from (seed, epoch, element index) independently,
+# so what has to hold is: identical masks on both sides, keep rate 1 - p, survivors scaled by 1 / (1 - p).
+# ---------------------------------------------------------------------------------------------------------------
+def _mask_of(with_drop, without, p):
+    """keep mask (0 / 1) recovered from an output computed with and without dropout; checks the scale"""
+    w, wo = with_drop.float(), without.float()
+    big = wo.abs() > 0.05 * wo.abs().mean()
+    ratio = (w / wo)[big]
+    keep = ratio.abs() > 0.5
+    assert (ratio[~keep].abs() < 1e-6).all()
+    assert ((ratio[keep] * (1 - p) - 1).abs() < 2e-2).all(), "survivors must be scaled by 1 / (1 - p)"
+    full = (w.abs() > 0).float()
+    return full, big
+
+
+@pytest.mark.parametrize("M,N,K", [(3992, 768, 768), (500, 512, 256)])
+def test_gemm_epilogue_dropout_matches_backward_mask(M, N, K):
+    """out-proj / FFN-out / feature-projection site: GEMM epilogue dropout (components.py:273,742,845) forward,
+    `epilogue_bwd` with the same seed backward"""
+    p, seed = 0.1, 1234567
+    x, w, bias = rnd(M, K, dtype=BF16), rnd(N, K, dtype=BF16, scale=0.05), rnd(N)
+    y0, y1 = zer(M, N, dtype=BF16), zer(M, N, dtype=BF16)
+    G.gemm(G.mat(x), G.mat(w), y0, M, N, K, bias=bias)
+    G.gemm(G.mat(x), G.mat(w), y1, M, N, K, bias=bias, drop_p=p, seed=seed)
+    torch.cuda.synchronize()
+    fwd_mask, big = _mask_of(y1, y0, p)
+    rate = fwd_mask[big].mean().item()
+    assert abs(rate - (1 - p)) < 3e-3, rate
+    dy = torch.ones(M, N, device=DEV, dtype=BF16)
+    g = zer(M, N, dtype=BF16)
+    db = zer(N)
+    ops.epilogue_bwd(dy, M, N, dout=g, dbias=db, drop_p=p, seed=seed)
+    torch.cuda.synchronize()
+    bwd_mask = (g.float() > 0).float()
+    assert ((g.float()[bwd_mask > 0] * (1 - p) - 1).abs() < 1e-2).all()
+    assert torch.equal(bwd_mask[big], fwd_mask[big]), "forward and backward dropout masks differ"
+    assert (db - g.float().sum(0)).abs().max().item() < 1e-2 * M ** 0.5
+    # a different seed gives a different, equally dense mask
+    y2 = zer(M, N, dtype=BF16)
+    G.gemm(G.mat(x), G.mat(w), y2, M, N, K, bias=bias, drop_p=p, seed=seed + 1)
+    torch.cuda.synchronize()
+    m2, _ = _mask_of(y2, y0, p)
+    agree = (m2[big] == fwd_mask[big]).float().mean().item()
+    assert abs(agree - ((1 - p) ** 2 + p ** 2)) < 5e-3, agree
+
+
+def test_ffn_intermediate_dropout_forward_backward_consistent():
+    """FFN hidden site (components.py:733-737): GEMM epilogue GELU -> dropout -> mask forward; `epilogue_bwd` computes
+    dz = dh * dropout * mask * GELU'(z) backward with the same seed"""
+    M, F, D, p, seed = 1000, 3072, 768, 0.1, 424242
+    x, w, bias = rnd(M, D, dtype=BF16), rnd(F, D, dtype=BF16, scale=0.05), rnd(F)
+    cm = torch.rand(F, device=DEV) * 0.5 + 0.5
+    h0, h1, z = zer(M, F, dtype=BF16), zer(M, F, dtype=BF16), zer(M, F, dtype=BF16)
+    G.gemm(G.mat(x), G.mat(w), h0, M, F, D, bias=bias, act=1, colmask=cm, c2=z)
+    G.gemm(G.mat(x), G.mat(w), h1, M, F, D, bias=bias, act=1, colmask=cm, drop_p=p, seed=seed, c2=z)
+    torch.cuda.synchronize()
+    fwd_mask, big = _mask_of(h1, h0, p)
+    assert abs(fwd_mask[big].mean().item() - (1 - p)) < 3e-3
+    dh = rnd(M, F, dtype=BF16)
+    dz0, dz1 = zer(M, F, dtype=BF16), zer(M, F, dtype=BF16)
+    dm0, dm1, db0, db1 = zer(F), zer(F), zer(F), zer(F)
+    ops.epilogue_bwd(dh, M, F, z=z, colmask=cm, dout=dz0, dmask=dm0, dbias=db0, act=1)
+    ops.epilogue_bwd(dh, M, F, z=z, colmask=cm, dout=dz1, dmask=dm1, dbias=db1, act=1, drop_p=p, seed=seed)
+    torch.cuda.synchronize()
+    bwd_mask, big2 = _mask_of(dz1, dz0, p)
+    both_big = big & big2
+    assert torch.equal(bwd_mask[both_big], fwd_mask[both_big]), "forward and backward dropout masks differ"
+    # mask gradient: d mask_j = sum_i dh_ij * dropout_ij * GELU(z_ij)
+    gz = torch.nn.functional.gelu(z.float())
+    ref = (dh.float() * fwd_mask / (1 - p) * gz).sum(0)
+    assert (dm1 - ref).abs().max().item() < 2e-2 * ref.abs().max().item()
+
+
+def test_layernorm_dropout_forward_backward_consistent():
+    """Transformer._preprocess site for pre-norm models (components.py:888-891): LayerNorm + dropout fused; the
+    backward re-derives the same mask"""
+    rows, D, p, seed = 3992, 768, 0.1, 99887766
+    x, w, b = rnd(rows, D, dtype=BF16), rnd(D) * 0.1 + 1.0, rnd(D) * 0.1
+    y0, y1 = zer(rows, D, dtype=BF16), zer(rows, D, dtype=BF16)
+    mean, rstd = zer(rows), zer(rows)
+    ops.layernorm_fwd(x, w, b, y0, rows, D, 1e-5, mean, rstd)
+    ops.layernorm_fwd(x, w, b, y1, rows, D, 1e-5, mean, rstd, drop_p=p, seed=seed)
+    torch.cuda.synchronize()
+    fwd_mask, big = _mask_of(y1, y0, p)
+    assert abs(fwd_mask[big].mean().item() - (1 - p)) < 3e-3
+    dy = rnd(rows, D, dtype=BF16)
+    dy_masked = (dy.float() * fwd_mask / (1 - p)).to(BF16)
+    dx0, dx1 = zer(rows, D, dtype=BF16), zer(rows, D, dtype=BF16)
+    dw0, dw1, db0, db1 = zer(D), zer(D), zer(D), zer(D)
+    ops.layernorm_bwd(dy_masked, x, w, b, mean, rstd, dx0, dw0, db0, rows, D)
+    ops.layernorm_bwd(dy, x, w, b, mean, rstd, dx1, dw1, db1, rows, D, drop_p=p, seed=seed)
+    torch.cuda.synchronize()
+    # elements where y0 ~ 0 are excluded from the mask comparison, so compare through the results instead
+    err = (dx1.float() - dx0.float()).abs().max().item() / dx0.float().abs().max().item()
+    assert err < 3e-2, err
+    assert (db1 - db0).abs().max().item() < 2e-2 * db0.abs().max().item() + 0.5

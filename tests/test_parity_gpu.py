@@ -169,3 +169,12 @@ def test_no_cpu_fallback():
     m = build_model(g["cfg"], g["state_dict"], torch.device("cpu"), torch.float32)
     with pytest.raises(_lib.DphError):
         m.extract_features(g["wave"], None)
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 2e-2)])
+def test_forward_with_aux_head_and_layerdrop(dtype, tol):
+    """public `forward` with the `aux` head, eval and train mode (LayerDrop keep pattern pinned by
+    seeding the host generator the reference draws from) — fixture from the reference itself."""
+    from test_engine_emulated import check_aux_and_layerdrop
+
+    check_aux_and_layerdrop(DEV, dtype, tol)
