@@ -41,6 +41,8 @@ SIGS = {
     "dph_conv0_fwd": [vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp],
     "dph_conv0_bwd": [vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32,
                       i32, i32, vp],
+    "dph_conv0_bwd_static": [vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32,
+                             i32, i32, i32, vp],
     "dph_wave_norm": [vp, i64, vp, i64, vp, i32, i32, f32, vp],
     # collate.cu
     "dph_collate_crop": [vp, i32, vp, vp, vp, vp, i32, i32, vp],

@@ -8,6 +8,8 @@
 //   sum_t z^2    = w[c,:] R w[c,:]^T   R[k,k'] = sum_t x[s t + k] x[s t + k']
 // i.e. a k + k(k+1)/2 element autocorrelation of the waveform per utterance (accumulated in fp64) gives the exact
 // per-(utterance, channel) mean / variance.  The backward recomputes z from the waveform instead of saving it.
+#include <mutex>
+
 #include "common.cuh"
 #include "vec.cuh"
 #include "../../include/dphubert_b200.h"
@@ -504,6 +506,66 @@ extern "C" int dph_conv0_bwd(const float* wave, int64_t wave_bs, const float* w,
                                                             dgamma, dbeta, B, C, k, T1, norm);
   dph_count_launch(2);
   return dph_check_last("conv0_bwd");
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// dph_conv0_bwd_static: dph_conv0_bwd with the 16 * B * C float scratch taken from a library-owned, file-scope
+// device array instead of a caller buffer, for callers that cannot allocate (CUDA graph capture, serving loops,
+// harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Limits: B * C <= DPH_CONV0_STATIC_MAX_BC (16384, e.g. 32 utterances x 512 channels; the array is 1 MiB and every
+// GPU that loads the library holds it until exit).  All calls share the one array, which keeps the previous call's
+// contents: it is cleared here (stream-ordered memset, as dph_conv0_bwd clears its caller's buffer), and two calls
+// that overlap on the GPU (different streams without an ordering between them) race on it.
+// In host code `g_conv0_static_scratch` is only a host-side stand-in for the symbol; the device address is looked
+// up once per device with cudaGetSymbolAddress while that device is current, and that pointer goes to the kernels.
+// ---------------------------------------------------------------------------------------------------------------
+#define DPH_CONV0_STATIC_MAX_BC 16384
+static __device__ __align__(256) float g_conv0_static_scratch[16 * DPH_CONV0_STATIC_MAX_BC];
+
+static int conv0_static_scratch_ptr(float** out) {
+  constexpr int kMaxDev = 64;
+  static float* ptrs[kMaxDev] = {};
+  static std::mutex mu;
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDev) {
+    set_error("conv0_bwd_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+    return DPH_ERR_CUDA;
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptrs[dev] == nullptr) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_conv0_static_scratch);  // address of the array on the CURRENT device
+    if (e != cudaSuccess || p == nullptr) {
+      set_error("conv0_bwd_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+      return DPH_ERR_CUDA;
+    }
+    ptrs[dev] = reinterpret_cast<float*>(p);
+  }
+  *out = ptrs[dev];
+  return DPH_OK;
+}
+
+extern "C" int dph_conv0_bwd_static(const float* wave, int64_t wave_bs, const float* w, const float* bias,
+                                    const float* gamma, const float* beta, const float* mean, const float* rstd,
+                                    const double* moments, const float* mask, const void* dy, float* dW, float* dbias,
+                                    float* dgamma, float* dbeta, float* dmask, int B, int C, int k, int stride, int T1,
+                                    int norm, int act, int dtype, void* stream) {
+  if (B <= 0 || C <= 0) {
+    set_error("conv0_bwd_static: bad sizes B=%d C=%d", B, C);
+    return DPH_ERR_ARG;
+  }
+  if ((long long)B * C > DPH_CONV0_STATIC_MAX_BC) {
+    set_error("conv0_bwd_static: B * C = %lld exceeds the static scratch limit of %d (B=%d, C=%d); use dph_conv0_bwd "
+              "with a caller-provided scratch buffer", (long long)B * C, DPH_CONV0_STATIC_MAX_BC, B, C);
+    return DPH_ERR_ARG;
+  }
+  float* scratch = nullptr;
+  int rc = conv0_static_scratch_ptr(&scratch);
+  if (rc) return rc;
+  // same launch sequence as dph_conv0_bwd (which starts by clearing the scratch on `stream`)
+  return dph_conv0_bwd(wave, wave_bs, w, bias, gamma, beta, mean, rstd, moments, mask, dy, scratch, dW, dbias, dgamma,
+                       dbeta, dmask, B, C, k, stride, T1, norm, act, dtype, stream);
 }
 
 extern "C" int dph_wave_norm(const float* in, int64_t in_bs, float* out, int64_t out_bs, const int64_t* lengths, int B,

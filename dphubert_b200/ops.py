@@ -142,6 +142,16 @@ def conv0_bwd(wave, w, bias, gamma, beta, mean, rstd, moments, mask, dy, scratch
           "dph_conv0_bwd")
 
 
+def conv0_bwd_static(wave, w, bias, gamma, beta, mean, rstd, moments, mask, dy, dW, dbias, dgamma, dbeta, dmask, B, C, k,
+                     stride, T1, norm, act):
+    """`conv0_bwd` with the scratch in the library's file-scope device array (no allocation; B * C <= 16384; calls
+    that overlap on the GPU race on the shared array).  Not used by the engine: for callers that cannot allocate."""
+    check(_L().dph_conv0_bwd_static(ptr(wave), wave.stride(0), ptr(w), ptr(bias), ptr(gamma), ptr(beta), ptr(mean),
+                                    ptr(rstd), ptr(moments), ptr(mask), ptr(dy), ptr(dW), ptr(dbias), ptr(dgamma),
+                                    ptr(dbeta), ptr(dmask), B, C, k, stride, T1, norm, act, dtype_code(dy), stream_ptr()),
+          "dph_conv0_bwd_static")
+
+
 def wave_norm(wave, out, lengths, B, T0, eps=1e-5):
     check(_L().dph_wave_norm(ptr(wave), wave.stride(0), ptr(out), out.stride(0), ptr(lengths), B, T0, eps, stream_ptr()),
           "dph_wave_norm")

@@ -151,6 +151,15 @@ int dph_conv0_bwd(const float* wave, int64_t wave_bs, const float* w, const floa
                   const float* mask, const void* dy, float* scratch /* 16*B*C */, float* dW, float* dbias,
                   float* dgamma, float* dbeta, float* dmask, int B, int C, int k, int stride, int T1, int norm, int act,
                   int dtype, void* stream);
+/* dph_conv0_bwd without a caller-provided scratch buffer: the 16*B*C floats live in a file-scope device array inside
+ * the library (1 MiB per GPU that loads it, held until exit), so the call allocates nothing.  NO COUNTERPART IN THE
+ * REFERENCE: added for callers that cannot call cudaMalloc (CUDA graph capture,
+ * serving loops, harnesses that forbid it).  Limit: B * C <= 16384 (DPH_ERR_ARG with a message beyond it).  Every call
+ * shares the array (cleared at the start of each call, stream-ordered): calls that overlap on the GPU race. */
+int dph_conv0_bwd_static(const float* wave, int64_t wave_bs, const float* w, const float* bias, const float* gamma,
+                         const float* beta, const float* mean, const float* rstd, const double* moments, const float* mask,
+                         const void* dy, float* dW, float* dbias, float* dgamma, float* dbeta, float* dmask, int B, int C,
+                         int k, int stride, int T1, int norm, int act, int dtype, void* stream);
 int dph_wave_norm(const float* in, int64_t in_bs, float* out, int64_t out_bs, const int64_t* lengths, int B, int T0,
                   float eps, void* stream);
 
