@@ -40,6 +40,8 @@ def parse():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--loader-batches", type=int, default=16,
+                    help="batches for the extra `fed_by_loader` key (0 = skip)")
     ap.add_argument("--sustain", type=float, default=3.0,
                     help="seconds of back-to-back replay for the extra `sustained` key (0 = skip)")
     ap.add_argument("--gemm-table", default="", help="write a per-shape timing table of the step's tensor-core GEMMs here")
@@ -448,6 +450,9 @@ def run_ours(args, rank, world, local_rank):
         line["roofline"] = roofline(step, wave, lengths, G, dev)
         if world == 1:
             line["roofline_hbm"] = hbm_kernels(B, secs, dev)
+    if world == 1 and args.loader_batches > 0:
+        line["fed_by_loader"] = loader_fed(args, teacher, student, projs, layers, dev, rank, world, B * secs,
+                                           args.loader_batches)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args)
     if rank == 0:
@@ -461,6 +466,61 @@ def run_ours(args, rank, world, local_rank):
         sys.stdout.flush()
         sys.stderr.flush()
         os._exit(0)
+
+
+def loader_fed(args, teacher, student, projs, layers, dev, rank, world, budget_s, n_batches):
+    """Extra key: the same training step fed by the data path the reference uses instead of a fixed
+    ring of equal-length batches — a synthetic LibriSpeech-like subset (utterances of 2 .. 15.6 s, int16 PCM, resident
+    in HBM), `BucketizeBatchSampler` (1000 buckets, `budget_s` seconds of audio per batch) -> `DistributedBatchSampler`
+    -> crop-to-shortest collate on the device.  Every batch has its own (B, T), so the step runs as an eager launch
+    sequence (a CUDA graph holds one shape).  Audio seconds actually processed / device time."""
+    from dphubert_b200 import data as D
+    from dphubert_b200.trainer import NativeDistillStep
+
+    gen = torch.Generator().manual_seed(7 + rank)
+    lens = torch.randint(32000, 250000, (600,), generator=gen).tolist()
+    waves = [torch.randint(-3000, 3000, (n,), generator=gen, dtype=torch.int16) for n in lens]
+    pool = D.WaveformPool(waves, dev, torch.int16)
+    del waves
+    torch.manual_seed(2022)
+    bs = D.BucketizeBatchSampler(lens, num_buckets=1000, max_token_count=int(budget_s * SR), min_len=32000,
+                                 max_len=250000, shuffle=False)
+    ds = D.DistributedBatchSampler(bs, num_replicas=world, rank=rank, shuffle=True)
+    loader = D.DeviceLoader(pool, ds, pad=False, rand_crop=True)
+    step = NativeDistillStep(teacher, student, layers, projs, "layer2layer", 0.0, 1.0, 1.0, "raw",
+                             use_reg=args.workload not in ("distill", "final"), learning_rate=2e-4, reg_learning_rate=0.02,
+                             warmup_updates=15000, max_updates=50000, target_sparsity=0.75, sparsity_warmup_updates=5000,
+                             clip_norm=10.0)
+    step.global_step = 5000
+    it = iter(loader)
+    shapes = []
+    # warm-up on the largest batches first so that the workspace reaches its final size before timing
+    order = sorted(range(len(ds.subset)), key=lambda i: -sum(lens[j] for j in ds.subset[i]))[:2]
+    for i in order:
+        w, l = loader.collate(ds.subset[i])
+        step.run_step(w, l)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    audio = 0.0
+    t_host = time.perf_counter()
+    e0.record()
+    for _ in range(n_batches):
+        try:
+            w, l = next(it)
+        except StopIteration:
+            it = iter(loader)
+            w, l = next(it)
+        step.run_step(w, l)
+        shapes.append((int(w.shape[0]), int(w.shape[1])))
+        audio += w.shape[0] * w.shape[1] / SR
+    e1.record()
+    host_s = time.perf_counter() - t_host   # time the host needed to ISSUE the steps (no sync inside)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    return {"value": audio / (ms / 1e3), "unit": "audio-s/s (this rank)", "batches": n_batches, "ms_per_batch": ms / n_batches,
+            "host_issue_ms_per_batch": host_s * 1e3 / n_batches, "audio_s_per_batch": audio / n_batches,
+            "batch_shapes_first4": shapes[:4], "distinct_shapes": len(set(shapes)), "seconds_per_batch_budget": budget_s,
+            "mode": "eager launch sequence (variable shapes), HBM-resident int16 pool, device collate"}
 
 
 def gemm_table(step, wave, lengths, G, path):

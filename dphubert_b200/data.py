@@ -191,3 +191,142 @@ class DeviceCollate:
         lengths = torch.empty(B, dtype=torch.int64, device=dev)
         ops.collate_crop(self.pool.data, start_d, take_d, out, lengths, B, T)
         return out, lengths
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# Manifest-driven loading (audio_dataset.py:220-283): tsv list -> decoded utterances -> HBM-resident pool
+# ----------------------------------------------------------------------------------------------------------------
+def read_manifest(tsv_dir, subset):
+    """`AudioDataset._get_lists` (audio_dataset.py:239-263): first line of `<tsv_dir>/<subset>.tsv` is the root
+    directory, every following line `relative/path<TAB>num_samples`.  Returns (paths, indices, lengths) as lists."""
+    import os
+
+    f_list, ind_list, len_list = [], [], []
+    with open(os.path.join(str(tsv_dir), "%s.tsv" % subset)) as f:
+        root = f.readline().rstrip()
+        for index, line in enumerate(f):
+            path, nsample = line.split("\t")
+            f_list.append("%s/%s" % (root, path))
+            ind_list.append(index)
+            len_list.append(int(nsample))
+    return f_list, ind_list, len_list
+
+
+def decode_audio(path):
+    """One utterance as a 1-D tensor: int16 PCM (kept as such: half the HBM and copy bytes, converted to the
+    reference's float scale x / 32768 inside `dph_collate_crop`) or float32.  PCM `.wav` through the standard library,
+    `.npy` / raw `.pcm` directly, anything else (`.flac`, ...) through `torchaudio.load` when its backend is installed
+    (`AudioDataset._load_audio`, audio_dataset.py:265-277).  Multi-channel files are refused like the reference's
+    collate would mis-handle them (it reads channel 0 only)."""
+    import numpy as np
+
+    ext = path.rsplit(".", 1)[-1].lower()
+    if ext == "wav":
+        import wave
+
+        with wave.open(path, "rb") as f:
+            nch, width, n = f.getnchannels(), f.getsampwidth(), f.getnframes()
+            raw = f.readframes(n)
+        if width == 2:
+            x = torch.from_numpy(np.frombuffer(raw, dtype="<i2").copy())
+        elif width == 4:
+            x = torch.from_numpy((np.frombuffer(raw, dtype="<i4") / 2147483648.0).astype(np.float32))
+        else:
+            raise ValueError("%s: unsupported PCM sample width %d" % (path, width))
+        if nch != 1:
+            x = x.view(-1, nch)[:, 0].contiguous()
+        return x
+    if ext == "npy":
+        x = torch.from_numpy(np.load(path))
+        return x.reshape(-1) if x.dtype in (torch.int16, torch.float32) else x.reshape(-1).float()
+    if ext in ("pcm", "raw"):
+        return torch.from_numpy(np.fromfile(path, dtype="<i2"))
+    try:
+        import torchaudio
+
+        w, _ = torchaudio.load(path)
+    except ImportError as e:
+        raise RuntimeError("decoding %s needs a torchaudio backend (torchcodec) that is not installed; convert the "
+                           "subset to PCM .wav / .npy or pass decode=<callable>" % path) from e
+    return w[0].contiguous()
+
+
+def load_pool(paths, lengths, device, keep=None, dtype=torch.int16, chunk_samples=1 << 24, workers=8,
+              decode=decode_audio):
+    """Decode the utterances `keep` (dataset indices; default all) ONCE and lay them back to back in one device
+    buffer.  Decoding runs on a thread pool; samples go through two pinned staging buffers and are copied on a side
+    stream, so decode of chunk i + 1 overlaps the host-to-device copy of chunk i.  Utterances the batch sampler
+    filtered out (min_len / max_len) are never read.  Returns a `WaveformPool` indexed by dataset index."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    device = torch.device(device)
+    order = sorted(range(len(paths)) if keep is None else set(int(i) for i in keep))
+    total = sum(int(lengths[i]) for i in order)
+    pool = WaveformPool.__new__(WaveformPool)
+    pool.data = torch.empty(max(total, 1), dtype=dtype, device=device)
+    pool.starts = [-1] * len(paths)
+    pool.lengths = [int(n) for n in lengths]
+    pool.device = pool.data.device
+    cuda = device.type == "cuda"
+    chunk = max(int(chunk_samples), max([pool.lengths[i] for i in order] or [1]))
+    stage = [torch.empty(chunk, dtype=dtype).pin_memory() if cuda else torch.empty(chunk, dtype=dtype) for _ in range(2)]
+    free = [torch.cuda.Event() if cuda else None for _ in range(2)]
+    used = [False, False]
+    copy_stream = torch.cuda.Stream(device) if cuda else None
+    state = {"buf": 0, "fill": 0, "pos": 0}
+
+    def flush():
+        b, n = state["buf"], state["fill"]
+        if n:
+            dst = pool.data[state["pos"]:state["pos"] + n]
+            if cuda:
+                with torch.cuda.stream(copy_stream):
+                    dst.copy_(stage[b][:n], non_blocking=True)
+                    free[b].record()
+                used[b] = True
+            else:
+                dst.copy_(stage[b][:n])
+            state["pos"] += n
+        state["buf"], state["fill"] = 1 - b, 0
+        if cuda and used[state["buf"]]:
+            free[state["buf"]].synchronize()   # the copy that last read this staging buffer has finished
+
+    def convert(x):
+        x = x.reshape(-1)
+        if dtype == torch.int16 and x.dtype != torch.int16:
+            x = torch.clamp(torch.round(x.float() * 32768.0), -32768, 32767).to(torch.int16)
+        elif dtype == torch.float32 and x.dtype == torch.int16:
+            x = x.float() / 32768.0
+        return x.to(dtype)
+
+    with ThreadPoolExecutor(max_workers=max(1, workers)) as ex:
+        for i, x in zip(order, ex.map(lambda j: convert(decode(paths[j])), order)):
+            n = x.numel()
+            if n != pool.lengths[i]:   # audio_dataset.py:276
+                raise AssertionError("%s has %d samples, the manifest says %d" % (paths[i], n, pool.lengths[i]))
+            if state["fill"] + n > chunk:
+                flush()
+            stage[state["buf"]][state["fill"]:state["fill"] + n].copy_(x)
+            pool.starts[i] = state["pos"] + state["fill"]
+            state["fill"] += n
+    flush()
+    if cuda:
+        torch.cuda.current_stream(device).wait_stream(copy_stream)
+    return pool
+
+
+class DeviceLoader:
+    """What `DataLoader(dataset, batch_sampler=..., collate_fn=CollateFnAudio(...))` is to the reference
+    (lightning.py:306-342): iterating yields `(waveforms (B, T) fp32, lengths (B,) int64)` per batch of the sampler —
+    already on the device, assembled by one gather kernel from the HBM-resident pool."""
+
+    def __init__(self, pool: WaveformPool, batch_sampler, pad: bool = False, rand_crop: bool = True):
+        self.pool, self.batch_sampler = pool, batch_sampler
+        self.collate = DeviceCollate(pool, pad=pad, rand_crop=rand_crop)
+
+    def __len__(self):
+        return len(self.batch_sampler)
+
+    def __iter__(self):
+        for batch in self.batch_sampler:
+            yield self.collate(batch)

@@ -21,6 +21,7 @@ from . import gemm as G
 from .gemm import View
 
 ALIGN = 8  # elements; keeps every bf16 view 16-byte aligned
+GRAD_TAIL = 8  # spare floats behind the gradient arena: the training step keeps d loss / d lambda there
 
 
 def _align(n):
@@ -58,16 +59,16 @@ class Plan:
         enc = model.encoder
         tr = enc.transformer
 
-        lin, la = [], []
-        for layer in tr.layers:
-            att, ff = layer.attention, layer.feed_forward
-            if att is not None:
-                lin += [att.k_proj.weight, att.v_proj.weight, att.q_proj.weight, att.out_proj.weight]
-            if ff is not None:
-                lin += [ff.intermediate_dense.weight, ff.output_dense.weight]
-        lin.append(enc.feature_projection.projection.weight)
-        if model.aux is not None:
-            lin.append(model.aux.weight)
+        # ---- arena order = order in which the backward pass COMPLETES gradients, so that the data-parallel gradient
+        # mean can be issued as a few contiguous slices while the rest of the backward still runs (trainer.py):
+        #   [layer 0 | layer 1 | ... | layer L-1 | projection, aux | transformer-level / positional conv / projection
+        #    vectors | conv n-1 .. conv 1 | conv 0, dummy_weight | every log_alpha]  (+ GRAD_TAIL floats in the gradient
+        #   arena only, for the caller's Lagrange multipliers).
+        # Inside a layer the Linear weights come first (K, V, Q back to back: fused projection), then its vectors.
+        def gates_of(mod):
+            return [m.log_alpha for m in mod.modules() if hasattr(m, "log_alpha") and hasattr(m, "n_in")]
+
+        la = []
         for blk in fe.conv_layers:
             if blk.hard_concrete is not None:
                 la.append(blk.hard_concrete.log_alpha)
@@ -81,32 +82,72 @@ class Plan:
                 for hc in (ff.hard_concrete_for_intermediate, ff.hard_concrete_for_layer):
                     if hc is not None:
                         la.append(hc.log_alpha)
-        special = {id(p) for p in lin} | {id(p) for p in la}
-        rest = [p for _, p in params if id(p) not in special]
-        ordered = lin + rest + la
-        assert len({id(p) for p in ordered}) == len(params)
+        la_ids = {id(p) for p in la}
+        groups = []   # per transformer layer
+        for layer in tr.layers:
+            att, ff = layer.attention, layer.feed_forward
+            ws = []
+            if att is not None:
+                ws += [att.k_proj.weight, att.v_proj.weight, att.q_proj.weight, att.out_proj.weight]
+            if ff is not None:
+                ws += [ff.intermediate_dense.weight, ff.output_dense.weight]
+            wid = {id(p) for p in ws}
+            groups.append(ws + [p for p in layer.parameters() if id(p) not in wid and id(p) not in la_ids])
+        lin_tail = [enc.feature_projection.projection.weight]
+        if model.aux is not None:
+            lin_tail.append(model.aux.weight)
+        conv_hi, conv_lo = [], []
+        blocks = list(fe.conv_layers)
+        for i in range(len(blocks) - 1, 0, -1):
+            conv_hi += [p for p in blocks[i].parameters() if id(p) not in la_ids]
+        if blocks:
+            conv_lo += [p for p in blocks[0].parameters() if id(p) not in la_ids]
+        conv_lo += [p for p in fe.parameters() if id(p) not in la_ids and
+                    all(p is not q for q in conv_hi + conv_lo)]   # dummy_weight
+        placed = {id(p) for g_ in groups for p in g_} | {id(p) for p in lin_tail + conv_hi + conv_lo} | la_ids
+        mid = [p for _, p in params if id(p) not in placed]
+        ordered = [p for g_ in groups for p in g_] + lin_tail + mid + conv_hi + conv_lo + la
+        assert len({id(p) for p in ordered}) == len(params) == len(ordered)
 
         self.offsets = {}
         off = 0
-        for p in lin:
-            self.offsets[id(p)] = off
-            off += _align(p.numel())
-        self.lin_total = off
-        for p in rest:
-            self.offsets[id(p)] = off
-            off += _align(p.numel())
+        marks = {}
+
+        def place(ps):
+            nonlocal off
+            start = off
+            for p in ps:
+                self.offsets[id(p)] = off
+                off += _align(p.numel())
+            return (start, off) if off > start else None
+
+        self.layer_lin_range = [place(g_) for g_ in groups]
+        enc_start = off
+        place(lin_tail)
+        self.lin_total = off      # the bf16 mirror covers [0, lin_total): every GEMM weight (and the layers' vectors)
+        place(mid)
+        marks["encoder"] = (enc_start, off)
+        marks["conv_hi"] = place(conv_hi)
+        lo_start = off
+        place(conv_lo)
         self.la_off = off
-        for p in la:
-            self.offsets[id(p)] = off
-            off += _align(p.numel())
+        place(la)
         self.total = off
         self.la_n = off - self.la_off
         self.la_params = la
+        marks["tail"] = (lo_start, self.total + GRAD_TAIL)
+        # gradient slices by completion event: int (transformer layer), "encoder" (everything between the transformer
+        # layers and the conv stack), "conv_hi" (conv layers n-1 .. 1), "tail" (conv 0, gates, the caller's tail)
+        self.grad_ranges = dict(marks)
+        for li, r in enumerate(self.layer_lin_range):
+            self.grad_ranges[li] = r
 
         dev = self.device
         self.arena = ops.zeros((self.total,), torch.float32, dev)
         self.any_grad = any(p.requires_grad for _, p in params)
-        self.garena = ops.zeros((self.total,), torch.float32, dev) if self.any_grad else None
+        self.garena_full = ops.zeros((self.total + GRAD_TAIL,), torch.float32, dev) if self.any_grad else None
+        self.garena = self.garena_full[: self.total] if self.any_grad else None
+        self.gtail = self.garena_full[self.total:] if self.any_grad else None
         with torch.no_grad():
             for p in ordered:
                 o, n = self.offsets[id(p)], p.numel()
@@ -118,22 +159,8 @@ class Plan:
         # optional second CUDA stream for the weight-gradient GEMMs of the transformer: they are off the critical
         # path of the backward pass (nothing downstream reads them) and fill the tail of the dgrad kernels
         self.side_stream = None
-        # called by encoder_bwd after each transformer layer's backward with the layer index (see layer_lin_range)
+        # called during the backward pass with a key of `grad_ranges` once every gradient of that slice has been issued
         self.grad_hook = None
-        self.layer_lin_range = []
-        for layer in tr.layers:
-            ws = []
-            if layer.attention is not None:
-                a_ = layer.attention
-                ws += [a_.k_proj.weight, a_.v_proj.weight, a_.q_proj.weight, a_.out_proj.weight]
-            if layer.feed_forward is not None:
-                ws += [layer.feed_forward.intermediate_dense.weight, layer.feed_forward.output_dense.weight]
-            if ws:
-                lo = min(self.offsets[id(w)] for w in ws)
-                hi = max(self.offsets[id(w)] + _align(w.numel()) for w in ws)
-                self.layer_lin_range.append((lo, hi))
-            else:
-                self.layer_lin_range.append(None)
 
         self.alias_params = []   # parameters of a real model that are views of this (padded shadow) model's
         self.dtype = None
@@ -815,6 +842,8 @@ def conv_stack_bwd(plan: Plan, st, dfeat, dmasks, A):
             dy = dx
         if dm_tmp is not None:
             ops.vec_mul(dm_tmp, plan.view(fe.dummy_weight), dmask, 1.0, 1.0)
+        if i == 1 and plan.grad_hook is not None:
+            plan.grad_hook("conv_hi")   # conv layers n-1 .. 1 are done; only layer 0 is left
 
 
 # ----------------------------------------------------------------------------------------------------------------
@@ -1431,6 +1460,8 @@ def backward_core(plan: Plan, st, dh, dmasks, A):
     M = enc["B"] * enc["T"]
     dh = [None if g is None else g.view(M, -1) for g in dh]
     dfeat = encoder_bwd(plan, enc, dh, dmasks, A)
+    if plan.grad_hook is not None:
+        plan.grad_hook("encoder")
     if dfeat is not None:
         conv_stack_bwd(plan, st["conv"], dfeat, dmasks, A)
     join_side(plan)

@@ -276,6 +276,48 @@ class DistillModule(nn.Module):
             self.native_step().load_state_dict(checkpoint["native_step"])
             self.global_step = self._native.global_step
 
+    # ---- data (lightning.py:306-342): same samplers / collate policy, batches assembled on the device
+    def _pool_and_lengths(self, subset, min_len=32000, max_len=250000):
+        from . import data
+
+        cache = self.__dict__.setdefault("_pools", {})
+        if subset not in cache:
+            paths, _, lens = data.read_manifest(self.tsv_dir, subset)
+            keep = [i for i, n in enumerate(lens) if min_len <= n <= max_len]   # what the bucket sampler can emit
+            device = next(self.student_model.parameters()).device
+            cache[subset] = (data.load_pool(paths, lens, device, keep=keep, workers=max(1, int(self.num_workers or 1))),
+                             lens)
+        return cache[subset]
+
+    def _bucket_sampler(self, lens):
+        from . import data
+
+        return data.BucketizeBatchSampler(lens, num_buckets=1000, max_token_count=self.seconds_per_batch * 16000,
+                                          min_len=32000, max_len=250000, shuffle=False)
+
+    def train_dataloader(self):
+        """lightning.py:306-324: 1000 length buckets, <= seconds_per_batch of audio per batch, 2 s <= len <= 15.6 s,
+        whole batches dealt to ranks with a seeded shuffle, crop to the shortest utterance with random offsets."""
+        import torch.distributed as dist
+
+        from . import data
+
+        pool, lens = self._pool_and_lengths(self.train_subset)
+        sampler = self._bucket_sampler(lens)
+        if dist.is_available() and dist.is_initialized():
+            sampler = data.DistributedBatchSampler(sampler, shuffle=True)
+        else:
+            sampler = data.DistributedBatchSampler(sampler, num_replicas=1, rank=0, shuffle=True)
+        sampler.set_epoch(self.current_epoch)
+        return data.DeviceLoader(pool, sampler, pad=False, rand_crop=True)
+
+    def val_dataloader(self):
+        """lightning.py:326-342 (not distributed: every rank sees the whole validation set)."""
+        from . import data
+
+        pool, lens = self._pool_and_lengths("valid")
+        return data.DeviceLoader(pool, self._bucket_sampler(lens), pad=False, rand_crop=True)
+
     def validation_step(self, batch, batch_idx):
         with torch.no_grad():
             return self._step(batch, batch_idx, mode="valid")

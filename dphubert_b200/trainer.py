@@ -25,7 +25,10 @@ class FlatParams:
     """Small flat fp32 arena (+ gradient arena, + bf16 copy) for parameters living outside a model: the distillation
     heads and the two Lagrange multipliers."""
 
-    def __init__(self, params: List[torch.nn.Parameter], device, align=ALIGN):
+    def __init__(self, params: List[torch.nn.Parameter], device, align=ALIGN, garena=None):
+        """`garena`: external gradient storage (a flat fp32 tensor of at least the arena's size) — the Lagrange
+        multipliers keep their gradients in the tail of the student's gradient arena so that they ride in the same
+        all-reduce call as the last student slice."""
         uniq = []
         seen = set()
         for p in params:
@@ -41,7 +44,12 @@ class FlatParams:
         self.total = (max(off, 1) + ALIGN - 1) // ALIGN * ALIGN
         self.device = device
         self.arena = ops.zeros((self.total,), torch.float32, device)
-        self.garena = ops.zeros((self.total,), torch.float32, device)
+        if garena is not None:
+            if garena.numel() < self.total:
+                raise _lib.DphError("external gradient storage too small")
+            self.garena = ops.memset(garena[: self.total])
+        else:
+            self.garena = ops.zeros((self.total,), torch.float32, device)
         self.a16 = torch.empty(self.total, dtype=torch.bfloat16, device=device)
         with torch.no_grad():
             for p in uniq:
@@ -119,8 +127,8 @@ class NativeDistillStep:
 
         self.tplan = get_plan(teacher)
         self.splan = get_plan(student)
-        self._pending, self._covered = [], []
-        self.splan.grad_hook = self._layer_grads_ready if self.world > 1 else None
+        self._pending, self._covered = [], set()
+        self.splan.grad_hook = self._grads_ready if self.world > 1 else None
         self.two_streams = True   # teacher forward / weight-gradient GEMMs on side streams (CUDA only)
         self.tstream = None
         dev = self.splan.device
@@ -139,7 +147,7 @@ class NativeDistillStep:
         else:
             self.lambdas = []
         self.heads = FlatParams(head_params, dev)
-        self.lam = FlatParams(self.lambdas, dev, align=1) if self.use_reg else None
+        self.lam = FlatParams(self.lambdas, dev, align=1, garena=self.splan.gtail) if self.use_reg else None
         if original_num_params is None:
             original_num_params = sum(p.numel() for p in teacher.parameters())
         self.n0 = float(original_num_params)
@@ -310,6 +318,7 @@ class NativeDistillStep:
                 G.gemm(G.mat(dpred), Wt, dh[src_i], M, D, Dt)
             else:
                 G.gemm(G.mat(dpred), Wt, dh[src_i], M, D, Dt, accumulate=True)
+        self._heads_ready()   # the heads' gradients are complete: their all-reduce overlaps the whole student backward
         # ---- backward: student
         dmasks = self.As("hc_dmasks", (max(splan.la_n, 1),), torch.float32)
         ops.memset(dmasks)
@@ -323,6 +332,10 @@ class NativeDistillStep:
                 # d loss / d lambda1 = (s - t), d loss / d lambda2 = (s - t)^2
                 ops.axpy(self.lam.garena[0:1], self.out[11:12], 1)
                 ops.axpy(self.lam.garena[1:2], self.out[12:13], 1)
+
+    def _grad_buffers(self):
+        """the distinct gradient storages: student arena + its tail (which holds the multipliers' gradients), heads"""
+        return [self.splan.garena_full, self.heads.garena]
 
     def arenas(self):
         """[(param arena, grad arena)] of everything trainable."""
@@ -411,7 +424,7 @@ class NativeDistillStep:
         if use_clip:
             # the norm covers every gradient (untouched parameters have zero gradients)
             ops.memset(self.gnorm)
-            for _, g in self.arenas():
+            for g in self._grad_buffers():
                 ops.sumsq(g, self.gnorm)
         for key, a, b, li, wd, mirror in segs:
             p, g, p16 = self._arena_of(key)
@@ -505,36 +518,46 @@ class NativeDistillStep:
             w = dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
             self._pending.append((w, t))
 
-    def _layer_grads_ready(self, li):
-        rng = self.splan.layer_lin_range[li]
-        if rng is None:
+    def _grads_ready(self, key):
+        """Backward-pass hook (engine.Plan.grad_ranges): every gradient of slice `key` — a transformer layer,
+        "encoder" (projection / positional conv / transformer-level vectors) or "conv_hi" (conv layers n-1 .. 1) — has
+        been issued; reduce it now, behind both streams that produced it, while the rest of the backward runs."""
+        rng = self.splan.grad_ranges.get(key)
+        if rng is None or key in self._covered:
             return
-        lo, hi = rng
+        self._reduce_slice(self.splan.garena_full[rng[0]:rng[1]])
+        self._covered.add(key)
+
+    def _reduce_slice(self, t):
         side = self.splan.side_stream
-        if side is not None:
-            # the slice holds Linear-weight gradients only, all produced on the side stream: NCCL orders itself after it
+        if side is not None and t.is_cuda:
+            # weight gradients come from the side stream, bias / norm gradients from the main one
+            side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
-                self._reduce_async(self.splan.garena[lo:hi])
+                self._reduce_async(t)
         else:
-            self._reduce_async(self.splan.garena[lo:hi])
-        self._covered.append((lo, hi))
+            self._reduce_async(t)
+
+    def _heads_ready(self):
+        if self.world > 1:
+            self._reduce_slice(self.heads.garena)
 
     def _allreduce(self):
+        """The last slice (conv layer 0, every log_alpha and — in the gradient tail — the two multipliers: one call),
+        any slice whose hook did not fire, then wait for everything."""
         if self.world <= 1:
             return
-        g = self.splan.garena
-        pos = 0
-        for lo, hi in sorted(self._covered):
-            self._reduce_async(g[pos:lo])
-            pos = max(pos, hi)
-        self._reduce_async(g[pos:])
-        for _, ga in self.arenas()[1:]:
-            self._reduce_async(ga)
+        plan = self.splan
+        rest = [k for k in plan.grad_ranges if k != "tail" and k not in self._covered and plan.grad_ranges[k] is not None]
+        for k in rest:
+            self._reduce_async(plan.garena_full[plan.grad_ranges[k][0]:plan.grad_ranges[k][1]])
+        lo, hi = plan.grad_ranges["tail"]
+        self._reduce_async(plan.garena_full[lo:hi])
         for w, t in self._pending:
             w.wait()
             if t is not None:
                 t.mul_(1.0 / self.world)
-        self._pending, self._covered = [], []
+        self._pending, self._covered = [], set()
 
     # ------------------------------------------------------------------------------------------------ public
     def zero_grad(self):

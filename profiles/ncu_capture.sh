@@ -23,5 +23,13 @@ for k in "$@"; do
   ncu --set full --clock-control none --import-source on --profile-from-start off -k "regex:$k" -c 2 -f \
       -o $OUT/${TAG}_${name} $CMD > $OUT/${TAG}_${name}.log 2>&1
   echo "$k rc=$?"
+  # the reports are ~35 MB each and gpurun_out/ travels back only below 64 MiB: keep the raw metric table and the
+  # per-source-line page as CSV, drop the report
+  if [ -f $OUT/${TAG}_${name}.ncu-rep ]; then
+    ncu -i $OUT/${TAG}_${name}.ncu-rep --page raw --csv > $OUT/${TAG}_${name}.raw.csv 2>/dev/null
+    ncu -i $OUT/${TAG}_${name}.ncu-rep --page source --csv 2>/dev/null | gzip > $OUT/${TAG}_${name}.source.csv.gz
+    rm -f $OUT/${TAG}_${name}.ncu-rep
+  fi
 done
+du -sh $OUT
 ls -la $OUT | head -60

@@ -510,7 +510,9 @@ def test_gemm_epilogue_dropout_matches_backward_mask(M, N, K):
     bwd_mask = (g.float() > 0).float()
     assert ((g.float()[bwd_mask > 0] * (1 - p) - 1).abs() < 1e-2).all()
     assert torch.equal(bwd_mask[big], fwd_mask[big]), "forward and backward dropout masks differ"
-    assert (db - g.float().sum(0)).abs().max().item() < 1e-2 * M ** 0.5
+    # bias gradient = column sums of the masked, scaled upstream gradient (fp32 inside the kernel; `g` is bf16-rounded)
+    ref_db = bwd_mask.sum(0) / (1 - p)
+    assert ((db - ref_db).abs() / ref_db).max().item() < 1e-3
     # a different seed gives a different, equally dense mask
     y2 = zer(M, N, dtype=BF16)
     G.gemm(G.mat(x), G.mat(w), y2, M, N, K, bias=bias, drop_p=p, seed=seed + 1)

@@ -233,9 +233,16 @@ def test_prune_step_at_real_dimensions(name, dtype, tol, gtol, gtol_max):
         if key not in g["grads"]:
             continue
         st = g["grad_stats"][key]
-        # gradients that are analytically zero (k_proj.bias: softmax shift invariance) carry only round-off
-        floor = (1e-6 if dtype == torch.float32 else 1e-4) * gmax
-        e = errs(sample(p.grad, NG), g["grads"][key], floor)
+        if st["max"] < 1e-6 * gmax:
+            # analytically zero in exact arithmetic (k_proj.bias: softmax is invariant to a shift of the keys); the
+            # reference holds 1e-11-sized round-off there.  What can be asked is that ours is also negligible against
+            # the gradients that matter: below 1e-4 (fp32) / 1e-2 (bf16) of the largest gradient entry of the model.
+            mag = float(p.grad.detach().abs().max()) / gmax
+            report(tag, "zero_grad:" + key, (mag, mag))
+            assert mag < (1e-4 if dtype == torch.float32 else 1e-2), (key, mag)
+            n_checked += 1
+            continue
+        e = errs(sample(p.grad, NG), g["grads"][key])
         report(tag, "grad:" + key, e)
         n_checked += 1
         if e[0] > worst[1]:
