@@ -187,14 +187,19 @@ def build_real_step(g, dtype):
 #    |pred - target| are tiny, so the L1 term's sign() is decided by round-off: fp32 heads 1.9e-4 L2 / 1.4e-3 max; in
 #    bf16 the worst weight gradient is 4.8e-2 L2.
 #  * bf16, well-conditioned cases: worst 2.5e-2 (Base), 9.2e-2 (Large, 24 layers) -> bars 5e-2 / 1.5e-1.
-#  * WavLM's gate parameters `gru_rel_pos_linear.bias` (8 values per layer) and `gru_rel_pos_const` (12) are sums of
-#    dS * bias over every score with massive cancellation (sum_j dS_ij = 0): fp32 already shows 1.4e-4 there and bf16
-#    0.6 L2 — they are reported, and bounded only loosely (LOOSE).
+#  * WavLM's gate parameters `gru_rel_pos_linear.{weight,bias}` and `gru_rel_pos_const` (8 x 64, 8 and 12 values per
+#    layer) are sums of dS * bias over every score with massive cancellation (sum_j dS_ij = 0 and the bias varies
+#    slowly along j): fp32 shows 1e-3 .. 3e-3 there, bf16 5e-2 (weight) to 0.6 (bias) — reported, loosely bounded (LOOSE).
 STEP = [("real_base_step", torch.float32, 1e-4, 1e-3, 5e-3), ("real_base_step", torch.bfloat16, 2e-2, 1e-1, 1e-1),
         ("real_base_step_p", torch.float32, 1e-4, 1e-4, 1e-4), ("real_base_step_p", torch.bfloat16, 2e-2, 5e-2, 5e-2),
-        ("real_wavlm_step", torch.float32, 1e-4, 1e-3, 1e-3), ("real_wavlm_step", torch.bfloat16, 2e-2, 5e-2, 5e-2),
+        ("real_wavlm_step", torch.float32, 1e-4, 1e-3, 5e-3), ("real_wavlm_step", torch.bfloat16, 2e-2, 5e-2, 5e-2),
         ("real_large_step", torch.float32, 1e-4, 5e-4, 5e-3), ("real_large_step", torch.bfloat16, 2e-2, 1.5e-1, 1.5e-1)]
-LOOSE = ("gru_rel_pos_linear.bias", "gru_rel_pos_const")
+# suffix -> (fp32 bar, bf16 bar), both norms
+# (None = reported only).  Evidence: oracle/grad_conditioning.py -> profiles/r02_grad_conditioning_wavlm.txt — the
+# reference's OWN fp32 arithmetic is 4.7e-2 from the fp64 value on layers.10.gru_rel_pos_linear.bias, 2e-3 .. 7e-3 on
+# the other gate gradients, 1e-4 in the median over all tensors; bf16 carries 65 000 x less precision into the same
+# cancellation, so there the gate bias / const gradients cannot be held to any bar.
+LOOSE = {"gru_rel_pos_linear.weight": (5e-2, 0.15), "gru_rel_pos_linear.bias": (1e-1, None), "gru_rel_pos_const": (5e-2, None)}
 
 
 @pytest.mark.parametrize("name,dtype,tol,gtol,gtol_max", STEP)
@@ -247,8 +252,12 @@ def test_prune_step_at_real_dimensions(name, dtype, tol, gtol, gtol_max):
         n_checked += 1
         if e[0] > worst[1]:
             worst = (key, e[0], e[1])
-        loose = dtype == torch.bfloat16 and key.endswith(LOOSE)
-        if not (e[0] < (1.0 if loose else gtol_max) and e[1] < (1.0 if loose else gtol)):
+        bar_max, bar_l2 = gtol_max, gtol
+        for suffix, (b32, b16) in LOOSE.items():
+            if key.endswith(suffix):
+                b = b32 if dtype == torch.float32 else b16
+                bar_max = bar_l2 = float("inf") if b is None else max(bar_l2, b)
+        if not (e[0] < bar_max and e[1] < bar_l2):
             bad[key] = e
     report(tag, "worst_grad", worst[1:])
     assert n_checked >= 200 and not bad, bad

@@ -72,10 +72,18 @@ def check_workspace_bounded(exact=True):
     b[0]._body(wave, ln)
     la, lb = a[0].loss_terms(), b[0].loss_terms()
     assert la == lb if exact else abs(la["loss"] - lb["loss"]) < 1e-6 * abs(lb["loss"])
-    for p, q in zip(a[2].parameters(), b[2].parameters()):
-        if p.grad is not None:
-            # GPU: weight gradients are accumulated with atomics, whose order is not fixed
-            assert torch.equal(p.grad, q.grad) if exact else rel_err(p.grad, q.grad, 1e-6) < 1e-4
+    names = [n for n, _ in a[2].named_parameters()]
+    gmax = max(float(q.grad.abs().max()) for q in b[2].parameters() if q.grad is not None)
+    for n, p, q in zip(names, a[2].parameters(), b[2].parameters()):
+        if p.grad is None:
+            continue
+        if exact:
+            assert torch.equal(p.grad, q.grad), n
+        else:
+            # GPU: weight gradients are accumulated with atomics, whose order is not fixed — compare against the
+            # largest gradient entry of the model (some gradients, e.g. k_proj.bias, are analytically zero)
+            err = float((p.grad - q.grad).abs().max()) / gmax
+            assert err < 1e-5, (n, err)
 
 
 def test_resume_is_bit_exact(emulated):
