@@ -62,6 +62,13 @@ class GemmDesc(ctypes.Structure):
         ("vec_sb0", ctypes.c_int64),
         ("scalar_sb0", ctypes.c_int64),
         ("cta_group", ctypes.c_int),
+        ("act_bwd", ctypes.c_int),
+        ("z", ctypes.c_void_p),
+        ("ldz", ctypes.c_int64),
+        ("z_sb0", ctypes.c_int64),
+        ("z_sb1", ctypes.c_int64),
+        ("dbias", ctypes.c_void_p),
+        ("dmask", ctypes.c_void_p),
     ]
 
 

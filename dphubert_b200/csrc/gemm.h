@@ -32,6 +32,11 @@ struct GemmParams {
   float drop_p;
   unsigned long long seed;
   long long vec_sb0, scalar_sb0;
+  // fused activation backward (EPI_BWD): saved pre-activation tile + column-sum outputs
+  const void* Z;
+  long long ldz, z_sb0, z_sb1;
+  float* dbias;
+  float* dmask;
 };
 
 int gemm_bf16_launch(const dph_gemm_desc_t* d, cudaStream_t stream);

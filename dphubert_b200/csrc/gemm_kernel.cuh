@@ -43,12 +43,14 @@ enum EpiFeature : int {
   F_C2 = 64,       // second output: pre-activation copy
   F_ACCUM = 128,   // c_mode 1 (atomic) / 2 (read-add-store)
   F_ALPHA = 256,   // * alpha
+  F_ACTBWD = 512,  // fused BACKWARD of an activation epilogue (see epilogue_chunk_bwd)
 };
 constexpr int EPI_LIN = F_BIAS | F_COLMASK | F_SMASK | F_RES;
 constexpr int EPI_ACT = F_BIAS | F_GELU | F_COLMASK | F_C2 | F_RES;
 constexpr int EPI_DROP = F_BIAS | F_COLMASK | F_SMASK | F_DROP | F_RES;
 constexpr int EPI_ACC = F_ALPHA | F_ACCUM;
 constexpr int EPI_ALL = 511;
+constexpr int EPI_BWD = F_ACTBWD | F_COLMASK | F_DROP;
 
 template <int BN, int CG>
 struct GemmCfg {
@@ -320,6 +322,101 @@ DPH_DEVICE void epilogue_chunk(const GemmParams& p, const TileCoord& tc, int row
   }
 }
 
+// Column sums over the 32 lanes of a warp of 32 per-lane values: a reduce-scatter butterfly (16 + 8 + 4 + 2 + 1
+// exchanges instead of 32 full reductions).  Returns, in lane l, the sum over all lanes of v[l].  Destroys v.
+DPH_DEVICE float warp_colsum32(float (&v)[32], int lane) {
+#pragma unroll
+  for (int w = 16; w >= 1; w >>= 1) {
+    const bool hi = (lane & w) != 0;
+#pragma unroll
+    for (int j = 0; j < w; ++j) {
+      const float send = hi ? v[j] : v[j + w];
+      const float keep = hi ? v[j + w] : v[j];
+      v[j] = keep + __shfl_xor_sync(0xffffffffu, send, w);
+    }
+  }
+  return v[0];
+}
+
+// Fused backward of the activation epilogue  o = dropout(colmask[n] * act(z[m, n]))  (FFN hidden, conv blocks:
+// components.py:110-114, 733-737): the accumulator of this GEMM is d loss / d o (it is a dgrad product), and instead
+// of writing it out for a separate elementwise pass the epilogue
+//   * reads the saved pre-activation tile z (bf16, its own strides),
+//   * writes  c = acc * dropout * colmask[n] * act'(z)   (the gradient wrt the pre-activation), and
+//   * adds the column sums  dbias[n] += sum_m c,  dmask[n] += sum_m acc * dropout * act(z)  with one coalesced RED per
+//     warp, chunk and quantity (the 32 lanes of a warp hold 32 rows: reduce-scatter, then lane l owns column l).
+// Warp-collective: every lane calls it; rows beyond M contribute zeros and store nothing.  Fast path only (32 valid
+// columns, 32-byte aligned rows) — the host refuses other shapes.
+template <int F>
+DPH_DEVICE void epilogue_chunk_bwd(const GemmParams& p, const TileCoord& tc, int row, bool row_ok, int col0,
+                                   uint32_t (&r)[32]) {
+  const int lane = threadIdx.x & 31;
+  float v[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] = row_ok ? __uint_as_float(r[j]) : 0.f;
+  uint32_t zr[2][8];
+  if (row_ok) {
+    const long long zoff = (long long)tc.b0 * p.z_sb0 + (long long)tc.b1 * p.z_sb1 + (long long)row * p.ldz + col0;
+    const bf16* zp = reinterpret_cast<const bf16*>(p.Z) + zoff;
+    ldg_nc_256(zp, zr[0]);
+    ldg_nc_256(zp + 16, zr[1]);
+  } else {
+#pragma unroll
+    for (int q = 0; q < 8; ++q) zr[0][q] = zr[1][q] = 0u;
+  }
+  if constexpr ((F & F_DROP) != 0) {
+    if (p.drop_p > 0.0f) {
+      const uint32_t thresh = (uint32_t)(p.drop_p * 4294967296.0);
+      const float inv_keep = 1.0f / (1.0f - p.drop_p);
+      const unsigned long long base =
+          (((unsigned long long)tc.b1 * p.nb0 + tc.b0) * (unsigned long long)p.M + row) * (unsigned long long)p.N +
+          col0;
+      dropout_apply_vec<32>(p.seed, base, thresh, inv_keep, v);
+    }
+  }
+  float dm[32];  // acc * dropout * act(z): the column-mask gradient's summand
+#pragma unroll
+  for (int j = 0; j < 32; j += 2) {
+    const float2 zz = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&zr[j >> 4][(j & 15) >> 1]));
+    float g0 = zz.x, g1 = zz.y, d0 = 1.f, d1 = 1.f;
+    if (p.act == 1) {
+      f32x2 g2, dg2;
+      gelu_and_grad_tanh2(pk2(zz.x, zz.y), g2, dg2);
+      upk2(g2, g0, g1);
+      upk2(dg2, d0, d1);
+    }
+    dm[j] = v[j] * g0;
+    dm[j + 1] = v[j + 1] * g1;
+    v[j] *= d0;
+    v[j + 1] *= d1;
+  }
+  if constexpr ((F & F_COLMASK) != 0) {
+    if (p.colmask != nullptr) {
+      const float4* mp = reinterpret_cast<const float4*>(p.colmask + tc.b0 * p.vec_sb0 + col0);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float4 m = __ldg(mp + j);
+        v[4 * j] *= m.x;
+        v[4 * j + 1] *= m.y;
+        v[4 * j + 2] *= m.z;
+        v[4 * j + 3] *= m.w;
+      }
+    }
+  }
+  if (row_ok) {
+    const long long coff = (long long)tc.b0 * p.c_sb0 + (long long)tc.b1 * p.c_sb1 + (long long)row * p.ldc + col0;
+    store_bf16x32(reinterpret_cast<bf16*>(p.C) + coff, v);
+  }
+  if (p.dbias != nullptr) {
+    const float sum = warp_colsum32(v, lane);
+    atomicAdd(p.dbias + tc.b0 * p.vec_sb0 + col0 + lane, sum);
+  }
+  if (p.dmask != nullptr) {
+    const float sum = warp_colsum32(dm, lane);
+    atomicAdd(p.dmask + tc.b0 * p.vec_sb0 + col0 + lane, sum);
+  }
+}
+
 template <int BN, bool A_MN, bool B_MN, int CG, int F>
 __global__ void __launch_bounds__(gemm_threads(BN), 1)
     gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -529,7 +626,11 @@ __global__ void __launch_bounds__(gemm_threads(BN), 1)
           tmem_ld_32x32(taddr + c * 32, r);
           tmem_ld_wait();
           release_acc();
-          if (row_ok) epilogue_chunk<F>(p, tc, row, col0, r);
+          if constexpr ((F & F_ACTBWD) != 0) {
+            epilogue_chunk_bwd<F>(p, tc, row, row_ok, col0, r);   // warp-collective (column sums)
+          } else {
+            if (row_ok) epilogue_chunk<F>(p, tc, row, col0, r);
+          }
         } else {
           // kept in its own branch: the accumulator registers of the fast path must not be live across this call
           epilogue_chunk_generic(p, tc.b0, tc.b1, row, row_ok, col0, taddr + c * 32);
@@ -647,6 +748,8 @@ int gemm_launch_drop(int bn, int cg, const CUtensorMap& ta, const CUtensorMap& t
 int gemm_launch_acc(int bn, int cg, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid,
                     bool a_mn, bool b_mn, cudaStream_t s);
 int gemm_launch_all(int bn, int cg, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid,
+                    bool a_mn, bool b_mn, cudaStream_t s);
+int gemm_launch_bwd(int bn, int cg, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid,
                     bool a_mn, bool b_mn, cudaStream_t s);
 
 }  // namespace dph

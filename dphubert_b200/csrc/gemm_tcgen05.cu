@@ -282,6 +282,23 @@ int gemm_bf16_launch(const dph_gemm_desc_t* d, cudaStream_t stream) {
   if (d->bias) vec = vec && ((reinterpret_cast<uintptr_t>(d->bias) & 15) == 0) && (d->vec_sb0 % 4 == 0);
   if (d->colmask) vec = vec && ((reinterpret_cast<uintptr_t>(d->colmask) & 15) == 0) && (d->vec_sb0 % 4 == 0);
   p.vec_ok = vec ? 1 : 0;
+  p.Z = d->z;
+  p.ldz = d->ldz;
+  p.z_sb0 = d->z_sb0;
+  p.z_sb1 = d->z_sb1;
+  p.dbias = d->dbias;
+  p.dmask = d->dmask;
+  if (d->act_bwd) {
+    // fused activation backward: fast epilogue path only, nothing else may be fused into the same launch
+    const bool z_ok = d->z != nullptr && (d->ldz % 16 == 0) && (d->z_sb0 % 16 == 0) && (d->z_sb1 % 16 == 0) &&
+                      ((reinterpret_cast<uintptr_t>(d->z) & 31) == 0);
+    if (d->c_dtype != DPH_DTYPE_BF16 || !vec || !z_ok || d->N % 32 != 0 || d->c_mode != 0 || ksplit != 1 || d->bias ||
+        d->residual || d->c2 || d->scalar_mask || d->alpha != 1.0f || (d->act != 0 && d->act != 1)) {
+      set_error("gemm: act_bwd needs a bf16 output, N %% 32 == 0 (N=%d), 32-byte aligned c / z rows, a pre-activation "
+                "tensor, and no bias / residual / c2 / scalar mask / alpha / accumulation in the same launch", d->N);
+      return DPH_ERR_UNSUPPORTED;
+    }
+  }
 
   CUtensorMap ta, tb;
   int rc = make_tmap(&ta, d->a, BM);
@@ -304,6 +321,7 @@ int gemm_bf16_launch(const dph_gemm_desc_t* d, cudaStream_t stream) {
   if (p.c_mode != 0) need |= F_ACCUM;
   if (d->alpha != 1.0f) need |= F_ALPHA;
   const bool kk = !a_mn && !b_mn;
+  if (d->act_bwd) return gemm_launch_bwd(bn, cg, ta, tb, p, grid, a_mn, b_mn, stream);
   if ((need & ~EPI_LIN) == 0) return gemm_launch_lin(bn, cg, ta, tb, p, grid, a_mn, b_mn, stream);
   if ((need & ~EPI_ACC) == 0) return gemm_launch_acc(bn, cg, ta, tb, p, grid, a_mn, b_mn, stream);
   if (kk && (need & ~EPI_ACT) == 0) return gemm_launch_act(bn, cg, ta, tb, p, grid, a_mn, b_mn, stream);

@@ -758,6 +758,7 @@ def conv_stack_bwd(plan: Plan, st, dfeat, dmasks, A):
     B = st["B"]
     wave = st["wave"]
     dy = dfeat
+    pre_dzp = None   # set by layer i + 1 when its dgrad GEMMs already produced this layer's dz (fused epilogue backward)
     for rec in reversed(st["layers"]):
         blk, i = rec["blk"], rec["i"]
         conv = blk.conv
@@ -800,8 +801,10 @@ def conv_stack_bwd(plan: Plan, st, dfeat, dmasks, A):
             Jmax = (k + s - 1) // s
             padr = Jmax + 1
             rows_pb = Tout + 2 * padr
-            dzp = A("conv%d_dzp" % i, (B, rows_pb, Cout), dt, zero=True)
-            if rec["mode"] == "ln":
+            dzp = A("conv%d_dzp" % i, (B, rows_pb, Cout), dt, zero=True) if pre_dzp is None else pre_dzp
+            if pre_dzp is not None:
+                pre_dzp = None   # dz, the mask gradient and the bias gradient of this layer are already in place
+            elif rec["mode"] == "ln":
                 ops.layernorm_bwd(dy, rec["z"], plan.view(ln.weight), plan.view(ln.bias), rec["mean"], rec["rstd"], dzp,
                                   plan.gview(ln.weight), plan.gview(ln.bias), B * Tout, Cout, colmask=colmask,
                                   dmask=dm_out, act=1, rows_per_batch=Tout, out_bs=rows_pb * Cout, out_row_off=padr,
@@ -824,7 +827,24 @@ def conv_stack_bwd(plan: Plan, st, dfeat, dmasks, A):
                 ops.conv_wgrad_unpermute(wg, plan.gview(conv.weight), Cout, Cin, k)
             # ---- input gradient, one GEMM per output phase (u = s t' + phase)
             _, phases = _conv_weight_views(plan, blk, i, dt)
-            dx = A("conv%d_dx" % i, (B, Tin, Cin), dt)
+            # the layer below, when it is a plain conv -> GELU -> mask block: its epilogue backward rides in this
+            # layer's dgrad GEMMs, which then write d z of the layer below straight into ITS padded row layout
+            below = st["layers"][i - 1] if i >= 2 else None
+            fuse = None
+            if below is not None and FUSED_ACT_BWD and below["mode"] == "none" and below["z"] is not None and k >= s:
+                kb_, sb_ = below["blk"].kernel_size, below["blk"].stride
+                padr_b = (kb_ + sb_ - 1) // sb_ + 1
+                rows_pb_b = Tin + 2 * padr_b
+                dzp_b = A("conv%d_dzp" % (i - 1), (B, rows_pb_b, Cin), dt, zero=True)
+                if G.act_bwd_ok(dzp_b, below["z"], Cin, s * Cin, s * Cin, (rows_pb_b * Cin, Tin * Cin),
+                                [(padr_b + ph) * Cin for ph in range(s)] + [ph * Cin for ph in range(s)]):
+                    bconv = below["blk"].conv
+                    fuse = dict(dzp=dzp_b, padr=padr_b, rows_pb=rows_pb_b, z=below["z"], colmask=below["colmask"],
+                                dmask=(dmasks[plan.offsets[id(below["blk"].hard_concrete.log_alpha)] - plan.la_off:][:Cin]
+                                       if below["has_mask"] else None),
+                                dbias=(plan.gview(bconv.bias) if (bconv.bias is not None and bconv.bias.requires_grad)
+                                       else None))
+            dx = A("conv%d_dx" % i, (B, Tin, Cin), dt) if fuse is None else None
             covered = set()
             for ph, J, wv in phases:
                 rows = (Tin - ph + s - 1) // s
@@ -832,10 +852,17 @@ def conv_stack_bwd(plan: Plan, st, dfeat, dmasks, A):
                     continue
                 a = View(dzp, rows, J * Cout, Cout, kin=Cout, kxs=Cout, sb0=rows_pb * Cout,
                          offset=(padr - (J - 1)) * Cout)
-                G.gemm(a, wv, dx, rows, Cin, J * Cout, nb0=B, ldc=s * Cin, c_sb0=Tin * Cin, c_offset=ph * Cin)
+                if fuse is None:
+                    G.gemm(a, wv, dx, rows, Cin, J * Cout, nb0=B, ldc=s * Cin, c_sb0=Tin * Cin, c_offset=ph * Cin)
+                else:
+                    G.gemm(a, wv, fuse["dzp"], rows, Cin, J * Cout, nb0=B, ldc=s * Cin, c_sb0=fuse["rows_pb"] * Cin,
+                           c_offset=(fuse["padr"] + ph) * Cin, act=1, colmask=fuse["colmask"], act_bwd=True, z=fuse["z"],
+                           ldz=s * Cin, z_sb0=Tin * Cin, z_offset=ph * Cin, dbias=fuse["dbias"], dmask=fuse["dmask"])
                 covered.add(ph)
+            if fuse is not None:
+                pre_dzp = fuse["dzp"]
             for ph in range(s):
-                if ph not in covered:  # stride > kernel: some input rows get no gradient
+                if ph not in covered and dx is not None:  # stride > kernel: some input rows get no gradient
                     rows = (Tin - ph + s - 1) // s
                     for b in range(B):
                         ops.memset2d(dx, (b * Tin + ph) * Cin, s * Cin, Cin, rows)
@@ -856,6 +883,9 @@ def _a8(n):
 # bf16 / head_dim 64: attention runs as the fused tcgen05 kernel (scores never reach HBM); set False to force the
 # unfused GEMM + softmax path (used by tests to cross-check the two)
 FUSED_ATTENTION = True
+# bf16: the backward of GELU / column-mask / dropout epilogues runs inside the dgrad GEMM that produces its input
+# (csrc/gemm_kernel.cuh: epilogue_chunk_bwd); False restores the separate elementwise pass (tests cross-check the two)
+FUSED_ACT_BWD = True
 
 
 def _mask_of(masks, hc):
@@ -1194,13 +1224,21 @@ def _ffn_bwd(plan, rec, dout, dresid, dmasks, A, tag):
     F = rec["F"]
     g = _out_proj_bwd(plan, dout, rec["pre"], rec["lmask"], ff.hard_concrete_for_layer, ff.output_dense.bias,
                       rec["p_o"], rec["seed_o"], dmasks, A, tag + "ffo_", M, D)
-    dh = A(tag + "ff_dh", (M, F), dt)
-    G.gemm(G.mat(g), G.mat_t(plan.W(ff.output_dense.weight, dt)), dh, M, F, D)
-    _wgrad(plan, g, rec["h"], ff.output_dense.weight, D, F, M)
     dz = A(tag + "ff_dz", (M, F), dt)
-    ops.epilogue_bwd(dh, M, F, z=rec["zpre"], colmask=rec["imask"], dout=dz,
-                     dmask=_gslot(plan, dmasks, ff.hard_concrete_for_intermediate) if rec["imask"] is not None else None,
-                     dbias=_gb(plan, ff.intermediate_dense.bias), act=1, drop_p=rec["p_i"], seed=rec["seed_i"])
+    dm_i = _gslot(plan, dmasks, ff.hard_concrete_for_intermediate) if rec["imask"] is not None else None
+    if FUSED_ACT_BWD and G.act_bwd_ok(dz, rec["zpre"], F, F, F):
+        # d hidden = g W2 and the backward of  h = dropout(mask * GELU(z))  in ONE launch: the dgrad GEMM's epilogue
+        # applies GELU'(z) * mask * dropout and reduces the bias / mask gradients (no (M, F) round trip through HBM)
+        G.gemm(G.mat(g), G.mat_t(plan.W(ff.output_dense.weight, dt)), dz, M, F, D, act=1, colmask=rec["imask"],
+               drop_p=rec["p_i"], seed=rec["seed_i"], act_bwd=True, z=rec["zpre"], dmask=dm_i,
+               dbias=_gb(plan, ff.intermediate_dense.bias))
+        _wgrad(plan, g, rec["h"], ff.output_dense.weight, D, F, M)
+    else:
+        dh = A(tag + "ff_dh", (M, F), dt)
+        G.gemm(G.mat(g), G.mat_t(plan.W(ff.output_dense.weight, dt)), dh, M, F, D)
+        _wgrad(plan, g, rec["h"], ff.output_dense.weight, D, F, M)
+        ops.epilogue_bwd(dh, M, F, z=rec["zpre"], colmask=rec["imask"], dout=dz, dmask=dm_i,
+                         dbias=_gb(plan, ff.intermediate_dense.bias), act=1, drop_p=rec["p_i"], seed=rec["seed_i"])
     dx = A(tag + "ff_dx", (M, D), dt)
     G.gemm(G.mat(dz), G.mat_t(plan.W(ff.intermediate_dense.weight, dt)), dx, M, D, F, residual=dresid)
     _wgrad(plan, dz, rec["xin"], ff.intermediate_dense.weight, F, D, M)

@@ -89,9 +89,11 @@ def _operand_f32(v):
 def gemm(a, b, c, M, N, K, *, ldc=None, nb0=1, nb1=1, c_sb0=0, c_sb1=0, c_offset=0, alpha=1.0, bias=None, act=0,
          colmask=None, scalar_mask=None, residual=None, ldr=None, r_sb0=0, r_sb1=0, r_offset=0, c2=None,
          accumulate=False, atomic=False, ksplit=1, drop_p=0.0, seed=0, block_n=0, vec_sb0=0, scalar_sb0=0,
-         cta_group=0):
+         cta_group=0, act_bwd=False, z=None, ldz=None, z_sb0=0, z_sb1=0, z_offset=0, dbias=None, dmask=None):
     """C[b][m, n] = epilogue(alpha * sum_k a(m,k) b(n,k)).  `a`, `b` are `View`s; dtype of `a.t` selects the path:
-    bf16 -> tcgen05 tensor-core kernel, fp32 -> CUDA-core kernel."""
+    bf16 -> tcgen05 tensor-core kernel, fp32 -> CUDA-core kernel.
+    `act_bwd` (bf16 only, see `act_bwd_ok`): the product is the gradient wrt dropout(colmask * act(z)); the epilogue
+    writes acc * dropout * colmask * act'(z) and accumulates `dbias` / `dmask` column sums."""
     L = _lib.lib()
     if ldc is None:
         ldc = N
@@ -120,11 +122,19 @@ def gemm(a, b, c, M, N, K, *, ldc=None, nb0=1, nb1=1, c_sb0=0, c_sb1=0, c_offset
         d.ldr, d.r_sb0, d.r_sb1 = ldr, r_sb0, r_sb1
         d.drop_p, d.seed = drop_p, seed
         d.vec_sb0, d.scalar_sb0 = vec_sb0, scalar_sb0
+        if act_bwd:
+            d.act_bwd = 1
+            d.z = z.data_ptr() + z_offset * z.element_size()
+            d.ldz, d.z_sb0, d.z_sb1 = (ldc if ldz is None else ldz), z_sb0, z_sb1
+            d.dbias = None if dbias is None else dbias.data_ptr()
+            d.dmask = None if dmask is None else dmask.data_ptr()
         if TRACE is not None:
             TRACE.append((d, 2.0 * M * N * K * nb0 * nb1))
         _lib.check(L.dph_gemm_bf16(ctypes.byref(d), _lib.stream_ptr()), "dph_gemm_bf16")
     else:
         assert a.t.dtype == torch.float32 and b.t.dtype == torch.float32 and c.dtype == torch.float32
+        if act_bwd:
+            raise _lib.DphError("the fused activation backward exists on the bf16 tensor-core path only")
         d = GemmF32Desc()
         d.a = _operand_f32(a)
         d.b = _operand_f32(b)
@@ -144,6 +154,15 @@ def gemm(a, b, c, M, N, K, *, ldc=None, nb0=1, nb1=1, c_sb0=0, c_sb1=0, c_offset
         d.vec_sb0, d.scalar_sb0 = vec_sb0, scalar_sb0
         _lib.check(L.dph_gemm_f32(ctypes.byref(d), _lib.stream_ptr()), "dph_gemm_f32")
     return c
+
+
+def act_bwd_ok(c, z, N, ldc, ldz, strides=(), offsets=()):
+    """Can `gemm(..., act_bwd=True)` take this launch? bf16 in / out, whole 32-column chunks, 32-byte aligned rows."""
+    if c.dtype != torch.bfloat16 or z is None or z.dtype != torch.bfloat16 or N % 32:
+        return False
+    if ldc % 16 or ldz % 16 or any(int(s_) % 16 for s_ in strides) or any(int(o) % 16 for o in offsets):
+        return False
+    return c.data_ptr() % 32 == 0 and z.data_ptr() % 32 == 0
 
 
 def replay(trace):

@@ -80,6 +80,18 @@ typedef struct {
   int64_t vec_sb0;          /* element offset added to bias / colmask per batch index b0 (grouped conv, heads) */
   int64_t scalar_sb0;       /* element offset added to scalar_mask per batch index b0 (per-head HardConcrete mask) */
   int cta_group;            /* 0 = auto; 1 = one CTA per 128-row tile; 2 = CTA pair (tcgen05 cta_group::2) per 256-row tile */
+  /* Fused BACKWARD of an activation epilogue (act_bwd != 0; bf16 output, N % 32 == 0, 32-byte aligned rows): the product
+   * is d loss / d o for a forward epilogue o = dropout(colmask[n] * act(z)); the kernel reads the saved pre-activation
+   * z[m, n] (same dtype as c, own strides), writes c = acc * dropout * colmask[n] * act'(z) and adds the column sums
+   * dbias[n] += sum_m c and dmask[n] += sum_m acc * dropout * act(z) (fp32, either may be NULL; indexed like colmask,
+   * i.e. + b0 * vec_sb0).  `act`, `colmask`, `drop_p`, `seed` describe the FORWARD epilogue being differentiated.
+   * Replaces autograd through components.py:110-114 (conv blocks) and :733-737 (FFN hidden) without a separate
+   * elementwise pass over the (rows, N) gradient. */
+  int act_bwd;
+  const void* z;
+  int64_t ldz, z_sb0, z_sb1;
+  float* dbias;
+  float* dmask;
 } dph_gemm_desc_t;
 
 int dph_gemm_bf16(const dph_gemm_desc_t* desc, void* stream);

@@ -56,7 +56,7 @@ def _gather(v, nb0, nb1):
 def gemm(a, b, c, M, N, K, *, ldc=None, nb0=1, nb1=1, c_sb0=0, c_sb1=0, c_offset=0, alpha=1.0, bias=None, act=0,
          colmask=None, scalar_mask=None, residual=None, ldr=None, r_sb0=0, r_sb1=0, r_offset=0, c2=None,
          accumulate=False, atomic=False, ksplit=1, drop_p=0.0, seed=0, block_n=0, vec_sb0=0, scalar_sb0=0,
-         cta_group=0):
+         cta_group=0, act_bwd=False, z=None, ldz=None, z_sb0=0, z_sb1=0, z_offset=0, dbias=None, dmask=None):
     assert drop_p == 0.0, "the emulator runs the dropout-free parity configuration"
     ldc = N if ldc is None else ldc
     ldr = ldc if ldr is None else ldr
@@ -80,6 +80,29 @@ def gemm(a, b, c, M, N, K, *, ldc=None, nb0=1, nb1=1, c_sb0=0, c_sb1=0, c_offset
     if bias is not None:
         v = v + _flat(bias)[b0 * vec_sb0 + n]
     cidx = (c_offset + b0 * c_sb0 + b1 * c_sb1 + m * ldc + n).expand(nb1, nb0, M, N)
+    if act_bwd:
+        # fused backward of o = colmask * act(z): c = acc * colmask * act'(z); dbias += colsum(c); dmask += colsum(acc * act(z))
+        assert a.t.dtype == torch.bfloat16 and c.dtype == torch.bfloat16 and z.dtype == torch.bfloat16
+        assert G.act_bwd_ok(c, z, N, ldc, ldc if ldz is None else ldz, (c_sb0, c_sb1, z_sb0, z_sb1), (c_offset, z_offset))
+        assert bias is None and residual is None and c2 is None and scalar_mask is None and alpha == 1.0
+        assert not (atomic or accumulate)
+        ldz = ldc if ldz is None else ldz
+        fz = _flat(z)
+        zidx = (z_offset + b0 * z_sb0 + b1 * z_sb1 + m * ldz + n).expand(nb1, nb0, M, N)
+        assert zidx.min() >= 0 and zidx.max() < fz.numel(), "pre-activation view reaches outside its buffer"
+        zz = fz[zidx].float()
+        gz, dgz = (_gelu(zz), _gelu_grad(zz)) if act == 1 else (zz, torch.ones_like(zz))
+        cm = _flat(colmask)[b0 * vec_sb0 + n] if colmask is not None else 1.0
+        vidx = (b0 * vec_sb0 + n).expand(nb1, nb0, M, N).reshape(-1)
+        out = v * cm * dgz
+        if dbias is not None:
+            _flat(dbias).index_add_(0, vidx, out.reshape(-1))
+        if dmask is not None:
+            _flat(dmask).index_add_(0, vidx, (v * gz).reshape(-1))
+        fc = _flat(c)
+        assert cidx.min() >= 0 and cidx.max() < fc.numel(), "GEMM output view reaches outside its buffer"
+        fc[cidx.reshape(-1)] = out.reshape(-1).to(c.dtype)
+        return c
     if c2 is not None:
         f2 = _flat(c2)
         assert cidx.max() < f2.numel()

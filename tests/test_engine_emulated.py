@@ -138,3 +138,30 @@ def check_aux_and_layerdrop(dev, dtype, tol):
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 4e-2)])
 def test_aux_head_and_layerdrop(emulated, dtype, tol):
     check_aux_and_layerdrop(CPU, dtype, tol)
+
+
+def check_fused_act_bwd_equals_separate_pass(dev, names=("step_base", "step_large", "step_base_allunits_predlayer")):
+    """bf16: the epilogue backward fused into the dgrad GEMMs (FFN hidden, conv blocks) gives the gradients of the
+    separate elementwise pass, up to the bf16 rounding of the intermediate the fused path no longer materialises."""
+    from dphubert_b200 import engine
+
+    for name in names:
+        g = load_golden(name)
+        grads = {}
+        for fused in (True, False):
+            engine.FUSED_ACT_BWD = fused
+            try:
+                step, teacher, student, projs, lam = build_step(g, dev, torch.bfloat16)
+                run_body(step, g, dev)
+            finally:
+                engine.FUSED_ACT_BWD = True
+            grads[fused] = {n: p.grad.detach().float().cpu().clone() for n, p in student.named_parameters()
+                            if p.grad is not None}
+        gmax = max(float(v.abs().max()) for v in grads[False].values())
+        for n, ref in grads[False].items():
+            err = float((grads[True][n] - ref).abs().max()) / max(float(ref.abs().max()), 1e-3 * gmax)
+            assert err < 3e-2, (name, n, err)
+
+
+def test_fused_act_bwd_equals_separate_pass(emulated):
+    check_fused_act_bwd_equals_separate_pass(CPU)

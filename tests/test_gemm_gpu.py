@@ -85,3 +85,55 @@ def test_strided_conv_view(cg):
     y = zer(B, To, C, dtype=BF16)
     both("gemm", (av, G.mat(w), y, To, C, k * C), dict(nb0=B, c_sb0=To * C, act=1, cta_group=cg), fn=G.gemm,
          ref=emu.gemm, tol=2e-2)
+
+
+@pytest.mark.parametrize("cg", [1, 2])
+@pytest.mark.parametrize("b_mn", [0, 1])
+@pytest.mark.parametrize("M,N,K", [(3992, 3072, 768), (500, 320, 192)])
+def test_fused_activation_backward(cg, b_mn, M, N, K):
+    """dgrad GEMM whose epilogue differentiates  o = colmask * GELU(z)  (EPI_BWD): dz, bias and mask column sums against
+    the restatement; ragged M (rows beyond M contribute nothing to the column sums)."""
+    a, b = _views(M, N, K, 0, b_mn)
+    z = rnd(M, N, dtype=BF16)
+    colmask = torch.rand(N, device=DEV) * 0.8 + 0.2
+    c = zer(M, N, dtype=BF16)
+    dbias, dmask = rnd(N), rnd(N)   # accumulated into
+    both("gemm", (a, b, c, M, N, K), dict(act=1, colmask=colmask, act_bwd=True, z=z, dbias=dbias, dmask=dmask,
+                                          cta_group=cg), fn=G.gemm, ref=emu.gemm, tol=2e-2)
+
+
+def test_fused_activation_backward_strided_batched():
+    """the conv-stack use: per-utterance batches, output rows interleaved by phase into a zero-padded row layout,
+    pre-activation read with its own strides"""
+    B, rows, C, K, s, ph, padr, Tin = 3, 130, 128, 256, 2, 1, 3, 261
+    rows_pb = Tin + 2 * padr
+    a = rnd(B, rows, K, dtype=BF16)
+    w = rnd(C, K, dtype=BF16, scale=0.05)
+    z = rnd(B, Tin, C, dtype=BF16)
+    out = zer(B, rows_pb, C, dtype=BF16)
+    colmask = torch.rand(C, device=DEV)
+    dbias, dmask = zer(C), zer(C)
+    av = G.View(a, rows, K, K, sb0=rows * K)
+    both("gemm", (av, G.mat(w), out, rows, C, K),
+         dict(nb0=B, ldc=s * C, c_sb0=rows_pb * C, c_offset=(padr + ph) * C, act=1, colmask=colmask, act_bwd=True, z=z,
+              ldz=s * C, z_sb0=Tin * C, z_offset=ph * C, dbias=dbias, dmask=dmask), fn=G.gemm, ref=emu.gemm, tol=2e-2)
+
+
+def test_fused_activation_backward_dropout_mask_matches_forward():
+    """with dropout: the backward epilogue regenerates the forward GEMM's keep mask (same seed, same element index)"""
+    M, F, D, p, seed = 1000, 3072, 768, 0.1, 777
+    x, w1, bias = rnd(M, D, dtype=BF16), rnd(F, D, dtype=BF16, scale=0.05), rnd(F)
+    h0, h1, z = zer(M, F, dtype=BF16), zer(M, F, dtype=BF16), zer(M, F, dtype=BF16)
+    G.gemm(G.mat(x), G.mat(w1), h0, M, F, D, bias=bias, act=1, c2=z)
+    G.gemm(G.mat(x), G.mat(w1), h1, M, F, D, bias=bias, act=1, drop_p=p, seed=seed, c2=z)
+    g, w2 = rnd(M, D, dtype=BF16), rnd(D, F, dtype=BF16, scale=0.05)
+    dz0, dz1 = zer(M, F, dtype=BF16), zer(M, F, dtype=BF16)
+    G.gemm(G.mat(g), G.mat_t(w2), dz0, M, F, D, act=1, act_bwd=True, z=z)
+    G.gemm(G.mat(g), G.mat_t(w2), dz1, M, F, D, act=1, drop_p=p, seed=seed, act_bwd=True, z=z)
+    torch.cuda.synchronize()
+    big = (h0.float().abs() > 0.05 * h0.float().abs().mean()) & (dz0.float().abs() > 0.05 * dz0.float().abs().mean())
+    fwd_keep = h1.float().abs() > 0
+    bwd_keep = dz1.float().abs() > 0
+    assert torch.equal(fwd_keep[big], bwd_keep[big])
+    ratio = (dz1.float() / dz0.float())[big & bwd_keep]
+    assert ((ratio * (1 - p) - 1).abs() < 2e-2).all()

@@ -178,3 +178,10 @@ def test_forward_with_aux_head_and_layerdrop(dtype, tol):
     from test_engine_emulated import check_aux_and_layerdrop
 
     check_aux_and_layerdrop(DEV, dtype, tol)
+
+
+def test_fused_act_bwd_equals_separate_pass():
+    """GELU' * mask * dropout backward inside the dgrad GEMM epilogue vs the separate `epilogue_bwd` pass, on the GPU."""
+    from test_engine_emulated import check_fused_act_bwd_equals_separate_pass
+
+    check_fused_act_bwd_equals_separate_pass(DEV)
