@@ -922,7 +922,7 @@ def _head_index(plan, att):
     return t
 
 
-def _attention_fwd(plan, att, xin, resid, B, T, lengths, masks, A, tag, train, p_drop, wl):
+def _attention_fwd(plan, att, xin, resid, B, T, lengths, masks, A, tag, train, p_drop, wl, save=True):
     """xin: attention input (M, D); resid: residual added after dropout. Returns (resid + dropout(attn)), record."""
     dt = xin.dtype
     D, H, Dh = att.embed_dim, att.num_heads, att.head_dim
@@ -953,7 +953,7 @@ def _attention_fwd(plan, att, xin, resid, B, T, lengths, masks, A, tag, train, p
     hmask = _mask_of(masks, att.hard_concrete_for_heads)
     lmask = _mask_of(masks, att.hard_concrete_for_layer)
     ctx = A(tag + "ctx", (M, inner), dt)
-    ctx_un = A(tag + "ctx_un", (M, inner), dt) if hmask is not None else None
+    ctx_un = A(tag + "ctx_un", (M, inner), dt) if (hmask is not None and save) else None
     fused = FUSED_ATTENTION and dt == torch.bfloat16 and Dh == 64 and T <= 1024
     P = Pd = lse = None
     if fused:
@@ -973,7 +973,7 @@ def _attention_fwd(plan, att, xin, resid, B, T, lengths, masks, A, tag, train, p
         G.gemm(pv, v, ctx, T, Dh, T, nb0=H, nb1=B, ldc=inner, c_sb0=Dh, c_sb1=T * inner, scalar_mask=hmask,
                scalar_sb0=1 if hmask is not None else 0, c2=ctx_un)
     out = A(tag + "attn_out", (M, D), dt)
-    pre = A(tag + "attn_pre", (M, D), dt) if lmask is not None else None
+    pre = A(tag + "attn_pre", (M, D), dt) if (lmask is not None and save) else None
     seed_o = _seed(p_drop)
     G.gemm(G.mat(ctx), G.mat(plan.W(att.out_proj.weight, dt)), out, M, D, inner, bias=plan.view(att.out_proj.bias),
            scalar_mask=lmask, drop_p=p_drop, seed=seed_o, residual=resid, c2=pre)
@@ -982,7 +982,7 @@ def _attention_fwd(plan, att, xin, resid, B, T, lengths, masks, A, tag, train, p
     return out, rec
 
 
-def _ffn_fwd(plan, ff, xin, resid, M, masks, A, tag, train):
+def _ffn_fwd(plan, ff, xin, resid, M, masks, A, tag, train, save=True):
     dt = xin.dtype
     D = ff.intermediate_dense.in_features
     F = ff.intermediate_dense.out_features
@@ -991,11 +991,11 @@ def _ffn_fwd(plan, ff, xin, resid, M, masks, A, tag, train):
     p_i, p_o = _p(ff.intermediate_dropout, train), _p(ff.output_dropout, train)
     seed_i, seed_o = _seed(p_i), _seed(p_o)
     h = A(tag + "ff_h", (M, F), dt)
-    zpre = A(tag + "ff_z", (M, F), dt)
+    zpre = A(tag + "ff_z", (M, F), dt) if save else None   # pre-activation copy: the backward's input only
     G.gemm(G.mat(xin), G.mat(plan.W(ff.intermediate_dense.weight, dt)), h, M, F, D,
            bias=plan.view(ff.intermediate_dense.bias), act=1, colmask=imask, drop_p=p_i, seed=seed_i, c2=zpre)
     out = A(tag + "ff_out", (M, D), dt)
-    pre = A(tag + "ff_pre", (M, D), dt) if lmask is not None else None
+    pre = A(tag + "ff_pre", (M, D), dt) if (lmask is not None and save) else None
     G.gemm(G.mat(h), G.mat(plan.W(ff.output_dense.weight, dt)), out, M, D, F, bias=plan.view(ff.output_dense.bias),
            scalar_mask=lmask, drop_p=p_o, seed=seed_o, residual=resid, c2=pre)
     rec = {"ff": ff, "xin": xin, "h": h, "zpre": zpre, "pre": pre, "imask": imask, "lmask": lmask, "p_i": p_i,
@@ -1023,7 +1023,7 @@ def _posconv_geometry(pc, dt):
     return D, K, Gn, Cg, Cgp
 
 
-def _posconv_fwd(plan, pc, h0, B, T, A, tag):
+def _posconv_fwd(plan, pc, h0, B, T, A, tag, save=True):
     """x + GELU(conv(x)) with the weight-normalised grouped conv as one batched implicit GEMM over a zero-padded,
     group-padded staging copy of x (rows: front + b * (T + pad) + t)."""
     dt = h0.dtype
@@ -1035,7 +1035,7 @@ def _posconv_fwd(plan, pc, h0, B, T, A, tag):
     xp = A(tag + "pos_xp", (rows, Wd), dt, zero=True)
     ops.posconv_pad(h0, xp, B, T, Gn, Cg, Cgp, front, pad)
     _, wp, _, _ = plan.pos_w
-    zpc = A(tag + "pos_z", (B * T, D), dt)
+    zpc = A(tag + "pos_z", (B * T, D), dt) if save else None
     xpre = A(tag + "pos_out", (B * T, D), dt)
     # output frame t reads staging rows (front + b (T+pad) + t) - K/2 + tap
     if ops.posconv_tc_ok(dt, Cg, Cgp, K):
@@ -1048,7 +1048,8 @@ def _posconv_fwd(plan, pc, h0, B, T, A, tag):
     return xpre, {"pc": pc, "xp": xp, "zpc": zpc, "front": front, "pad": pad, "rows": rows}
 
 
-def encoder_fwd(plan: Plan, feat, lengths, masks, A, train, num_layers=None, final_norm=False, layer_keep=None):
+def encoder_fwd(plan: Plan, feat, lengths, masks, A, train, num_layers=None, final_norm=False, layer_keep=None,
+                save=True):
     """feat (B, T, C) compute dtype -> list of hidden states [(B, T, D)] (index 0 = encoder input after padding
     zeroing), plus the record needed by `encoder_bwd`."""
     model = plan.model
@@ -1072,7 +1073,7 @@ def encoder_fwd(plan: Plan, feat, lengths, masks, A, train, num_layers=None, fin
     st["fp"] = {"ln": rec_ln, "xn": xn, "p_in": p_in, "seed_in": seed_in}
     hiddens = [h0]
     # ---- positional conv + (Base) LayerNorm + dropout
-    xpre, rec_pc = _posconv_fwd(plan, tr.pos_conv_embed, h0, B, T, A, "")
+    xpre, rec_pc = _posconv_fwd(plan, tr.pos_conv_embed, h0, B, T, A, "", save)
     st["pc"] = rec_pc
     p_tr = _p(tr.dropout, train)
     if tr.layer_norm_first:
@@ -1108,19 +1109,19 @@ def encoder_fwd(plan: Plan, feat, lengths, masks, A, train, num_layers=None, fin
                 xa, rec["ln1"] = _ln_fwd(plan, layer.layer_norm, x, M, D, A, tag + "ln1_")
             else:
                 xa = x
-            x1, rec["att"] = _attention_fwd(plan, att, xa, x, B, T, lengths, masks, A, tag, train, p_drop, wl_here)
+            x1, rec["att"] = _attention_fwd(plan, att, xa, x, B, T, lengths, masks, A, tag, train, p_drop, wl_here, save)
         else:
             x1 = x
         if layer.layer_norm_first:
             if ff is not None:
                 xf, rec["ln2"] = _ln_fwd(plan, layer.final_layer_norm, x1, M, D, A, tag + "ln2_")
-                x2, rec["ff"] = _ffn_fwd(plan, ff, xf, x1, M, masks, A, tag, train)
+                x2, rec["ff"] = _ffn_fwd(plan, ff, xf, x1, M, masks, A, tag, train, save)
             else:
                 x2 = x1
         else:
             xl, rec["ln1"] = _ln_fwd(plan, layer.layer_norm, x1, M, D, A, tag + "ln1_")
             if ff is not None:
-                xs, rec["ff"] = _ffn_fwd(plan, ff, xl, xl, M, masks, A, tag, train)
+                xs, rec["ff"] = _ffn_fwd(plan, ff, xl, xl, M, masks, A, tag, train, save)
             else:
                 xs = xl
             x2, rec["ln2"] = _ln_fwd(plan, layer.final_layer_norm, xs, M, D, A, tag + "ln2_")
@@ -1486,7 +1487,7 @@ def forward_core(plan: Plan, wave, lengths, masks, A, train, save=True, num_laye
     if flen is not None:
         flen = flen.contiguous()
     hiddens, st_enc = encoder_fwd(plan, feat, flen, masks, A, train, num_layers=num_layers, final_norm=final_norm,
-                                  layer_keep=layer_keep)
+                                  layer_keep=layer_keep, save=save)
     return hiddens, flen, {"conv": st_conv, "enc": st_enc}
 
 

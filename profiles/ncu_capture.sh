@@ -15,12 +15,13 @@ echo "launch list rc=$?"
 if [ $# -eq 0 ]; then
   set -- attn_fwd_kernel attn_bwd_kernel attn_bwd_prep conv0_fwd_tc conv0_bwd_fused posconv_tc_kernel \
          epilogue_bwd_kernel layernorm_fwd layernorm_bwd adamw_kernel distill_loss_fwd distill_loss_bwd sumsq_kernel \
-         "gemm_bf16_kernel<256, 0, 0, 2, 103>" "gemm_bf16_kernel<192, 0, 0, 2, 45>" "gemm_bf16_kernel<256, 1, 1, 2, 384>" \
-         "gemm_bf16_kernel<256, 0, 1, 2, 45>" "gemm_bf16_kernel<64, 1, 1, 1, 45>"
+         "gemm_bf16_kernel<256, false, false, 2, 103>" "gemm_bf16_kernel<192, false, false, 2, 45>" \
+         "gemm_bf16_kernel<256, true, true, 2, 384>" "gemm_bf16_kernel<256, false, true, 2, 45>" \
+         "gemm_bf16_kernel<64, true, true, 1, 45>" "gemm_bf16_kernel<256, false, true, 2, 532>"
 fi
 for k in "$@"; do
   name=$(echo "$k" | tr -c 'A-Za-z0-9_' '_' | sed 's/__*/_/g')
-  ncu --set full --clock-control none --import-source on --profile-from-start off -k "regex:$k" -c 2 -f \
+  ncu --set full --clock-control none --import-source on --profile-from-start off --kernel-name-base demangled -k "regex:$k" -c 2 -f \
       -o $OUT/${TAG}_${name} $CMD > $OUT/${TAG}_${name}.log 2>&1
   echo "$k rc=$?"
   # the reports are ~35 MB each and gpurun_out/ travels back only below 64 MiB: keep the raw metric table and the
