@@ -347,22 +347,37 @@ DPH_DEVICE float warp_colsum32(float (&v)[32], int lane) {
 //     warp, chunk and quantity (the 32 lanes of a warp hold 32 rows: reduce-scatter, then lane l owns column l).
 // Warp-collective: every lane calls it; rows beyond M contribute zeros and store nothing.  Fast path only (32 valid
 // columns, 32-byte aligned rows) — the host refuses other shapes.
-template <int F>
-DPH_DEVICE void epilogue_chunk_bwd(const GemmParams& p, const TileCoord& tc, int row, bool row_ok, int col0,
-                                   uint32_t (&r)[32]) {
-  const int lane = threadIdx.x & 31;
-  float v[32];
-#pragma unroll
-  for (int j = 0; j < 32; ++j) v[j] = row_ok ? __uint_as_float(r[j]) : 0.f;
-  uint32_t zr[2][8];
+// 32 bf16 of the saved pre-activation tile for (row, col0 .. col0 + 31): issued one chunk ahead of their use (and,
+// for the first chunk of a tile, before the wait for the accumulator) so that the global-load latency hides behind
+// the previous chunk's arithmetic / the main loop
+DPH_DEVICE void bwd_fetch_z(const GemmParams& p, const TileCoord& tc, int row, bool row_ok, int col0, uint32_t (&zr)[16]) {
   if (row_ok) {
     const long long zoff = (long long)tc.b0 * p.z_sb0 + (long long)tc.b1 * p.z_sb1 + (long long)row * p.ldz + col0;
     const bf16* zp = reinterpret_cast<const bf16*>(p.Z) + zoff;
-    ldg_nc_256(zp, zr[0]);
-    ldg_nc_256(zp + 16, zr[1]);
+    uint32_t a[8], b[8];
+    ldg_nc_256(zp, a);
+    ldg_nc_256(zp + 16, b);
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      zr[q] = a[q];
+      zr[8 + q] = b[q];
+    }
   } else {
 #pragma unroll
-    for (int q = 0; q < 8; ++q) zr[0][q] = zr[1][q] = 0u;
+    for (int q = 0; q < 16; ++q) zr[q] = 0u;
+  }
+}
+
+template <int F>
+DPH_DEVICE void epilogue_chunk_bwd(const GemmParams& p, const TileCoord& tc, int row, bool row_ok, int col0,
+                                   uint32_t (&r)[32], const uint32_t (&zr)[16]) {
+  const int lane = threadIdx.x & 31;
+  float v[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+  if (__any_sync(0xffffffffu, !row_ok)) {  // warp-uniform: only the last M tile has rows beyond M
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = row_ok ? v[j] : 0.f;
   }
   if constexpr ((F & F_DROP) != 0) {
     if (p.drop_p > 0.0f) {
@@ -377,18 +392,12 @@ DPH_DEVICE void epilogue_chunk_bwd(const GemmParams& p, const TileCoord& tc, int
   float dm[32];  // acc * dropout * act(z): the column-mask gradient's summand
 #pragma unroll
   for (int j = 0; j < 32; j += 2) {
-    const float2 zz = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&zr[j >> 4][(j & 15) >> 1]));
-    float g0 = zz.x, g1 = zz.y, d0 = 1.f, d1 = 1.f;
-    if (p.act == 1) {
-      f32x2 g2, dg2;
-      gelu_and_grad_tanh2(pk2(zz.x, zz.y), g2, dg2);
-      upk2(g2, g0, g1);
-      upk2(dg2, d0, d1);
-    }
-    dm[j] = v[j] * g0;
-    dm[j + 1] = v[j + 1] * g1;
-    v[j] *= d0;
-    v[j + 1] *= d1;
+    const float2 zz = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&zr[j >> 1]));
+    const f32x2 z2 = pk2(zz.x, zz.y), v2 = pk2(v[j], v[j + 1]);
+    f32x2 g2 = z2, dg2 = bc2(1.f);
+    if (p.act == 1) gelu_and_grad_tanh2(z2, g2, dg2);
+    upk2(mul2(v2, g2), dm[j], dm[j + 1]);
+    upk2(mul2(v2, dg2), v[j], v[j + 1]);
   }
   if constexpr ((F & F_COLMASK) != 0) {
     if (p.colmask != nullptr) {
@@ -396,10 +405,8 @@ DPH_DEVICE void epilogue_chunk_bwd(const GemmParams& p, const TileCoord& tc, int
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const float4 m = __ldg(mp + j);
-        v[4 * j] *= m.x;
-        v[4 * j + 1] *= m.y;
-        v[4 * j + 2] *= m.z;
-        v[4 * j + 3] *= m.w;
+        upk2(mul2(pk2(v[4 * j], v[4 * j + 1]), pk2(m.x, m.y)), v[4 * j], v[4 * j + 1]);
+        upk2(mul2(pk2(v[4 * j + 2], v[4 * j + 3]), pk2(m.z, m.w)), v[4 * j + 2], v[4 * j + 3]);
       }
     }
   }
@@ -600,12 +607,14 @@ __global__ void __launch_bounds__(gemm_threads(BN), 1)
       const int n0 = tc.n0 * BN + half * (BN / 2);
       const int kb_begin = tc.ks * p.kb_per_split;
       const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
+      const int row = tc.m0 + rank * BM + q * 32 + lane;
+      const bool row_ok = (row < p.M) && (kb_end > kb_begin);
+      [[maybe_unused]] uint32_t zr[16], zn[16];
+      if constexpr ((F & F_ACTBWD) != 0) bwd_fetch_z(p, tc, row, row_ok, n0, zn);  // does not depend on the MMAs
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
       if (warp == 2 && lane == 0) stamp(tl, 32 + 2 * ti);
-      const int row = tc.m0 + rank * BM + q * 32 + lane;
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + half * (BN / 2));
-      const bool row_ok = (row < p.M) && (kb_end > kb_begin);
 #pragma unroll 1
       for (int c = 0; c < CHUNKS; ++c) {
         const int col0 = n0 + c * 32;
@@ -624,10 +633,15 @@ __global__ void __launch_bounds__(gemm_threads(BN), 1)
         if (fast) {
           uint32_t r[32];
           tmem_ld_32x32(taddr + c * 32, r);
+          if constexpr ((F & F_ACTBWD) != 0) {
+#pragma unroll
+            for (int q2 = 0; q2 < 16; ++q2) zr[q2] = zn[q2];
+            if (c + 1 < CHUNKS) bwd_fetch_z(p, tc, row, row_ok, col0 + 32, zn);
+          }
           tmem_ld_wait();
           release_acc();
           if constexpr ((F & F_ACTBWD) != 0) {
-            epilogue_chunk_bwd<F>(p, tc, row, row_ok, col0, r);   // warp-collective (column sums)
+            epilogue_chunk_bwd<F>(p, tc, row, row_ok, col0, r, zr);   // warp-collective (column sums)
           } else {
             if (row_ok) epilogue_chunk<F>(p, tc, row, col0, r);
           }

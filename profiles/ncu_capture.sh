@@ -15,9 +15,12 @@ echo "launch list rc=$?"
 if [ $# -eq 0 ]; then
   set -- attn_fwd_kernel attn_bwd_kernel attn_bwd_prep conv0_fwd_tc conv0_bwd_fused posconv_tc_kernel \
          epilogue_bwd_kernel layernorm_fwd layernorm_bwd adamw_kernel distill_loss_fwd distill_loss_bwd sumsq_kernel \
-         "gemm_bf16_kernel<256, false, false, 2, 103>" "gemm_bf16_kernel<192, false, false, 2, 45>" \
-         "gemm_bf16_kernel<256, true, true, 2, 384>" "gemm_bf16_kernel<256, false, true, 2, 45>" \
-         "gemm_bf16_kernel<64, true, true, 1, 45>" "gemm_bf16_kernel<256, false, true, 2, 532>"
+         "gemm_bf16_kernel<.int.256, .bool.0, .bool.0, .int.2, .int.103>" \
+         "gemm_bf16_kernel<.int.192, .bool.0, .bool.0, .int.2, .int.45>" \
+         "gemm_bf16_kernel<.int.256, .bool.1, .bool.1, .int.2, .int.384>" \
+         "gemm_bf16_kernel<.int.256, .bool.0, .bool.1, .int.2, .int.45>" \
+         "gemm_bf16_kernel<.int.64, .bool.1, .bool.1, .int.1, .int.45>" \
+         "gemm_bf16_kernel<.int.256, .bool.0, .bool.1, .int.2, .int.532>"
 fi
 for k in "$@"; do
   name=$(echo "$k" | tr -c 'A-Za-z0-9_' '_' | sed 's/__*/_/g')

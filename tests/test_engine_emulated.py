@@ -159,7 +159,8 @@ def check_fused_act_bwd_equals_separate_pass(dev, names=("step_base", "step_larg
                             if p.grad is not None}
         gmax = max(float(v.abs().max()) for v in grads[False].values())
         for n, ref in grads[False].items():
-            err = float((grads[True][n] - ref).abs().max()) / max(float(ref.abs().max()), 1e-3 * gmax)
+            # floor: gradients that are analytically zero (k_proj.bias) hold only bf16 round-off of either path
+            err = float((grads[True][n] - ref).abs().max()) / max(float(ref.abs().max()), 1e-2 * gmax)
             assert err < 3e-2, (name, n, err)
 
 
