@@ -137,7 +137,14 @@ def check(rc, what=""):
         raise DphError("%s failed (%d): %s" % (what, rc, lib().dph_last_error().decode()))
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def stream_ptr():
+    """torch's current CUDA stream as a raw handle.  Called once per kernel launch: the raw getter avoids building a
+    `torch.cuda.Stream` object each time (that alone was ~30 % of the host time of an eager training step)."""
+    if _raw_stream is not None:
+        return ctypes.c_void_p(_raw_stream(torch.cuda.current_device()))
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 

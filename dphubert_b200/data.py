@@ -164,13 +164,18 @@ class DeviceCollate:
     `torch.randint(diff, size=(1,))` per over-long utterance in batch order — the reference's exact RNG usage
     (:303-309) — so a seeded run produces bit-identical batches."""
 
-    def __init__(self, pool: WaveformPool, pad: bool = False, rand_crop: bool = True) -> None:
-        self.pool, self.pad, self.rand_crop = pool, pad, rand_crop
+    def __init__(self, pool: WaveformPool, pad: bool = False, rand_crop: bool = True, quantum: int = 0) -> None:
+        """`quantum` > 0 (extension, crop mode only): the common length is rounded DOWN to a multiple of `quantum`
+        samples, i.e. every utterance is cropped by up to quantum - 1 samples more than the reference would — so that
+        batch shapes recur and `NativeDistillStep.step` can replay captured graphs.  0 = the reference's exact lengths."""
+        self.pool, self.pad, self.rand_crop, self.quantum = pool, pad, rand_crop, int(quantum)
 
     def plan(self, batch: List[int]):
         """Host side: (start offsets into the pool, lengths to copy, num_frames)."""
         lens = [self.pool.lengths[i] for i in batch]
         num_frames = max(lens) if self.pad else min(lens)
+        if self.quantum > 0 and not self.pad and num_frames >= self.quantum:
+            num_frames -= num_frames % self.quantum
         starts, take = [], []
         for i, n in zip(batch, lens):
             off = 0
@@ -320,9 +325,9 @@ class DeviceLoader:
     (lightning.py:306-342): iterating yields `(waveforms (B, T) fp32, lengths (B,) int64)` per batch of the sampler —
     already on the device, assembled by one gather kernel from the HBM-resident pool."""
 
-    def __init__(self, pool: WaveformPool, batch_sampler, pad: bool = False, rand_crop: bool = True):
+    def __init__(self, pool: WaveformPool, batch_sampler, pad: bool = False, rand_crop: bool = True, quantum: int = 0):
         self.pool, self.batch_sampler = pool, batch_sampler
-        self.collate = DeviceCollate(pool, pad=pad, rand_crop=rand_crop)
+        self.collate = DeviceCollate(pool, pad=pad, rand_crop=rand_crop, quantum=quantum)
 
     def __len__(self):
         return len(self.batch_sampler)

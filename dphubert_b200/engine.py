@@ -143,6 +143,7 @@ class Plan:
             self.grad_ranges[li] = r
 
         dev = self.device
+        self._vcache, self._gcache, self._wcache = {}, {}, {}
         self.arena = ops.zeros((self.total,), torch.float32, dev)
         self.any_grad = any(p.requires_grad for _, p in params)
         self.garena_full = ops.zeros((self.total + GRAD_TAIL,), torch.float32, dev) if self.any_grad else None
@@ -173,13 +174,20 @@ class Plan:
         self._rel_tables = {}
 
     # ------------------------------------------------------------------ parameter / gradient views
+    # views of the (never re-allocated) arenas are cached: an eager step asks for ~2500 of them
     def view(self, p):
-        o = self.offsets[id(p)]
-        return self.arena[o:o + p.numel()].view(p.shape)
+        v = self._vcache.get(id(p))
+        if v is None:
+            o = self.offsets[id(p)]
+            v = self._vcache[id(p)] = self.arena[o:o + p.numel()].view(p.shape)
+        return v
 
     def gview(self, p):
-        o = self.offsets[id(p)]
-        return self.garena[o:o + p.numel()].view(p.shape)
+        v = self._gcache.get(id(p))
+        if v is None:
+            o = self.offsets[id(p)]
+            v = self._gcache[id(p)] = self.garena[o:o + p.numel()].view(p.shape)
+        return v
 
     def bind_grads(self):
         """(Re-)attach `p.grad` to the gradient arena; a grad that was set to None counts as zero."""
@@ -247,6 +255,7 @@ class Plan:
         if bf:
             if self.lin16 is None:
                 self.lin16 = torch.empty(self.lin_total, dtype=torch.bfloat16, device=dev)
+                self._wcache = {}
                 cast_lin = True
             if cast_lin:
                 ops.cast(self.arena[: self.lin_total], self.lin16)
@@ -282,8 +291,11 @@ class Plan:
 
     def w16(self, p):
         """bf16 copy of a Linear weight (view into the bf16 arena)."""
-        o = self.offsets[id(p)]
-        return self.lin16[o:o + p.numel()].view(p.shape)
+        v = self._wcache.get(id(p))
+        if v is None:
+            o = self.offsets[id(p)]
+            v = self._wcache[id(p)] = self.lin16[o:o + p.numel()].view(p.shape)
+        return v
 
     def W(self, p, dtype):
         """GEMM operand copy of a Linear weight in the compute dtype."""
@@ -701,12 +713,18 @@ class StaticAlloc:
         self.views = {}   # name -> last view
         self.seen = set() # every (name, shape, dtype) ever handed out
         self.frozen = False  # set once a CUDA graph holds these addresses: shapes may no longer change
+        self.generation = 0  # bumped whenever a storage is re-allocated: graphs captured before hold stale addresses
+        # shape-keyed graph cache (trainer): several captured graphs of different shapes share this storage, so the
+        # clearing of a `zero=True` staging buffer has to be part of every graph instead of happening once
+        self.always_zero = False
 
     def __call__(self, name, shape, dtype, zero=False):
         name = self.prefix + name
         shape = tuple(int(s) for s in shape)
         key = (shape, dtype)
         if self.shapes.get(name) == key:
+            if zero and self.always_zero:
+                ops.memset(self.views[name])
             return self.views[name]
         if self.frozen and (name, key) not in self.seen:
             raise _lib.DphError(
@@ -725,6 +743,7 @@ class StaticAlloc:
                     torch.cuda.synchronize(self.device)
             store = torch.empty(max(int(n * self.SLACK), n, 1), dtype=dtype, device=self.device)
             self.bufs[name] = store
+            self.generation += 1
         t = store[:n].view(shape)
         if zero:
             ops.memset(t)

@@ -51,31 +51,24 @@ def mat_t(t):
     return View(t, t.shape[1], t.shape[0], 1, cs=t.stride(0))
 
 
-def _operand_bf16(v, nb0, nb1):
-    o = Operand()
-    esz = v.t.element_size()
-    o.ptr = v.t.data_ptr() + v.offset * esz
+def _operand_bf16(v, nb0, nb1, o=None):
+    o = Operand() if o is None else o
+    o.ptr = v.t.data_ptr() + v.offset * 2
     d3 = nb0 if v.sb0 != 0 else 1
     d4 = nb1 if v.sb1 != 0 else 1
     if v.cs == 1:
         o.major_mn = 0
         kx = (v.K + v.kin - 1) // v.kin
-        dims = (v.kin, v.rows, kx, d3, d4)
-        strides = (v.rs, v.kxs if kx > 1 else 8, v.sb0 if d3 > 1 else 8, v.sb1 if d4 > 1 else 8)
-        o.b0_mul = 1 if d3 > 1 else 0
-        o.b1_mul = 1 if d4 > 1 else 0
+        o.dims[:] = (v.kin, v.rows, kx, d3, d4)
+        o.strides[:] = (v.rs, v.kxs if kx > 1 else 8, v.sb0 if d3 > 1 else 8, v.sb1 if d4 > 1 else 8)
     elif v.rs == 1 and v.kin == v.K:
         o.major_mn = 1
-        dims = (v.rows, v.K, d3, d4, 1)
-        strides = (v.cs, v.sb0 if d3 > 1 else 8, v.sb1 if d4 > 1 else 8, 8)
-        o.b0_mul = 1 if d3 > 1 else 0
-        o.b1_mul = 1 if d4 > 1 else 0
+        o.dims[:] = (v.rows, v.K, d3, d4, 1)
+        o.strides[:] = (v.cs, v.sb0 if d3 > 1 else 8, v.sb1 if d4 > 1 else 8, 8)
     else:
         raise _lib.DphError("bf16 GEMM operand must be K-major (cs==1) or MN-major (rs==1)")
-    for i in range(5):
-        o.dims[i] = int(dims[i])
-    for i in range(4):
-        o.strides[i] = int(strides[i])
+    o.b0_mul = 1 if d3 > 1 else 0
+    o.b1_mul = 1 if d4 > 1 else 0
     return o
 
 

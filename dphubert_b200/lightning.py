@@ -260,7 +260,7 @@ class DistillModule(nn.Module):
         `training_step` + Lightning's optimizer loop; it must not be called from inside one."""
         waveforms, lengths = batch
         step = self.native_step()
-        out = step.run_step(waveforms, lengths)
+        out = step.step(waveforms, lengths)   # eager the first time a batch shape is seen, a replayed graph afterwards
         self.global_step = step.global_step
         return out
 
@@ -295,7 +295,7 @@ class DistillModule(nn.Module):
         return data.BucketizeBatchSampler(lens, num_buckets=1000, max_token_count=self.seconds_per_batch * 16000,
                                           min_len=32000, max_len=250000, shuffle=False)
 
-    def train_dataloader(self):
+    def train_dataloader(self, quantum: int = 0):
         """lightning.py:306-324: 1000 length buckets, <= seconds_per_batch of audio per batch, 2 s <= len <= 15.6 s,
         whole batches dealt to ranks with a seeded shuffle, crop to the shortest utterance with random offsets."""
         import torch.distributed as dist
@@ -309,7 +309,7 @@ class DistillModule(nn.Module):
         else:
             sampler = data.DistributedBatchSampler(sampler, num_replicas=1, rank=0, shuffle=True)
         sampler.set_epoch(self.current_epoch)
-        return data.DeviceLoader(pool, sampler, pad=False, rand_crop=True)
+        return data.DeviceLoader(pool, sampler, pad=False, rand_crop=True, quantum=quantum)
 
     def val_dataloader(self):
         """lightning.py:326-342 (not distributed: every rank sees the whole validation set)."""

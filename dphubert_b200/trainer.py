@@ -172,6 +172,8 @@ class NativeDistillStep:
         # gate-noise stream: seeded from the host seed stream (ops.manual_seed / next_seed), saved in state_dict()
         self._hc_seed = ops.next_seed()
         self._graph = None
+        self._gcache, self._gcache_gen, self._shape_seen = {}, None, {}
+        self.graph_capacity = 128   # graphs kept by `step()` (least recently used dropped first); 0 disables the cache
         self._static_in = None
         self.comm_stream = None
 
@@ -209,7 +211,7 @@ class NativeDistillStep:
         # host-side staleness checks that a captured graph cannot replay: derived GEMM operands follow
         # parameters changed by load_state_dict / in-place edits
         self.heads.refresh_if_changed() if self.dt == torch.bfloat16 else None
-        if self._graph is not None:
+        if self._graph is not None or self._gcache:
             self.splan.refresh(self.dt)
             self.tplan.refresh(self.dt)
 
@@ -494,7 +496,7 @@ class NativeDistillStep:
         self._hc_seed = int(sd["hc_seed"])
         ops.set_seed_state(sd["seed_counter"])
         ops.rng_set(int(sd["rng_epoch"]))
-        if self._graph is not None and int(sd["hc_seed"]) != self._captured_hc_seed:
+        if (self._graph is not None or self._gcache) and int(sd["hc_seed"]) != self._captured_hc_seed:
             raise _lib.DphError("the gate-noise seed is baked into the captured graph: load the state before capture()")
         # parameters were (re)loaded by the caller: rebuild every derived operand from them
         self.heads.refresh()
@@ -571,6 +573,66 @@ class NativeDistillStep:
         self._body(wave, lengths)
         self._allreduce()
         self._optimizer_step()
+        self.global_step += 1
+        return self.out
+
+    # ------------------------------------------------------------------------------------------------ shape-keyed graphs
+    def step(self, wave, lengths=None):
+        """`run_step` for variable-shape batches without the host cost of an eager launch sequence.
+
+        The reference crops every batch to its shortest utterance (audio_dataset.py:285-363), so (B, T) changes from
+        batch to batch and one captured CUDA graph cannot serve; issued eagerly, the ~480 launches of a step cost more
+        host time than the GPU needs to run them.  This entry point keeps a cache of captured graphs keyed by the batch
+        shape: a shape runs eagerly the first time it is seen (which sizes the workspace), is captured the second time,
+        and is replayed from then on.  All graphs share the one name-keyed workspace (their staging buffers are cleared
+        inside each graph); if a later, larger shape makes a workspace buffer grow, the cached graphs hold stale
+        addresses and are dropped.  Use `DeviceLoader(..., quantum=...)` so that shapes actually recur."""
+        if not wave.is_cuda or self.graph_capacity <= 0:
+            return self.run_step(wave, lengths)
+        allocs = (self.At, self.As, self.Ah)
+        key = (tuple(wave.shape), lengths is not None)
+        gen = tuple(a.generation for a in allocs)
+        if gen != self._gcache_gen:
+            self._gcache.clear()
+            self._gcache_gen = gen
+        ent = self._gcache.get(key)
+        if ent is None:
+            seen = self._shape_seen.get(key, 0)
+            self._shape_seen[key] = seen + 1
+            if seen == 0 or self._opt_state is None:
+                return self.run_step(wave, lengths)
+            w_in = self.As("in_wave", tuple(wave.shape), torch.float32)
+            l_in = self.As("in_lengths", (wave.shape[0],), torch.int64) if lengths is not None else None
+            if tuple(a.generation for a in allocs) != gen:   # the input buffers themselves grew: next time
+                return self.run_step(wave, lengths)
+            for a in allocs:
+                a.always_zero = True
+            try:
+                torch.cuda.synchronize()
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    self._body(w_in, l_in)
+                    self._allreduce()
+                    self._optimizer_step()
+            finally:
+                for a in allocs:
+                    a.always_zero = False
+            if tuple(a.generation for a in allocs) != gen:
+                raise _lib.DphError("a workspace buffer was re-allocated during graph capture")
+            self._captured_hc_seed = self._hc_seed
+            ent = (g, w_in, l_in)
+            self._gcache[key] = ent
+            while len(self._gcache) > self.graph_capacity:
+                self._gcache.pop(next(iter(self._gcache)))
+        else:
+            self._gcache.pop(key)      # re-insert: most recently used last
+            self._gcache[key] = ent
+        g, w_in, l_in = ent
+        w_in.copy_(wave, non_blocking=True)
+        if l_in is not None:
+            l_in.copy_(lengths, non_blocking=True)
+        self._push_scalars()
+        g.replay()
         self.global_step += 1
         return self.out
 

@@ -82,3 +82,40 @@ def test_resume_through_a_captured_graph():
     assert c[0].global_step == 5
     for p, q in zip(S._params(a[2], a[3], a[4]), S._params(c[2], c[3], c[4])):
         assert S.rel_err(p, q) < 2e-3   # see check_resume_bit_exact: atomics order + Adam's sign-like first steps
+
+
+def test_shape_keyed_graph_cache_matches_eager():
+    """`step()` (eager on first sight of a shape, captured on the second, replayed afterwards; all graphs share one
+    workspace) walks the same trajectory as eager `run_step` over interleaved batch shapes."""
+    from dphubert_b200 import ops
+
+    g = load_golden("step_base")
+
+    def fresh():
+        ops.manual_seed(21)
+        ops.rng_set(0)
+        s = build_step(g, DEV, torch.float32, learning_rate=1e-3, reg_learning_rate=0.05)
+        for h in s[2].modules():
+            if hasattr(h, "noise"):
+                h.noise = None
+        return s
+
+    shapes = [8000, 5000, 8000, 5000, 6500, 8000, 5000, 6500, 8000, 6500, 5000]
+    a, b = fresh(), fresh()
+    for i, T0 in enumerate(shapes):
+        wave = (g["wave"][:, :T0] * (1.0 + 0.01 * i)).contiguous().to(DEV)
+        ln = torch.tensor([T0, T0 - 300]).to(DEV)
+        a[0].run_step(wave, ln)
+        b[0].step(wave, ln)
+    torch.cuda.synchronize()
+    assert len(b[0]._gcache) == 3 and b[0].global_step == a[0].global_step == len(shapes)
+    for p, q in zip(S._params(a[2], a[3], a[4]), S._params(b[2], b[3], b[4])):
+        assert S.rel_err(p, q) < 2e-3
+    la, lb = a[0].loss_terms(), b[0].loss_terms()
+    assert abs(la["loss"] - lb["loss"]) < 1e-3 * abs(la["loss"])
+    # a larger shape re-allocates workspace buffers: the cached graphs are dropped, not replayed on stale addresses
+    big = torch.cat([g["wave"], g["wave"][:, :4000]], 1).contiguous().to(DEV)
+    b[0].step(big, torch.tensor([12000, 12000]).to(DEV))
+    b[0].step(g["wave"].to(DEV), g["lengths"].to(DEV))
+    torch.cuda.synchronize()
+    assert all(torch.isfinite(p).all() for p in b[2].parameters())
