@@ -528,7 +528,7 @@ def loader_fed(args, teacher, student, projs, layers, dev, rank, world, budget_s
     # crop quantum 0.2 s + shape-keyed graph cache: epochs 1 and 2 see / capture every shape, then replay
     qloader = D.DeviceLoader(pool, ds, pad=False, rand_crop=True, quantum=3200)
     n_epoch = len(qloader)
-    for _ in range(2):
+    for _ in range(3):   # see every shape, capture it, and re-capture what a late workspace growth invalidated
         for w, l in qloader:
             step.step(w, l)
     torch.cuda.synchronize()

@@ -590,6 +590,18 @@ class NativeDistillStep:
         if not wave.is_cuda or self.graph_capacity <= 0:
             return self.run_step(wave, lengths)
         allocs = (self.At, self.As, self.Ah)
+
+        def eager():
+            # graph replays rewrite the shared staging buffers behind the allocator's back: an eager step in between
+            # must clear them itself instead of trusting "same shape as my last request"
+            for a in allocs:
+                a.always_zero = True
+            try:
+                return self.run_step(wave, lengths)
+            finally:
+                for a in allocs:
+                    a.always_zero = False
+
         key = (tuple(wave.shape), lengths is not None)
         gen = tuple(a.generation for a in allocs)
         if gen != self._gcache_gen:
@@ -600,11 +612,11 @@ class NativeDistillStep:
             seen = self._shape_seen.get(key, 0)
             self._shape_seen[key] = seen + 1
             if seen == 0 or self._opt_state is None:
-                return self.run_step(wave, lengths)
+                return eager()
             w_in = self.As("in_wave", tuple(wave.shape), torch.float32)
             l_in = self.As("in_lengths", (wave.shape[0],), torch.int64) if lengths is not None else None
             if tuple(a.generation for a in allocs) != gen:   # the input buffers themselves grew: next time
-                return self.run_step(wave, lengths)
+                return eager()
             for a in allocs:
                 a.always_zero = True
             try:

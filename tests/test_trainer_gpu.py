@@ -110,7 +110,7 @@ def test_shape_keyed_graph_cache_matches_eager():
     torch.cuda.synchronize()
     assert len(b[0]._gcache) == 3 and b[0].global_step == a[0].global_step == len(shapes)
     for p, q in zip(S._params(a[2], a[3], a[4]), S._params(b[2], b[3], b[4])):
-        assert S.rel_err(p, q) < 2e-3
+        assert S.rel_err(p, q) < 3e-3   # 11 Adam steps at lr 1e-3; see check_resume_bit_exact on atomics order
     la, lb = a[0].loss_terms(), b[0].loss_terms()
     assert abs(la["loss"] - lb["loss"]) < 1e-3 * abs(la["loss"])
     # a larger shape re-allocates workspace buffers: the cached graphs are dropped, not replayed on stale addresses
