@@ -86,36 +86,57 @@ def test_resume_through_a_captured_graph():
 
 def test_shape_keyed_graph_cache_matches_eager():
     """`step()` (eager on first sight of a shape, captured on the second, replayed afterwards; all graphs share one
-    workspace) walks the same trajectory as eager `run_step` over interleaved batch shapes."""
+    workspace) against eager `run_step` over interleaved batch shapes.  With the learning rates at zero the weights
+    stay put, so loss and global gradient norm of every step must agree to round-off — any stale staging buffer in
+    the forward or the backward would show; with learning rates on, the two trajectories stay within Adam's
+    +-lr-per-step sensitivity to round-off."""
     from dphubert_b200 import ops
 
     g = load_golden("step_base")
 
-    def fresh():
+    def fresh(**kw):
         ops.manual_seed(21)
         ops.rng_set(0)
-        s = build_step(g, DEV, torch.float32, learning_rate=1e-3, reg_learning_rate=0.05)
+        s = build_step(g, DEV, torch.float32, **kw)
         for h in s[2].modules():
             if hasattr(h, "noise"):
                 h.noise = None
         return s
 
     shapes = [8000, 5000, 8000, 5000, 6500, 8000, 5000, 6500, 8000, 6500, 5000]
-    a, b = fresh(), fresh()
+
+    def batch(i, T0):
+        return ((g["wave"][:, :T0] * (1.0 + 0.01 * i)).contiguous().to(DEV), torch.tensor([T0, T0 - 300]).to(DEV))
+
+    a, b = fresh(learning_rate=0.0, reg_learning_rate=0.0), fresh(learning_rate=0.0, reg_learning_rate=0.0)
     for i, T0 in enumerate(shapes):
-        wave = (g["wave"][:, :T0] * (1.0 + 0.01 * i)).contiguous().to(DEV)
-        ln = torch.tensor([T0, T0 - 300]).to(DEV)
+        wave, ln = batch(i, T0)
+        a[0].run_step(wave, ln)
+        b[0].step(wave, ln)
+        la, lb = a[0].loss_terms(), b[0].loss_terms()
+        ga, gb = float(a[0].gnorm.sqrt()), float(b[0].gnorm.sqrt())
+        assert abs(la["loss"] - lb["loss"]) < 1e-5 * abs(la["loss"]), (i, la, lb)
+        assert abs(ga - gb) < 1e-4 * ga, (i, ga, gb)
+    assert len(b[0]._gcache) == 3 and b[0].global_step == len(shapes)
+    # a larger shape re-allocates workspace buffers: the cached graphs are dropped, not replayed on stale addresses
+    big = torch.cat([g["wave"], g["wave"][:, :4000]], 1).contiguous().to(DEV)
+    for s_ in (a, b):
+        (s_[0].run_step if s_ is a else s_[0].step)(big, torch.tensor([12000, 12000]).to(DEV))
+    assert len(b[0]._gcache) == 0 or b[0]._gcache_gen == tuple(x.generation for x in (b[0].At, b[0].As, b[0].Ah))
+    for i, T0 in enumerate(shapes[:4]):
+        wave, ln = batch(i, T0)
+        a[0].run_step(wave, ln)
+        b[0].step(wave, ln)
+        la, lb = a[0].loss_terms(), b[0].loss_terms()
+        assert abs(la["loss"] - lb["loss"]) < 1e-5 * abs(la["loss"]), (i, la, lb)
+    # learning rates on
+    a, b = fresh(learning_rate=1e-4, reg_learning_rate=0.01), fresh(learning_rate=1e-4, reg_learning_rate=0.01)
+    for i, T0 in enumerate(shapes):
+        wave, ln = batch(i, T0)
         a[0].run_step(wave, ln)
         b[0].step(wave, ln)
     torch.cuda.synchronize()
-    assert len(b[0]._gcache) == 3 and b[0].global_step == a[0].global_step == len(shapes)
-    for p, q in zip(S._params(a[2], a[3], a[4]), S._params(b[2], b[3], b[4])):
-        assert S.rel_err(p, q) < 3e-3   # 11 Adam steps at lr 1e-3; see check_resume_bit_exact on atomics order
     la, lb = a[0].loss_terms(), b[0].loss_terms()
-    assert abs(la["loss"] - lb["loss"]) < 1e-3 * abs(la["loss"])
-    # a larger shape re-allocates workspace buffers: the cached graphs are dropped, not replayed on stale addresses
-    big = torch.cat([g["wave"], g["wave"][:, :4000]], 1).contiguous().to(DEV)
-    b[0].step(big, torch.tensor([12000, 12000]).to(DEV))
-    b[0].step(g["wave"].to(DEV), g["lengths"].to(DEV))
-    torch.cuda.synchronize()
-    assert all(torch.isfinite(p).all() for p in b[2].parameters())
+    assert abs(la["loss"] - lb["loss"]) < 2e-3 * abs(la["loss"])
+    for p, q in zip(S._params(a[2], a[3], a[4])[:-2], S._params(b[2], b[3], b[4])[:-2]):
+        assert float((p - q).abs().max()) < 2 * len(shapes) * 1e-4
