@@ -111,7 +111,9 @@ def test_shape_keyed_graph_cache_matches_eager():
     a, b = fresh(learning_rate=0.0, reg_learning_rate=0.0), fresh(learning_rate=0.0, reg_learning_rate=0.0)
     for i, T0 in enumerate(shapes):
         wave, ln = batch(i, T0)
+        ops.rng_set(100 + i)   # the noise epoch is one device-wide counter: pin it so both twins draw the same gates
         a[0].run_step(wave, ln)
+        ops.rng_set(100 + i)
         b[0].step(wave, ln)
         la, lb = a[0].loss_terms(), b[0].loss_terms()
         ga, gb = float(a[0].gnorm.sqrt()), float(b[0].gnorm.sqrt())
@@ -121,11 +123,14 @@ def test_shape_keyed_graph_cache_matches_eager():
     # a larger shape re-allocates workspace buffers: the cached graphs are dropped, not replayed on stale addresses
     big = torch.cat([g["wave"], g["wave"][:, :4000]], 1).contiguous().to(DEV)
     for s_ in (a, b):
+        ops.rng_set(99)
         (s_[0].run_step if s_ is a else s_[0].step)(big, torch.tensor([12000, 12000]).to(DEV))
     assert len(b[0]._gcache) == 0 or b[0]._gcache_gen == tuple(x.generation for x in (b[0].At, b[0].As, b[0].Ah))
     for i, T0 in enumerate(shapes[:4]):
         wave, ln = batch(i, T0)
+        ops.rng_set(200 + i)
         a[0].run_step(wave, ln)
+        ops.rng_set(200 + i)
         b[0].step(wave, ln)
         la, lb = a[0].loss_terms(), b[0].loss_terms()
         assert abs(la["loss"] - lb["loss"]) < 1e-5 * abs(la["loss"]), (i, la, lb)
@@ -133,7 +138,9 @@ def test_shape_keyed_graph_cache_matches_eager():
     a, b = fresh(learning_rate=1e-4, reg_learning_rate=0.01), fresh(learning_rate=1e-4, reg_learning_rate=0.01)
     for i, T0 in enumerate(shapes):
         wave, ln = batch(i, T0)
+        ops.rng_set(300 + i)
         a[0].run_step(wave, ln)
+        ops.rng_set(300 + i)
         b[0].step(wave, ln)
     torch.cuda.synchronize()
     la, lb = a[0].loss_terms(), b[0].loss_terms()
