@@ -125,7 +125,7 @@ def test_shape_keyed_graph_cache_matches_eager():
     for s_ in (a, b):
         ops.rng_set(99)
         (s_[0].run_step if s_ is a else s_[0].step)(big, torch.tensor([12000, 12000]).to(DEV))
-    assert len(b[0]._gcache) == 0 or b[0]._gcache_gen == tuple(x.generation for x in (b[0].At, b[0].As, b[0].Ah))
+    assert b[0]._gcache_gen != tuple(x.generation for x in (b[0].At, b[0].As, b[0].Ah))   # dropped at the next call
     for i, T0 in enumerate(shapes[:4]):
         wave, ln = batch(i, T0)
         ops.rng_set(200 + i)
