@@ -23,6 +23,9 @@ constexpr int ATT_D = 64;        // head dim
 constexpr int ATT_BQ = 128;      // queries per CTA
 constexpr int ATT_BK = 128;      // keys per tile
 constexpr float kLog2e = 1.4426950408889634f;
+// The relative-position bias table lives in shared memory as tb[j - i + T - 1], pre-multiplied by log2(e).  Query rows
+// beyond T (last query tile) index a few entries below 0: TB_PAD zeroed floats in front keep those reads in bounds.
+constexpr int TB_PAD = 128;
 
 struct AttnParams {
   int B, H, T, inner;            // inner = H * 64
@@ -69,8 +72,8 @@ constexpr int FWD_SQ = 0;                                // Q   [128][64]       
 constexpr int FWD_SK = FWD_SQ + ATT_BQ * ATT_D * 2;      // K   [128][64]        16 KB
 constexpr int FWD_SV = FWD_SK + ATT_BK * ATT_D * 2;      // V   [128][64]        16 KB
 constexpr int FWD_SP = FWD_SV + ATT_BK * ATT_D * 2;      // P   2 x [128][64]    32 KB (two 64-key blocks)
-constexpr int FWD_TB = FWD_SP + ATT_BQ * ATT_BK * 2;     // bias table, up to 2*1024 floats 8 KB
-constexpr int FWD_BAR = FWD_TB + 2048 * 4;               // mbarriers + tmem slot
+constexpr int FWD_TB = FWD_SP + ATT_BQ * ATT_BK * 2;     // bias table, TB_PAD + up to 2*1024 floats 8.5 KB
+constexpr int FWD_BAR = FWD_TB + (2048 + TB_PAD) * 4;    // mbarriers + tmem slot
 constexpr int FWD_SMEM = FWD_BAR + 64 + 1024;            // + alignment slack
 
 template <bool BIAS, bool DROP>
@@ -81,7 +84,7 @@ __global__ void __launch_bounds__(128, 2)
   const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* gbase = smem_raw + (sbase - smem_u32(smem_raw));
   const uint32_t sQ = sbase + FWD_SQ, sK = sbase + FWD_SK, sV = sbase + FWD_SV, sP = sbase + FWD_SP;
-  float* tb = reinterpret_cast<float*>(gbase + FWD_TB);
+  float* tb = reinterpret_cast<float*>(gbase + FWD_TB) + TB_PAD;
   const uint32_t bar_q = sbase + FWD_BAR, bar_k = bar_q + 8, bar_v = bar_q + 16, bar_mma = bar_q + 24,
                  tmem_slot = bar_q + 32, bar_o = bar_q + 40;
   const int tid = threadIdx.x, warp = tid >> 5;
@@ -111,7 +114,9 @@ __global__ void __launch_bounds__(128, 2)
   const int i = q0 + tid;  // query row of this thread
   if constexpr (BIAS) {
     htot = p.head_index ? p.head_index[h] : h;
-    for (int r = tid; r < 2 * T - 1; r += 128) tb[r] = __ldg(p.emb + (long long)p.rel_table[r] * p.Htot + htot);
+    for (int r = tid; r < 2 * T - 1; r += 128)
+      tb[r] = __ldg(p.emb + (long long)p.rel_table[r] * p.Htot + htot) * kLog2e;
+    for (int r = tid; r < TB_PAD; r += 128) tb[-1 - r] = 0.f;
     if (p.gate && i < T) gate_i = p.gate[((long long)b * p.Htot + htot) * T + i];
   }
   tc_fence_before();
@@ -172,43 +177,43 @@ __global__ void __launch_bounds__(128, 2)
       tma_load_2d(sK, &tmQKV, bar_k, h * ATT_D, b * T + k0 + ATT_BK);
     }
 
-    // Interior tiles without a position bias take the lean path: the row maximum is taken on the raw scores
-    // (the scale is positive) and each probability costs one FFMA + one MUFU.EX2.  CTA-uniform branch.
-    const bool edge = BIAS || (k0 + ATT_BK > T) || (k0 + ATT_BK > len);
+    // Per 32-key chunk: chunks whose keys are all real (below T and below the padding length) take a lean path —
+    // without a position bias the row maximum is taken on the raw scores (the scale is positive) and a probability
+    // costs one FFMA + one MUFU.EX2; with a bias one shared-memory load and one more FFMA.  Only the chunk that
+    // straddles the end of the utterance pays for the general logit (clamped table index, key-validity tests, padding
+    // mask).  Warp-uniform choice (in fact CTA-uniform).
+    const int lim = min(T, len);
     // general logit (log2 domain) of key j for this thread's query
     auto logit = [&](uint32_t raw, int j) {
       float x = __uint_as_float(raw) * sc2;
-      if constexpr (BIAS) x += gate_i * tb[min(max(j - i + T - 1, 0), 2 * T - 2)] * kLog2e;
+      if constexpr (BIAS) x += gate_i * tb[min(max(j - i + T - 1, -TB_PAD), 2 * T - 2)];
       if (j >= len) x += -10000.0f * kLog2e;
       return x;
     };
     // ---- pass A: row maximum of this tile (log2 domain)
-    float mx = m2;
-    if (!edge) {
-      float mr = -INFINITY;
+    float mx = m2, mr = -INFINITY;
 #pragma unroll 1
-      for (int c = 0; c < ATT_BK / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32(tS + lane_off + c * 32, r);
-        tmem_ld_wait();
+    for (int c = 0; c < ATT_BK / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32(tS + lane_off + c * 32, r);
+      tmem_ld_wait();
+      const int j0 = k0 + c * 32;
+      if (j0 + 32 > lim) {
+#pragma unroll
+        for (int jj = 0; jj < 32; ++jj) {
+          const float x = logit(r[jj], j0 + jj);
+          if (j0 + jj < T) mx = fmaxf(mx, x);
+        }
+      } else if constexpr (BIAS) {
+        const float* tp = tb + (j0 - i + T - 1);
+#pragma unroll
+        for (int jj = 0; jj < 32; ++jj) mx = fmaxf(mx, fmaf(__uint_as_float(r[jj]), sc2, gate_i * tp[jj]));
+      } else {
 #pragma unroll
         for (int jj = 0; jj < 32; ++jj) mr = fmaxf(mr, __uint_as_float(r[jj]));
       }
-      mx = fmaxf(mx, mr * sc2);
-    } else {
-#pragma unroll 1
-      for (int c = 0; c < ATT_BK / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32(tS + lane_off + c * 32, r);
-        tmem_ld_wait();
-#pragma unroll
-        for (int jj = 0; jj < 32; ++jj) {
-          const int j = k0 + c * 32 + jj;
-          const float x = logit(r[jj], j);
-          if (j < T) mx = fmaxf(mx, x);
-        }
-      }
     }
+    mx = fmaxf(mx, mr * sc2);
     const float alpha = fast_exp2(m2 - mx);  // m2 = -inf on the first tile -> 0; applied to O when the tile is added
     m2 = mx;
     l *= alpha;
@@ -221,13 +226,19 @@ __global__ void __launch_bounds__(128, 2)
       tmem_ld_32x32(tS + lane_off + c * 32, r);
       tmem_ld_wait();
       uint32_t pk[16];
+      [[maybe_unused]] const float* tp = tb + (k0 + c * 32 - i + T - 1);
 #pragma unroll
       for (int jj = 0; jj < 32; jj += 2) {
         const int j = k0 + c * 32 + jj;
         float p0, p1;
         if constexpr (!EDGE) {
           float e0, e1;
-          upk2(fma2(pk2(__uint_as_float(r[jj]), __uint_as_float(r[jj + 1])), bc2(sc2), bc2(nm2)), e0, e1);
+          if constexpr (BIAS) {
+            e0 = fmaf(__uint_as_float(r[jj]), sc2, fmaf(gate_i, tp[jj], nm2));
+            e1 = fmaf(__uint_as_float(r[jj + 1]), sc2, fmaf(gate_i, tp[jj + 1], nm2));
+          } else {
+            upk2(fma2(pk2(__uint_as_float(r[jj]), __uint_as_float(r[jj + 1])), bc2(sc2), bc2(nm2)), e0, e1);
+          }
           p0 = fast_exp2(e0);
           p1 = fast_exp2(e1);
         } else {
@@ -253,12 +264,10 @@ __global__ void __launch_bounds__(128, 2)
                      : "memory");
       }
     };
-    if (edge) {
 #pragma unroll 1
-      for (int c = 0; c < ATT_BK / 32; ++c) pass_b(std::true_type{}, c);
-    } else {
-#pragma unroll 1
-      for (int c = 0; c < ATT_BK / 32; ++c) pass_b(std::false_type{}, c);
+    for (int c = 0; c < ATT_BK / 32; ++c) {
+      if (k0 + c * 32 + 32 > lim) pass_b(std::true_type{}, c);
+      else pass_b(std::false_type{}, c);
     }
     l += lsum;
     fence_async_smem();
@@ -439,9 +448,9 @@ constexpr int BWD_SQ = BWD_SV + ATT_BK * ATT_D * 2;      // Q    2 x [128 i][64]
 constexpr int BWD_SDO = BWD_SQ + 2 * ATT_BQ * ATT_D * 2; // dO   2 x [128 i][64]        32 KB
 constexpr int BWD_SP = BWD_SDO + 2 * ATT_BQ * ATT_D * 2; // Pd   2 x [128 i][64 j]      32 KB
 constexpr int BWD_SDS = BWD_SP + ATT_BQ * ATT_BK * 2;    // dS   2 x [128 i][64 j]      32 KB
-constexpr int BWD_TB = BWD_SDS + ATT_BQ * ATT_BK * 2;    // bias table (2T-1 floats)     8 KB
-constexpr int BWD_DIAG = BWD_TB + 2048 * 4;              // embedding gradient per diagonal j - i (2T-1 floats) 8 KB
-constexpr int BWD_HIST = BWD_DIAG + 2048 * 4;            // ... folded into buckets at the end    4 KB
+constexpr int BWD_TB = BWD_SDS + ATT_BQ * ATT_BK * 2;    // bias table (TB_PAD + 2T-1 floats)     8.5 KB
+constexpr int BWD_DIAG = BWD_TB + (2048 + TB_PAD) * 4;   // embedding gradient per diagonal j - i (TB_PAD + 2T-1) 8.5 KB
+constexpr int BWD_HIST = BWD_DIAG + (2048 + TB_PAD) * 4; // ... folded into buckets at the end    4 KB
 constexpr int BWD_BAR = BWD_HIST + 1024 * 4;
 constexpr int BWD_SMEM = BWD_BAR + 64 + 1024;
 
@@ -462,8 +471,8 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
   const uint32_t sK = sbase + BWD_SK, sV = sbase + BWD_SV, sQ = sbase + BWD_SQ, sDO = sbase + BWD_SDO,
                  sP = sbase + BWD_SP, sDS = sbase + BWD_SDS;
   constexpr uint32_t QBUF = ATT_BQ * ATT_D * 2;  // bytes of one Q / dO buffer
-  float* tb = reinterpret_cast<float*>(gbase + BWD_TB);
-  float* sdiag = reinterpret_cast<float*>(gbase + BWD_DIAG);
+  float* tb = reinterpret_cast<float*>(gbase + BWD_TB) + TB_PAD;
+  float* sdiag = reinterpret_cast<float*>(gbase + BWD_DIAG) + TB_PAD;
   float* hist = reinterpret_cast<float*>(gbase + BWD_HIST);
   const uint32_t bar_kv = sbase + BWD_BAR, bar_qdo = bar_kv + 8 /* [2] */, bar_s = bar_kv + 24, bar_g = bar_kv + 32,
                  tmem_slot = bar_kv + 40;
@@ -495,10 +504,11 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
   if constexpr (BIAS) {
     htot = p.head_index ? p.head_index[h] : h;
     for (int r = tid; r < 2 * T - 1; r += BWD_THREADS)
-      tb[r] = __ldg(p.emb + (long long)p.rel_table[r] * p.Htot + htot);
+      tb[r] = __ldg(p.emb + (long long)p.rel_table[r] * p.Htot + htot) * kLog2e;
+    for (int r = tid; r < TB_PAD; r += BWD_THREADS) tb[-1 - r] = 0.f;
     if (demb) {
       for (int r = tid; r < num_buckets; r += BWD_THREADS) hist[r] = 0.f;
-      for (int r = tid; r < 2 * T - 1; r += BWD_THREADS) sdiag[r] = 0.f;
+      for (int r = tid - TB_PAD; r < 2 * T - 1; r += BWD_THREADS) sdiag[r] = 0.f;
     }
   }
   tc_fence_before();
@@ -576,7 +586,9 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
     // Frames beyond T arrive as zeros (3-D tensor maps), which makes partial tiles harmless on the lean path: a
     // zero dO row adds nothing to dV, its dP and (L2 = delta = 0) dS vanish, and a zero K / V row adds nothing to dQ
     // while its own dK / dV rows are never stored.  Only a real padding mask (len < T) needs the general path.
-    const bool edge = BIAS || (len < T && k0 + ATT_BK > len);
+    // (decided per 32-key chunk; with a position bias the garbage probabilities of keys beyond T would also leak into
+    // the gate / embedding gradients, so there the chunk that straddles T takes the general path as well)
+    const int lim = BIAS ? min(T, len) : (len < T ? len : T + ATT_BK);
     const float nL2 = -L2, ndl = -dl;
     auto do_chunk = [&](auto edge_tag, int cc) {
       constexpr bool EDGE = decltype(edge_tag)::value;
@@ -586,6 +598,8 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
       tmem_ld_32x32(tP + lane_off + c * 32, rp);
       tmem_ld_wait();
       uint32_t pk[16], dk[16];
+      [[maybe_unused]] const float* tp = tb + (k0 + c * 32 - i + T - 1);      // bias (pre-scaled by log2 e)
+      [[maybe_unused]] float* sd = sdiag + (k0 + c * 32 - i + T - 1);          // per-diagonal embedding gradient
 #pragma unroll
       for (int jj = 0; jj < 32; jj += 2) {
         float pv[2], dv[2];
@@ -593,9 +607,17 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
         if constexpr (DROP)
           dropout_row_pair(drop_rkey, (uint32_t)(k0 + c * 32 + jj) >> 1, thresh, inv_keep, dsc[0], dsc[1]);
         if constexpr (!EDGE) {
-          // interior tile: the key pair on packed fp32x2 lanes (FFMA2 / FMUL2), two MUFU.EX2
+          // interior chunk: the key pair on packed fp32x2 lanes (FFMA2 / FMUL2), two MUFU.EX2
           float e0, e1;
-          upk2(fma2(pk2(__uint_as_float(rs[jj]), __uint_as_float(rs[jj + 1])), bc2(sc2), bc2(nL2)), e0, e1);
+          [[maybe_unused]] float b0 = 0.f, b1 = 0.f;
+          if constexpr (BIAS) {
+            b0 = tp[jj];
+            b1 = tp[jj + 1];
+            e0 = fmaf(__uint_as_float(rs[jj]), sc2, fmaf(gate_i, b0, nL2));
+            e1 = fmaf(__uint_as_float(rs[jj + 1]), sc2, fmaf(gate_i, b1, nL2));
+          } else {
+            upk2(fma2(pk2(__uint_as_float(rs[jj]), __uint_as_float(rs[jj + 1])), bc2(sc2), bc2(nL2)), e0, e1);
+          }
           const f32x2 pe2 = pk2(fast_exp2(e0), fast_exp2(e1));
           const f32x2 rp2 = pk2(__uint_as_float(rp[jj]), __uint_as_float(rp[jj + 1]));
           f32x2 t2, pv2 = pe2;
@@ -608,6 +630,14 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
           }
           upk2(pv2, pv[0], pv[1]);
           upk2(mul2(pe2, t2), dv[0], dv[1]);
+          if constexpr (BIAS) {
+            // rows beyond T carry dS = 0 (their dO, delta are zero), keys are all real in an interior chunk
+            dg = fmaf(dv[0], b0, fmaf(dv[1], b1, dg));
+            if (demb) {
+              atomicAdd(sd + jj, dv[0] * gate_i);
+              atomicAdd(sd + jj + 1, dv[1] * gate_i);
+            }
+          }
         }
 #pragma unroll
         for (int u = 0; u < (EDGE ? 2 : 0); ++u) {
@@ -620,8 +650,8 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
           } else {
             float x = fmaf(__uint_as_float(rs[jj + u]), sc2, nL2);
             if constexpr (BIAS) {
-              tbv = tb[min(max(j - i + T - 1, 0), 2 * T - 2)];
-              x += gate_i * tbv * kLog2e;
+              tbv = tb[min(max(j - i + T - 1, -TB_PAD), 2 * T - 2)];
+              x += gate_i * tbv;
             }
             if (j >= len) x += -10000.0f * kLog2e;
             ok = row_ok && (j < T);
@@ -639,7 +669,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
               dg += ds * tbv;
               // per-diagonal sums: the lanes of a warp hold 32 consecutive rows i at the same key j, i.e. 32
               // consecutive diagonals -> conflict-free shared-memory atomics (buckets would collide heavily)
-              if (demb) atomicAdd(&sdiag[j - i + T - 1], ds * gate_i);
+              if (demb) atomicAdd(&sdiag[min(max(j - i + T - 1, -TB_PAD), 2 * T - 2)], ds * gate_i);
             }
           }
         }
@@ -658,14 +688,14 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
                      : "memory");
       }
     };
-    if (edge) {
 #pragma unroll 1
-      for (int cc = 0; cc < 2; ++cc) do_chunk(std::true_type{}, cc);
-    } else {
-#pragma unroll 1
-      for (int cc = 0; cc < 2; ++cc) do_chunk(std::false_type{}, cc);
+    for (int cc = 0; cc < 2; ++cc) {
+      if (k0 + (half * 2 + cc) * 32 + 32 > lim) do_chunk(std::true_type{}, cc);
+      else do_chunk(std::false_type{}, cc);
     }
-    if (BIAS && dgate && p.gate && row_ok) atomicAdd(dgate + ((long long)b * p.Htot + htot) * T + i, dg);
+    // (the table is pre-scaled by log2 e: undo it for the gate gradient)
+    if (BIAS && dgate && p.gate && row_ok)
+      atomicAdd(dgate + ((long long)b * p.Htot + htot) * T + i, dg * (1.f / kLog2e));
     fence_async_smem();
     tc_fence_before();
     __syncthreads();  // P / dS complete, S / dP consumed, dQ of the previous tile drained

@@ -7,6 +7,7 @@
 //
 // One warp owns one score row (T <= 1024 keys, i.e. ~20 s of audio; the reference caps utterances at 15.6 s).
 #include "common.cuh"
+#include "vec.cuh"
 #include "../../include/dphubert_b200.h"
 
 namespace dph {
@@ -167,10 +168,22 @@ __global__ void __launch_bounds__(256)
 
 // WavLM gate (components.py:636-644):  g8 = Linear(64->8)(x[b,t,h,:]);  ga = sigmoid(sum g8[0:4]); gb = sigmoid(sum g8[4:8])
 //   gate = ga * (gb * const[h] - 1) + 2.   x is the layer input viewed as (B, T, Htot, head_dim).
+// One thread per (b, t, h): the four outputs of each half are only ever summed, so the 8 x Dh weight collapses to two
+// rows WA = sum W[0:4], WB = sum W[4:8] (shared memory); the Dh inputs of a thread are contiguous (128-bit loads, and
+// consecutive threads read consecutive 2 * Dh-byte segments).  Memory-bound: reads x once (6 MB at B = 8 x 10 s).
 template <typename T>
-__global__ void wavlm_gate_fwd_kernel(const T* __restrict__ x, const float* __restrict__ Wg, const float* __restrict__ bg,
-                                      const float* __restrict__ cst, float* __restrict__ gate, float* __restrict__ ga_out,
-                                      float* __restrict__ gb_out, int B, int Tn, int Htot, int Dh) {
+__global__ void __launch_bounds__(256)
+    wavlm_gate_fwd_kernel(const T* __restrict__ x, const float* __restrict__ Wg, const float* __restrict__ bg,
+                          const float* __restrict__ cst, float* __restrict__ gate, float* __restrict__ ga_out,
+                          float* __restrict__ gb_out, int B, int Tn, int Htot, int Dh) {
+  extern __shared__ float sw[];  // WA[Dh], WB[Dh]
+  float* WA = sw;
+  float* WB = sw + Dh;
+  for (int d = threadIdx.x; d < Dh; d += blockDim.x) {
+    WA[d] = (__ldg(Wg + d) + __ldg(Wg + Dh + d)) + (__ldg(Wg + 2 * Dh + d) + __ldg(Wg + 3 * Dh + d));
+    WB[d] = (__ldg(Wg + 4 * Dh + d) + __ldg(Wg + 5 * Dh + d)) + (__ldg(Wg + 6 * Dh + d) + __ldg(Wg + 7 * Dh + d));
+  }
+  __syncthreads();
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // over (b, t, h)
   const long long total = (long long)B * Tn * Htot;
   if (idx >= total) return;
@@ -178,16 +191,27 @@ __global__ void wavlm_gate_fwd_kernel(const T* __restrict__ x, const float* __re
   const long long bt = idx / Htot;
   const int t = (int)(bt % Tn), b = (int)(bt / Tn);
   const T* xv = x + bt * ((long long)Htot * Dh) + (long long)h * Dh;
-  float acc[8];
+  constexpr int VEC = VecOf<T>::N;
+  float a = (bg[0] + bg[1]) + (bg[2] + bg[3]), c = (bg[4] + bg[5]) + (bg[6] + bg[7]);
+  if ((Dh % VEC) == 0 && ((reinterpret_cast<uintptr_t>(xv) & 15) == 0)) {
+    for (int d0 = 0; d0 < Dh; d0 += VEC) {
+      float v[VEC];
+      load_vec(xv + d0, v);
 #pragma unroll
-  for (int o = 0; o < 8; ++o) acc[o] = bg[o];
-  for (int d = 0; d < Dh; ++d) {
-    const float xd = to_f(xv[d]);
-#pragma unroll
-    for (int o = 0; o < 8; ++o) acc[o] = fmaf(xd, __ldg(Wg + o * Dh + d), acc[o]);
+      for (int j = 0; j < VEC; ++j) {
+        a = fmaf(v[j], WA[d0 + j], a);
+        c = fmaf(v[j], WB[d0 + j], c);
+      }
+    }
+  } else {
+    for (int d = 0; d < Dh; ++d) {
+      const float xd = to_f(xv[d]);
+      a = fmaf(xd, WA[d], a);
+      c = fmaf(xd, WB[d], c);
+    }
   }
-  const float ga = sigmoidf_(acc[0] + acc[1] + acc[2] + acc[3]);
-  const float gb = sigmoidf_(acc[4] + acc[5] + acc[6] + acc[7]);
+  const float ga = sigmoidf_(a);
+  const float gb = sigmoidf_(c);
   const long long o = ((long long)b * Htot + h) * Tn + t;
   gate[o] = ga * (gb * cst[h] - 1.f) + 2.f;
   if (ga_out) ga_out[o] = ga;
@@ -322,12 +346,13 @@ extern "C" int dph_softmax_bwd(const void* P, const float* dPd, int64_t lds, voi
 extern "C" int dph_wavlm_gate_fwd(const void* x, const float* Wg, const float* bg, const float* cst, float* gate,
                                   float* ga, float* gb, int B, int T, int Htot, int Dh, int dtype, void* stream) {
   const long long total = (long long)B * T * Htot;
-  const int grid = (int)((total + 127) / 128);
+  const int grid = (int)((total + 255) / 256);
+  const size_t smem = sizeof(float) * 2 * (size_t)Dh;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   if (dtype == DPH_DTYPE_BF16)
-    wavlm_gate_fwd_kernel<bf16><<<grid, 128, 0, s>>>((const bf16*)x, Wg, bg, cst, gate, ga, gb, B, T, Htot, Dh);
+    wavlm_gate_fwd_kernel<bf16><<<grid, 256, smem, s>>>((const bf16*)x, Wg, bg, cst, gate, ga, gb, B, T, Htot, Dh);
   else
-    wavlm_gate_fwd_kernel<float><<<grid, 128, 0, s>>>((const float*)x, Wg, bg, cst, gate, ga, gb, B, T, Htot, Dh);
+    wavlm_gate_fwd_kernel<float><<<grid, 256, smem, s>>>((const float*)x, Wg, bg, cst, gate, ga, gb, B, T, Htot, Dh);
   dph_count_launch();
   return dph_check_last("wavlm_gate_fwd");
 }
