@@ -451,7 +451,8 @@ constexpr int BWD_SDS = BWD_SP + ATT_BQ * ATT_BK * 2;    // dS   2 x [128 i][64 
 constexpr int BWD_TB = BWD_SDS + ATT_BQ * ATT_BK * 2;    // bias table (TB_PAD + 2T-1 floats)     8.5 KB
 constexpr int BWD_DIAG = BWD_TB + (2048 + TB_PAD) * 4;   // embedding gradient per diagonal j - i (TB_PAD + 2T-1) 8.5 KB
 constexpr int BWD_HIST = BWD_DIAG + (2048 + TB_PAD) * 4; // ... folded into buckets at the end    4 KB
-constexpr int BWD_BAR = BWD_HIST + 1024 * 4;
+constexpr int BWD_GATE = BWD_HIST + 1024 * 4;            // gate of the 128 query rows of the current tile  0.5 KB
+constexpr int BWD_BAR = BWD_GATE + ATT_BQ * 4;
 constexpr int BWD_SMEM = BWD_BAR + 64 + 1024;
 
 // Pipeline per query tile qt (tensor core work is issued by thread 0, everything else by all 8 warps):
@@ -474,6 +475,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
   float* tb = reinterpret_cast<float*>(gbase + BWD_TB) + TB_PAD;
   float* sdiag = reinterpret_cast<float*>(gbase + BWD_DIAG) + TB_PAD;
   float* hist = reinterpret_cast<float*>(gbase + BWD_HIST);
+  float* sgate = reinterpret_cast<float*>(gbase + BWD_GATE);
   const uint32_t bar_kv = sbase + BWD_BAR, bar_qdo = bar_kv + 8 /* [2] */, bar_s = bar_kv + 24, bar_g = bar_kv + 32,
                  tmem_slot = bar_kv + 40;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -508,7 +510,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
     for (int r = tid; r < TB_PAD; r += BWD_THREADS) tb[-1 - r] = 0.f;
     if (demb) {
       for (int r = tid; r < num_buckets; r += BWD_THREADS) hist[r] = 0.f;
-      for (int r = tid - TB_PAD; r < 2 * T - 1; r += BWD_THREADS) sdiag[r] = 0.f;
+      for (int r = tid - TB_PAD; r < 2048; r += BWD_THREADS) sdiag[r] = 0.f;
     }
   }
   tc_fence_before();
@@ -599,7 +601,6 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
       tmem_ld_wait();
       uint32_t pk[16], dk[16];
       [[maybe_unused]] const float* tp = tb + (k0 + c * 32 - i + T - 1);      // bias (pre-scaled by log2 e)
-      [[maybe_unused]] float* sd = sdiag + (k0 + c * 32 - i + T - 1);          // per-diagonal embedding gradient
 #pragma unroll
       for (int jj = 0; jj < 32; jj += 2) {
         float pv[2], dv[2];
@@ -633,10 +634,6 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
           if constexpr (BIAS) {
             // rows beyond T carry dS = 0 (their dO, delta are zero), keys are all real in an interior chunk
             dg = fmaf(dv[0], b0, fmaf(dv[1], b1, dg));
-            if (demb) {
-              atomicAdd(sd + jj, dv[0] * gate_i);
-              atomicAdd(sd + jj + 1, dv[1] * gate_i);
-            }
           }
         }
 #pragma unroll
@@ -665,12 +662,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
           pv[u] = DROP ? pe * dsc[u] : pe;
           dv[u] = ds;
           if constexpr (BIAS) {
-            if (ok) {
-              dg += ds * tbv;
-              // per-diagonal sums: the lanes of a warp hold 32 consecutive rows i at the same key j, i.e. 32
-              // consecutive diagonals -> conflict-free shared-memory atomics (buckets would collide heavily)
-              if (demb) atomicAdd(&sdiag[min(max(j - i + T - 1, -TB_PAD), 2 * T - 2)], ds * gate_i);
-            }
+            if (ok) dg += ds * tbv;
           }
         }
         pk[jj >> 1] = pack_bf16x2(pv[0], pv[1]);
@@ -696,6 +688,9 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
     // (the table is pre-scaled by log2 e: undo it for the gate gradient)
     if (BIAS && dgate && p.gate && row_ok)
       atomicAdd(dgate + ((long long)b * p.Htot + htot) * T + i, dg * (1.f / kLog2e));
+    if constexpr (BIAS) {
+      if (demb && half == 0) sgate[rit] = gate_i;
+    }
     fence_async_smem();
     tc_fence_before();
     __syncthreads();  // P / dS complete, S / dP consumed, dQ of the previous tile drained
@@ -717,6 +712,27 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
                     make_smem_desc(sK + k * 2048, ATT_BK * 128, 1024, 2), idesc_q, k > 0 ? 1u : 0u);
       umma_commit(bar_g);
       if (qt + 1 < nq) issue_scores(qt + 1);  // runs on the tensor core while the warps drain dQ below
+    }
+    if constexpr (BIAS) {
+      if (demb) {
+        // Embedding gradient: sum of gate_i * dS_ij along every diagonal j - i of this 128 x 128 tile, read back from
+        // the bf16 dS tile the gradient MMAs consume.  One thread per diagonal, each adding into its own slot of the
+        // per-diagonal array: no atomics (shared-memory float atomics are compare-and-swap loops), and it runs while
+        // the tensor core works on dV / dK / dQ.  Rows beyond T and keys beyond T hold dS = 0.
+        const int dd = tid - (ATT_BQ - 1);  // j_local - i_local, -127 .. 127 (thread 255 idles)
+        if (dd < ATT_BK) {
+          const uint8_t* ds_tile = gbase + BWD_SDS;
+          const int i_lo = max(0, -dd), i_hi = min(ATT_BQ - 1, ATT_BK - 1 - dd);
+          float acc = 0.f;
+          for (int il = i_lo; il <= i_hi; ++il) {
+            const int jl = il + dd, jc = jl & 63;
+            const uint32_t off = (uint32_t)(jl >> 6) * (ATT_BQ * 128) + sw128(il, jc >> 3) + (uint32_t)(jc & 7) * 2;
+            acc = fmaf(sgate[il], __bfloat162float(*reinterpret_cast<const bf16*>(ds_tile + off)), acc);
+          }
+          sdiag[(k0 - q0) + dd + T - 1] += acc;
+        }
+        __syncthreads();  // nobody overwrites the dS tile (next query tile) before every diagonal has been read
+      }
     }
     mbar_wait(bar_g, ph);
     tc_fence_after();
