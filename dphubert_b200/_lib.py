@@ -69,6 +69,7 @@ class GemmDesc(ctypes.Structure):
         ("z_sb1", ctypes.c_int64),
         ("dbias", ctypes.c_void_p),
         ("dmask", ctypes.c_void_p),
+        ("b_nsplit", ctypes.c_int),
     ]
 
 

@@ -37,6 +37,7 @@ struct GemmParams {
   long long ldz, z_sb0, z_sb1;
   float* dbias;
   float* dmask;
+  int b_nsplit;  // > 0: MN-major B whose N index is (tap, channel): see the producer warp in gemm_kernel.cuh
 };
 
 int gemm_bf16_launch(const dph_gemm_desc_t* d, cudaStream_t stream);

@@ -524,8 +524,14 @@ __global__ void __launch_bounds__(gemm_threads(BN), 1)
             load(sB, &tmB, (kb % p.b_kdiv) * BK, n0, kb / p.b_kdiv, tc.b0 * p.b_b0, tc.b1 * p.b_b1);
           } else {
 #pragma unroll
-            for (int j = 0; j < Cfg::B_ROWS / 64; ++j)
-              load(sB + j * (BK * 128), &tmB, n0 + 64 * j, kb * BK, tc.b0 * p.b_b0, tc.b1 * p.b_b1, 0);
+            for (int j = 0; j < Cfg::B_ROWS / 64; ++j) {
+              const int nn = n0 + 64 * j;
+              // b_nsplit > 0: the N index is (tap, channel) = (nn / b_nsplit, nn % b_nsplit) and the tap is the 4th
+              // tensor-map dimension (an overlapping, row-shifted view of the same activation: grouped-conv weight
+              // gradient with the taps folded into N)
+              if (p.b_nsplit > 0) load(sB + j * (BK * 128), &tmB, nn % p.b_nsplit, kb * BK, tc.b0 * p.b_b0, nn / p.b_nsplit, 0);
+              else load(sB + j * (BK * 128), &tmB, nn, kb * BK, tc.b0 * p.b_b0, tc.b1 * p.b_b1, 0);
+            }
           }
           if (++stage == STAGES) {
             stage = 0;

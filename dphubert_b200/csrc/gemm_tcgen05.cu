@@ -288,6 +288,15 @@ int gemm_bf16_launch(const dph_gemm_desc_t* d, cudaStream_t stream) {
   p.z_sb1 = d->z_sb1;
   p.dbias = d->dbias;
   p.dmask = d->dmask;
+  p.b_nsplit = d->b_nsplit;
+  if (d->b_nsplit != 0) {
+    if (!b_mn || d->b_nsplit < 64 || d->b_nsplit % 64 != 0 || d->N % d->b_nsplit != 0 || d->nb1 != 1 ||
+        (long long)d->b.dims[0] != d->b_nsplit || (long long)d->b.dims[3] * d->b_nsplit != d->N) {
+      set_error("gemm: b_nsplit needs an MN-major B with dims[0] == b_nsplit (a multiple of 64), dims[3] == N / "
+                "b_nsplit taps and nb1 == 1");
+      return DPH_ERR_ARG;
+    }
+  }
   if (d->act_bwd) {
     // fused activation backward: fast epilogue path only, nothing else may be fused into the same launch
     const bool z_ok = d->z != nullptr && (d->ldz % 16 == 0) && (d->z_sb0 % 16 == 0) && (d->z_sb1 % 16 == 0) &&

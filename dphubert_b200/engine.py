@@ -1449,7 +1449,12 @@ def encoder_bwd(plan: Plan, st, dh, dmasks, A):
             dwp = A("pos_dwp", (Gn, Cgp, K, Cgp), torch.float32)
             a = View(dzp, Cgp, Kext, 1, cs=Wd, sb0=Cgp, offset=front * Wd)
             bv = View(pcr["xp"], Cgp, Kext, 1, cs=Wd, sb0=Cgp, sb1=Wd)
-            G.gemm(a, bv, dwp, Cgp, Cgp, Kext, nb0=Gn, nb1=K, ldc=K * Cgp, c_sb0=Cgp * K * Cgp, c_sb1=Cgp)
+            if dt == torch.bfloat16 and Cgp % 64 == 0:
+                # all K taps folded into N (column = tap * Cgp + ci): one A tile feeds 4 taps of a 256-wide MMA instead
+                # of K separate 64 x 64 products per group (which were bound by L2 -> shared-memory traffic)
+                G.gemm(a, bv, dwp, Cgp, K * Cgp, Kext, nb0=Gn, ldc=K * Cgp, c_sb0=Cgp * K * Cgp, b_taps=K, cta_group=1)
+            else:
+                G.gemm(a, bv, dwp, Cgp, Cgp, Kext, nb0=Gn, nb1=K, ldc=K * Cgp, c_sb0=Cgp * K * Cgp, c_sb1=Cgp)
             scratch = A("pos_wb_scratch", (K,), torch.float32)
             ops.posconv_weight_bwd(dwp, plan.view(pc.conv.weight_v), plan.view(pc.conv.weight_g), norm, scratch,
                                    plan.gview(pc.conv.weight_v), plan.gview(pc.conv.weight_g), D, Gn, Cg, Cgp, Cgp, K)

@@ -82,9 +82,12 @@ def _operand_f32(v):
 def gemm(a, b, c, M, N, K, *, ldc=None, nb0=1, nb1=1, c_sb0=0, c_sb1=0, c_offset=0, alpha=1.0, bias=None, act=0,
          colmask=None, scalar_mask=None, residual=None, ldr=None, r_sb0=0, r_sb1=0, r_offset=0, c2=None,
          accumulate=False, atomic=False, ksplit=1, drop_p=0.0, seed=0, block_n=0, vec_sb0=0, scalar_sb0=0,
-         cta_group=0, act_bwd=False, z=None, ldz=None, z_sb0=0, z_sb1=0, z_offset=0, dbias=None, dmask=None):
+         cta_group=0, act_bwd=False, z=None, ldz=None, z_sb0=0, z_sb1=0, z_offset=0, dbias=None, dmask=None,
+         b_taps=0):
     """C[b][m, n] = epilogue(alpha * sum_k a(m,k) b(n,k)).  `a`, `b` are `View`s; dtype of `a.t` selects the path:
     bf16 -> tcgen05 tensor-core kernel, fp32 -> CUDA-core kernel.
+    `b_taps` > 0 (bf16, MN-major `b` with rows = N / b_taps channels): column n reads channel n % rows of tap n // rows,
+    `b.sb1` being the element offset between taps (overlapping view; grouped-conv weight gradient).
     `act_bwd` (bf16 only, see `act_bwd_ok`): the product is the gradient wrt dropout(colmask * act(z)); the epilogue
     writes acc * dropout * colmask * act'(z) and accumulates `dbias` / `dmask` column sums."""
     L = _lib.lib()
@@ -96,7 +99,10 @@ def gemm(a, b, c, M, N, K, *, ldc=None, nb0=1, nb1=1, c_sb0=0, c_sb1=0, c_offset
         assert b.t.dtype == torch.bfloat16
         d = GemmDesc()
         d.a = _operand_bf16(a, nb0, nb1)
-        d.b = _operand_bf16(b, nb0, nb1)
+        d.b = _operand_bf16(b, nb0, b_taps if b_taps else nb1)
+        if b_taps:
+            assert nb1 == 1 and b.rows * b_taps == N and b.sb1 != 0
+            d.b_nsplit = b.rows
         d.M, d.N, d.K, d.nb0, d.nb1 = M, N, K, nb0, nb1
         d.block_n, d.ksplit, d.cta_group = block_n, ksplit, cta_group
         d.c = c.data_ptr() + c_offset * c.element_size()

@@ -92,6 +92,11 @@ typedef struct {
   int64_t ldz, z_sb0, z_sb1;
   float* dbias;
   float* dmask;
+  /* b_nsplit > 0 (MN-major B only, a multiple of 64 dividing N, nb1 == 1): column n of the product reads B "row"
+   * n % b_nsplit of tap n / b_nsplit, the tap being b.dims[3] / b.strides[2] — an overlapping, row-shifted view of the
+   * same activation.  Used for the weight gradient of the grouped positional conv (components.py:319-333 backward)
+   * with all 128 taps folded into N instead of 128 separate 64 x 64 products. */
+  int b_nsplit;
 } dph_gemm_desc_t;
 
 int dph_gemm_bf16(const dph_gemm_desc_t* desc, void* stream);

@@ -56,8 +56,18 @@ def _gather(v, nb0, nb1):
 def gemm(a, b, c, M, N, K, *, ldc=None, nb0=1, nb1=1, c_sb0=0, c_sb1=0, c_offset=0, alpha=1.0, bias=None, act=0,
          colmask=None, scalar_mask=None, residual=None, ldr=None, r_sb0=0, r_sb1=0, r_offset=0, c2=None,
          accumulate=False, atomic=False, ksplit=1, drop_p=0.0, seed=0, block_n=0, vec_sb0=0, scalar_sb0=0,
-         cta_group=0, act_bwd=False, z=None, ldz=None, z_sb0=0, z_sb1=0, z_offset=0, dbias=None, dmask=None):
+         cta_group=0, act_bwd=False, z=None, ldz=None, z_sb0=0, z_sb1=0, z_offset=0, dbias=None, dmask=None,
+         b_taps=0):
     assert drop_p == 0.0, "the emulator runs the dropout-free parity configuration"
+    if b_taps:
+        # taps folded into N: column n = tap * rows + channel reads the view shifted by tap * sb1
+        assert a.t.dtype == torch.bfloat16 and nb1 == 1 and b.rows * b_taps == N and b.rs == 1 and b.rows % 64 == 0
+        _check_bf16_operand(b, nb0, b_taps)
+        for tap in range(b_taps):
+            bt = G.View(b.t, b.rows, b.K, b.rs, b.cs, b.kin, b.kxs, b.sb0, 0, b.offset + tap * b.sb1)
+            gemm(a, bt, c, M, b.rows, K, ldc=ldc, nb0=nb0, nb1=1, c_sb0=c_sb0, c_sb1=0,
+                 c_offset=c_offset + tap * b.rows, alpha=alpha, accumulate=accumulate, atomic=atomic, ksplit=ksplit)
+        return c
     ldc = N if ldc is None else ldc
     ldr = ldc if ldr is None else ldr
     assert a.rows == M and b.rows == N and a.K == K and b.K == K, "view extents disagree with the problem size"

@@ -137,3 +137,25 @@ def test_fused_activation_backward_dropout_mask_matches_forward():
     assert torch.equal(fwd_keep[big], bwd_keep[big])
     ratio = (dz1.float() / dz0.float())[big & bwd_keep]
     assert ((ratio * (1 - p) - 1).abs() < 2e-2).all()
+
+
+@pytest.mark.parametrize("bn", [0, 256, 128])
+def test_taps_folded_into_n(bn):
+    """grouped-conv weight gradient with the taps folded into N (b_nsplit): column n = tap * 64 + channel reads the
+    activation view shifted by `tap` rows; the restatement runs one product per tap"""
+    Gn, Cgp, K, Text = 3, 64, 16, 700
+    Wd = Gn * Cgp
+    front = K // 2
+    rows = front + Text + K
+    dzp = rnd(rows, Wd, dtype=BF16)
+    xp = rnd(rows, Wd, dtype=BF16)
+    dwp = zer(Gn, Cgp, K, Cgp)
+    a = G.View(dzp, Cgp, Text, 1, cs=Wd, sb0=Cgp, offset=front * Wd)
+    bv = G.View(xp, Cgp, Text, 1, cs=Wd, sb0=Cgp, sb1=Wd)
+    both("gemm", (a, bv, dwp, Cgp, K * Cgp, Text), dict(nb0=Gn, ldc=K * Cgp, c_sb0=Cgp * K * Cgp, b_taps=K, cta_group=1,
+                                                       block_n=bn), fn=G.gemm, ref=emu.gemm, tol=2e-3)
+    # and it equals the per-tap batched formulation it replaces
+    ref = zer(Gn, Cgp, K, Cgp)
+    G.gemm(a, bv, ref, Cgp, Cgp, Text, nb0=Gn, nb1=K, ldc=K * Cgp, c_sb0=Cgp * K * Cgp, c_sb1=Cgp)
+    torch.cuda.synchronize()
+    assert (dwp - ref).abs().max().item() < 1e-3 * ref.abs().max().item()
