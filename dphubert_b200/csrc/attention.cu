@@ -451,8 +451,8 @@ constexpr int BWD_SDS = BWD_SP + ATT_BQ * ATT_BK * 2;    // dS   2 x [128 i][64 
 constexpr int BWD_TB = BWD_SDS + ATT_BQ * ATT_BK * 2;    // bias table (TB_PAD + 2T-1 floats)     8.5 KB
 constexpr int BWD_DIAG = BWD_TB + (2048 + TB_PAD) * 4;   // embedding gradient per diagonal j - i (TB_PAD + 2T-1) 8.5 KB
 constexpr int BWD_HIST = BWD_DIAG + (2048 + TB_PAD) * 4; // ... folded into buckets at the end    4 KB
-constexpr int BWD_GATE = BWD_HIST + 1024 * 4;            // gate of the 128 query rows of the current tile  0.5 KB
-constexpr int BWD_BAR = BWD_GATE + ATT_BQ * 4;
+constexpr int BWD_WDIAG = BWD_HIST + 1024 * 4;           // per-warp tile-local diagonal sums, 8 x 256 floats   8 KB
+constexpr int BWD_BAR = BWD_WDIAG + 8 * 256 * 4;
 constexpr int BWD_SMEM = BWD_BAR + 64 + 1024;
 
 // Pipeline per query tile qt (tensor core work is issued by thread 0, everything else by all 8 warps):
@@ -475,7 +475,8 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
   float* tb = reinterpret_cast<float*>(gbase + BWD_TB) + TB_PAD;
   float* sdiag = reinterpret_cast<float*>(gbase + BWD_DIAG) + TB_PAD;
   float* hist = reinterpret_cast<float*>(gbase + BWD_HIST);
-  float* sgate = reinterpret_cast<float*>(gbase + BWD_GATE);
+  float* wdiag_all = reinterpret_cast<float*>(gbase + BWD_WDIAG);
+  float* wdiag = wdiag_all + (threadIdx.x >> 5) * 256;  // this warp's private sums, index (j_local - i_local) + 127
   const uint32_t bar_kv = sbase + BWD_BAR, bar_qdo = bar_kv + 8 /* [2] */, bar_s = bar_kv + 24, bar_g = bar_kv + 32,
                  tmem_slot = bar_kv + 40;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -511,6 +512,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
     if (demb) {
       for (int r = tid; r < num_buckets; r += BWD_THREADS) hist[r] = 0.f;
       for (int r = tid - TB_PAD; r < 2048; r += BWD_THREADS) sdiag[r] = 0.f;
+      for (int r = tid; r < 8 * 256; r += BWD_THREADS) wdiag_all[r] = 0.f;
     }
   }
   tc_fence_before();
@@ -601,6 +603,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
       tmem_ld_wait();
       uint32_t pk[16], dk[16];
       [[maybe_unused]] const float* tp = tb + (k0 + c * 32 - i + T - 1);      // bias (pre-scaled by log2 e)
+      [[maybe_unused]] float* wd = wdiag + (c * 32 - rit + 127);               // tile-local diagonal of key c*32 + 0
 #pragma unroll
       for (int jj = 0; jj < 32; jj += 2) {
         float pv[2], dv[2];
@@ -634,6 +637,16 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
           if constexpr (BIAS) {
             // rows beyond T carry dS = 0 (their dO, delta are zero), keys are all real in an interior chunk
             dg = fmaf(dv[0], b0, fmaf(dv[1], b1, dg));
+            if (demb) {
+              // embedding gradient: gate_i * dS_ij summed per diagonal j - i.  The 32 lanes of a warp hold 32
+              // consecutive rows at the same key, i.e. 32 distinct diagonals per instruction: plain read-modify-write
+              // on the warp's private array (shared-memory float atomics are compare-and-swap loops); successive keys
+              // alias across lanes, hence the __syncwarp between them
+              wd[jj] = fmaf(dv[0], gate_i, wd[jj]);
+              __syncwarp();
+              wd[jj + 1] = fmaf(dv[1], gate_i, wd[jj + 1]);
+              __syncwarp();
+            }
           }
         }
 #pragma unroll
@@ -663,6 +676,10 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
           dv[u] = ds;
           if constexpr (BIAS) {
             if (ok) dg += ds * tbv;
+            if (demb) {  // all lanes take part (warp-uniform condition): masked rows / keys add zero
+              wd[jj + u] = fmaf(ok ? ds : 0.f, gate_i, wd[jj + u]);
+              __syncwarp();
+            }
           }
         }
         pk[jj >> 1] = pack_bf16x2(pv[0], pv[1]);
@@ -688,9 +705,6 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
     // (the table is pre-scaled by log2 e: undo it for the gate gradient)
     if (BIAS && dgate && p.gate && row_ok)
       atomicAdd(dgate + ((long long)b * p.Htot + htot) * T + i, dg * (1.f / kLog2e));
-    if constexpr (BIAS) {
-      if (demb && half == 0) sgate[rit] = gate_i;
-    }
     fence_async_smem();
     tc_fence_before();
     __syncthreads();  // P / dS complete, S / dP consumed, dQ of the previous tile drained
@@ -715,23 +729,18 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
     }
     if constexpr (BIAS) {
       if (demb) {
-        // Embedding gradient: sum of gate_i * dS_ij along every diagonal j - i of this 128 x 128 tile, read back from
-        // the bf16 dS tile the gradient MMAs consume.  One thread per diagonal, each adding into its own slot of the
-        // per-diagonal array: no atomics (shared-memory float atomics are compare-and-swap loops), and it runs while
-        // the tensor core works on dV / dK / dQ.  Rows beyond T and keys beyond T hold dS = 0.
-        const int dd = tid - (ATT_BQ - 1);  // j_local - i_local, -127 .. 127 (thread 255 idles)
-        if (dd < ATT_BK) {
-          const uint8_t* ds_tile = gbase + BWD_SDS;
-          const int i_lo = max(0, -dd), i_hi = min(ATT_BQ - 1, ATT_BK - 1 - dd);
+        // fold the eight warps' tile-local diagonal sums into the utterance-level array (one thread per diagonal, each
+        // owning its slot: no atomics) and clear them for the next query tile
+        if (tid < ATT_BQ + ATT_BK - 1) {
           float acc = 0.f;
-          for (int il = i_lo; il <= i_hi; ++il) {
-            const int jl = il + dd, jc = jl & 63;
-            const uint32_t off = (uint32_t)(jl >> 6) * (ATT_BQ * 128) + sw128(il, jc >> 3) + (uint32_t)(jc & 7) * 2;
-            acc = fmaf(sgate[il], __bfloat162float(*reinterpret_cast<const bf16*>(ds_tile + off)), acc);
+#pragma unroll
+          for (int w8 = 0; w8 < 8; ++w8) {
+            acc += wdiag_all[w8 * 256 + tid];
+            wdiag_all[w8 * 256 + tid] = 0.f;
           }
-          sdiag[(k0 - q0) + dd + T - 1] += acc;
+          sdiag[(k0 - q0) + (tid - (ATT_BQ - 1)) + T - 1] += acc;
         }
-        __syncthreads();  // nobody overwrites the dS tile (next query tile) before every diagonal has been read
+        __syncthreads();  // the warp arrays are clear before the next query tile adds to them
       }
     }
     mbar_wait(bar_g, ph);
