@@ -11,6 +11,20 @@
 #include "../../include/dphubert_b200.h"
 
 namespace dph {
+DPH_DEVICE void load_pair(const float* p, float& a, float& b) {
+  const float2 f = *reinterpret_cast<const float2*>(p);
+  a = f.x;
+  b = f.y;
+}
+DPH_DEVICE void load_pair(const bf16* p, float& a, float& b) {
+  const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p));
+  a = f.x;
+  b = f.y;
+}
+DPH_DEVICE void store_pair(float* p, float a, float b) { *reinterpret_cast<float2*>(p) = make_float2(a, b); }
+DPH_DEVICE void store_pair(bf16* p, float a, float b) {
+  *reinterpret_cast<__nv_bfloat162*>(p) = __floats2bfloat162_rn(a, b);
+}
 void set_error(const char* fmt, ...);
 
 constexpr int SM_NPL = 32;  // keys per lane -> T <= 1024
@@ -228,31 +242,41 @@ __global__ void __launch_bounds__(256)
                           const float* __restrict__ ga_in, const float* __restrict__ gb_in,
                           const float* __restrict__ dgate, T* __restrict__ dx, float* __restrict__ dWg,
                           float* __restrict__ dbg, float* __restrict__ dcst, int B, int Tn, int Htot, int Dh) {
-  constexpr int NPL = 4;          // head-dim elements per lane (Dh <= 128)
-  extern __shared__ float sh[];   // [2*Dh + 2 + Htot]
+  // One warp per (b, t, h) row; lane l owns the ADJACENT head-dim elements 2l, 2l+1 (+64 per extra pass), so a row is
+  // one coalesced 4-byte-per-lane access for x and for the dx read-modify-write.  Per-warp partial sums live in
+  // registers (dWg: two accumulators per owned element, since outputs 0-3 share dpa and 4-7 share dpb) and in a
+  // per-warp slice of shared memory (dconst[h], written by lane 0 only: plain adds, no atomics); they meet once at
+  // the end of the block.
+  constexpr int NP = 2;           // passes of 64 elements (Dh <= 128)
+  extern __shared__ float sh[];   // s_A[Dh] s_B[Dh] s_db[2] | per warp: s_dc[Htot]
   float* s_A = sh;
   float* s_B = sh + Dh;
   float* s_db = sh + 2 * Dh;
-  float* s_dc = s_db + 2;
-  for (int q = threadIdx.x; q < 2 * Dh + 2 + Htot; q += blockDim.x) sh[q] = 0.f;
+  float* s_dc_all = s_db + 2;
+  const int nwarp = blockDim.x >> 5;
+  for (int q = threadIdx.x; q < 2 * Dh + 2 + nwarp * Htot; q += blockDim.x) sh[q] = 0.f;
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  float wA[NPL], wB[NPL], accA[NPL], accB[NPL];
+  float* s_dc = s_dc_all + warp * Htot;
+  float wA[NP][2], wB[NP][2], accA[NP][2], accB[NP][2];
 #pragma unroll
-  for (int q = 0; q < NPL; ++q) {
-    const int d = lane + 32 * q;
-    wA[q] = wB[q] = accA[q] = accB[q] = 0.f;
-    if (d < Dh) {
+  for (int q = 0; q < NP; ++q)
 #pragma unroll
-      for (int o8 = 0; o8 < 4; ++o8) {
-        wA[q] += __ldg(Wg + o8 * Dh + d);
-        wB[q] += __ldg(Wg + (o8 + 4) * Dh + d);
+    for (int e = 0; e < 2; ++e) {
+      const int d = 64 * q + 2 * lane + e;
+      wA[q][e] = wB[q][e] = accA[q][e] = accB[q][e] = 0.f;
+      if (d < Dh) {
+#pragma unroll
+        for (int o8 = 0; o8 < 4; ++o8) {
+          wA[q][e] += __ldg(Wg + o8 * Dh + d);
+          wB[q][e] += __ldg(Wg + (o8 + 4) * Dh + d);
+        }
       }
     }
-  }
   float dbA = 0.f, dbB = 0.f;
   const long long total = (long long)B * Tn * Htot;
-  for (long long idx = (long long)blockIdx.x * 8 + warp; idx < total; idx += (long long)gridDim.x * 8) {
+  const bool even = (Dh % 2) == 0;
+  for (long long idx = (long long)blockIdx.x * nwarp + warp; idx < total; idx += (long long)gridDim.x * nwarp) {
     const int h = (int)(idx % Htot);
     const long long bt = idx / Htot;
     const int t = (int)(bt % Tn), b = (int)(bt / Tn);
@@ -261,29 +285,47 @@ __global__ void __launch_bounds__(256)
     // gate = ga * (gb * c - 1) + 2
     const float dga = dg * (gb * c - 1.f), dgb = dg * ga * c;
     const float dpa = dga * ga * (1.f - ga), dpb = dgb * gb * (1.f - gb);  // wrt the pre-sigmoid sums
-    if (lane == 0) atomicAdd(&s_dc[h], dg * ga * gb);
+    if (lane == 0) s_dc[h] += dg * ga * gb;
     dbA += dpa;
     dbB += dpb;
     const long long xo = bt * ((long long)Htot * Dh) + (long long)h * Dh;
 #pragma unroll
-    for (int q = 0; q < NPL; ++q) {
-      const int d = lane + 32 * q;
-      if (d < Dh) {
-        const float xd = to_f(x[xo + d]);
-        accA[q] = fmaf(dpa, xd, accA[q]);
-        accB[q] = fmaf(dpb, xd, accB[q]);
-        if (dx) dx[xo + d] = from_f<T>(to_f(dx[xo + d]) + dpa * wA[q] + dpb * wB[q]);
+    for (int q = 0; q < NP; ++q) {
+      const int d = 64 * q + 2 * lane;
+      if (d >= Dh) continue;
+      float x0, x1 = 0.f;
+      if (even) {
+        load_pair(x + xo + d, x0, x1);
+      } else {
+        x0 = to_f(x[xo + d]);
+        if (d + 1 < Dh) x1 = to_f(x[xo + d + 1]);
+      }
+      accA[q][0] = fmaf(dpa, x0, accA[q][0]);
+      accB[q][0] = fmaf(dpb, x0, accB[q][0]);
+      accA[q][1] = fmaf(dpa, x1, accA[q][1]);
+      accB[q][1] = fmaf(dpb, x1, accB[q][1]);
+      if (dx) {
+        if (even) {
+          float g0, g1;
+          load_pair(dx + xo + d, g0, g1);
+          store_pair(dx + xo + d, g0 + dpa * wA[q][0] + dpb * wB[q][0], g1 + dpa * wA[q][1] + dpb * wB[q][1]);
+        } else {
+          dx[xo + d] = from_f<T>(to_f(dx[xo + d]) + dpa * wA[q][0] + dpb * wB[q][0]);
+          if (d + 1 < Dh) dx[xo + d + 1] = from_f<T>(to_f(dx[xo + d + 1]) + dpa * wA[q][1] + dpb * wB[q][1]);
+        }
       }
     }
   }
 #pragma unroll
-  for (int q = 0; q < NPL; ++q) {
-    const int d = lane + 32 * q;
-    if (d < Dh) {
-      atomicAdd(&s_A[d], accA[q]);
-      atomicAdd(&s_B[d], accB[q]);
+  for (int q = 0; q < NP; ++q)
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int d = 64 * q + 2 * lane + e;
+      if (d < Dh) {
+        atomicAdd(&s_A[d], accA[q][e]);   // once per warp per element
+        atomicAdd(&s_B[d], accB[q][e]);
+      }
     }
-  }
   if (lane == 0) {
     atomicAdd(&s_db[0], dbA);
     atomicAdd(&s_db[1], dbB);
@@ -291,7 +333,11 @@ __global__ void __launch_bounds__(256)
   __syncthreads();
   for (int q = threadIdx.x; q < 8 * Dh; q += blockDim.x) atomicAdd(dWg + q, (q / Dh) < 4 ? s_A[q % Dh] : s_B[q % Dh]);
   for (int q = threadIdx.x; q < 8; q += blockDim.x) atomicAdd(dbg + q, q < 4 ? s_db[0] : s_db[1]);
-  for (int q = threadIdx.x; q < Htot; q += blockDim.x) atomicAdd(dcst + q, s_dc[q]);
+  for (int q = threadIdx.x; q < Htot; q += blockDim.x) {
+    float tsum = 0.f;
+    for (int w8 = 0; w8 < nwarp; ++w8) tsum += s_dc_all[w8 * Htot + q];
+    atomicAdd(dcst + q, tsum);
+  }
 }
 
 }  // namespace dph
@@ -364,7 +410,7 @@ extern "C" int dph_wavlm_gate_bwd(const void* x, const float* Wg, const float* c
     set_error("wavlm_gate_bwd: head dim %d not supported (<= 128)", Dh);
     return DPH_ERR_UNSUPPORTED;
   }
-  const size_t smem = sizeof(float) * (2 * Dh + 2 + Htot);
+  const size_t smem = sizeof(float) * (2 * Dh + 2 + 8 * Htot);   // 8 warps per block, one dconst slice each
   const long long rows = (long long)B * T * Htot;
   const int grid = (int)(rows / 8 < 148 * 4 ? (rows + 7) / 8 : 148 * 4);
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);

@@ -1452,7 +1452,8 @@ def encoder_bwd(plan: Plan, st, dh, dmasks, A):
             if dt == torch.bfloat16 and Cgp % 64 == 0:
                 # all K taps folded into N (column = tap * Cgp + ci): one A tile feeds 4 taps of a 256-wide MMA instead
                 # of K separate 64 x 64 products per group (which were bound by L2 -> shared-memory traffic)
-                G.gemm(a, bv, dwp, Cgp, K * Cgp, Kext, nb0=Gn, ldc=K * Cgp, c_sb0=Cgp * K * Cgp, b_taps=K, cta_group=1)
+                G.gemm(a, bv, dwp, Cgp, K * Cgp, Kext, nb0=Gn, ldc=K * Cgp, c_sb0=Cgp * K * Cgp, b_taps=K, cta_group=1,
+                       block_n=256)
             else:
                 G.gemm(a, bv, dwp, Cgp, Cgp, Kext, nb0=Gn, nb1=K, ldc=K * Cgp, c_sb0=Cgp * K * Cgp, c_sb1=Cgp)
             scratch = A("pos_wb_scratch", (K,), torch.float32)
