@@ -305,6 +305,197 @@ __global__ void __launch_bounds__(LNB_WARPS * 32, 1)
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Vectorised variants WITH the conv-block fusions of the Large extractor (components.py:54-61, 108-114):
+//   forward   y = colmask * GELU(LN(x))
+//   backward  through mask / GELU / LN in one pass, mask gradient reduced like dw / db, output rows optionally
+//             re-mapped into the zero-padded per-utterance layout the strided-conv dgrad GEMM reads.
+// These tensors are the largest of the whole Large step (8 x 47999 x 512 in layer 0); the generic one-scalar-per-lane
+// kernels ran them at a fifth of the memory bandwidth.  bf16 uses the tanh-form GELU of the other bf16 kernels
+// (error below bf16 resolution; one MUFU per element keeps the kernel memory-bound), fp32 the erf form.
+// ---------------------------------------------------------------------------------------------------------------
+template <typename T>
+DPH_DEVICE void gelu_pair_fwd(float& a, float& b) {
+  if constexpr (sizeof(T) == 2) {
+    upk2(gelu_tanh2(pk2(a, b)), a, b);
+  } else {
+    a = gelu_erf(a);
+    b = gelu_erf(b);
+  }
+}
+template <typename T>
+DPH_DEVICE void gelu_pair_bwd(float ua, float ub, float& ga, float& gb, float& da, float& db) {
+  if constexpr (sizeof(T) == 2) {
+    f32x2 g2, d2;
+    gelu_and_grad_tanh2(pk2(ua, ub), g2, d2);
+    upk2(g2, ga, gb);
+    upk2(d2, da, db);
+  } else {
+    ga = gelu_erf(ua);
+    gb = gelu_erf(ub);
+    da = gelu_erf_grad(ua);
+    db = gelu_erf_grad(ub);
+  }
+}
+
+template <typename T, int Q>
+__global__ void __launch_bounds__(256)
+    layernorm_fwd_vecf_kernel(const T* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
+                              T* __restrict__ y, float* __restrict__ mean_out, float* __restrict__ rstd_out,
+                              const float* __restrict__ colmask, int rows, int D, float eps, int act) {
+  constexpr int VEC = VecOf<T>::N;
+  const int lane = threadIdx.x & 31;
+  const int warps_per_blk = blockDim.x >> 5;
+  pdl_wait();
+  pdl_trigger();
+  float wv[Q][VEC], bv[Q][VEC], mv[Q][VEC];
+#pragma unroll
+  for (int q = 0; q < Q; ++q) {
+    load_vec_f32(w + (lane + 32 * q) * VEC, wv[q]);
+    load_vec_f32(b + (lane + 32 * q) * VEC, bv[q]);
+    if (colmask) {
+      load_vec_f32(colmask + (lane + 32 * q) * VEC, mv[q]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) mv[q][j] = 1.f;
+    }
+  }
+  for (int row = blockIdx.x * warps_per_blk + (threadIdx.x >> 5); row < rows; row += gridDim.x * warps_per_blk) {
+    const T* xr = x + (long long)row * D;
+    float v[Q][VEC];
+    float s = 0.f;
+#pragma unroll
+    for (int q = 0; q < Q; ++q) {
+      load_vec(xr + (lane + 32 * q) * VEC, v[q]);
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) s += v[q][j];
+    }
+    const float mean = warp_sum(s) / D;
+    float qs = 0.f;
+#pragma unroll
+    for (int q = 0; q < Q; ++q)
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) {
+        const float d = v[q][j] - mean;
+        qs += d * d;
+      }
+    const float rstd = rsqrtf(warp_sum(qs) / D + eps);
+    if (lane == 0) {
+      if (mean_out) mean_out[row] = mean;
+      if (rstd_out) rstd_out[row] = rstd;
+    }
+    T* yr = y + (long long)row * D;
+#pragma unroll
+    for (int q = 0; q < Q; ++q) {
+      float o[VEC];
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) o[j] = (v[q][j] - mean) * rstd * wv[q][j] + bv[q][j];
+      if (act == 1) {
+#pragma unroll
+        for (int j = 0; j < VEC; j += 2) gelu_pair_fwd<T>(o[j], o[j + 1]);
+      }
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) o[j] *= mv[q][j];
+      store_vec(yr + (lane + 32 * q) * VEC, o);
+    }
+  }
+}
+
+template <typename T, int Q>
+__global__ void __launch_bounds__(LNB_WARPS * 32, 1)
+    layernorm_bwd_vecf_kernel(const T* __restrict__ dy, const T* __restrict__ x, const float* __restrict__ w,
+                              const float* __restrict__ b, const float* __restrict__ mean_in,
+                              const float* __restrict__ rstd_in, T* __restrict__ dx, float* __restrict__ dw,
+                              float* __restrict__ db, const float* __restrict__ colmask, float* __restrict__ dmask,
+                              int rows, int D, int act, int rows_per_batch, long long out_bs, int out_row_off) {
+  constexpr int VEC = VecOf<T>::N;
+  extern __shared__ float sh[];  // [LNB_WARPS][D]
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  // (512 threads -> 128 registers: scale, shift and mask are re-read per row through L1 instead of living in registers)
+  float a_dw[Q][VEC], a_db[Q][VEC], a_dm[Q][VEC];
+  pdl_wait();
+  pdl_trigger();
+#pragma unroll
+  for (int q = 0; q < Q; ++q) {
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) a_dw[q][j] = a_db[q][j] = a_dm[q][j] = 0.f;
+  }
+  for (int row = blockIdx.x * LNB_WARPS + wid; row < rows; row += gridDim.x * LNB_WARPS) {
+    const long long off = (long long)row * D;
+    const float mean = mean_in[row], rstd = rstd_in[row];
+    float g[Q][VEC], xh[Q][VEC];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int q = 0; q < Q; ++q) {
+      const int c0 = (lane + 32 * q) * VEC;
+      load_vec(dy + off + c0, g[q]);
+      load_vec(x + off + c0, xh[q]);
+      float wvq[VEC], bvq[VEC], mvq[VEC];
+      load_vec_f32(w + c0, wvq);
+      load_vec_f32(b + c0, bvq);
+      if (colmask) {
+        load_vec_f32(colmask + c0, mvq);
+      } else {
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) mvq[j] = 1.f;
+      }
+#pragma unroll
+      for (int j = 0; j < VEC; j += 2) {
+        const float xa = (xh[q][j] - mean) * rstd, xb = (xh[q][j + 1] - mean) * rstd;
+        const float ua = xa * wvq[j] + bvq[j], ub = xb * wvq[j + 1] + bvq[j + 1];
+        float ga = ua, gb = ub, da = 1.f, dbb = 1.f;
+        if (act == 1) gelu_pair_bwd<T>(ua, ub, ga, gb, da, dbb);
+        float d0 = g[q][j], d1 = g[q][j + 1];
+        a_dm[q][j] += d0 * ga;            // d mask = sum dy * act(u)
+        a_dm[q][j + 1] += d1 * gb;
+        d0 *= mvq[j] * da;                // through the mask and the activation
+        d1 *= mvq[j + 1] * dbb;
+        a_dw[q][j] += d0 * xa;
+        a_dw[q][j + 1] += d1 * xb;
+        a_db[q][j] += d0;
+        a_db[q][j + 1] += d1;
+        const float g0 = d0 * wvq[j], g1 = d1 * wvq[j + 1];
+        g[q][j] = g0;
+        g[q][j + 1] = g1;
+        xh[q][j] = xa;
+        xh[q][j + 1] = xb;
+        s1 += g0 + g1;
+        s2 += g0 * xa + g1 * xb;
+      }
+    }
+    s1 = warp_sum(s1) / D;
+    s2 = warp_sum(s2) / D;
+    const int ob = row / rows_per_batch;
+    const long long ooff = (long long)ob * out_bs + (long long)(row - ob * rows_per_batch + out_row_off) * D;
+#pragma unroll
+    for (int q = 0; q < Q; ++q) {
+      float o[VEC];
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) o[j] = rstd * (g[q][j] - s1 - xh[q][j] * s2);
+      store_vec(dx + ooff + (lane + 32 * q) * VEC, o);
+    }
+  }
+#pragma unroll
+  for (int which = 0; which < 3; ++which) {
+    float* outp = which == 0 ? dw : (which == 1 ? db : dmask);
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < Q; ++q)
+#pragma unroll
+      for (int j = 0; j < VEC; ++j)
+        sh[wid * D + (lane + 32 * q) * VEC + j] = which == 0 ? a_dw[q][j] : (which == 1 ? a_db[q][j] : a_dm[q][j]);
+    __syncthreads();
+    if (outp) {
+      for (int c = threadIdx.x; c < D; c += blockDim.x) {
+        float t = 0.f;
+#pragma unroll
+        for (int q = 0; q < LNB_WARPS; ++q) t += sh[q * D + c];
+        atomicAdd(outp + c, t);
+      }
+    }
+  }
+}
+
 }  // namespace dph
 
 using namespace dph;
@@ -339,6 +530,24 @@ extern "C" int dph_layernorm_fwd(const void* x, const float* w, const float* b, 
 #undef LN_FV
       dph_count_launch();
       return dph_check_last("layernorm_fwd_vec");
+    }
+    // the same with GELU / column mask fused (conv blocks of the Large extractor)
+    const bool alm = !colmask || (reinterpret_cast<uintptr_t>(colmask) & 15) == 0;
+    if (al && alm && !y_pre && (colmask || act == 1) && drop_p == 0.f && d_valid == D && D % (32 * vec) == 0 &&
+        q >= 1 && q <= 4) {
+      int g = (rows + warps_per_blk - 1) / warps_per_blk;
+      if (g > 148 * 8) g = 148 * 8;
+#define LN_FF(T, Q)                                                                                                   \
+  launch_pdl(layernorm_fwd_vecf_kernel<T, Q>, dim3(g), dim3(256), 0, s, (const T*)x, w, b, (T*)y, mean, rstd, colmask, \
+             rows, D, eps, act)
+      if (dtype == DPH_DTYPE_BF16) {
+        if (q == 1) LN_FF(bf16, 1); else if (q == 2) LN_FF(bf16, 2); else if (q == 3) LN_FF(bf16, 3); else LN_FF(bf16, 4);
+      } else {
+        if (q == 1) LN_FF(float, 1); else if (q == 2) LN_FF(float, 2); else if (q == 3) LN_FF(float, 3); else LN_FF(float, 4);
+      }
+#undef LN_FF
+      dph_count_launch();
+      return dph_check_last("layernorm_fwd_vecf");
     }
   }
   const int grid = (rows + warps_per_blk - 1) / warps_per_blk;
@@ -411,6 +620,34 @@ extern "C" int dph_layernorm_bwd(const void* dy, const void* dy2, const void* x,
 #undef LN_BV
       dph_count_launch();
       return dph_check_last("layernorm_bwd_vec");
+    }
+    // fused variant: mask / GELU backward, mask gradient, re-mapped output rows (no dropout, no second gradient)
+    const bool alm = !colmask || (reinterpret_cast<uintptr_t>(colmask) & 15) == 0;
+    const bool rows_al = (out_bs % vec == 0);
+    if (al && alm && rows_al && !dy2 && drop_p == 0.f && d_valid == D && D % (32 * vec) == 0 && q >= 1 &&
+        q * vec <= 16 /* <= 16 elements per lane: D <= 512 */ && (size_t)LNB_WARPS * D * sizeof(float) <= 96 * 1024) {
+      int g = (rows + LNB_WARPS - 1) / LNB_WARPS;
+      if (g > 148) g = 148;
+      const size_t smem = (size_t)LNB_WARPS * D * sizeof(float);
+#define LN_BF(T, Q)                                                                                                   \
+  do {                                                                                                                \
+    static bool attr = false;                                                                                         \
+    if (!attr) {                                                                                                      \
+      cudaFuncSetAttribute(layernorm_bwd_vecf_kernel<T, Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);  \
+      attr = true;                                                                                                    \
+    }                                                                                                                 \
+    launch_pdl(layernorm_bwd_vecf_kernel<T, Q>, dim3(g), dim3(LNB_WARPS * 32), smem, s, (const T*)dy, (const T*)x, w, \
+               b, mean, rstd, (T*)dx, dw, db, colmask, dmask, rows, D, act, rows_per_batch, (long long)out_bs,        \
+               out_row_off);                                                                                          \
+  } while (0)
+      if (dtype == DPH_DTYPE_BF16) {
+        if (q == 1) LN_BF(bf16, 1); else if (q == 2) LN_BF(bf16, 2); else if (q == 3) LN_BF(bf16, 3); else LN_BF(bf16, 4);
+      } else {
+        if (q == 1) LN_BF(float, 1); else if (q == 2) LN_BF(float, 2); else if (q == 3) LN_BF(float, 3); else LN_BF(float, 4);
+      }
+#undef LN_BF
+      dph_count_launch();
+      return dph_check_last("layernorm_bwd_vecf");
     }
   }
   // ~4 CTAs per SM worth of work; each warp walks rows_per_warp consecutive rows

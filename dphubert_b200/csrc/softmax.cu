@@ -521,7 +521,8 @@ extern "C" int dph_wavlm_gate_bwd(const void* x, const float* Wg, const float* c
   if (fast) {
     const int rpw = 32 / (Dh / vec);
     const long long passes = (rows + rpw - 1) / rpw;
-    const int g2 = (int)(passes / 8 < 148 * 8 ? (passes + 7) / 8 : 148 * 8);
+    // two blocks per SM: every block ends with ~8 * Dh global atomics onto the same addresses, keep them few
+    const int g2 = (int)(passes / 8 < 148 * 2 ? (passes + 7) / 8 : 148 * 2);
     if (dtype == DPH_DTYPE_BF16)
       wavlm_gate_bwd_vec_kernel<bf16><<<g2, 256, smem, s>>>((const bf16*)x, Wg, cst, ga, gb, dgate, (bf16*)dx, dWg, dbg,
                                                             dcst, B, T, Htot, Dh);

@@ -102,6 +102,30 @@ def test_layernorm_fwd_bwd(dt, D):
 
 
 @pytest.mark.parametrize("dt", [F32, BF16])
+@pytest.mark.parametrize("D", [512, 256, 1024])
+def test_layernorm_conv_block_fusions(dt, D):
+    """the Large extractor's conv blocks (components.py:54-61, 108-114): y = mask * GELU(LN(x)) and its backward into
+    the zero-padded per-utterance row layout — the fused vectorised kernels (D <= 512) and the generic ones (1024)"""
+    Bn, Tn, padr = 3, 1111, 3
+    rows = Bn * Tn
+    x, w, b = rnd(rows, D, dtype=dt), rnd(D) * 0.2 + 1, rnd(D) * 0.1
+    cm = torch.rand(D, device=DEV)
+    y, mean, rstd = zer(rows, D, dtype=dt), zer(rows), zer(rows)
+    both("layernorm_fwd", (x, w, b, y, rows, D, 1e-5), dict(mean=mean, rstd=rstd, colmask=cm, act=1),
+         tol=2e-2 if dt == BF16 else 2e-5)
+    dy = rnd(rows, D, dtype=dt)
+    dzp = zer(Bn, Tn + 2 * padr, D, dtype=dt)
+    both("layernorm_bwd", (dy, x, w, b, mean, rstd, dzp, zer(D), zer(D), rows, D),
+         dict(colmask=cm, dmask=zer(D), act=1, rows_per_batch=Tn, out_bs=(Tn + 2 * padr) * D, out_row_off=padr),
+         tol=3e-2 if dt == BF16 else 2e-4)
+    assert float(dzp[:, :padr].abs().max()) == 0.0 and float(dzp[:, -padr:].abs().max()) == 0.0
+    # no remap, no mask (conv layer 0 of the Large extractor without a gate)
+    dx = zer(rows, D, dtype=dt)
+    both("layernorm_bwd", (dy, x, w, b, mean, rstd, dx, zer(D), zer(D), rows, D), dict(act=1),
+         tol=3e-2 if dt == BF16 else 2e-4)
+
+
+@pytest.mark.parametrize("dt", [F32, BF16])
 @pytest.mark.parametrize("D,Dv", [(448, 397), (512, 500), (64, 50)])
 def test_layernorm_zero_padded_width(dt, D, Dv):
     """d_valid < D: only the real columns of a zero-padded row are normalised; padding comes back as exact zeros."""
