@@ -434,7 +434,8 @@ def test_attention_dropout_keep_rate():
 
 def test_conv0_full_size_tensor_core_vs_fp32():
     """BASELINE size (8 x 10 s): the bf16 tensor-core forward (hi/lo split taps, tanh-form GELU) against the fp32
-    CUDA-core kernel (exact FMA chain, erf GELU) on the same inputs; every frame of every utterance is written"""
+    CUDA-core kernel (exact FMA chain, erf GELU) on the same inputs — every frame of every utterance is written — and
+    both against torch.nn.functional conv1d + group_norm + gelu on the CPU for (utterance, channel) slices"""
     Bn, T0, k, s, C = 8, 160000, 10, 5, 512
     T1 = (T0 - k) // s + 1
     wave = rnd(Bn, T0) * 0.1
@@ -459,6 +460,17 @@ def test_conv0_full_size_tensor_core_vs_fp32():
     var = z.var(1, unbiased=False)
     assert zn.mean(1).abs().max() < 1e-3
     assert (zn.var(1, unbiased=False) - var / (var + 1e-5)).abs().max() < 2e-4  # rstd = 1 / sqrt(var + eps)
+    # and both kernels against torch on the CPU (conv1d -> per-channel GroupNorm -> erf GELU -> mask), for slices of
+    # (utterance, channel block) spread over the batch and the 512 channels (components.py:94-120)
+    F = torch.nn.functional
+    for bi, c0 in [(0, 0), (3, 252), (7, 508), (5, 129)]:
+        cs = slice(c0, c0 + 4)
+        zc = F.conv1d(wave[bi].cpu()[None, None, :], w[cs].cpu(), stride=s)
+        ref = F.gelu(F.group_norm(zc, 4, gamma[cs].cpu(), beta[cs].cpu(), 1e-5))[0].t() * mask[cs].cpu()
+        e32 = (y32[bi, :, cs].cpu() - ref).abs()
+        e16 = (y16[bi, :, cs].float().cpu() - ref).abs()
+        assert e32.max() < 1e-4 * max(1.0, float(ref.abs().max())), (bi, c0, e32.max().item())
+        assert (e16 <= 4e-3 * ref.abs() + 1e-3).all(), (bi, c0, e16.max().item())
 
 
 def test_fused_attention_full_size_vs_torch():

@@ -101,6 +101,12 @@ def test_shape_keyed_graph_cache_matches_eager():
         for h in s[2].modules():
             if hasattr(h, "noise"):
                 h.noise = None
+        # A SMOOTH objective for the twin comparison: the L1 term's gradient is w1 * sign(pred - target) / N, and the
+        # forward pass is reproducible only to fp32 round-off (atomically accumulated reductions), so an element with
+        # pred - target ~ 0 flips between -1 / 0 / +1 from run to run — measured with profiles/diag_graph_vs_eager.py:
+        # one such element at step 7 moves the gradient norm by exact multiples of 5.4e-5, in the eager twin as often
+        # as in the graph twin, with or without side streams / PDL.  MSE + cosine have no such jump.
+        s[0].w2, s[0].w1 = 1.0, 0.0
         return s
 
     shapes = [8000, 5000, 8000, 5000, 6500, 8000, 5000, 6500, 8000, 6500, 5000]
