@@ -419,6 +419,18 @@ __global__ void __launch_bounds__(1024)
 using namespace dph;
 
 namespace dph {
+int conv0_bwd_tc(const float* wave, long long wave_bs, const float* w, const float* bias, const float* gamma,
+                 const float* beta, const float* mean, const float* rstd, const float* mask, const bf16* dy,
+                 float* scratch, float* dmask, int B, int C, int k, int stride, int T1, int norm, int act,
+                 cudaStream_t s);
+// DPH_CONV0_BWD_TC=0 keeps the CUDA-core backward (debugging / A-B timing)
+static bool conv0_bwd_tc_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("DPH_CONV0_BWD_TC");
+    return !(e != nullptr && e[0] == '0');
+  }();
+  return on;
+}
 int conv0_fwd_tc(const float* wave, long long wave_bs, const float* w, const float* bias, const float* gamma,
                  const float* beta, const float* mean, const float* rstd, const float* mask, bf16* y, int B, int C, int k,
                  int stride, int T1, int norm, int act, cudaStream_t s);
@@ -494,7 +506,16 @@ extern "C" int dph_conv0_bwd(const float* wave, int64_t wave_bs, const float* w,
   dim3 grid((T1 + C0F_TT - 1) / C0F_TT, B);
   const int pair_vec = (C % 2 == 0) && ((reinterpret_cast<uintptr_t>(dy) & 3) == 0);
   cudaMemsetAsync(scratch, 0, sizeof(float) * 16 * (size_t)B * C, s);
-  if (dtype == DPH_DTYPE_BF16)
+  bool on_tc = false;
+  if (dtype == DPH_DTYPE_BF16 && conv0_bwd_tc_enabled()) {
+    // tensor-core formulation of the same per-(b, c) sums (conv0_bwd_tc.cu); shapes outside its envelope fall through
+    rc = conv0_bwd_tc(wave, wave_bs, w, bias, gamma, beta, mean, rstd, mask, (const bf16*)dy, scratch, dmask, B, C, k,
+                      stride, T1, norm, act, s);
+    if (rc == DPH_OK) on_tc = true;
+    else if (rc != DPH_ERR_UNSUPPORTED) return rc;
+  }
+  if (on_tc) {
+  } else if (dtype == DPH_DTYPE_BF16)
     conv0_bwd_fused_kernel<bf16><<<grid, C0_THREADS, 0, s>>>(wave, wave_bs, w, bias, gamma, beta, mean, rstd, mask,
                                                              (const bf16*)dy, scratch, dmask, C, k, stride, T1, norm,
                                                              act, pair_vec);

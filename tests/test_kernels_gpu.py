@@ -473,6 +473,34 @@ def test_conv0_full_size_tensor_core_vs_fp32():
         assert (e16 <= 4e-3 * ref.abs() + 1e-3).all(), (bi, c0, e16.max().item())
 
 
+def test_conv0_bwd_full_size_tensor_core_vs_fp32():
+    """BASELINE size (8 x 10 s, 512 channels): the tensor-core backward (conv0_bwd_tc.cu: recompute + gradient sums
+    as two tcgen05 products, du rounded to bf16) against the fp32 CUDA-core kernel fed with the SAME (bf16-valued)
+    upstream gradient; a ragged last tile (49 999 frames) and every utterance boundary of the persistent CTAs"""
+    Bn, T0, k, s, C = 8, 160000, 10, 5, 512
+    T1 = (T0 - k) // s + 1
+    wave = rnd(Bn, T0) * 0.1
+    w = rnd(C, 1, k) * 0.3
+    gamma, beta, mask = rnd(C) * 0.2 + 1, rnd(C) * 0.1, torch.rand(C, device=DEV)
+    mean, rstd = zer(Bn * C), zer(Bn * C)
+    moments = torch.zeros(Bn * 65, device=DEV, dtype=torch.float64)
+    ops.conv0_stats(wave, w, None, moments, mean, rstd, Bn, C, k, s, T1, 1e-5)
+    dy16 = (rnd(Bn, T1, C) * (1.0 + rnd(1, 1, C).abs())).to(BF16)
+    outs = {}
+    for name, dy in (("fp32", dy16.float()), ("tc", dy16)):
+        o = [zer(C, 1, k), zer(C), zer(C), zer(C)]   # dW, dgamma, dbeta, dmask
+        ops.conv0_bwd(wave, w, None, gamma, beta, mean, rstd, moments, mask, dy, zer(16 * Bn * C), o[0], None, o[1], o[2],
+                      o[3], Bn, C, k, s, T1, 1, 1)
+        outs[name] = o
+    torch.cuda.synchronize()
+    for nm, a, b in zip(("dW", "dgamma", "dbeta", "dmask"), outs["tc"], outs["fp32"]):
+        assert torch.isfinite(a).all()
+        e_max = (a - b).abs().max().item() / b.abs().max().item()
+        e_l2 = (a - b).norm().item() / b.norm().item()
+        # sums of ~400 000 terms each rounded to 2^-9: measured 1e-3 .. 4e-3
+        assert e_max < 2e-2 and e_l2 < 1e-2, (nm, e_max, e_l2)
+
+
 def test_fused_attention_full_size_vs_torch():
     """BASELINE size (B = 8, H = 12, T = 499): fused tcgen05 attention forward / backward against plain torch fp32
     matmul + softmax + autograd on the same bf16-rounded inputs (tolerance 3e-2 of the tensor's max: bf16 P / dS tiles,
