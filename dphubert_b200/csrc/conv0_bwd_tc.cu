@@ -44,7 +44,8 @@ constexpr int S_E = S_A + 2 * TT * 128;           // constant tile: column 31 = 
 constexpr int S_H = S_E + TT * 128;               // du tile: 2 sub-tiles [128 frames][64 ch] bf16          32 KB
 constexpr int S_G = S_H + 2 * TT * 128;           // dy * act(u) tile, same layout                          32 KB
 constexpr int S_TAB = S_G + 2 * TT * 128;         // per channel pair {sc0, sc1, sh0, sh1}                   4 KB
-constexpr int S_BAR = S_TAB + (MAXC / 2) * 16;
+constexpr int S_DY = S_TAB + (MAXC / 2) * 16;    // dy staging, 2 KB per epilogue warp (coalesced -> row per thread) 32 KB
+constexpr int S_BAR = S_DY + EPI_WARPS * 2048;
 constexpr int SMEM = S_BAR + 256 + 1024;
 constexpr int D2_COL = 2 * NB;                    // TMEM: two Z accumulators (2 x 128 columns), then 4 x 32 columns of D
 
@@ -285,25 +286,37 @@ __global__ void __launch_bounds__(THREADS, 1) conv0_bwd_tc_kernel(const __grid_c
     int cur_b = -1;
     uint32_t touched = 0, nflush = 0;
     // position of a unit, advanced incrementally (no divisions in the unit loop)
+    // (kernel parameters the unit loop needs, held in registers: a constant-bank load per use is a scoreboard stall)
+    const int nblk = p.nblk, ntile = p.ntile, T1 = p.T1, C = p.C;
+    const bf16* const dyp = p.dy;
+    uint32_t act_mask = 0;   // bit blk: this warp's 32-column slice lies inside channel block blk
+    for (int q = 0; q < nblk; ++q) act_mask |= (cl < min(NB, C - q * NB) ? 1u : 0u) << q;
     struct Pos { int b, tile, blk; };
     auto advance = [&](Pos q) {
-      if (++q.blk == p.nblk) {
+      if (++q.blk == nblk) {
         q.blk = 0;
-        if (++q.tile == p.ntile) { q.tile = 0; ++q.b; }
+        if (++q.tile == ntile) { q.tile = 0; ++q.b; }
       }
       return q;
     };
-    // 64 bytes of dy per thread and unit: frame t0 + frow, channels c0 .. c0 + 31 (zeros outside the tensor)
+    // dy of a unit for this warp: 32 frames x 32 channels (64 B per frame).  Loaded COALESCED — request e of lane l is the
+    // 16-byte piece l % 4 of frame 8 e + l / 4, so one warp request covers 8 rows x 64 B (a row-per-thread load touches
+    // 32 cache lines per request and saturates the L1 tag stage: ncu l1tex 71 %, the first use of dy 19 % of all
+    // stall samples) — one unit ahead, and transposed to row-per-thread through a 2 KB shared-memory tile per warp.
     auto load_dy = [&](bool valid, Pos q, uint4 (&v)[4]) {
 #pragma unroll
       for (int e = 0; e < 4; ++e) v[e] = make_uint4(0u, 0u, 0u, 0u);
-      const int tn = q.tile * TT + frow;
-      if (valid && cl < min(NB, p.C - q.blk * NB) && tn < p.T1) {
-        const uint4* src = reinterpret_cast<const uint4*>(p.dy + ((long long)q.b * p.T1 + tn) * p.C + q.blk * NB + cl);
+      if (valid && ((act_mask >> q.blk) & 1u)) {
+        const int tq = q.tile * TT + quad * 32 + (lane >> 2);
+        const bf16* src = dyp + ((long long)q.b * T1 + tq) * C + q.blk * NB + cl + (lane & 3) * 8;
 #pragma unroll
-        for (int e = 0; e < 4; ++e) v[e] = __ldg(src + e);
+        for (int e = 0; e < 4; ++e)
+          if (tq + 8 * e < T1) v[e] = __ldg(reinterpret_cast<const uint4*>(src + (long long)(8 * e) * C));
       }
     };
+    const uint32_t dstage = sbase + S_DY + (uint32_t)ew * 2048u;
+    // staging address of (row, 16-byte piece): pieces XOR-swizzled by row pair, conflict-free for both access patterns
+    auto dy_addr = [&](int row, int piece) { return dstage + (uint32_t)(row * 64 + ((piece ^ ((row >> 1) & 3)) << 4)); };
     Pos cur;
     cur.blk = u0 % p.nblk;
     cur.tile = (u0 / p.nblk) % p.ntile;
@@ -316,13 +329,23 @@ __global__ void __launch_bounds__(THREADS, 1) conv0_bwd_tc_kernel(const __grid_c
       const int blk = cur.blk, acc = i & 1;
       const int b = cur.b, t0 = cur.tile * TT;
       const bool flush = u + 1 == u1 || nxt.b != cur.b;   // the sums in D belong to one utterance
-      const int nb = min(NB, p.C - blk * NB);
-      const bool active = cl < nb;       // C is a multiple of 32: a warp's 32 columns are all in or all out
+      const bool active = (act_mask >> blk) & 1u;   // C is a multiple of 32: a warp's 32 columns are all in or all out
       const int c0 = blk * NB + cl;
       // this thread's 32 upstream gradients (64 bytes) were requested one unit ahead; request the next unit's now
       uint4 dyv[4];
 #pragma unroll
-      for (int q = 0; q < 4; ++q) dyv[q] = dyn[q];
+      for (int e = 0; e < 4; ++e)
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dy_addr(8 * e + (lane >> 2), lane & 3)), "r"(dyn[e].x),
+                     "r"(dyn[e].y), "r"(dyn[e].z), "r"(dyn[e].w)
+                     : "memory");
+      __syncwarp();
+#pragma unroll
+      for (int e = 0; e < 4; ++e)
+        asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(dyv[e].x), "=r"(dyv[e].y), "=r"(dyv[e].z), "=r"(dyv[e].w)
+                     : "r"(dy_addr(lane, e))
+                     : "memory");
+      __syncwarp();
       load_dy(u + 1 < u1, nxt, dyn);
       if (b != cur_b) {
         // per-channel table of this utterance, interleaved per channel PAIR: {sc0, sc1, sh0, sh1}, u = sc z + sh

@@ -187,6 +187,25 @@ __global__ void posconv_pad_kernel(const T* __restrict__ x, T* __restrict__ xp, 
   }
 }
 
+// bf16, Cg % 8 == 0, Cgp % 8 == 0, 16-byte aligned buffers: one thread per 16-byte piece of an output row (the scalar
+// kernel above spends a 64-bit division chain per 2-byte element: 28.6 us for 3992 x 1024, this one moves the same
+// 14 MB at copy speed).  blockIdx.y = row, pieces across the threads.
+__global__ void __launch_bounds__(128)
+    posconv_pad_vec_kernel(const bf16* __restrict__ x, bf16* __restrict__ xp, int Tn, int G, int Cg, int Cgp, int front,
+                           int pad) {
+  const int row = blockIdx.x;                 // b * Tn + t
+  const int b = row / Tn, t = row - b * Tn;
+  const int ppg = Cgp >> 3;                   // pieces per group in the padded row
+  const uint4* src = reinterpret_cast<const uint4*>(x + (long long)row * (G * Cg));
+  uint4* dst = reinterpret_cast<uint4*>(xp + ((long long)front + (long long)b * (Tn + pad) + t) * (G * Cgp));
+  for (int pc = threadIdx.x; pc < G * ppg; pc += blockDim.x) {
+    const int g = pc / ppg, j = pc - g * ppg;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (j * 8 < Cg) v = __ldg(src + ((g * Cg) >> 3) + j);
+    dst[pc] = v;
+  }
+}
+
 // inverse gather: staging rows -> dense (B,T,G*Cg), optionally accumulating into the destination
 template <typename T>
 __global__ void posconv_unpad_kernel(const T* __restrict__ xp, T* __restrict__ x, int B, int Tn, int G, int Cg, int Cgp,
@@ -376,6 +395,12 @@ extern "C" int dph_posconv_pad(const void* x, void* xp, int B, int T, int G, int
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   long long total = (long long)B * T * G * Cgp;
   int grid = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+  if (dtype == DPH_DTYPE_BF16 && Cg % 8 == 0 && Cgp % 8 == 0 &&
+      ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(xp)) & 15) == 0 && (long long)B * T < (1LL << 31)) {
+    posconv_pad_vec_kernel<<<B * T, 128, 0, s>>>((const bf16*)x, (bf16*)xp, T, G, Cg, Cgp, front, pad);
+    dph_count_launch();
+    return dph_check_last("posconv_pad");
+  }
   if (dtype == DPH_DTYPE_BF16)
     posconv_pad_kernel<bf16><<<grid, 256, 0, s>>>((const bf16*)x, (bf16*)xp, B, T, G, Cg, Cgp, front, pad);
   else

@@ -173,9 +173,9 @@ def test_small_elementwise(dt):
     x = rnd(3, 50, 40, dtype=dt)
     lengths = torch.tensor([50, 20, 0], device=DEV)
     both("pad_rows_zero", (x, lengths, 3, 50, 40))
-    Bn, Tn, Gn, Cg, Cgp, front, pad = 2, 37, 4, 48, 64, 8, 16
-    xp = zer(front + Bn * (Tn + pad) + 16, Gn * Cgp, dtype=dt)
-    both("posconv_pad", (rnd(Bn, Tn, Gn * Cg, dtype=dt), xp, Bn, Tn, Gn, Cg, Cgp, front, pad))
+    for Bn, Tn, Gn, Cg, Cgp, front, pad in ((2, 37, 4, 48, 64, 8, 16), (3, 21, 2, 12, 16, 4, 8)):   # vectorised / scalar
+        xp = zer(front + Bn * (Tn + pad) + 16, Gn * Cgp, dtype=dt)
+        both("posconv_pad", (rnd(Bn, Tn, Gn * Cg, dtype=dt), xp, Bn, Tn, Gn, Cg, Cgp, front, pad))
     src = rnd(777)
     both("cast", (src, zer(777, dtype=BF16)))
     both("vec_mul", (rnd(100), rnd(100), rnd(100), 0.5, 1.0))
@@ -308,12 +308,14 @@ def test_adamw_and_sumsq():
     both("counter_inc", (step,))
 
 
-def test_weight_prep():
-    Cout, Cin, k = 64, 128, 3
+@pytest.mark.parametrize("Cout,Cin,k,perm,D,Gn,K", [(64, 128, 3, [1, 2, 0], 192, 4, 16),        # tiled kernels
+                                                     (512, 512, 2, [1, 0], 768, 16, 128),         # the real geometry
+                                                     (48, 40, 5, [4, 3, 2, 1, 0], 96, 2, 24)])    # general fallbacks
+def test_weight_prep(Cout, Cin, k, perm, D, Gn, K):
     w = rnd(Cout, Cin, k)
-    both("conv_weight_prep", (w, zer(Cout, k, Cin, dtype=BF16), zer(k, Cin, Cout, dtype=BF16), Cout, Cin, k, [1, 2, 0]))
+    both("conv_weight_prep", (w, zer(Cout, k, Cin, dtype=BF16), zer(k, Cin, Cout, dtype=BF16), Cout, Cin, k, perm))
     both("conv_wgrad_unpermute", (rnd(Cout, k * Cin), zer(Cout, Cin, k), Cout, Cin, k))
-    D, Gn, Cg, Cgp, K = 192, 4, 48, 64, 16
+    Cg, Cgp = 48, 64
     v, g = rnd(D, Cg, K), rnd(1, 1, K) + 2
     norm = zer(K)
     both("posconv_weight_prep", (v, g, norm, zer(D, Cg, K), zer(Gn, Cg, K, Cgp, dtype=BF16), zer(Gn, Cg, K, Cgp, dtype=BF16),
