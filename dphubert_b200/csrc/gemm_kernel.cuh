@@ -28,10 +28,13 @@ namespace dph {
 
 constexpr int BM = 128;
 constexpr int BK = 64;
-// Eight epilogue warps: measured best. Sixteen (one per 64-column slice of a 256-wide tile) cap the kernel at 96
-// registers per thread and lose more to spills and barrier traffic than the extra latency hiding returns.
-constexpr int epi_warps(int) { return 8; }
-constexpr int gemm_threads(int bn) { return 64 + 32 * epi_warps(bn); }
+// Eight epilogue warps: measured best for the forward classes. Sixteen (one per 64-column slice of a 256-wide tile)
+// cap the kernel at 96 registers per thread and lose more to spills and barrier traffic than the extra latency hiding
+// returns.  The fused-backward class (F_ACTBWD = 512) is the exception: its epilogue waits on the pre-activation
+// loads (ncu: issue slots 32 % busy, long-scoreboard stalls on z, 16 us per tile against a 3.3 us main loop), so it
+// runs sixteen warps over 16-column half chunks that fit the 96-register budget.
+__host__ __device__ constexpr int epi_warps(int bn, int f) { return ((f & 512) != 0 && bn % 128 == 0) ? 16 : 8; }
+__host__ __device__ constexpr int gemm_threads(int bn, int f) { return 64 + 32 * epi_warps(bn, f); }
 
 enum EpiFeature : int {
   F_BIAS = 1,      // + bias[n]
@@ -338,6 +341,32 @@ DPH_DEVICE float warp_colsum32(float (&v)[32], int lane) {
   return v[0];
 }
 
+// 16 per-lane values: after the butterfly lanes l and l + 16 both hold the sum over all lanes of v[l % 16]. Destroys v.
+DPH_DEVICE float warp_colsum16(float (&v)[16], int lane) {
+#pragma unroll
+  for (int w = 8; w >= 1; w >>= 1) {
+    const bool hi = (lane & w) != 0;
+#pragma unroll
+    for (int j = 0; j < w; ++j) {
+      const float send = hi ? v[j] : v[j + w];
+      const float keep = hi ? v[j + w] : v[j];
+      v[j] = keep + __shfl_xor_sync(0xffffffffu, send, w);
+    }
+  }
+  return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 16);
+}
+
+// 32 lanes x 16 columns of 32-bit from tensor memory
+DPH_DEVICE void tmem_ld_32x16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+
 // Fused backward of the activation epilogue  o = dropout(colmask[n] * act(z[m, n]))  (FFN hidden, conv blocks:
 // components.py:110-114, 733-737): the accumulator of this GEMM is d loss / d o (it is a dgrad product), and instead
 // of writing it out for a separate elementwise pass the epilogue
@@ -424,8 +453,74 @@ DPH_DEVICE void epilogue_chunk_bwd(const GemmParams& p, const TileCoord& tc, int
   }
 }
 
+// ---- the same on a 16-column half chunk (sixteen-warp variant of the class: 96 registers per thread) ----
+DPH_DEVICE void bwd_fetch_z16(const GemmParams& p, const TileCoord& tc, int row, bool row_ok, int col0, uint32_t (&zr)[8]) {
+  if (row_ok) {
+    const long long zoff = (long long)tc.b0 * p.z_sb0 + (long long)tc.b1 * p.z_sb1 + (long long)row * p.ldz + col0;
+    ldg_nc_256(reinterpret_cast<const bf16*>(p.Z) + zoff, zr);
+  } else {
+#pragma unroll
+    for (int q = 0; q < 8; ++q) zr[q] = 0u;
+  }
+}
+
+template <int F>
+DPH_DEVICE void epilogue_half_bwd(const GemmParams& p, const TileCoord& tc, int row, bool row_ok, int col0,
+                                  uint32_t (&r)[16], const uint32_t (&zr)[8]) {
+  const int lane = threadIdx.x & 31;
+  float v[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) v[j] = row_ok ? __uint_as_float(r[j]) : 0.f;
+  if constexpr ((F & F_DROP) != 0) {
+    if (p.drop_p > 0.0f) {
+      const uint32_t thresh = (uint32_t)(p.drop_p * 4294967296.0);
+      const float inv_keep = 1.0f / (1.0f - p.drop_p);
+      const unsigned long long base =
+          (((unsigned long long)tc.b1 * p.nb0 + tc.b0) * (unsigned long long)p.M + row) * (unsigned long long)p.N +
+          col0;
+      dropout_apply_vec<16>(p.seed, base, thresh, inv_keep, v);
+    }
+  }
+  float dm[16];
+#pragma unroll
+  for (int j = 0; j < 16; j += 2) {
+    const float2 zz = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&zr[j >> 1]));
+    const f32x2 z2 = pk2(zz.x, zz.y), v2 = pk2(v[j], v[j + 1]);
+    f32x2 g2 = z2, dg2 = bc2(1.f);
+    if (p.act == 1) gelu_and_grad_tanh2(z2, g2, dg2);
+    upk2(mul2(v2, g2), dm[j], dm[j + 1]);
+    upk2(mul2(v2, dg2), v[j], v[j + 1]);
+  }
+  if constexpr ((F & F_COLMASK) != 0) {
+    if (p.colmask != nullptr) {
+      const float4* mp = reinterpret_cast<const float4*>(p.colmask + tc.b0 * p.vec_sb0 + col0);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float4 m = __ldg(mp + j);
+        upk2(mul2(pk2(v[4 * j], v[4 * j + 1]), pk2(m.x, m.y)), v[4 * j], v[4 * j + 1]);
+        upk2(mul2(pk2(v[4 * j + 2], v[4 * j + 3]), pk2(m.z, m.w)), v[4 * j + 2], v[4 * j + 3]);
+      }
+    }
+  }
+  if (row_ok) {
+    const long long coff = (long long)tc.b0 * p.c_sb0 + (long long)tc.b1 * p.c_sb1 + (long long)row * p.ldc + col0;
+    uint32_t u[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) u[q] = pack_bf16x2(v[2 * q], v[2 * q + 1]);
+    stg_256(reinterpret_cast<bf16*>(p.C) + coff, u);
+  }
+  if (p.dbias != nullptr) {
+    const float sum = warp_colsum16(v, lane);
+    if (lane < 16) atomicAdd(p.dbias + tc.b0 * p.vec_sb0 + col0 + lane, sum);
+  }
+  if (p.dmask != nullptr) {
+    const float sum = warp_colsum16(dm, lane);
+    if (lane < 16) atomicAdd(p.dmask + tc.b0 * p.vec_sb0 + col0 + lane, sum);
+  }
+}
+
 template <int BN, bool A_MN, bool B_MN, int CG, int F>
-__global__ void __launch_bounds__(gemm_threads(BN), 1)
+__global__ void __launch_bounds__(gemm_threads(BN, F), 1)
     gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                      const __grid_constant__ GemmParams p) {
   using Cfg = GemmCfg<BN, CG>;
@@ -464,7 +559,7 @@ __global__ void __launch_bounds__(gemm_threads(BN), 1)
       }
       for (int a = 0; a < 2; ++a) {
         mbar_init(tfull_bar(a), 1);
-        mbar_init(tempty_bar(a), epi_warps(BN) * CG);  // leader's barrier collects the epilogue warps of both CTAs
+        mbar_init(tempty_bar(a), epi_warps(BN, F) * CG);  // leader's barrier collects the epilogue warps of both CTAs
       }
       mbar_fence_init();
     }
@@ -603,24 +698,63 @@ __global__ void __launch_bounds__(gemm_threads(BN), 1)
   } else {
     // ======================= epilogue warps (both CTAs: own 128 rows, all BN columns) =======================
     const int q = warp & 3;           // TMEM lane quadrant this warp may access
-    const int half = (warp - 2) >> 2; // which half of the tile's columns
-    constexpr int CHUNKS = BN / 64;   // 32-column chunks per warp
+    constexpr int NSL = epi_warps(BN, F) / 4;   // column slices of the tile (one per group of four warps)
+    constexpr int SLW = BN / NSL;               // columns per slice
+    const int half = (warp - 2) >> 2; // which slice of the tile's columns
+    constexpr int CHUNKS = SLW / 32;  // 32-column chunks per warp
     int acc = 0;
     uint32_t acc_phase = 0;
     int ti = 0;
     for (int t = unit; t < total_tiles; t += nunits, ++ti) {
       TileCoord tc = decode_tile<CG>(p, t);
-      const int n0 = tc.n0 * BN + half * (BN / 2);
+      const int n0 = tc.n0 * BN + half * SLW;
       const int kb_begin = tc.ks * p.kb_per_split;
       const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
       const int row = tc.m0 + rank * BM + q * 32 + lane;
       const bool row_ok = (row < p.M) && (kb_end > kb_begin);
-      [[maybe_unused]] uint32_t zr[16], zn[16];
-      if constexpr ((F & F_ACTBWD) != 0) bwd_fetch_z(p, tc, row, row_ok, n0, zn);  // does not depend on the MMAs
+      constexpr bool W16 = (F & F_ACTBWD) != 0 && NSL == 4;   // sixteen-warp fused-backward variant
+      [[maybe_unused]] uint32_t zr[W16 ? 1 : 16], zn[W16 ? 1 : 16];
+      [[maybe_unused]] uint32_t hz[8], hn[8];
+      // (the host admits the fused backward only with 32-byte aligned rows and N % 32 == 0: a 16-column half chunk is
+      // either inside N or outside it, never split)
+      if constexpr (W16) {
+        bwd_fetch_z16(p, tc, row, row_ok && n0 + 16 <= p.N, n0, hn);   // does not depend on the MMAs
+      } else if constexpr ((F & F_ACTBWD) != 0) {
+        bwd_fetch_z(p, tc, row, row_ok, n0, zn);
+      }
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
       if (warp == 2 && lane == 0) stamp(tl, 32 + 2 * ti);
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + half * (BN / 2));
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + half * SLW);
+      if constexpr (W16) {
+        {
+          constexpr int HALVES = SLW / 16;
+#pragma unroll 1
+          for (int h = 0; h < HALVES; ++h) {
+            const int col0 = n0 + h * 16;
+            uint32_t r[16];
+            tmem_ld_32x16(taddr + h * 16, r);
+#pragma unroll
+            for (int q2 = 0; q2 < 8; ++q2) hz[q2] = hn[q2];
+            if (h + 1 < HALVES) bwd_fetch_z16(p, tc, row, row_ok && col0 + 32 <= p.N, col0 + 16, hn);
+            tmem_ld_wait();
+            if (h == HALVES - 1) {   // all TMEM reads of this accumulator are done: hand it back
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) {
+                if constexpr (CG == 2) mbar_arrive_cluster(mapa_shared(tempty_bar(acc), 0));
+                else mbar_arrive(tempty_bar(acc));
+              }
+            }
+            if (col0 + 16 <= p.N) epilogue_half_bwd<F>(p, tc, row, row_ok, col0, r, hz);   // warp-collective, uniform
+          }
+          if (warp == 2 && lane == 0) stamp(tl, 33 + 2 * ti);
+          acc ^= 1;
+          if (acc == 0) acc_phase ^= 1u;
+          continue;
+        }
+      }
+      if constexpr (!W16) {
 #pragma unroll 1
       for (int c = 0; c < CHUNKS; ++c) {
         const int col0 = n0 + c * 32;
@@ -657,6 +791,7 @@ __global__ void __launch_bounds__(gemm_threads(BN), 1)
           release_acc();
         }
       }
+      }
       if (warp == 2 && lane == 0) stamp(tl, 33 + 2 * ti);
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1u;
@@ -692,7 +827,7 @@ static int launch_inst(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)grid);
-  cfg.blockDim = dim3(gemm_threads(BN));
+  cfg.blockDim = dim3(gemm_threads(BN, F));
   cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
   cfg.stream = stream;
   cudaLaunchAttribute attr[2];

@@ -12,3 +12,6 @@ for w in distill wavlm large final; do
 import json,sys
 d=json.loads(open('gpurun_out/r02_bench_$w.json').read().strip().splitlines()[-1]); print('$w', d['value'], d['ms_per_step'], d['e2e']['value'], d['roofline']['frac'])"
 done
+# launch list of one eager step at HEAD (serialised, cold: shares only)
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file gpurun_out/r02_ncu_launches_step_head.csv python bench.py --profile-step > gpurun_out/r02_ncu_launches_head.log 2>&1
+timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/r02_bench_reference_arm.json 2> gpurun_out/r02_bench_reference_arm.err; tail -c 400 gpurun_out/r02_bench_reference_arm.json
