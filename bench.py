@@ -641,12 +641,33 @@ def hbm_kernels(B, seconds, dev):
         return sorted(ts)[len(ts) // 2]
 
     out = []
+    # measured DRAM bytes of the same kernels inside one eager step (ncu dram__bytes_read + dram__bytes_write, cold
+    # caches; profiles/step_traffic.py): traffic well above the algorithmic bytes means wasted re-reads
+    try:
+        with open(os.path.join(ROOT, "profiles", "r02_step_dram_traffic.json")) as f:
+            measured = json.load(f)["kernels"]
+    except Exception:  # noqa: BLE001
+        measured = {}
+    ncu_name = {"conv0_fwd": "conv0_fwd_tc_kernel", "conv0_bwd": "conv0_bwd_tc_kernel", "layernorm_fwd": "layernorm_fwd_vec_kernel",
+                "layernorm_bwd": "layernorm_bwd_vec_kernel", "epilogue_bwd": "epilogue_bwd_kernel",
+                "distill_loss_fwd": "distill_loss_fwd_kernel", "distill_loss_bwd": "distill_loss_bwd_kernel",
+                "adamw": "adamw_kernel<1>", "sumsq": "sumsq_kernel"}
+
+    def traffic_of(name):
+        key = ncu_name.get(name.split(" ")[0])
+        hits = [(k, v) for k, v in measured.items() if key and key in k]
+        if not hits:
+            return None, None
+        k, v = max(hits, key=lambda kv: kv[1]["max_launch_bytes"])
+        return v["max_launch_bytes"], "largest launch of %s in the step (%d launches), profiles/r02_step_dram_traffic.json" % (
+            k, v["launches"])
 
     def add(name, nbytes, fn, what, sets=1):
         us = timeit(fn) if sets == 1 else timeit_sets(fn, sets)
         gbs = nbytes / us / 1e3
+        tr, tsrc = traffic_of(name)
         out.append({"kernel": name, "us": round(us, 2), "algorithmic_bytes": int(nbytes), "achieved_gbs": round(gbs, 1),
-                    "frac": round(gbs / peak, 3), "bytes_model": what,
+                    "frac": round(gbs / peak, 3), "traffic": tr, "traffic_source": tsrc, "bytes_model": what,
                     "timing": "single launch" if sets == 1 else "%d back-to-back launches on distinct buffers" % sets})
 
     def nsets(nbytes):

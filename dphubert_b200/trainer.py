@@ -241,6 +241,23 @@ class NativeDistillStep:
             out[id(h)] = masks[o:o + h.n_in]
         return out, u
 
+    def _expected_size(self):
+        """Expected size + Lagrangian (lightning.py:267-271): (gate tables, regulariser on?, d n_hat / d norms)."""
+        splan = self.splan
+        tb = hc_tables(splan)
+        reg_on = self.use_reg and tb.nseg > 0
+        dnorm = None
+        if reg_on:
+            A = self.Ah
+            la = splan.arena[splan.la_off:]
+            norms = A("l0_norms", (tb.nseg,), torch.float32)
+            nhat = A("n_hat", (1,), torch.float32)
+            dnorm = A("dnorm", (tb.nseg,), torch.float32)
+            ops.l0_norms(la, tb.seg_off, tb.seg_len, tb.nseg, tb.bias, norms)
+            ops.num_params(tb.prog, norms, tb.nseg, nhat, dnorm)
+            ops.lagrangian(nhat, self.lam.arena, self.n0, self.lr_dev[3:4], self.out[8:13])
+        return tb, reg_on, dnorm
+
     def _body(self, wave, lengths):
         dt = self.dt
         splan, tplan = self.splan, self.tplan
@@ -254,9 +271,13 @@ class NativeDistillStep:
             main = torch.cuda.current_stream()
             self.tstream.wait_stream(main)
             with torch.cuda.stream(self.tstream):
+                # the regulariser depends on log_alpha only: its three small, latency-bound kernels run here, off the
+                # student's critical path (they used to sit between the loss forward and the loss backward)
+                reg = self._expected_size()
                 t_h, _, _ = engine.forward_core(tplan, wave, lengths, {}, self.At, False, save=False)
         else:
             main = None
+            reg = self._expected_size()
             t_h, _, _ = engine.forward_core(tplan, wave, lengths, {}, self.At, False, save=False)
         # ---- student
         masks, u = self._sample_masks()
@@ -286,17 +307,7 @@ class NativeDistillStep:
                                  i == 0, i == nL - 1, total_rows)
             preds.append(pred)
             recs.append((lin, gelu, pre, rowstat, tgt, src_i, Dt))
-        # ---- expected size + Lagrangian (lightning.py:267-271)
-        tb = hc_tables(splan)
-        reg_on = self.use_reg and tb.nseg > 0
-        if reg_on:
-            la = splan.arena[splan.la_off:]
-            norms = A("l0_norms", (tb.nseg,), torch.float32)
-            nhat = A("n_hat", (1,), torch.float32)
-            dnorm = A("dnorm", (tb.nseg,), torch.float32)
-            ops.l0_norms(la, tb.seg_off, tb.seg_len, tb.nseg, tb.bias, norms)
-            ops.num_params(tb.prog, norms, tb.nseg, nhat, dnorm)
-            ops.lagrangian(nhat, self.lam.arena, self.n0, self.lr_dev[3:4], self.out[8:13])
+        tb, reg_on, dnorm = reg
         # ---- backward: heads
         splan.prepare_backward()
         dh = [None] * len(s_h)

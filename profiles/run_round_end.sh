@@ -15,3 +15,7 @@ done
 # launch list of one eager step at HEAD (serialised, cold: shares only)
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file gpurun_out/r02_ncu_launches_step_head.csv python bench.py --profile-step > gpurun_out/r02_ncu_launches_head.log 2>&1
 timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/r02_bench_reference_arm.json 2> gpurun_out/r02_bench_reference_arm.err; tail -c 400 gpurun_out/r02_bench_reference_arm.json
+# per-kernel DRAM traffic of the same eager step (bench.py reads profiles/r02_step_dram_traffic.json / r02_gemm_dram_traffic.json)
+timeout 900 ncu --profile-from-start off --clock-control none --page raw --csv --log-file gpurun_out/r02_step_traffic_raw.csv \
+  --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum python bench.py --profile-step > gpurun_out/r02_step_traffic.log 2>&1
+python profiles/step_traffic.py gpurun_out/r02_step_traffic_raw.csv gpurun_out/r02_step_dram_traffic.json gpurun_out/r02_gemm_dram_traffic.json | tail -12
