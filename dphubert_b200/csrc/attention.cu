@@ -68,18 +68,28 @@ DPH_DEVICE void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta
 DPH_DEVICE uint32_t sw128(int r, int c) { return (uint32_t)(r * 128 + ((c ^ (r & 7)) << 4)); }
 
 // shared memory map of the forward kernel (all tiles 1024-byte aligned)
-constexpr int FWD_SQ = 0;                                // Q   [128][64]        16 KB
-constexpr int FWD_SK = FWD_SQ + ATT_BQ * ATT_D * 2;      // K   [128][64]        16 KB
-constexpr int FWD_SV = FWD_SK + ATT_BK * ATT_D * 2;      // V   [128][64]        16 KB
-constexpr int FWD_SP = FWD_SV + ATT_BK * ATT_D * 2;      // P   2 x [128][64]    32 KB (two 64-key blocks)
-constexpr int FWD_TB = FWD_SP + ATT_BQ * ATT_BK * 2;     // bias table, TB_PAD + up to 2*1024 floats 8.5 KB
-constexpr int FWD_BAR = FWD_TB + (2048 + TB_PAD) * 4;    // mbarriers + tmem slot
-constexpr int FWD_SMEM = FWD_BAR + 64 + 1024;            // + alignment slack
+// BK = keys per tile.  128: two CTAs per SM (88.5 KB, 256 TMEM columns).  64: 56.5 KB and 128 TMEM columns, THREE CTAs
+// per SM — the kernel is latency-bound at four warps per CTA (ncu: issue slots 36 % busy), and 384 query tiles on
+// 148 x 2 slots are 1.3 waves whose second round runs on a third of the machine; at three per SM they are one wave.
+template <int BK>
+struct FwdL {
+  static constexpr int SQ = 0;                               // Q   [128][64]                    16 KB
+  static constexpr int SK = SQ + ATT_BQ * ATT_D * 2;         // K   [BK][64]                     16 / 8 KB
+  static constexpr int SV = SK + BK * ATT_D * 2;             // V   [BK][64]                     16 / 8 KB
+  static constexpr int SP = SV + BK * ATT_D * 2;             // P   (BK / 64) x [128][64]        32 / 16 KB
+  static constexpr int TB = SP + ATT_BQ * BK * 2;            // bias table, TB_PAD + up to 2*1024 floats 8.5 KB
+  static constexpr int BAR = TB + (2048 + TB_PAD) * 4;       // mbarriers + tmem slot
+  static constexpr int SMEM = BAR + 64 + 1024;               // + alignment slack
+  static constexpr int TMEM = BK + ATT_D <= 128 ? 128 : 256; // S (BK columns) | O tile (64 columns)
+};
 
-template <bool BIAS, bool DROP>
-__global__ void __launch_bounds__(128, 2)
-    attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p, bf16* __restrict__ ctx,
-                    bf16* __restrict__ ctx_un, float* __restrict__ lse) {
+template <bool BIAS, bool DROP, int BK>
+__global__ void __launch_bounds__(128, BK == 64 ? 3 : 2)
+    attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmKV, const AttnParams p,
+                    bf16* __restrict__ ctx, bf16* __restrict__ ctx_un, float* __restrict__ lse) {
+  constexpr int FWD_SQ = FwdL<BK>::SQ, FWD_SK = FwdL<BK>::SK, FWD_SV = FwdL<BK>::SV, FWD_SP = FwdL<BK>::SP,
+                FWD_TB = FwdL<BK>::TB, FWD_BAR = FwdL<BK>::BAR;
+  constexpr int ATT_BK = BK;   // (shadows the file-scope tile size of the backward kernel)
   extern __shared__ uint8_t smem_raw[];
   const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* gbase = smem_raw + (sbase - smem_u32(smem_raw));
@@ -102,10 +112,11 @@ __global__ void __launch_bounds__(128, 2)
     mbar_init(bar_o, 1);
     mbar_fence_init();
     tma_prefetch_desc(&tmQKV);
+    tma_prefetch_desc(&tmKV);
   }
   if (warp == 0) {
     __syncwarp();
-    tmem_alloc(tmem_slot, 256);
+    tmem_alloc(tmem_slot, FwdL<BK>::TMEM);
     tmem_relinquish();
   }
   pdl_wait();  // PDL: barrier init / TMEM allocation above overlap the previous kernel's tail
@@ -124,16 +135,16 @@ __global__ void __launch_bounds__(128, 2)
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
-  const uint32_t tS = tmem_base, tO = tmem_base + 128;
+  const uint32_t tS = tmem_base, tO = tmem_base + BK;
   const uint32_t lane_off = ((uint32_t)(warp * 32)) << 16;
 
   if (warp == 0 && elect_one()) {
     mbar_expect_tx(bar_q, ATT_BQ * ATT_D * 2);
     tma_load_2d(sQ, &tmQKV, bar_q, 2 * p.inner + h * ATT_D, row_q);
     mbar_expect_tx(bar_k, ATT_BK * ATT_D * 2);
-    tma_load_2d(sK, &tmQKV, bar_k, h * ATT_D, b * T);
+    tma_load_2d(sK, &tmKV, bar_k, h * ATT_D, b * T);
     mbar_expect_tx(bar_v, ATT_BK * ATT_D * 2);
-    tma_load_2d(sV, &tmQKV, bar_v, p.inner + h * ATT_D, b * T);
+    tma_load_2d(sV, &tmKV, bar_v, p.inner + h * ATT_D, b * T);
   }
   const int len = p.lengths ? (int)p.lengths[b] : T;
   const uint32_t thresh = (uint32_t)(p.drop_p * 4294967296.0);
@@ -174,7 +185,7 @@ __global__ void __launch_bounds__(128, 2)
     tc_fence_after();
     if (warp == 0 && elect_one() && t + 1 < ntiles) {  // K tile is free again: fetch the next one while the softmax runs
       mbar_expect_tx(bar_k, ATT_BK * ATT_D * 2);
-      tma_load_2d(sK, &tmQKV, bar_k, h * ATT_D, b * T + k0 + ATT_BK);
+      tma_load_2d(sK, &tmKV, bar_k, h * ATT_D, b * T + k0 + ATT_BK);
     }
 
     // Per 32-key chunk: chunks whose keys are all real (below T and below the padding length) take a lean path —
@@ -290,7 +301,7 @@ __global__ void __launch_bounds__(128, 2)
     tc_fence_after();
     if (warp == 0 && elect_one() && t + 1 < ntiles) {
       mbar_expect_tx(bar_v, ATT_BK * ATT_D * 2);
-      tma_load_2d(sV, &tmQKV, bar_v, p.inner + h * ATT_D, b * T + k0 + ATT_BK);
+      tma_load_2d(sV, &tmKV, bar_v, p.inner + h * ATT_D, b * T + k0 + ATT_BK);
     }
 #pragma unroll
     for (int c = 0; c < ATT_D / 32; ++c) {
@@ -335,7 +346,7 @@ __global__ void __launch_bounds__(128, 2)
   __syncthreads();
   if (warp == 0) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 256);
+    tmem_dealloc(tmem_base, FwdL<BK>::TMEM);
   }
 }
 
@@ -877,15 +888,24 @@ extern "C" int dph_attn_fwd(const void* qkv, void* ctx, void* ctx_un, float* lse
     return DPH_ERR_ARG;
   }
   const int inner = H * ATT_D;
-  CUtensorMap tm;
-  rc = make_tmap_2d(&tm, qkv, 3ull * inner, (uint64_t)B * T, 3ull * inner, ATT_D, ATT_BK);
+  // keys per tile: 64 (three CTAs per SM) unless DPH_ATT_BK=128 asks for the two-per-SM variant (A / B timing)
+  static const int fwd_bk = [] {
+    const char* e = getenv("DPH_ATT_BK");
+    return (e != nullptr && atoi(e) == 128) ? 128 : 64;
+  }();
+  CUtensorMap tm, tmkv;
+  rc = make_tmap_2d(&tm, qkv, 3ull * inner, (uint64_t)B * T, 3ull * inner, ATT_D, ATT_BQ);
+  if (rc) return rc;
+  rc = make_tmap_2d(&tmkv, qkv, 3ull * inner, (uint64_t)B * T, 3ull * inner, ATT_D, fwd_bk);
   if (rc) return rc;
   static bool attr = false;
   if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(attn_fwd_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(attn_fwd_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(attn_fwd_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(attn_fwd_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
+    cudaError_t e = cudaSuccess;
+#define ATT_ATTR(BI, DR)                                                                                                   \
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(attn_fwd_kernel<BI, DR, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, FwdL<64>::SMEM); \
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(attn_fwd_kernel<BI, DR, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, FwdL<128>::SMEM);
+    ATT_ATTR(false, false) ATT_ATTR(false, true) ATT_ATTR(true, false) ATT_ATTR(true, true)
+#undef ATT_ATTR
     if (e != cudaSuccess) {
       set_error("attn_fwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
       return DPH_ERR_CUDA;
@@ -896,8 +916,15 @@ extern "C" int dph_attn_fwd(const void* qkv, void* ctx, void* ctx_un, float* lse
   dim3 grid((T + ATT_BQ - 1) / ATT_BQ, H, B);
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   const bool bias = emb != nullptr, drop = drop_p > 0.f;
-#define ATT_FWD(BI, DR) \
-  launch_pdl(attn_fwd_kernel<BI, DR>, grid, dim3(128), FWD_SMEM, s, tm, p, (bf16*)ctx, (bf16*)ctx_un, lse)
+#define ATT_FWD(BI, DR)                                                                                              \
+  do {                                                                                                               \
+    if (fwd_bk == 64)                                                                                                \
+      launch_pdl(attn_fwd_kernel<BI, DR, 64>, grid, dim3(128), FwdL<64>::SMEM, s, tm, tmkv, p, (bf16*)ctx,           \
+                 (bf16*)ctx_un, lse);                                                                                \
+    else                                                                                                             \
+      launch_pdl(attn_fwd_kernel<BI, DR, 128>, grid, dim3(128), FwdL<128>::SMEM, s, tm, tmkv, p, (bf16*)ctx,         \
+                 (bf16*)ctx_un, lse);                                                                                \
+  } while (0)
   if (bias) {
     if (drop) ATT_FWD(true, true); else ATT_FWD(true, false);
   } else {
