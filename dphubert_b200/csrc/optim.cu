@@ -67,17 +67,19 @@ __global__ void __launch_bounds__(256)
   // 16-byte main loop (all four arrays 16-byte aligned: checked by the launcher), scalar tail
   const long long n4 = vec_ok ? n / 4 : 0;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
-    float4 p4 = reinterpret_cast<float4*>(p)[i];
+    // master weights and moments are touched once per step by this kernel only: streaming (evict-first) accesses keep
+    // them from displacing the bf16 weight mirror and the activations the next step's GEMMs find in L2
+    float4 p4 = __ldcs(reinterpret_cast<const float4*>(p) + i);
     const float4 g4 = reinterpret_cast<const float4*>(g)[i];
-    float4 m4 = reinterpret_cast<float4*>(m)[i];
-    float4 v4 = reinterpret_cast<float4*>(v)[i];
+    float4 m4 = __ldcs(reinterpret_cast<const float4*>(m) + i);
+    float4 v4 = __ldcs(reinterpret_cast<const float4*>(v) + i);
     upd(p4.x, g4.x, m4.x, v4.x);
     upd(p4.y, g4.y, m4.y, v4.y);
     upd(p4.z, g4.z, m4.z, v4.z);
     upd(p4.w, g4.w, m4.w, v4.w);
-    reinterpret_cast<float4*>(p)[i] = p4;
-    reinterpret_cast<float4*>(m)[i] = m4;
-    reinterpret_cast<float4*>(v)[i] = v4;
+    __stcs(reinterpret_cast<float4*>(p) + i, p4);
+    __stcs(reinterpret_cast<float4*>(m) + i, m4);
+    __stcs(reinterpret_cast<float4*>(v) + i, v4);
     if (WRITE_BF16) {
       uint2 u;
       u.x = pack_bf16x2(p4.x, p4.y);
