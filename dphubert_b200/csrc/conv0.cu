@@ -32,6 +32,8 @@ constexpr int MOM_TT = 1024;
 __global__ void __launch_bounds__(256)
     conv0_moments_kernel(const float* __restrict__ wave, long long wave_bs, int T1, int k, int stride,
                          double* __restrict__ R) {
+  pdl_wait();
+  pdl_trigger();
   extern __shared__ float mx[];  // (MOM_TT - 1) * stride + k samples
   __shared__ double part[3][C0_NR];
   const int b = blockIdx.y;
@@ -73,6 +75,8 @@ __global__ void __launch_bounds__(256)
 __global__ void conv0_stats_kernel(const double* __restrict__ R, const float* __restrict__ w,
                                    const float* __restrict__ bias, float* __restrict__ mean, float* __restrict__ rstd,
                                    int B, int C, int k, int T1, float eps) {
+  pdl_wait();
+  pdl_trigger();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= B * C) return;
   const int b = i / C, c = i - b * C;
@@ -326,6 +330,8 @@ __global__ void conv0_bwd_finalize_kernel(const float* __restrict__ scratch, con
                                           const float* __restrict__ rstd, float* __restrict__ dW,
                                           float* __restrict__ dbias, float* __restrict__ dgamma,
                                           float* __restrict__ dbeta, int B, int C, int k, int T1, int norm) {
+  pdl_wait();
+  pdl_trigger();
   // one thread per (utterance, channel): the per-utterance terms are independent and meet in the final atomics
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= B * C) return;
@@ -457,8 +463,9 @@ extern "C" int dph_conv0_stats(const float* wave, int64_t wave_bs, const float* 
     set_error("conv0_stats: stride %d too large for the moment kernel's staging buffer", stride);
     return DPH_ERR_UNSUPPORTED;
   }
-  conv0_moments_kernel<<<dim3(gx, B), 256, mom_smem, s>>>(wave, wave_bs, T1, k, stride, moments);
-  conv0_stats_kernel<<<(B * C + 127) / 128, 128, 0, s>>>(moments, w, bias, mean, rstd, B, C, k, T1, eps);
+  launch_pdl(conv0_moments_kernel, dim3(gx, B), dim3(256), mom_smem, s, wave, (long long)wave_bs, T1, k, stride, moments);
+  launch_pdl(conv0_stats_kernel, dim3((B * C + 127) / 128), dim3(128), 0, s, (const double*)moments, w, bias, mean, rstd, B, C,
+             k, T1, eps);
   dph_count_launch(2);
   return dph_check_last("conv0_stats");
 }
@@ -523,8 +530,8 @@ extern "C" int dph_conv0_bwd(const float* wave, int64_t wave_bs, const float* w,
     conv0_bwd_fused_kernel<float><<<grid, C0_THREADS, 0, s>>>(wave, wave_bs, w, bias, gamma, beta, mean, rstd, mask,
                                                               (const float*)dy, scratch, dmask, C, k, stride, T1, norm,
                                                               act, pair_vec);
-  conv0_bwd_finalize_kernel<<<(B * C + 127) / 128, 128, 0, s>>>(scratch, moments, w, bias, gamma, mean, rstd, dW, dbias,
-                                                            dgamma, dbeta, B, C, k, T1, norm);
+  launch_pdl(conv0_bwd_finalize_kernel, dim3((B * C + 127) / 128), dim3(128), 0, s, (const float*)scratch, moments, w, bias,
+             gamma, mean, rstd, dW, dbias, dgamma, dbeta, B, C, k, T1, norm);
   dph_count_launch(2);
   return dph_check_last("conv0_bwd");
 }

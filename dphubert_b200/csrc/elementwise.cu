@@ -158,6 +158,8 @@ __global__ void __launch_bounds__(256, 2)
 
 template <typename T>
 __global__ void pad_rows_zero_kernel(T* __restrict__ x, const long long* __restrict__ lengths, int B, int Tn, int D) {
+  pdl_wait();
+  pdl_trigger();
   // one block per (b, t) candidate row in the padded region; grid = B * Tn blocks is wasteful, so walk rows per block
   const int b = blockIdx.y;
   long long len = lengths[b];
@@ -193,6 +195,8 @@ __global__ void posconv_pad_kernel(const T* __restrict__ x, T* __restrict__ xp, 
 __global__ void __launch_bounds__(128)
     posconv_pad_vec_kernel(const bf16* __restrict__ x, bf16* __restrict__ xp, int Tn, int G, int Cg, int Cgp, int front,
                            int pad) {
+  pdl_wait();
+  pdl_trigger();
   const int row = blockIdx.x;                 // b * Tn + t
   const int b = row / Tn, t = row - b * Tn;
   const int ppg = Cgp >> 3;                   // pieces per group in the padded row
@@ -266,6 +270,8 @@ __global__ void transpose_kernel(const TI* __restrict__ in, TO* __restrict__ out
 // dst[i] += src[i]
 template <typename T, int VEC>
 __global__ void axpy_kernel(T* __restrict__ dst, const T* __restrict__ src, long long n) {
+  pdl_wait();
+  pdl_trigger();
   const long long nv = n / VEC;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += (long long)gridDim.x * blockDim.x) {
     if constexpr (VEC == 1) {
@@ -383,9 +389,9 @@ extern "C" int dph_pad_rows_zero(void* x, const int64_t* lengths, int B, int T, 
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   dim3 grid(8, B);
   if (dtype == DPH_DTYPE_BF16)
-    pad_rows_zero_kernel<bf16><<<grid, 128, 0, s>>>((bf16*)x, (const long long*)lengths, B, T, D);
+    launch_pdl(pad_rows_zero_kernel<bf16>, dim3(grid), dim3(128), 0, s, (bf16*)x, (const long long*)lengths, B, T, D);
   else
-    pad_rows_zero_kernel<float><<<grid, 128, 0, s>>>((float*)x, (const long long*)lengths, B, T, D);
+    launch_pdl(pad_rows_zero_kernel<float>, dim3(grid), dim3(128), 0, s, (float*)x, (const long long*)lengths, B, T, D);
   dph_count_launch();
   return dph_check_last("pad_rows_zero");
 }
@@ -397,7 +403,7 @@ extern "C" int dph_posconv_pad(const void* x, void* xp, int B, int T, int G, int
   int grid = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
   if (dtype == DPH_DTYPE_BF16 && Cg % 8 == 0 && Cgp % 8 == 0 &&
       ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(xp)) & 15) == 0 && (long long)B * T < (1LL << 31)) {
-    posconv_pad_vec_kernel<<<B * T, 128, 0, s>>>((const bf16*)x, (bf16*)xp, T, G, Cg, Cgp, front, pad);
+    launch_pdl(posconv_pad_vec_kernel, dim3(B * T), dim3(128), 0, s, (const bf16*)x, (bf16*)xp, T, G, Cg, Cgp, front, pad);
     dph_count_launch();
     return dph_check_last("posconv_pad");
   }
@@ -497,11 +503,11 @@ extern "C" int dph_axpy(void* dst, const void* src, int64_t n, int dtype, void* 
   int grid = (int)((nv + 255) / 256 < 148 * 16 ? (nv + 255) / 256 : 148 * 16);
   if (grid < 1) grid = 1;
   if (dtype == DPH_DTYPE_BF16) {
-    if (al) axpy_kernel<bf16, 8><<<grid, 256, 0, s>>>((bf16*)dst, (const bf16*)src, n);
-    else axpy_kernel<bf16, 1><<<148 * 8, 256, 0, s>>>((bf16*)dst, (const bf16*)src, n);
+    if (al) launch_pdl(axpy_kernel<bf16, 8>, dim3(grid), dim3(256), 0, s, (bf16*)dst, (const bf16*)src, n);
+    else launch_pdl(axpy_kernel<bf16, 1>, dim3(148 * 8), dim3(256), 0, s, (bf16*)dst, (const bf16*)src, n);
   } else {
-    if (al) axpy_kernel<float, 4><<<grid, 256, 0, s>>>((float*)dst, (const float*)src, n);
-    else axpy_kernel<float, 1><<<148 * 8, 256, 0, s>>>((float*)dst, (const float*)src, n);
+    if (al) launch_pdl(axpy_kernel<float, 4>, dim3(grid), dim3(256), 0, s, (float*)dst, (const float*)src, n);
+    else launch_pdl(axpy_kernel<float, 1>, dim3(148 * 8), dim3(256), 0, s, (float*)dst, (const float*)src, n);
   }
   dph_count_launch();
   return dph_check_last("axpy");

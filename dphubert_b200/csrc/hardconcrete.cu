@@ -20,6 +20,8 @@ DPH_DEVICE float hc_uniform(unsigned long long seed, unsigned long long idx, flo
 __global__ void hardconcrete_fwd_kernel(const float* __restrict__ la, const float* __restrict__ u_in,
                                         float* __restrict__ u_out, float* __restrict__ mask, long long n, float beta,
                                         float l, float r, float eps, unsigned long long seed) {
+  pdl_wait();
+  pdl_trigger();
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const float u = u_in ? u_in[i] : hc_uniform(seed, (unsigned long long)i, eps);
@@ -33,6 +35,8 @@ __global__ void hardconcrete_fwd_kernel(const float* __restrict__ la, const floa
 __global__ void hardconcrete_bwd_kernel(const float* __restrict__ la, const float* __restrict__ u_in,
                                         const float* __restrict__ dmask, float* __restrict__ dla, long long n,
                                         float beta, float l, float r) {
+  pdl_wait();
+  pdl_trigger();
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const float u = u_in[i];
@@ -163,8 +167,8 @@ extern "C" int dph_hardconcrete_fwd(const float* log_alpha, const float* u_in, f
     set_error("hardconcrete_fwd: bad arguments");
     return DPH_ERR_ARG;
   }
-  hardconcrete_fwd_kernel<<<(unsigned)((n + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      log_alpha, u_in, u_out, mask, n, beta, limit_l, limit_r, eps, seed);
+  launch_pdl(hardconcrete_fwd_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream),
+             log_alpha, u_in, u_out, mask, n, beta, limit_l, limit_r, eps, seed);
   dph_count_launch();
   return dph_check_last("hardconcrete_fwd");
 }

@@ -19,6 +19,8 @@ template <typename T>
 __global__ void __launch_bounds__(256)
     distill_loss_fwd_kernel(const T* __restrict__ a, const T* __restrict__ b, float* __restrict__ rowstat,
                             float* __restrict__ acc, long long rows, int D, int cos_type, float eps, int vec) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ float red[3][8];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const long long row = (long long)blockIdx.x * 8 + w;
@@ -84,6 +86,8 @@ __global__ void __launch_bounds__(256)
 // out[0] = total, out[1] = mse, out[2] = l1, out[3] = cos loss   (means + weights applied here)
 __global__ void distill_loss_finalize_kernel(const float* __restrict__ acc, float* __restrict__ out, float n_elem,
                                              float n_rows, float w2, float w1, float wc) {
+  pdl_wait();
+  pdl_trigger();
   if (threadIdx.x != 0) return;
   const float mse = (w2 != 0.f) ? acc[0] / n_elem : 0.f;
   const float l1 = (w1 != 0.f) ? acc[1] / n_elem : 0.f;
@@ -100,6 +104,8 @@ __global__ void __launch_bounds__(256)
     distill_loss_bwd_kernel(const T* __restrict__ a, const T* __restrict__ b, const float* __restrict__ rowstat,
                             const float* __restrict__ upstream, T* __restrict__ da, long long rows, int D, float w2,
                             float w1, float wc, int cos_type, float eps, float n_elem, float n_rows, int vec) {
+  pdl_wait();
+  pdl_trigger();
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const long long row = (long long)blockIdx.x * 8 + w;
   if (row >= rows) return;
@@ -159,13 +165,14 @@ extern "C" int dph_distill_loss_fwd(const void* a, const void* b, float* rowstat
   const int vw = dtype == DPH_DTYPE_BF16 ? 8 : 4;
   const int vec = (D % vw == 0) && (((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b)) & 15) == 0);
   if (dtype == DPH_DTYPE_BF16)
-    distill_loss_fwd_kernel<bf16><<<grid, 256, 0, s>>>((const bf16*)a, (const bf16*)b, rowstat, acc, rows, D, cos_type,
-                                                       1e-8f, vec);
+    launch_pdl(distill_loss_fwd_kernel<bf16>, dim3(grid), dim3(256), 0, s, (const bf16*)a, (const bf16*)b, rowstat, acc, rows,
+               D, cos_type, 1e-8f, vec);
   else
-    distill_loss_fwd_kernel<float><<<grid, 256, 0, s>>>((const float*)a, (const float*)b, rowstat, acc, rows, D,
-                                                        cos_type, 1e-8f, vec);
+    launch_pdl(distill_loss_fwd_kernel<float>, dim3(grid), dim3(256), 0, s, (const float*)a, (const float*)b, rowstat, acc,
+               rows, D, cos_type, 1e-8f, vec);
   if (last)
-    distill_loss_finalize_kernel<<<1, 32, 0, s>>>(acc, out, (float)total_rows * (float)D, (float)total_rows, w2, w1, wc);
+    launch_pdl(distill_loss_finalize_kernel, dim3(1), dim3(32), 0, s, (const float*)acc, out, (float)total_rows * (float)D,
+               (float)total_rows, w2, w1, wc);
   dph_count_launch(last ? 2 : 1);
   return dph_check_last("distill_loss_fwd");
 }
@@ -184,11 +191,11 @@ extern "C" int dph_distill_loss_bwd(const void* a, const void* b, const float* r
   const int vec = (D % vw == 0) && (((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) |
                                       reinterpret_cast<uintptr_t>(da)) & 15) == 0);
   if (dtype == DPH_DTYPE_BF16)
-    distill_loss_bwd_kernel<bf16><<<grid, 256, 0, s>>>((const bf16*)a, (const bf16*)b, rowstat, upstream, (bf16*)da, rows,
-                                                       D, w2, w1, wc, cos_type, 1e-8f, ne, nr, vec);
+    launch_pdl(distill_loss_bwd_kernel<bf16>, dim3(grid), dim3(256), 0, s, (const bf16*)a, (const bf16*)b, rowstat, upstream,
+               (bf16*)da, rows, D, w2, w1, wc, cos_type, 1e-8f, ne, nr, vec);
   else
-    distill_loss_bwd_kernel<float><<<grid, 256, 0, s>>>((const float*)a, (const float*)b, rowstat, upstream, (float*)da,
-                                                        rows, D, w2, w1, wc, cos_type, 1e-8f, ne, nr, vec);
+    launch_pdl(distill_loss_bwd_kernel<float>, dim3(grid), dim3(256), 0, s, (const float*)a, (const float*)b, rowstat,
+               upstream, (float*)da, rows, D, w2, w1, wc, cos_type, 1e-8f, ne, nr, vec);
   dph_count_launch();
   return dph_check_last("distill_loss_bwd");
 }

@@ -12,6 +12,8 @@ namespace dph {
 void set_error(const char* fmt, ...);
 
 __global__ void __launch_bounds__(256) sumsq_kernel(const float* __restrict__ x, long long n, double* __restrict__ out) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ double sh[8];
   double acc = 0.0;
   const long long stride = (long long)gridDim.x * blockDim.x * 4;
@@ -34,6 +36,8 @@ __global__ void __launch_bounds__(256) sumsq_kernel(const float* __restrict__ x,
 }
 
 __global__ void counter_inc_kernel(int* c) {
+  pdl_wait();
+  pdl_trigger();
   if (threadIdx.x == 0 && blockIdx.x == 0) c[0] += 1;
 }
 
@@ -44,6 +48,8 @@ __global__ void __launch_bounds__(256)
                  const float* __restrict__ lr_dev, float beta1, float beta2, float eps, float wd,
                  const int* __restrict__ step_dev, const double* __restrict__ gnorm_sq, float max_norm,
                  bf16* __restrict__ p_bf16, int zero_grad, int vec_ok) {
+  pdl_wait();
+  pdl_trigger();
   const float lr = lr_dev[0];
   const int step = step_dev[0];
   float clip = 1.f;
@@ -118,13 +124,13 @@ extern "C" int dph_sumsq(const float* x, int64_t n, double* out, void* stream) {
   long long blocks = (n / 4 + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
   if (blocks < 1) blocks = 1;
-  sumsq_kernel<<<(unsigned)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(x, n, out);
+  launch_pdl(sumsq_kernel, dim3((unsigned)blocks), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream), x, n, out);
   dph_count_launch();
   return dph_check_last("sumsq");
 }
 
 extern "C" int dph_counter_inc(int* counter, void* stream) {
-  counter_inc_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(counter);
+  launch_pdl(counter_inc_kernel, dim3(1), dim3(32), 0, reinterpret_cast<cudaStream_t>(stream), counter);
   dph_count_launch();
   return dph_check_last("counter_inc");
 }
@@ -143,11 +149,11 @@ extern "C" int dph_adamw(float* p, float* g, float* m, float* v, int64_t n, cons
   if (blocks < 1) blocks = 1;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   if (p_bf16)
-    adamw_kernel<true><<<(unsigned)blocks, 256, 0, s>>>(p, g, m, v, n, lr_dev, beta1, beta2, eps, weight_decay, step_dev,
-                                                        gnorm_sq, max_norm, (bf16*)p_bf16, zero_grad, vec_ok);
+    launch_pdl(adamw_kernel<true>, dim3((unsigned)blocks), dim3(256), 0, s, p, g, m, v, n, lr_dev, beta1, beta2, eps,
+               weight_decay, step_dev, gnorm_sq, max_norm, (bf16*)p_bf16, zero_grad, vec_ok);
   else
-    adamw_kernel<false><<<(unsigned)blocks, 256, 0, s>>>(p, g, m, v, n, lr_dev, beta1, beta2, eps, weight_decay, step_dev,
-                                                         gnorm_sq, max_norm, nullptr, zero_grad, vec_ok);
+    launch_pdl(adamw_kernel<false>, dim3((unsigned)blocks), dim3(256), 0, s, p, g, m, v, n, lr_dev, beta1, beta2, eps,
+               weight_decay, step_dev, gnorm_sq, max_norm, (bf16*)nullptr, zero_grad, vec_ok);
   dph_count_launch();
   return dph_check_last("adamw");
 }

@@ -37,6 +37,8 @@ template <typename T>
 __global__ void __launch_bounds__(256)
     conv_weight_prep_tiled_kernel(const float* __restrict__ w, T* __restrict__ wf, T* __restrict__ wd, int Cout, int Cin,
                                   int k, TapPerm perm) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ float tile[32][32 * 4 + 1];
   const int ci0 = blockIdx.x * 32, co0 = blockIdx.y * 32;
   const int rowlen = 32 * k;
@@ -75,6 +77,8 @@ __global__ void conv_wgrad_unpermute_kernel(const float* __restrict__ src, float
 // read-modify-writes
 __global__ void __launch_bounds__(256)
     conv_wgrad_unpermute_tiled_kernel(const float* __restrict__ src, float* __restrict__ dw, int Cout, int Cin, int k) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ float tile[32][32 * 4 + 1];
   const int ci0 = blockIdx.x * 32, co0 = blockIdx.y * 32;
   const int rowlen = 32 * k;
@@ -162,6 +166,8 @@ __global__ void posconv_wbwd_apply_kernel(const float* __restrict__ dwp, const f
 // thread always meets the same tap.  normsq must be zero on entry.
 __global__ void __launch_bounds__(256)
     posconv_normsq_kernel(const float* __restrict__ v, float* __restrict__ normsq, long long total, int K) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ float red[256];
   const long long chunk = ((total + gridDim.x - 1) / gridDim.x + 255) / 256 * 256;
   const long long e0 = (long long)blockIdx.x * chunk, e1 = e0 + chunk < total ? e0 + chunk : total;
@@ -179,6 +185,8 @@ __global__ void __launch_bounds__(256)
   }
 }
 __global__ void posconv_sqrt_kernel(float* __restrict__ x, int n) {
+  pdl_wait();
+  pdl_trigger();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) x[i] = sqrtf(x[i]);
 }
@@ -190,6 +198,8 @@ __global__ void __launch_bounds__(256)
     posconv_weight_prep_tiled_kernel(const float* __restrict__ v, const float* __restrict__ g,
                                      const float* __restrict__ norm, float* __restrict__ wn, T* __restrict__ wp,
                                      T* __restrict__ wdp, int G, int Cg, int Cgp, int K) {
+  pdl_wait();
+  pdl_trigger();
   extern __shared__ float tile[];  // [q][co][Cg + 1]
   const int grp = blockIdx.y, tap0 = blockIdx.x * TC;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -269,6 +279,8 @@ __global__ void __launch_bounds__(256)
     posconv_wbwd_tiled_kernel(const float* __restrict__ dwp, const float* __restrict__ v, const float* __restrict__ g,
                               const float* __restrict__ norm, float* __restrict__ s, float* __restrict__ dv,
                               float* __restrict__ dg, int Cg, int Cop, int Cgp, int K) {
+  pdl_wait();
+  pdl_trigger();
   extern __shared__ float dws[];   // [tap][Cg + 1]
   __shared__ float red[256];
   const int d = blockIdx.x;
@@ -326,9 +338,9 @@ extern "C" int dph_conv_weight_prep(const float* w, void* wf, void* wd, int Cout
   if (k <= 4 && Cout % 32 == 0 && Cin % 32 == 0) {
     const dim3 grid(Cin / 32, Cout / 32);
     if (dtype == DPH_DTYPE_BF16)
-      conv_weight_prep_tiled_kernel<bf16><<<grid, 256, 0, s>>>(w, (bf16*)wf, (bf16*)wd, Cout, Cin, k, perm);
+      launch_pdl(conv_weight_prep_tiled_kernel<bf16>, grid, dim3(256), 0, s, w, (bf16*)wf, (bf16*)wd, Cout, Cin, k, perm);
     else
-      conv_weight_prep_tiled_kernel<float><<<grid, 256, 0, s>>>(w, (float*)wf, (float*)wd, Cout, Cin, k, perm);
+      launch_pdl(conv_weight_prep_tiled_kernel<float>, grid, dim3(256), 0, s, w, (float*)wf, (float*)wd, Cout, Cin, k, perm);
     dph_count_launch();
     return dph_check_last("conv_weight_prep");
   }
@@ -343,8 +355,8 @@ extern "C" int dph_conv_weight_prep(const float* w, void* wf, void* wd, int Cout
 extern "C" int dph_conv_wgrad_unpermute(const float* src, float* dw, int Cout, int Cin, int k, void* stream) {
   const long long total = (long long)Cout * Cin * k;
   if (k <= 4 && Cout % 32 == 0 && Cin % 32 == 0)
-    conv_wgrad_unpermute_tiled_kernel<<<dim3(Cin / 32, Cout / 32), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-        src, dw, Cout, Cin, k);
+    launch_pdl(conv_wgrad_unpermute_tiled_kernel, dim3(Cin / 32, Cout / 32), dim3(256), 0,
+               reinterpret_cast<cudaStream_t>(stream), src, dw, Cout, Cin, k);
   else
     conv_wgrad_unpermute_kernel<<<grid_for(total), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(src, dw, Cout, Cin, k);
   dph_count_launch();
@@ -362,8 +374,8 @@ extern "C" int dph_posconv_weight_prep(const float* v, const float* g, float* no
   int launches = 2;
   if (256 % K == 0) {
     cudaMemsetAsync(norm, 0, sizeof(float) * K, s);
-    posconv_normsq_kernel<<<148 * 2, 256, 0, s>>>(v, norm, total, K);
-    posconv_sqrt_kernel<<<1, 256, 0, s>>>(norm, K);
+    launch_pdl(posconv_normsq_kernel, dim3(148 * 2), dim3(256), 0, s, v, norm, total, K);
+    launch_pdl(posconv_sqrt_kernel, dim3(1), dim3(256), 0, s, norm, K);
     launches = 3;
   } else {
     posconv_norm_kernel<<<K, 256, 0, s>>>(v, norm, D, Cg, K);
@@ -379,11 +391,11 @@ extern "C" int dph_posconv_weight_prep(const float* v, const float* g, float* no
     }
     dim3 grid((K + TC - 1) / TC, G);
     if (dtype == DPH_DTYPE_BF16)
-      posconv_weight_prep_tiled_kernel<bf16, TC><<<grid, 256, tile_bytes, s>>>(v, g, norm, wn, (bf16*)wp, (bf16*)wdp, G,
-                                                                               Cg, Cgp, K);
+      launch_pdl(posconv_weight_prep_tiled_kernel<bf16, TC>, grid, dim3(256), tile_bytes, s, v, g, (const float*)norm, wn,
+                 (bf16*)wp, (bf16*)wdp, G, Cg, Cgp, K);
     else
-      posconv_weight_prep_tiled_kernel<float, TC><<<grid, 256, tile_bytes, s>>>(v, g, norm, wn, (float*)wp, (float*)wdp,
-                                                                                G, Cg, Cgp, K);
+      launch_pdl(posconv_weight_prep_tiled_kernel<float, TC>, grid, dim3(256), tile_bytes, s, v, g, (const float*)norm, wn,
+                 (float*)wp, (float*)wdp, G, Cg, Cgp, K);
   } else if (dtype == DPH_DTYPE_BF16) {
     posconv_weight_prep_kernel<bf16><<<grid_for(total), 256, 0, s>>>(v, g, norm, wn, (bf16*)wp, (bf16*)wdp, D, G, Cg, Cgp, K);
   } else {
@@ -405,8 +417,8 @@ extern "C" int dph_posconv_weight_bwd(const float* dwp, const float* v, const fl
   const size_t dws_bytes = sizeof(float) * K * (Cg + 1);
   if (K <= 256 && 256 % K == 0 && dws_bytes <= 46 * 1024) {
     cudaMemsetAsync(scratch, 0, sizeof(float) * K, s);
-    posconv_wbwd_tiled_kernel<1><<<D, 256, dws_bytes, s>>>(dwp, v, g, norm, scratch, dv, dg, Cg, Cop, Cgp, K);
-    posconv_wbwd_tiled_kernel<2><<<D, 256, dws_bytes, s>>>(dwp, v, g, norm, scratch, dv, dg, Cg, Cop, Cgp, K);
+    launch_pdl(posconv_wbwd_tiled_kernel<1>, dim3(D), dim3(256), dws_bytes, s, dwp, v, g, norm, scratch, dv, dg, Cg, Cop, Cgp, K);
+    launch_pdl(posconv_wbwd_tiled_kernel<2>, dim3(D), dim3(256), dws_bytes, s, dwp, v, g, norm, scratch, dv, dg, Cg, Cop, Cgp, K);
     dph_count_launch(2);
     return dph_check_last("posconv_weight_bwd");
   }
