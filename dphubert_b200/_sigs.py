@@ -75,6 +75,7 @@ SIGS = {
     "dph_counter_inc": [vp, vp],
     "dph_adamw": [vp, vp, vp, vp, i64, vp, f32, f32, f32, f32, vp, vp, f32, vp, i32, vp],
     "dph_scale": [vp, i64, f32, vp],
+    "dph_multimem_allreduce": [vp, i64, i32, i32, f32, i32, vp],
 }
 
 RESTYPES = {

@@ -203,6 +203,20 @@ class Plan:
                 g.copy_(p.grad)
                 p.grad = g
 
+    def rebind_grad_arena(self, storage):
+        """Move the gradient arena into caller-provided storage of the same size (`total + GRAD_TAIL` floats) — the
+        data-parallel step keeps it in symmetric memory so that ranks can reduce it over NVSwitch multicast."""
+        assert self.garena_full is not None and storage.numel() == self.garena_full.numel() and storage.dtype == torch.float32
+        with torch.no_grad():
+            storage.copy_(self.garena_full)
+        self.garena_full = storage
+        self.garena = storage[: self.total]
+        self.gtail = storage[self.total:]
+        self._gcache = {}
+        for p in self.params:
+            if p.requires_grad:
+                p.grad = self.gview(p)
+
     def grads_ok(self):
         if self.garena is None:
             return True

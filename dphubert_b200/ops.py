@@ -279,6 +279,12 @@ def scale_(x, a):
     check(_L().dph_scale(ptr(x), x.numel(), a, stream_ptr()), "dph_scale")
 
 
+def multimem_allreduce(mc_addr, n, rank, world, scale, ctas=0):
+    """`mc_addr`: integer multicast address of the slice (symmetric memory handle's multicast_ptr + byte offset)."""
+    check(_L().dph_multimem_allreduce(ctypes.c_void_p(int(mc_addr)), int(n), int(rank), int(world), float(scale), int(ctas),
+                                      stream_ptr()), "dph_multimem_allreduce")
+
+
 # ----------------------------------------------------------------------------------------------------------------
 # HardConcrete
 # ----------------------------------------------------------------------------------------------------------------

@@ -322,6 +322,12 @@ int dph_adamw(float* p, float* g, float* m, float* v, int64_t n, const float* lr
               float weight_decay, const int* step_dev, const double* gnorm_sq, float max_norm, void* p_bf16, int zero_grad,
               void* stream);
 int dph_scale(float* x, int64_t n, float a, void* stream);
+/* In-place all-reduce (x = scale * sum over ranks) of n floats at `mc_ptr`, the MULTICAST address of a slice of a
+ * symmetric-memory allocation (torch.distributed._symmetric_memory: same offset on every rank); rank r reduces the
+ * r-th 1/world of the slice inside the NVSwitch (multimem.ld_reduce) and stores the result to all ranks (multimem.st).
+ * Replaces DDP's NCCL all-reduce of a gradient bucket (distill.py:41).  The caller orders the ranks with a
+ * symmetric-memory barrier on `stream` before and after the call.  n % 4 == 0, 16-byte aligned; ctas <= 0: 16. */
+int dph_multimem_allreduce(void* mc_ptr, int64_t n, int rank, int world, float scale, int ctas, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * Batch assembly (memory-bound gather): out[b, t] = pool[start[b] + t] for t < len[b], zero beyond; lengths_out[b] =
