@@ -60,8 +60,11 @@ def _worker(rank, world, port, case, q):
         q.put((rank, None, None, None, traceback.format_exc() + repr(e)))
 
 
+@pytest.mark.parametrize("ar_group", ["1", "2"])
 @pytest.mark.parametrize("case", ["step_base"])
-def test_two_rank_gradient_mean_matches_full_batch_reference(case):
+def test_two_rank_gradient_mean_matches_full_batch_reference(case, ar_group, monkeypatch):
+    # transformer layers per collective (trainer.ar_group): one slice per layer / both layers of the fixture in one
+    monkeypatch.setenv("DPH_AR_GROUP", ar_group)
     world = 2
     ctx = mp.get_context("spawn")
     q = ctx.Queue()

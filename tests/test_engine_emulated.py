@@ -166,3 +166,27 @@ def check_fused_act_bwd_equals_separate_pass(dev, names=("step_base", "step_larg
 
 def test_fused_act_bwd_equals_separate_pass(emulated):
     check_fused_act_bwd_equals_separate_pass(CPU)
+
+
+def test_gradient_arena_can_move_into_caller_storage(emulated):
+    """`Plan.rebind_grad_arena` (the data-parallel step keeps the arena in symmetric memory for the multicast
+    all-reduce): contents, offsets and every `p.grad` view follow the new storage."""
+    from dphubert_b200.engine import GRAD_TAIL, get_plan
+
+    g = load_golden("step_base")
+    step, teacher, student, projs, lam = build_step(g, torch.device("cpu"), torch.float32)
+    plan = get_plan(student)
+    with torch.no_grad():
+        plan.garena_full.copy_(torch.arange(plan.garena_full.numel(), dtype=torch.float32))
+    old = plan.garena_full.clone()
+    new = torch.full((plan.total + GRAD_TAIL,), -1.0)
+    plan.rebind_grad_arena(new)
+    assert plan.garena_full.data_ptr() == new.data_ptr() and torch.equal(new, old)
+    assert plan.garena.numel() == plan.total and plan.gtail.numel() == GRAD_TAIL
+    assert plan.grads_ok()
+    lo, hi = new.data_ptr(), new.data_ptr() + 4 * plan.total
+    for p in student.parameters():
+        if p.requires_grad:
+            assert lo <= p.grad.data_ptr() < hi
+            o = plan.offsets[id(p)]
+            assert torch.equal(p.grad.flatten(), old[o:o + p.numel()])
