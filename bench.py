@@ -421,7 +421,7 @@ def run_ours(args, rank, world, local_rank):
     # extra (not the headline): the same step replayed back to back for >= 3 s, so that the power cap and the clocks
     # it settles at are part of the number (the 20-step headline region lasts 0.2 s)
     sustained = None
-    if args.sustain > 0:
+    if args.sustain > 0 and world == 1:   # an extra of the single-GPU headline line; the N > 1 lines are the timed regions only
         n_sus = max(args.steps, int(args.sustain * 1e3 / (ms_dev / args.steps)) + 1)
         s2 = ClockSampler(local_rank, power=True)
         s2.start()
@@ -746,10 +746,17 @@ def roofline(step, wave, lengths, G, dev):
     """Dominant kernel = the tcgen05 GEMM (every Linear / conv / attention product): re-issue exactly the GEMM launches
     of one step back to back and time them with CUDA events -> algorithmic TFLOP/s against the measured bf16 peak."""
     G.TRACE = []
-    hook, step.splan.grad_hook = step.splan.grad_hook, None  # rank-local pass: no collectives
-    step._push_scalars()
-    step._body(wave, lengths)
-    step.splan.grad_hook = hook
+    # rank-local pass (only rank 0 gets here while the other ranks wait at the final barrier): NO collective may be
+    # issued — neither the per-slice gradient reductions (grad_hook) nor the heads' early all-reduce (`_heads_ready`
+    # checks `world`); an orphan all-reduce would pair with the peers' barrier and hang
+    hook, step.splan.grad_hook = step.splan.grad_hook, None
+    world_was, step.world = step.world, 1
+    try:
+        step._push_scalars()
+        step._body(wave, lengths)
+    finally:
+        step.splan.grad_hook = hook
+        step.world = world_was
     trace, G.TRACE = G.TRACE, None
     step.zero_grad()
     torch.cuda.synchronize()
